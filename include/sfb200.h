@@ -1,0 +1,178 @@
+/*
+ * sfb200.h -- C ABI of libsfb200.so: the B200 (sm_100a) kernels behind the drop-in
+ * replacement of zc402/video-classification's SlowFast hot path.
+ *
+ * The reference has no FFI of its own: its hot path is `init_my_slowfast`
+ * (reference model/my_slowfast.py:44-126) -> torch.nn modules -> cuDNN/cuBLAS/ATen.
+ * Every entry point below names the reference module call it replaces.  A reference
+ * maintainer binds these with ctypes; no torch types appear here.
+ *
+ * Conventions
+ *   - activations: bf16, NDHWC ("channels last 3d").  A tensor argument is a
+ *     (pointer, ld, coff) triple: `ld` = channels per pixel of the underlying buffer,
+ *     `coff` = first channel of the view.  This is how the Fast->Slow lateral output and
+ *     the Slow stage output share ONE buffer (torch.cat at my_slowfast.py:343 becomes a no-op).
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden syncs.
+ *   - return value: 0 on success, negative SfbStatus otherwise; sfb_strerror() explains.
+ *   - `impl`: SFB_IMPL_TC = tcgen05/TMEM tensor-core kernel, SFB_IMPL_SIMT = plain CUDA-core
+ *     kernel with the same contract (kept as an on-device cross-check; never a CPU path).
+ */
+#ifndef SFB200_H
+#define SFB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum SfbStatus {
+  SFB_OK = 0,
+  SFB_ERR_BAD_ARG = -1,      /* shape / alignment / null pointer rejected before any launch */
+  SFB_ERR_CUDA = -2,         /* a CUDA runtime call or launch failed (see sfb_last_cuda_error) */
+  SFB_ERR_UNSUPPORTED = -3,  /* valid request outside what the kernels implement */
+  SFB_ERR_DRIVER = -4        /* could not resolve cuTensorMapEncodeTiled from the driver */
+} SfbStatus;
+
+enum { SFB_IMPL_TC = 0, SFB_IMPL_SIMT = 1 };
+
+/* Geometry of one implicit-GEMM convolution pass.
+ *   fprop   (transposed=0): out[m, co] = sum_{tap,c} G[in(m,tap), c] * Wp[co][tap*Cg + c]
+ *                           in = out*s - p + k                      (nn.Conv3d forward)
+ *   dgrad   (transposed=1): same GEMM, G = dY, in = (out + p - k)/s where divisible
+ *                           (autograd of nn.Conv3d w.r.t. its input)
+ * G is the gathered tensor (N,Ti,Hi,Wi,Cg), the result is (N,To,Ho,Wo,Co). */
+typedef struct SfbConvGeom {
+  int32_t N, Ti, Hi, Wi, Cg;
+  int32_t To, Ho, Wo, Co;
+  int32_t kT, kH, kW;
+  int32_t sT, sH, sW;
+  int32_t pT, pH, pW;
+  int32_t g_ld, g_coff;
+  int32_t o_ld, o_coff;
+  int32_t transposed;
+} SfbConvGeom;
+
+/* Optional per-channel affine(+ReLU) applied to the gathered operand while it is staged
+ * ("consumer prologue": BatchNorm3d+ReLU of the producer layer, reference
+ * pytorchvideo BottleneckBlock norm_a/act_a etc.).  Padding stays exactly zero. */
+typedef struct SfbPrologue {
+  const float* scale;   /* [Cg] or NULL = identity */
+  const float* shift;   /* [Cg] */
+  int32_t relu;
+} SfbPrologue;
+
+/* Optional fused epilogue of the GEMM. */
+typedef struct SfbEpilogue {
+  const float* scale;    /* [Co] or NULL: y = acc*scale + shift (inference-folded BatchNorm3d) */
+  const float* shift;
+  const void* residual;  /* bf16 or NULL: y += residual[m, co] (ResBlock branch_fusion / grad accumulation) */
+  int32_t res_ld, res_coff;
+  int32_t relu;
+  float* stats;          /* [2*Co] fp32 or NULL: stats[co] += sum_m y, stats[Co+co] += sum_m y*y
+                            (training BatchNorm3d batch statistics, fused) */
+} SfbEpilogue;
+
+const char* sfb_strerror(int status);
+const char* sfb_last_cuda_error(void);
+int sfb_version(void);
+/* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
+int64_t sfb_launch_count(void);
+
+/* sizes of the packed bf16 weight matrix for a conv with `taps`=kT*kH*kW over Cg gathered
+ * channels producing Co channels: rows are padded to the N tile, K to 64. */
+int sfb_packed_weight_dims(int32_t Co, int32_t Cg, int32_t taps, int32_t* rows_pad, int32_t* k_pad);
+
+/* replaces: nn.Conv3d.weight as consumed by cuDNN.  fp32 OIDHW (Co, Ci, taps) ->
+ * bf16 [rows_pad][k_pad], k = tap*Cg + c.  transposed=0: rows=Co, c runs over Ci (zero padded to Cg).
+ * transposed=1 (dgrad operand): rows = Ci, k = tap*Cg + co with Cg = padded Co. */
+int sfb_pack_weight(const float* w, int32_t Co, int32_t Ci, int32_t taps, int32_t Cg,
+                    int32_t transposed, void* wp, int32_t rows_pad, int32_t k_pad, void* stream);
+
+/* replaces: train.py:136-140 (_prepare_slowfast_data permute + channel slices) feeding Conv3d.
+ * fp32 tensor with arbitrary element strides (n,c,t,h,w) -> bf16 NDHWC, channels zero-padded to ld. */
+int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw,
+                     int32_t N, int32_t C, int32_t T, int32_t H, int32_t W,
+                     void* out, int32_t out_ld, void* stream);
+
+/* replaces: nn.Conv3d forward (cuDNN fprop) and its input-gradient (cuDNN bwd-data), with the
+ * BatchNorm3d/ReLU/residual work of pytorchvideo ResBlock fused as prologue/epilogue. */
+int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro,
+                  const void* wp, int32_t rows_pad, int32_t k_pad,
+                  void* out, const SfbEpilogue* epi, int32_t impl, void* stream);
+
+/* replaces: nn.Conv3d weight gradient (cuDNN bwd-filter).
+ * dw[co][ci][tap] += sum_m dy[m, co] * pro(x)[in(m,tap), ci]   (fp32, OIDHW, accumulated) */
+int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pro,
+                   const void* dy, int32_t dy_ld, int32_t dy_coff,
+                   float* dw, int32_t Ci_real, int32_t impl, void* stream);
+
+/* replaces: nn.BatchNorm3d training statistics finalisation + running-stat update.
+ * stats = [sum(C), sumsq(C)] over `count` elements per channel.
+ * scale = gamma*invstd, shift = beta - mean*scale; save_mean/save_invstd kept for backward;
+ * running = (1-momentum)*running + momentum*{mean, unbiased var}.  running_* may be NULL. */
+int sfb_bn_finalize(const float* stats, int32_t C, int64_t count, const float* gamma, const float* beta,
+                    float eps, float momentum, float* running_mean, float* running_var,
+                    float* scale, float* shift, float* save_mean, float* save_invstd, void* stream);
+
+/* eval-mode BatchNorm3d fold: scale = gamma/sqrt(running_var+eps), shift = beta - running_mean*scale */
+int sfb_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                float eps, int32_t C, float* scale, float* shift, void* stream);
+
+/* replaces: ResBlock tail  out = ReLU( BN_c(y) + shortcut )  (branch_fusion + activation).
+ * shortcut = r*r_scale + r_shift when r_scale != NULL (branch1_conv+branch1_norm), else r. */
+int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift,
+                    const void* r, int32_t r_ld, int32_t r_coff, const float* r_scale, const float* r_shift,
+                    void* out, int32_t o_ld, int32_t o_coff, int64_t M, int32_t C, int32_t relu, void* stream);
+
+/* BatchNorm3d(+ReLU) backward, phase 1: per-channel reductions accumulated (atomically) into
+ * dgamma/dbeta:  g = dz * [relu ? (y*scale+shift > 0) : 1] ;  dbeta += sum g ; dgamma += sum g*xhat.
+ * mask_src: optional bf16 tensor whose sign gives the ReLU mask instead (block output O). */
+int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff,
+                      const void* y, int32_t y_ld, int32_t y_coff,
+                      const void* mask_src, int32_t m_ld, int32_t m_coff,
+                      const float* scale, const float* shift, const float* mean, const float* invstd,
+                      int32_t relu, int64_t M, int32_t C, float* dgamma, float* dbeta, void* stream);
+
+/* phase 2:  dy = gamma*invstd * (g - dbeta/M - xhat*dgamma/M)  -> bf16.
+ * If g_out != NULL also writes g (masked dz) there (identity-shortcut gradient). */
+int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff,
+                     const void* y, int32_t y_ld, int32_t y_coff,
+                     const void* mask_src, int32_t m_ld, int32_t m_coff,
+                     const float* scale, const float* shift, const float* mean, const float* invstd,
+                     const float* gamma, const float* dgamma, const float* dbeta,
+                     int32_t relu, int64_t M, int32_t C,
+                     void* dy, int32_t dy_ld, int32_t dy_coff,
+                     void* g_out, int32_t g_ld, int32_t g_coff, int32_t g_accumulate, void* stream);
+
+/* replaces: ResNetBasicStem norm+activation+pool: out = MaxPool3d((1,3,3),s(1,2,2),p(0,1,1))(ReLU(y*scale+shift)).
+ * idx (uint8, may be NULL) records the arg-max tap for backward. */
+int sfb_maxpool_fwd(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift,
+                    int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                    void* out, int32_t o_ld, int32_t o_coff, uint8_t* idx, void* stream);
+/* dz[n,t,h,w,c] = sum over windows whose arg-max is (h,w) of dout[window]  (gradient w.r.t. the ReLU output) */
+int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx,
+                    int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                    void* dz, int32_t dz_ld, int32_t dz_coff, void* stream);
+
+/* replaces: PoolConcatPathway AvgPool3d(k, stride 1) + ResNetBasicHead Dropout + AdaptiveAvgPool3d(1)
+ * (the Linear commutes with the mean).  feat[n, f_off + c] = mean_p drop(avgpool_k(x))[n, p, c].
+ * dropout_p = 0 disables dropout; otherwise a counter-based mask from `seed` (recomputed in backward). */
+int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed,
+                      float* feat, int32_t f_ld, int32_t f_off, void* stream);
+int sfb_head_pool_bwd(const float* dfeat, int32_t f_ld, int32_t f_off, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed,
+                      void* dx, int32_t dx_ld, int32_t dx_coff, void* stream);
+
+/* replaces: ResNetBasicHead.proj (nn.Linear 2304 -> NUM_CLASS), fp32. */
+int sfb_fc_fwd(const float* feat, const float* w, const float* b, int32_t N, int32_t K, int32_t C,
+               float* logits, void* stream);
+/* dfeat = dlogits @ w ; dw += dlogits^T @ feat ; db += sum_n dlogits */
+int sfb_fc_bwd(const float* dlogits, const float* feat, const float* w, int32_t N, int32_t K, int32_t C,
+               float* dfeat, float* dw, float* db, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFB200_H */

@@ -1,0 +1,233 @@
+"""Kernel-level parity (B200): every libsfb200 kernel vs a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from video_classification_b200 import _ffi, ops  # noqa: E402
+from video_classification_b200.ops import Act  # noqa: E402
+
+import kernel_cases as kc  # noqa: E402
+
+DEV = "cuda"
+
+
+# ------------------------------------------------------------------ elementwise / pooling / head
+def test_layout_input_strided():
+    x = torch.randn(2, 6, 21, 10, 12, device=DEV)  # (N,T,C,H,W) like the reference loader
+    v = x.permute(0, 2, 1, 3, 4)[:, 5:20]          # train.py:136-140: non-contiguous NCTHW view
+    a = ops.layout_input(v, 16)
+    got = a.buf.float()
+    ref = torch.zeros_like(got)
+    ref[..., :15] = v.permute(0, 2, 3, 4, 1).bfloat16().float()
+    assert torch.equal(got, ref)
+
+
+def test_pack_weight_roundtrip():
+    w = torch.randn(24, 5, 1, 7, 7, device=DEV)
+    wp = ops.pack_weight(w, 8)
+    rows, kpad = wp.shape
+    ref = torch.zeros(rows, kpad, device=DEV)
+    wr = w.reshape(24, 5, 49).permute(0, 2, 1)  # (co, tap, ci)
+    tmp = torch.zeros(24, 49, 8, device=DEV)
+    tmp[:, :, :5] = wr
+    ref[:24, :49 * 8] = tmp.reshape(24, -1)
+    assert torch.equal(wp.float(), ref.bfloat16().float())
+    wpt = ops.pack_weight(w, 24, transposed=True)
+    tmp = w.reshape(24, 5, 49).permute(1, 2, 0)  # (ci, tap, co)
+    ref = torch.zeros(wpt.shape, device=DEV)
+    ref[:5, :49 * 24] = tmp.reshape(5, -1)
+    assert torch.equal(wpt.float(), ref.bfloat16().float())
+
+
+def _bn_ref(y, gamma, beta, eps=1e-5):
+    mean = y.mean(dim=(0, 2, 3, 4))
+    var = y.var(dim=(0, 2, 3, 4), unbiased=False)
+    invstd = (var + eps).rsqrt()
+    return mean, var, invstd
+
+
+def test_bn_finalize_and_fold():
+    C_, cnt = 64, 1000
+    y = torch.randn(cnt, C_, device=DEV) * 2 + 0.5
+    stats = torch.cat([y.sum(0), (y * y).sum(0)])
+    gamma, beta = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)
+    rm, rv = torch.zeros(C_, device=DEV), torch.ones(C_, device=DEV)
+    sc, sh, mean, invstd = (torch.empty(C_, device=DEV) for _ in range(4))
+    ops.bn_finalize(stats, cnt, gamma, beta, 1e-5, 0.1, rm, rv, sc, sh, mean, invstd)
+    m = y.mean(0)
+    v = y.var(0, unbiased=False)
+    torch.testing.assert_close(mean, m, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(invstd, (v + 1e-5).rsqrt(), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(sc, gamma * (v + 1e-5).rsqrt(), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(sh, beta - m * sc, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(rm, 0.1 * m, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(rv, 0.9 + 0.1 * y.var(0, unbiased=True), rtol=1e-4, atol=1e-5)
+    ops.bn_fold(gamma, beta, rm, rv, 1e-5, sc, sh)
+    torch.testing.assert_close(sc, gamma / (rv + 1e-5).sqrt(), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(sh, beta - rm * sc, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("C_,with_rbn", [(64, False), (256, True), (8, False), (1280, True)])
+def test_bn_add_relu(C_, with_rbn):
+    y = torch.randn(2, C_, 3, 6, 6, device=DEV)
+    r = torch.randn(2, C_, 3, 6, 6, device=DEV)
+    ya, ra = kc.to_act(y, ld=C_ + 8, coff=8), kc.to_act(r)
+    s, b = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)
+    rs, rb = (torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)) if with_rbn else (None, None)
+    out = Act.empty(2, 3, 6, 6, C_ + 16, coff=16, C=C_, zero=True)
+    ops.bn_add_relu(ya, s, b, ra, rs, rb, out)
+    bc = lambda t: t.view(1, -1, 1, 1, 1)
+    rr = kc.from_act(ra)
+    if with_rbn:
+        rr = rr * bc(rs) + bc(rb)
+    ref = torch.relu(kc.from_act(ya) * bc(s) + bc(b) + rr)
+    assert kc.relerr(kc.from_act(out), ref) < 6e-3
+    assert out.buf[..., :16].abs().max() == 0
+
+
+@pytest.mark.parametrize("C_,relu,use_mask", [(64, True, False), (256, True, True), (8, False, False), (1280, True, False)])
+def test_bn_bwd(C_, relu, use_mask):
+    N, T, H, W = 2, 3, 6, 6
+    y = (torch.randn(N, C_, T, H, W, device=DEV) * 1.5 + 0.3)
+    ya = kc.to_act(y)
+    yq = kc.from_act(ya).requires_grad_(True)
+    gamma = (torch.rand(C_, device=DEV) + 0.5).requires_grad_(True)
+    beta = (torch.randn(C_, device=DEV) * 0.2).requires_grad_(True)
+    dz = torch.randn(N, C_, T, H, W, device=DEV)
+    dza = kc.to_act(dz, ld=C_ + 8, coff=0)
+    bn = F.batch_norm(yq, None, None, gamma, beta, True, 0.1, 1e-5)
+    extra = torch.randn(N, C_, T, H, W, device=DEV) if use_mask else None
+    pre = bn + extra if use_mask else bn
+    z = torch.relu(pre) if relu else pre
+    z.backward(kc.from_act(dza))
+    mean, var, invstd = _bn_ref(yq.detach(), gamma, beta)
+    scale = (gamma * invstd).detach()
+    shift = (beta - mean * gamma * invstd).detach()
+    mask = kc.to_act(z.detach()) if use_mask else None
+    dgamma, dbeta = torch.zeros(C_, device=DEV), torch.zeros(C_, device=DEV)
+    ops.bn_bwd_reduce(dza, ya, mask, scale, shift, mean, invstd, relu, dgamma, dbeta)
+    dy = Act.empty(N, T, H, W, C_)
+    gout = Act.empty(N, T, H, W, C_)
+    ops.bn_bwd_apply(dza, ya, mask, scale, shift, mean, invstd, gamma.detach(), dgamma, dbeta, relu, dy, gout)
+    torch.cuda.synchronize()
+    assert kc.relerr(dgamma, gamma.grad) < 1e-2
+    assert kc.relerr(dbeta, beta.grad) < 1e-2
+    assert kc.relerr(kc.from_act(dy), yq.grad) < 1.5e-2
+    gref = kc.from_act(dza) * ((z.detach() > 0).float() if relu else 1.0)
+    assert kc.relerr(kc.from_act(gout), gref) < 1e-2
+
+
+@pytest.mark.parametrize("C_,H,W", [(64, 16, 16), (8, 15, 13)])
+def test_maxpool(C_, H, W):
+    N, T = 2, 3
+    y = torch.randn(N, C_, T, H, W, device=DEV)
+    ya = kc.to_act(y)
+    s, b = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV) * 0.2
+    s[0] = -s[0]
+    Ho, Wo = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    out = Act.empty(N, T, Ho, Wo, C_ + 16, coff=0, C=C_, zero=True)
+    idx = torch.empty((N, T, Ho, Wo, C_), dtype=torch.uint8, device=DEV)
+    ops.maxpool_fwd(ya, s, b, out, idx)
+    z = torch.relu(kc.from_act(ya) * s.view(1, -1, 1, 1, 1) + b.view(1, -1, 1, 1, 1)).requires_grad_(True)
+    ref = F.max_pool3d(z, (1, 3, 3), (1, 2, 2), (0, 1, 1))
+    assert kc.relerr(kc.from_act(out), ref) < 5e-3
+    assert out.buf[..., C_:].abs().max() == 0
+    d = torch.randn_like(ref)
+    da = kc.to_act(d)
+    ref.backward(kc.from_act(da))
+    dz = Act.empty(N, T, H, W, C_)
+    ops.maxpool_bwd(da, idx, dz)
+    got = kc.from_act(dz)
+    # ties (bf16-equal maxima / all-zero windows) may pick a different arg-max than torch; compare where z>0
+    m = (z.detach() > 0)
+    diff = ((got - z.grad).abs() * m).max() / z.grad.abs().max()
+    frac_bad = (((got - z.grad).abs() > 1e-2 * z.grad.abs().max()) & m).float().mean()
+    assert frac_bad < 2e-3, (diff.item(), frac_bad.item())
+
+
+@pytest.mark.parametrize("T,H,W,k", [(20, 2, 2, (4, 2, 2)), (8, 7, 7, (8, 7, 7)), (20, 4, 4, (4, 2, 2))])
+def test_head_pool(T, H, W, k):
+    N, C_ = 3, 64
+    x = torch.relu(torch.randn(N, C_, T, H, W, device=DEV))
+    xa = kc.to_act(x)
+    xq = kc.from_act(xa).requires_grad_(True)
+    feat = torch.zeros(N, C_ + 8, device=DEV)
+    ops.head_pool_fwd(xa, k, 0.0, 0, feat, 8)
+    ref = F.avg_pool3d(xq, k, 1).mean(dim=(2, 3, 4))
+    torch.testing.assert_close(feat[:, 8:], ref, rtol=1e-4, atol=1e-5)
+    df = torch.randn(N, C_ + 8, device=DEV)
+    ref.backward(df[:, 8:])
+    dx = Act.empty(N, T, H, W, C_)
+    ops.head_pool_bwd(df, 8, k, 0.0, 0, dx)
+    assert kc.relerr(kc.from_act(dx), xq.grad) < 6e-3
+    # dropout: forward/backward consistency (d feat / d x == backward weights) and keep-rate
+    feat_d = torch.zeros(N, C_ + 8, device=DEV)
+    ops.head_pool_fwd(xa, k, 0.5, 1234, feat_d, 8)
+    ones = torch.ones(N, C_ + 8, device=DEV)
+    dxd = Act.empty(N, T, H, W, C_)
+    ops.head_pool_bwd(ones, 8, k, 0.5, 1234, dxd)
+    recon = (kc.from_act(dxd) * xq.detach()).sum(dim=(2, 3, 4))
+    assert kc.relerr(recon, feat_d[:, 8:]) < 2e-2
+
+
+def test_fc():
+    N, K, C_ = 5, 2304, 249
+    feat, w, b = torch.randn(N, K, device=DEV), torch.randn(C_, K, device=DEV) * 0.01, torch.randn(C_, device=DEV)
+    logits = torch.empty(N, C_, device=DEV)
+    ops.fc_fwd(feat, w, b, logits)
+    torch.testing.assert_close(logits, feat @ w.t() + b, rtol=1e-4, atol=1e-4)
+    dl = torch.randn(N, C_, device=DEV)
+    dfeat, dw, db = torch.empty(N, K, device=DEV), torch.zeros(C_, K, device=DEV), torch.zeros(C_, device=DEV)
+    ops.fc_bwd(dl, feat, w, dfeat, dw, db)
+    torch.testing.assert_close(dfeat, dl @ w, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(dw, dl.t() @ feat, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(db, dl.sum(0), rtol=1e-4, atol=1e-4)
+
+
+# ------------------------------------------------------------------ conv GEMM: SIMT cross-check first, then tcgen05
+IMPLS = [("simt", _ffi.IMPL_SIMT), ("tc", _ffi.IMPL_TC)]
+
+
+@pytest.mark.parametrize("impl_name,impl", IMPLS)
+@pytest.mark.parametrize("case", kc.CONV_CASES, ids=[c[0] for c in kc.CONV_CASES])
+def test_conv_fprop(case, impl_name, impl):
+    r = kc.run_conv_case(case, impl, "plain")
+    assert r["err"] < 1e-2, r
+
+
+@pytest.mark.parametrize("impl_name,impl", IMPLS)
+@pytest.mark.parametrize("variant", ["pro", "epi", "stats"])
+@pytest.mark.parametrize("case", [kc.CONV_CASES[i] for i in (1, 2, 3, 5, 8, 10, 12)], ids=lambda c: c[0])
+def test_conv_fprop_fused(case, variant, impl_name, impl):
+    r = kc.run_conv_case(case, impl, variant)
+    assert r["err"] < 1e-2, r
+    if variant == "stats":
+        assert r["err_sum"] < 2e-2 and r["err_sq"] < 1e-2, r
+    if variant == "epi":
+        assert r["clobber"] == 0.0, r
+
+
+@pytest.mark.parametrize("impl_name,impl", IMPLS)
+@pytest.mark.parametrize("case", [c for c in kc.CONV_CASES if not c[0].startswith("stem")], ids=lambda c: c[0])
+def test_conv_dgrad(case, impl_name, impl):
+    r = kc.run_dgrad_case(case, impl, accumulate=(case[0] in ("1x1x1_64_256", "1x3x3_128_128_s2")))
+    assert r["err"] < 1e-2, r
+
+
+@pytest.mark.parametrize("impl_name,impl", IMPLS)
+@pytest.mark.parametrize("case", kc.CONV_CASES, ids=[c[0] for c in kc.CONV_CASES])
+def test_conv_wgrad(case, impl_name, impl):
+    name = case[0]
+    ci_real = {"stem_slow_8_64": 5, "stem_fast_16_8": 15}.get(name)
+    r = kc.run_wgrad_case(case, impl, pro=name in ("1x3x3_64_64", "3x1x1_256_128", "fast_3x1x1_32_8"), ci_real=ci_real)
+    assert r["err"] < 2e-2, r
+
+
+def test_bad_args_rejected():
+    x = Act.empty(1, 2, 4, 4, 12)  # 12 channels: not a multiple of 8
+    w = torch.empty(64, 64, dtype=torch.bfloat16, device=DEV)
+    out = Act.empty(1, 2, 4, 4, 64)
+    with pytest.raises(_ffi.SfbError):
+        ops.conv_gemm(x, w, out, (1, 1, 1), (1, 1, 1), (0, 0, 0))

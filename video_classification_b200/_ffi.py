@@ -1,0 +1,112 @@
+"""ctypes binding of libsfb200.so (C ABI declared in include/sfb200.h).
+
+The product path has no fallback: if the shared library is missing or a call fails, an
+exception is raised (SfbError).  torch is used only to own device memory and streams.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libsfb200.so")
+
+IMPL_TC = 0
+IMPL_SIMT = 1
+
+
+class SfbError(RuntimeError):
+    pass
+
+
+class ConvGeom(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "N", "Ti", "Hi", "Wi", "Cg", "To", "Ho", "Wo", "Co", "kT", "kH", "kW", "sT", "sH", "sW",
+        "pT", "pH", "pW", "g_ld", "g_coff", "o_ld", "o_coff", "transposed")]
+
+
+class Prologue(C.Structure):
+    _fields_ = [("scale", C.c_void_p), ("shift", C.c_void_p), ("relu", C.c_int32)]
+
+
+class Epilogue(C.Structure):
+    _fields_ = [("scale", C.c_void_p), ("shift", C.c_void_p), ("residual", C.c_void_p),
+                ("res_ld", C.c_int32), ("res_coff", C.c_int32), ("relu", C.c_int32), ("stats", C.c_void_p)]
+
+
+_i32, _i64, _u64, _f32, _vp = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_void_p
+
+# name -> argtypes; every function returns int (status) unless listed in _SPECIAL
+SIGNATURES = {
+    "sfb_packed_weight_dims": [_i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
+    "sfb_pack_weight": [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
+    "sfb_layout_input": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
+    "sfb_conv_gemm": [C.POINTER(ConvGeom), _vp, C.POINTER(Prologue), _vp, _i32, _i32, _vp, C.POINTER(Epilogue), _i32, _vp],
+    "sfb_conv_wgrad": [C.POINTER(ConvGeom), _vp, C.POINTER(Prologue), _vp, _i32, _i32, _vp, _i32, _i32, _vp],
+    "sfb_bn_finalize": [_vp, _i32, _i64, _vp, _vp, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "sfb_bn_fold": [_vp, _vp, _vp, _vp, _f32, _i32, _vp, _vp, _vp],
+    "sfb_bn_add_relu": [_vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i64, _i32, _i32, _vp],
+    "sfb_bn_bwd_reduce": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _vp, _vp],
+    "sfb_bn_bwd_apply": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                         _i32, _i64, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp],
+    "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
+    "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
+    "sfb_head_pool_fwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
+    "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
+    "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],
+    "sfb_fc_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
+}
+_SPECIAL = {
+    "sfb_strerror": ([_i32], C.c_char_p),
+    "sfb_last_cuda_error": ([], C.c_char_p),
+    "sfb_version": ([], _i32),
+    "sfb_launch_count": ([], _i64),
+}
+ALL_SYMBOLS = sorted(list(SIGNATURES) + list(_SPECIAL))
+
+_lib = None
+
+
+def lib():
+    """Load libsfb200.so (once).  Raises SfbError if it has not been built -- there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SfbError(f"{LIB_PATH} not found: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(the sm_100a CUDA extension is mandatory; there is no CPU/PyTorch fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, args in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.argtypes = args
+            fn.restype = C.c_int
+        for name, (args, res) in _SPECIAL.items():
+            fn = getattr(l, name)
+            fn.argtypes = args
+            fn.restype = res
+        _lib = l
+    return _lib
+
+
+def check(status, what=""):
+    if status != 0:
+        l = lib()
+        msg = l.sfb_strerror(status).decode()
+        extra = l.sfb_last_cuda_error().decode()
+        raise SfbError(f"{what}: {msg} [{status}] {extra}")
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def packed_weight_dims(Co, Cg, taps):
+    r, k = _i32(), _i32()
+    check(lib().sfb_packed_weight_dims(Co, Cg, taps, C.byref(r), C.byref(k)), "sfb_packed_weight_dims")
+    return r.value, k.value
+
+
+def launch_count():
+    return int(lib().sfb_launch_count())
+
+
+def ptr(t):
+    return 0 if t is None else t.data_ptr()

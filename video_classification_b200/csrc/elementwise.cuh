@@ -1,0 +1,486 @@
+// elementwise.cuh -- HBM-bound kernels of the SlowFast hot path: layout conversion, weight packing,
+// BatchNorm finalize / fold / backward, residual tail, stem max-pool, head pooling, FC head.
+// All activation tensors are bf16 NDHWC views (ptr, ld, coff); every thread moves 16 bytes
+// (8 channels) per access; per-channel reductions use registers -> shared -> one atomic per block.
+#pragma once
+#include "common.cuh"
+
+namespace sfb {
+
+struct View {
+  const __nv_bfloat16* p;
+  int ld, coff;
+};
+struct ViewW {
+  __nv_bfloat16* p;
+  int ld, coff;
+};
+__device__ __forceinline__ uint4 vload(const View& v, long long m, int c) {
+  return *reinterpret_cast<const uint4*>(v.p + (size_t)m * v.ld + v.coff + c);
+}
+__device__ __forceinline__ void vstore(const ViewW& v, long long m, int c, const uint4& q) {
+  *reinterpret_cast<uint4*>(v.p + (size_t)m * v.ld + v.coff + c) = q;
+}
+__device__ __forceinline__ void load8f(const float* p, float* f) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
+
+// ---- input layout: fp32 strided NCTHW -> bf16 NDHWC (channels zero padded to ld) ----------------
+__global__ void layout_input_kernel(const float* __restrict__ x, long long sn, long long sc, long long st,
+                                    long long sh, long long sw, int N, int C, int T, int H, int W,
+                                    __nv_bfloat16* __restrict__ out, int ld) {
+  const long long total = (long long)N * T * H * W;
+  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < total;
+       pix += (long long)gridDim.x * blockDim.x) {
+    const int w = (int)(pix % W);
+    long long q = pix / W;
+    const int h = (int)(q % H);
+    q /= H;
+    const int t = (int)(q % T);
+    const int n = (int)(q / T);
+    const float* src = x + n * sn + t * st + h * sh + w * sw;
+    __nv_bfloat16* dst = out + (size_t)pix * ld;
+    for (int c0 = 0; c0 < ld; c0 += 8) {
+      float f[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] = (c0 + i < C) ? __ldg(src + (long long)(c0 + i) * sc) : 0.f;
+      *reinterpret_cast<uint4*>(dst + c0) = pack8(f);
+    }
+  }
+}
+
+// ---- weight packing: fp32 OIDHW -> bf16 [rows_pad][k_pad] ---------------------------------------
+__global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, int taps, int Cg, int transposed,
+                                   __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+  const long long total = (long long)rows_pad * k_pad;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(idx % k_pad);
+    const int row = (int)(idx / k_pad);
+    float v = 0.f;
+    const int tap = k / Cg, c = k % Cg;
+    if (tap < taps) {
+      if (!transposed) {
+        if (row < Co && c < Ci) v = w[((size_t)row * Ci + c) * taps + tap];
+      } else {
+        if (row < Ci && c < Co) v = w[((size_t)c * Ci + row) * taps + tap];
+      }
+    }
+    wp[idx] = __float2bfloat16_rn(v);
+  }
+}
+
+// ---- BatchNorm finalize / fold ---------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double inv_count, double unbias,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                   float momentum, float* running_mean, float* running_var, float* scale,
+                                   float* shift, float* save_mean, float* save_invstd) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double mean = (double)stats[c] * inv_count;
+  double var = (double)stats[C + c] * inv_count - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float sc = gamma[c] * invstd;
+  scale[c] = sc;
+  shift[c] = beta[c] - (float)mean * sc;
+  save_mean[c] = (float)mean;
+  save_invstd[c] = invstd;
+  if (running_mean) {
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)(var * unbias);
+  }
+}
+
+__global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                               const float* __restrict__ rm, const float* __restrict__ rv, float eps, int C,
+                               float* scale, float* shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = gamma[c] * rsqrtf(rv[c] + eps);
+  scale[c] = sc;
+  shift[c] = beta[c] - rm[c] * sc;
+}
+
+// ---- residual tail: out = relu(y*s+b + (r*rs+rb | r)) -------------------------------------------------
+__global__ void bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, View r,
+                                   const float* __restrict__ r_scale, const float* __restrict__ r_shift, ViewW out,
+                                   long long M, int C, int relu) {
+  const int CV = C >> 3;
+  const long long total = M * CV;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % CV) << 3;
+    const long long m = idx / CV;
+    float f[8], s[8], b[8];
+    unpack8(vload(y, m, c), f);
+    load8f(scale + c, s);
+    load8f(shift + c, b);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], s[i], b[i]);
+    if (r.p) {
+      float rf[8];
+      unpack8(vload(r, m, c), rf);
+      if (r_scale) {
+        load8f(r_scale + c, s);
+        load8f(r_shift + c, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rf[i] = fmaf(rf[i], s[i], b[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] += rf[i];
+    }
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+    }
+    vstore(out, m, c, pack8(f));
+  }
+}
+
+// ---- BatchNorm(+ReLU) backward ----------------------------------------------------------------------
+// masked gradient g for 8 channels of row m
+__device__ __forceinline__ void bn_bwd_load(const View& dz, const View& y, const View& msk, const float* scale,
+                                            const float* shift, const float* mean, const float* invstd, int relu,
+                                            long long m, int c, float* g, float* xhat) {
+  float yv[8], mu[8], is[8];
+  unpack8(vload(dz, m, c), g);
+  unpack8(vload(y, m, c), yv);
+  load8f(mean + c, mu);
+  load8f(invstd + c, is);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) xhat[i] = (yv[i] - mu[i]) * is[i];
+  if (relu) {
+    if (msk.p) {
+      float mv[8];
+      unpack8(vload(msk, m, c), mv);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
+    } else {
+      float s[8], b[8];
+      load8f(scale + c, s);
+      load8f(shift + c, b);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], s[i], b[i]) > 0.f ? g[i] : 0.f;
+    }
+  }
+}
+
+constexpr int kRedThreads = 256;
+// block = (CV channel-vectors) x (RL row lanes); grid.x strides over row groups
+__global__ void __launch_bounds__(kRedThreads)
+bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale, const float* __restrict__ shift,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, long long M, int C,
+                     float* dgamma, float* dbeta) {
+  __shared__ float red[kRedThreads * 16];
+  const int CV = C >> 3;
+  const int RL = kRedThreads / CV;  // >= 1 (C <= 2048)
+  const int tx = threadIdx.x % CV;
+  const int ty = threadIdx.x / CV;
+  const int c = tx << 3;
+  float s1[8], s2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+  if (ty < RL) {
+    for (long long m = (long long)blockIdx.x * RL + ty; m < M; m += (long long)gridDim.x * RL) {
+      float g[8], xh[8];
+      bn_bwd_load(dz, y, msk, scale, shift, mean, invstd, relu, m, c, g, xh);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], xh[i], s2[i]); }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    red[threadIdx.x * 16 + i] = s1[i];
+    red[threadIdx.x * 16 + 8 + i] = s2[i];
+  }
+  __syncthreads();
+  // thread t < CV*16 sums over row lanes
+  for (int t = threadIdx.x; t < CV * 16; t += kRedThreads) {
+    const int cv = t / 16, e = t % 16;
+    float acc = 0.f;
+    for (int r = 0; r < RL; ++r) acc += red[(r * CV + cv) * 16 + e];
+    if (e < 8) atomicAdd(dbeta + cv * 8 + e, acc);
+    else atomicAdd(dgamma + cv * 8 + (e - 8), acc);
+  }
+}
+
+__global__ void bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
+                                    const float* __restrict__ shift, const float* __restrict__ mean,
+                                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ dgamma, const float* __restrict__ dbeta, int relu,
+                                    long long M, int C, float invM, ViewW dy, ViewW gout, int g_accumulate) {
+  const int CV = C >> 3;
+  const long long total = M * CV;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % CV) << 3;
+    const long long m = idx / CV;
+    float g[8], xh[8], ga[8], is[8], dg[8], db[8], o[8];
+    bn_bwd_load(dz, y, msk, scale, shift, mean, invstd, relu, m, c, g, xh);
+    load8f(gamma + c, ga);
+    load8f(invstd + c, is);
+    load8f(dgamma + c, dg);
+    load8f(dbeta + c, db);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = ga[i] * is[i] * (g[i] - db[i] * invM - xh[i] * dg[i] * invM);
+    vstore(dy, m, c, pack8(o));
+    if (gout.p) {
+      if (g_accumulate) {
+        float old[8];
+        View gv{gout.p, gout.ld, gout.coff};
+        unpack8(vload(gv, m, c), old);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g[i] += old[i];
+      }
+      vstore(gout, m, c, pack8(g));
+    }
+  }
+}
+
+// ---- stem max-pool (1,3,3)/s(1,2,2)/p(0,1,1) with fused BN+ReLU on load ---------------------------------
+__global__ void maxpool_fwd_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, int N,
+                                   int T, int H, int W, int C, ViewW out, uint8_t* __restrict__ idx_out) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int CV = C >> 3;
+  const long long total = (long long)N * T * Ho * Wo * CV;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % CV) << 3;
+    long long q = idx / CV;
+    const long long opix = q;
+    const int wo = (int)(q % Wo);
+    q /= Wo;
+    const int ho = (int)(q % Ho);
+    q /= Ho;  // q = n*T + t
+    float s[8], b[8], best[8];
+    int bi[8];
+    if (scale) { load8f(scale + c, s); load8f(shift + c, b); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; bi[i] = 0; }
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int h = ho * 2 - 1 + kh;
+      if ((unsigned)h >= (unsigned)H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int w = wo * 2 - 1 + kw;
+        if ((unsigned)w >= (unsigned)W) continue;
+        float f[8];
+        unpack8(vload(y, (q * H + h) * W + w, c), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float v = f[i];
+          if (scale) v = fmaxf(fmaf(v, s[i], b[i]), 0.f);
+          if (v > best[i]) { best[i] = v; bi[i] = kh * 3 + kw; }
+        }
+      }
+    }
+    vstore(out, opix, c, pack8(best));
+    if (idx_out) {
+      uint2 pk;
+      pk.x = (uint32_t)bi[0] | ((uint32_t)bi[1] << 8) | ((uint32_t)bi[2] << 16) | ((uint32_t)bi[3] << 24);
+      pk.y = (uint32_t)bi[4] | ((uint32_t)bi[5] << 8) | ((uint32_t)bi[6] << 16) | ((uint32_t)bi[7] << 24);
+      *reinterpret_cast<uint2*>(idx_out + (size_t)opix * C + c) = pk;
+    }
+  }
+}
+
+__global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, int N, int T, int H, int W, int C,
+                                   ViewW dz) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int CV = C >> 3;
+  const long long total = (long long)N * T * H * W * CV;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % CV) << 3;
+    long long q = idx / CV;
+    const long long ipix = q;
+    const int w = (int)(q % W);
+    q /= W;
+    const int h = (int)(q % H);
+    q /= H;  // n*T + t
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int hn = h + 1 - kh;
+      if (hn < 0 || (hn & 1)) continue;
+      const int ho = hn >> 1;
+      if (ho >= Ho) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int wn = w + 1 - kw;
+        if (wn < 0 || (wn & 1)) continue;
+        const int wo = wn >> 1;
+        if (wo >= Wo) continue;
+        const long long opix = (q * Ho + ho) * Wo + wo;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
+        float d[8];
+        unpack8(vload(dout, opix, c), d);
+        const int tap = kh * 3 + kw;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t word = i < 4 ? pk.x : pk.y;
+          const int sel = (word >> ((i & 3) * 8)) & 0xFF;
+          if (sel == tap) acc[i] += d[i];
+        }
+      }
+    }
+    vstore(dz, ipix, c, pack8(acc));
+  }
+}
+
+// ---- head: AvgPool3d(k, stride 1) -> dropout -> mean over positions -----------------------------------
+__device__ __forceinline__ float dropout_keep_scale(uint64_t seed, int n, int c, int pos, float p) {
+  // counter-based hash (splitmix64 finaliser) -> uniform in [0,1)
+  uint64_t z = seed + 0x9E3779B97F4A7C15ull * ((uint64_t)n * 0x100000001B3ull + (uint64_t)c * 0x1000193ull + (uint64_t)pos + 1ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  const float u = (float)(z >> 40) * (1.0f / 16777216.0f);
+  return u >= p ? 1.f / (1.f - p) : 0.f;
+}
+
+__global__ void head_pool_fwd_kernel(View x, int N, int T, int H, int W, int C, int kT, int kH, int kW, float p_drop,
+                                     uint64_t seed, float* __restrict__ feat, int f_ld, int f_off) {
+  const int CV = C >> 3;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * CV) return;
+  const int c = (idx % CV) << 3;
+  const int n = idx / CV;
+  const int Pt = T - kT + 1, Ph = H - kH + 1, Pw = W - kW + 1;
+  const float inv = 1.f / ((float)(Pt * Ph * Pw) * (float)(kT * kH * kW));
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  if (p_drop <= 0.f) {
+    // weight of an input position = number of windows covering it
+    for (int t = 0; t < T; ++t) {
+      const int wt = min(t, Pt - 1) - max(0, t - kT + 1) + 1;
+      for (int h = 0; h < H; ++h) {
+        const int wh = min(h, Ph - 1) - max(0, h - kH + 1) + 1;
+        for (int w = 0; w < W; ++w) {
+          const int ww = min(w, Pw - 1) - max(0, w - kW + 1) + 1;
+          float f[8];
+          unpack8(vload(x, (((long long)n * T + t) * H + h) * W + w, c), f);
+          const float wgt = (float)(wt * wh * ww);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = fmaf(f[i], wgt, acc[i]);
+        }
+      }
+    }
+  } else {
+    int pos = 0;
+    for (int pt = 0; pt < Pt; ++pt)
+      for (int ph = 0; ph < Ph; ++ph)
+        for (int pw = 0; pw < Pw; ++pw, ++pos) {
+          float s[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s[i] = 0.f;
+          for (int t = pt; t < pt + kT; ++t)
+            for (int h = ph; h < ph + kH; ++h)
+              for (int w = pw; w < pw + kW; ++w) {
+                float f[8];
+                unpack8(vload(x, (((long long)n * T + t) * H + h) * W + w, c), f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) s[i] += f[i];
+              }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[i] = fmaf(s[i], dropout_keep_scale(seed, n, f_off + c + i, pos, p_drop), acc[i]);
+        }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) feat[(size_t)n * f_ld + f_off + c + i] = acc[i] * inv;
+}
+
+__global__ void head_pool_bwd_kernel(const float* __restrict__ dfeat, int f_ld, int f_off, int N, int T, int H, int W,
+                                     int C, int kT, int kH, int kW, float p_drop, uint64_t seed, ViewW dx) {
+  const int CV = C >> 3;
+  const long long total = (long long)N * T * H * W * CV;
+  const int Pt = T - kT + 1, Ph = H - kH + 1, Pw = W - kW + 1;
+  const float inv = 1.f / ((float)(Pt * Ph * Pw) * (float)(kT * kH * kW));
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(idx % CV) << 3;
+    long long q = idx / CV;
+    const long long pix = q;
+    const int w = (int)(q % W);
+    q /= W;
+    const int h = (int)(q % H);
+    q /= H;
+    const int t = (int)(q % T);
+    const int n = (int)(q / T);
+    const int t_lo = max(0, t - kT + 1), t_hi = min(t, Pt - 1);
+    const int h_lo = max(0, h - kH + 1), h_hi = min(h, Ph - 1);
+    const int w_lo = max(0, w - kW + 1), w_hi = min(w, Pw - 1);
+    float wsum[8];
+    if (p_drop <= 0.f) {
+      const float cnt = (float)((t_hi - t_lo + 1) * (h_hi - h_lo + 1) * (w_hi - w_lo + 1));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) wsum[i] = cnt;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) wsum[i] = 0.f;
+      for (int pt = t_lo; pt <= t_hi; ++pt)
+        for (int ph = h_lo; ph <= h_hi; ++ph)
+          for (int pw = w_lo; pw <= w_hi; ++pw) {
+            const int pos = (pt * Ph + ph) * Pw + pw;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) wsum[i] += dropout_keep_scale(seed, n, f_off + c + i, pos, p_drop);
+          }
+    }
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = dfeat[(size_t)n * f_ld + f_off + c + i] * wsum[i] * inv;
+    vstore(dx, pix, c, pack8(o));
+  }
+}
+
+// ---- FC head (fp32) ---------------------------------------------------------------------------------------
+// one warp per (n, k)
+__global__ void fc_fwd_kernel(const float* __restrict__ feat, const float* __restrict__ w, const float* __restrict__ b,
+                              int N, int K, int C, float* __restrict__ logits) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= N * C) return;
+  const int k = gw % C, n = gw / C;
+  const float* f = feat + (size_t)n * K;
+  const float* wr = w + (size_t)k * K;
+  float acc = 0.f;
+  for (int i = lane; i < K; i += 32) acc = fmaf(f[i], wr[i], acc);
+#pragma unroll
+  for (int off = 16; off; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (lane == 0) logits[(size_t)n * C + k] = acc + (b ? b[k] : 0.f);
+}
+// dfeat[n][i] = sum_k dl[n][k] w[k][i]
+__global__ void fc_bwd_dfeat_kernel(const float* __restrict__ dl, const float* __restrict__ w, int N, int K, int C,
+                                    float* __restrict__ dfeat) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * K) return;
+  const int i = idx % K, n = idx / K;
+  float acc = 0.f;
+  for (int k = 0; k < C; ++k) acc = fmaf(dl[(size_t)n * C + k], w[(size_t)k * K + i], acc);
+  dfeat[idx] = acc;
+}
+// dw[k][i] += sum_n dl[n][k] feat[n][i];  db[k] += sum_n dl[n][k]
+__global__ void fc_bwd_dw_kernel(const float* __restrict__ dl, const float* __restrict__ feat, int N, int K, int C,
+                                 float* __restrict__ dw, float* __restrict__ db) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < C * K) {
+    const int i = idx % K, k = idx / K;
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc = fmaf(dl[(size_t)n * C + k], feat[(size_t)n * K + i], acc);
+    dw[idx] += acc;
+  }
+  if (idx < C && db) {
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc += dl[(size_t)n * C + idx];
+    db[idx] += acc;
+  }
+}
+
+}  // namespace sfb

@@ -1,0 +1,444 @@
+// sfb200.cu -- C ABI of libsfb200.so (see include/sfb200.h): argument validation, TMA tensor-map
+// cache, kernel dispatch.  Single translation unit; links only cudart (static).  The driver entry point
+// cuTensorMapEncodeTiled is resolved at run time so the library also loads on a box without a GPU.
+#include "conv_simt.cuh"
+#include "elementwise.cuh"
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+using namespace sfb;
+
+namespace {
+
+thread_local char g_cuda_err[256] = "";
+std::atomic<long long> g_launches{0};
+
+int cuda_fail(cudaError_t e, const char* where) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", where, cudaGetErrorString(e));
+  return SFB_ERR_CUDA;
+}
+#define SFB_CHECK_LAUNCH(where)                         \
+  do {                                                  \
+    g_launches.fetch_add(1, std::memory_order_relaxed); \
+    cudaError_t e__ = cudaGetLastError();               \
+    if (e__ != cudaSuccess) return cuda_fail(e__, where); \
+  } while (0)
+
+inline int grid_for(long long total, int threads, int cap = 148 * 16) {
+  long long b = (total + threads - 1) / threads;
+  if (b < 1) b = 1;
+  if (b > cap) b = cap;
+  return (int)b;
+}
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// ---- N tile / padding policy (shared with sfb_packed_weight_dims) ----
+int pick_bn(int Co) {
+  if (Co <= 32) return 32;
+  if (Co <= 64) return 64;
+  if (Co <= 128) return 128;
+  return 256;
+}
+
+// ---- TMA tensor maps for packed weights ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+std::mutex g_mu;
+EncodeTiledFn g_encode = nullptr;
+std::map<std::tuple<const void*, int, int, int>, CUtensorMap> g_tmaps;
+
+int get_weight_tmap(const void* wp, int rows_pad, int k_pad, int bn, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  auto key = std::make_tuple(wp, rows_pad, k_pad, bn);
+  auto it = g_tmaps.find(key);
+  if (it != g_tmaps.end()) {
+    *out = it->second;
+    return SFB_OK;
+  }
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+      snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaGetDriverEntryPoint(cuTensorMapEncodeTiled) failed");
+      return SFB_ERR_DRIVER;
+    }
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  CUtensorMap tm;
+  cuuint64_t gdim[2] = {(cuuint64_t)k_pad, (cuuint64_t)rows_pad};
+  cuuint64_t gstr[1] = {(cuuint64_t)k_pad * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)bn};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(wp), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled failed: %d", (int)r);
+    return SFB_ERR_DRIVER;
+  }
+  if (g_tmaps.size() > 4096) g_tmaps.clear();
+  g_tmaps[key] = tm;
+  *out = tm;
+  return SFB_OK;
+}
+
+int check_geom(const SfbConvGeom* g) {
+  if (!g) return SFB_ERR_BAD_ARG;
+  if (g->N <= 0 || g->Ti <= 0 || g->Hi <= 0 || g->Wi <= 0 || g->To <= 0 || g->Ho <= 0 || g->Wo <= 0) return SFB_ERR_BAD_ARG;
+  if (g->Cg <= 0 || (g->Cg & 7) || g->Co <= 0 || (g->Co & 7)) return SFB_ERR_BAD_ARG;
+  if (g->kT <= 0 || g->kH <= 0 || g->kW <= 0 || g->sT <= 0 || g->sH <= 0 || g->sW <= 0) return SFB_ERR_BAD_ARG;
+  if (g->pT < 0 || g->pH < 0 || g->pW < 0) return SFB_ERR_BAD_ARG;
+  if ((g->g_ld & 7) || (g->g_coff & 7) || (g->o_ld & 7) || (g->o_coff & 7)) return SFB_ERR_BAD_ARG;
+  if (g->g_coff + g->Cg > g->g_ld || g->o_coff + g->Co > g->o_ld) return SFB_ERR_BAD_ARG;
+  const long long M = (long long)g->N * g->To * g->Ho * g->Wo;
+  const long long Pin = (long long)g->N * g->Ti * g->Hi * g->Wi;
+  if (M >= (1ll << 31) - 256 || Pin >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+  return SFB_OK;
+}
+
+template <int BN, int STAGES>
+int launch_conv_tc(const CUtensorMap& tm, const ConvTcParams& p, cudaStream_t st) {
+  using L = ConvTcSmem<BN, STAGES>;
+  const size_t smem = L::bytes(p.g.Cg, p.pro_scale != nullptr);
+  static bool attr_done = false;
+  static size_t attr_bytes = 0;
+  if (!attr_done || smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(L::bytes(2048, true)));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_gemm_tc)");
+    attr_done = true;
+    attr_bytes = L::bytes(2048, true);
+  }
+  dim3 grid((p.M + kTileM - 1) / kTileM, (p.g.Co + BN - 1) / BN);
+  conv_gemm_tc_kernel<BN, STAGES><<<grid, kProducerThreads + 64, smem, st>>>(tm, p);
+  SFB_CHECK_LAUNCH("conv_gemm_tc_kernel");
+  return SFB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* sfb_strerror(int status) {
+  switch (status) {
+    case SFB_OK: return "ok";
+    case SFB_ERR_BAD_ARG: return "bad argument (shape, alignment or null pointer)";
+    case SFB_ERR_CUDA: return "CUDA error (see sfb_last_cuda_error)";
+    case SFB_ERR_UNSUPPORTED: return "unsupported configuration";
+    case SFB_ERR_DRIVER: return "driver entry point unavailable (no CUDA driver?)";
+  }
+  return "unknown status";
+}
+const char* sfb_last_cuda_error(void) { return g_cuda_err; }
+int sfb_version(void) { return 100; }
+int64_t sfb_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int sfb_packed_weight_dims(int32_t Co, int32_t Cg, int32_t taps, int32_t* rows_pad, int32_t* k_pad) {
+  if (Co <= 0 || Cg <= 0 || (Cg & 7) || taps <= 0 || !rows_pad || !k_pad) return SFB_ERR_BAD_ARG;
+  const int bn = pick_bn(Co);
+  *rows_pad = (Co + bn - 1) / bn * bn;
+  *k_pad = (taps * Cg + 63) / 64 * 64;
+  return SFB_OK;
+}
+
+int sfb_pack_weight(const float* w, int32_t Co, int32_t Ci, int32_t taps, int32_t Cg, int32_t transposed, void* wp,
+                    int32_t rows_pad, int32_t k_pad, void* stream) {
+  if (!w || !wp || Co <= 0 || Ci <= 0 || taps <= 0 || (Cg & 7) || (k_pad & 63) || k_pad < taps * Cg) return SFB_ERR_BAD_ARG;
+  if (!transposed && (Cg < Ci || rows_pad < Co)) return SFB_ERR_BAD_ARG;
+  if (transposed && (Cg < Co || rows_pad < Ci)) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)rows_pad * k_pad;
+  pack_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, Co, Ci, taps, Cg, transposed,
+                                                                             (__nv_bfloat16*)wp, rows_pad, k_pad);
+  SFB_CHECK_LAUNCH("pack_weight_kernel");
+  return SFB_OK;
+}
+
+int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw, int32_t N, int32_t C,
+                     int32_t T, int32_t H, int32_t W, void* out, int32_t out_ld, void* stream) {
+  if (!x || !out || N <= 0 || C <= 0 || T <= 0 || H <= 0 || W <= 0 || (out_ld & 7) || out_ld < C || !aligned16(out))
+    return SFB_ERR_BAD_ARG;
+  const long long total = (long long)N * T * H * W;
+  layout_input_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(
+      x, sn, sc, st, sh, sw, N, C, T, H, W, (__nv_bfloat16*)out, out_ld);
+  SFB_CHECK_LAUNCH("layout_input_kernel");
+  return SFB_OK;
+}
+
+int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro, const void* wp, int32_t rows_pad,
+                  int32_t k_pad, void* out, const SfbEpilogue* epi, int32_t impl, void* stream) {
+  int rc = check_geom(geom);
+  if (rc) return rc;
+  if (!g || !wp || !out || !aligned16(g) || !aligned16(wp) || !aligned16(out)) return SFB_ERR_BAD_ARG;
+  const int taps = geom->kT * geom->kH * geom->kW;
+  if ((k_pad & 63) || k_pad < taps * geom->Cg || rows_pad < geom->Co) return SFB_ERR_BAD_ARG;
+  ConvTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.g = *geom;
+  p.G = (const __nv_bfloat16*)g;
+  if (pro && pro->scale) {
+    if (!pro->shift) return SFB_ERR_BAD_ARG;
+    p.pro_scale = pro->scale; p.pro_shift = pro->shift; p.pro_relu = pro->relu;
+  }
+  p.out = (__nv_bfloat16*)out;
+  if (epi) {
+    if (epi->scale && !epi->shift) return SFB_ERR_BAD_ARG;
+    p.epi_scale = epi->scale; p.epi_shift = epi->shift;
+    p.res = (const __nv_bfloat16*)epi->residual; p.res_ld = epi->res_ld; p.res_coff = epi->res_coff;
+    if (p.res && ((p.res_ld & 7) || (p.res_coff & 7) || !aligned16(p.res))) return SFB_ERR_BAD_ARG;
+    p.epi_relu = epi->relu;
+    p.stats = epi->stats;
+  }
+  p.M = geom->N * geom->To * geom->Ho * geom->Wo;
+  p.Ktot = taps * geom->Cg;
+  p.nk = k_pad / 64;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (impl == SFB_IMPL_SIMT) {
+    ConvSimtParams q;
+    q.c = p; q.wp = (const __nv_bfloat16*)wp; q.k_pad = k_pad;
+    const long long total = (long long)p.M * geom->Co;
+    const long long blocks = (total + 255) / 256;
+    if (blocks >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+    conv_gemm_simt_kernel<<<(unsigned)blocks, 256, 0, st>>>(q);
+    SFB_CHECK_LAUNCH("conv_gemm_simt_kernel");
+    return SFB_OK;
+  }
+  if (impl != SFB_IMPL_TC) return SFB_ERR_BAD_ARG;
+  if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
+  const int bn = pick_bn(geom->Co);
+  if (rows_pad % bn) return SFB_ERR_BAD_ARG;
+  CUtensorMap tm;
+  rc = get_weight_tmap(wp, rows_pad, k_pad, bn, &tm);
+  if (rc) return rc;
+  switch (bn) {
+    case 32: return launch_conv_tc<32, 4>(tm, p, st);
+    case 64: return launch_conv_tc<64, 4>(tm, p, st);
+    case 128: return launch_conv_tc<128, 3>(tm, p, st);
+    default: return launch_conv_tc<256, 4>(tm, p, st);
+  }
+}
+
+int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pro, const void* dy, int32_t dy_ld,
+                   int32_t dy_coff, float* dw, int32_t Ci_real, int32_t impl, void* stream) {
+  int rc = check_geom(geom);
+  if (rc) return rc;
+  if (geom->transposed) return SFB_ERR_BAD_ARG;
+  if (!x || !dy || !dw || !aligned16(x) || !aligned16(dy)) return SFB_ERR_BAD_ARG;
+  if ((dy_ld & 7) || (dy_coff & 7) || dy_coff + geom->Co > dy_ld || Ci_real <= 0 || Ci_real > geom->Cg) return SFB_ERR_BAD_ARG;
+  WgradTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.g = *geom;
+  p.X = (const __nv_bfloat16*)x;
+  if (pro && pro->scale) {
+    if (!pro->shift) return SFB_ERR_BAD_ARG;
+    p.pro_scale = pro->scale; p.pro_shift = pro->shift; p.pro_relu = pro->relu;
+  }
+  p.dY = (const __nv_bfloat16*)dy; p.dy_ld = dy_ld; p.dy_coff = dy_coff;
+  p.dW = dw; p.Ci_real = Ci_real;
+  p.taps = geom->kT * geom->kH * geom->kW;
+  p.M = geom->N * geom->To * geom->Ho * geom->Wo;
+  p.Ktot = p.taps * geom->Cg;
+  p.chunks_total = (p.M + 63) / 64;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (impl == SFB_IMPL_SIMT) {
+    WgradSimtParams q;
+    q.w = p;
+    const long long total = (long long)geom->Co * Ci_real * p.taps;
+    int splits = (int)((148ll * 8 * 256 + total - 1) / total);
+    if (splits < 1) splits = 1;
+    if (splits > 1024) splits = 1024;
+    q.m_per_split = (p.M + splits - 1) / splits;
+    splits = (p.M + q.m_per_split - 1) / q.m_per_split;
+    dim3 grid((unsigned)((total + 255) / 256), splits);
+    conv_wgrad_simt_kernel<<<grid, 256, 0, st>>>(q);
+    SFB_CHECK_LAUNCH("conv_wgrad_simt_kernel");
+    return SFB_OK;
+  }
+  if (impl != SFB_IMPL_TC) return SFB_ERR_BAD_ARG;
+  if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
+  const int kpad = (p.Ktot + 63) / 64 * 64;
+  const int gx = (kpad + 255) / 256;
+  const int gy = (geom->Co + 127) / 128;
+  int splits = (148 * 2 + gx * gy - 1) / (gx * gy);
+  if (splits < 1) splits = 1;
+  if (splits > p.chunks_total) splits = p.chunks_total;
+  p.chunks_per_split = (p.chunks_total + splits - 1) / splits;
+  splits = (p.chunks_total + p.chunks_per_split - 1) / p.chunks_per_split;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)wgrad_smem_bytes(2048, true));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_wgrad_tc)");
+    attr_done = true;
+  }
+  dim3 grid(gx, gy, splits);
+  conv_wgrad_tc_kernel<<<grid, kProducerThreads + 32, wgrad_smem_bytes(geom->Cg, p.pro_scale != nullptr), st>>>(p);
+  SFB_CHECK_LAUNCH("conv_wgrad_tc_kernel");
+  return SFB_OK;
+}
+
+int sfb_bn_finalize(const float* stats, int32_t C, int64_t count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                    float* save_mean, float* save_invstd, void* stream) {
+  if (!stats || !gamma || !beta || !scale || !shift || !save_mean || !save_invstd || C <= 0 || count <= 0)
+    return SFB_ERR_BAD_ARG;
+  if ((running_mean == nullptr) != (running_var == nullptr)) return SFB_ERR_BAD_ARG;
+  const double unbias = count > 1 ? (double)count / (double)(count - 1) : 1.0;
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, C, 1.0 / (double)count, unbias, gamma,
+                                                                        beta, eps, momentum, running_mean, running_var,
+                                                                        scale, shift, save_mean, save_invstd);
+  SFB_CHECK_LAUNCH("bn_finalize_kernel");
+  return SFB_OK;
+}
+
+int sfb_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
+                int32_t C, float* scale, float* shift, void* stream) {
+  if (!gamma || !beta || !running_mean || !running_var || !scale || !shift || C <= 0) return SFB_ERR_BAD_ARG;
+  bn_fold_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, C,
+                                                                    scale, shift);
+  SFB_CHECK_LAUNCH("bn_fold_kernel");
+  return SFB_OK;
+}
+
+static bool view_ok(const void* p, int ld, int coff, int C) {
+  return p && aligned16(p) && !(ld & 7) && !(coff & 7) && coff + C <= ld;
+}
+
+int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift, const void* r,
+                    int32_t r_ld, int32_t r_coff, const float* r_scale, const float* r_shift, void* out, int32_t o_ld,
+                    int32_t o_coff, int64_t M, int32_t C, int32_t relu, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || !scale || !shift) return SFB_ERR_BAD_ARG;
+  if (!view_ok(y, y_ld, y_coff, C) || !view_ok(out, o_ld, o_coff, C)) return SFB_ERR_BAD_ARG;
+  if (r && !view_ok(r, r_ld, r_coff, C)) return SFB_ERR_BAD_ARG;
+  if (r_scale && (!r || !r_shift)) return SFB_ERR_BAD_ARG;
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  View vr{(const __nv_bfloat16*)r, r_ld, r_coff};
+  ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
+  bn_add_relu_kernel<<<grid_for(M * (C >> 3), 256), 256, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale,
+                                                                                    r_shift, vo, M, C, relu);
+  SFB_CHECK_LAUNCH("bn_add_relu_kernel");
+  return SFB_OK;
+}
+
+int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
+                      const void* mask_src, int32_t m_ld, int32_t m_coff, const float* scale, const float* shift,
+                      const float* mean, const float* invstd, int32_t relu, int64_t M, int32_t C, float* dgamma,
+                      float* dbeta, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !mean || !invstd || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dz, dz_ld, dz_coff, C) || !view_ok(y, y_ld, y_coff, C)) return SFB_ERR_BAD_ARG;
+  if (mask_src && !view_ok(mask_src, m_ld, m_coff, C)) return SFB_ERR_BAD_ARG;
+  if (relu && !mask_src && (!scale || !shift)) return SFB_ERR_BAD_ARG;
+  View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
+  const int RL = kRedThreads / (C >> 3);
+  const int grid = grid_for((M + RL - 1) / RL, 1, 148 * 4);
+  bn_bwd_reduce_kernel<<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, vy, vm, scale, shift, mean, invstd, relu, M,
+                                                                       C, dgamma, dbeta);
+  SFB_CHECK_LAUNCH("bn_bwd_reduce_kernel");
+  return SFB_OK;
+}
+
+int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
+                     const void* mask_src, int32_t m_ld, int32_t m_coff, const float* scale, const float* shift,
+                     const float* mean, const float* invstd, const float* gamma, const float* dgamma,
+                     const float* dbeta, int32_t relu, int64_t M, int32_t C, void* dy, int32_t dy_ld, int32_t dy_coff,
+                     void* g_out, int32_t g_ld, int32_t g_coff, int32_t g_accumulate, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dz, dz_ld, dz_coff, C) || !view_ok(y, y_ld, y_coff, C) || !view_ok(dy, dy_ld, dy_coff, C))
+    return SFB_ERR_BAD_ARG;
+  if (mask_src && !view_ok(mask_src, m_ld, m_coff, C)) return SFB_ERR_BAD_ARG;
+  if (g_out && !view_ok(g_out, g_ld, g_coff, C)) return SFB_ERR_BAD_ARG;
+  if (relu && !mask_src && (!scale || !shift)) return SFB_ERR_BAD_ARG;
+  View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
+  ViewW vdy{(__nv_bfloat16*)dy, dy_ld, dy_coff};
+  ViewW vg{(__nv_bfloat16*)g_out, g_ld, g_coff};
+  bn_bwd_apply_kernel<<<grid_for(M * (C >> 3), 256), 256, 0, (cudaStream_t)stream>>>(
+      vdz, vy, vm, scale, shift, mean, invstd, gamma, dgamma, dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, g_accumulate);
+  SFB_CHECK_LAUNCH("bn_bwd_apply_kernel");
+  return SFB_OK;
+}
+
+int sfb_maxpool_fwd(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift, int32_t N,
+                    int32_t T, int32_t H, int32_t W, int32_t C, void* out, int32_t o_ld, int32_t o_coff, uint8_t* idx,
+                    void* stream) {
+  if (N <= 0 || T <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7)) return SFB_ERR_BAD_ARG;
+  if (!view_ok(y, y_ld, y_coff, C) || !view_ok(out, o_ld, o_coff, C)) return SFB_ERR_BAD_ARG;
+  if ((scale == nullptr) != (shift == nullptr)) return SFB_ERR_BAD_ARG;
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
+  const long long total = (long long)N * T * Ho * Wo * (C >> 3);
+  maxpool_fwd_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(vy, scale, shift, N, T, H, W, C,
+                                                                                       vo, idx);
+  SFB_CHECK_LAUNCH("maxpool_fwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx, int32_t N, int32_t T, int32_t H,
+                    int32_t W, int32_t C, void* dz, int32_t dz_ld, int32_t dz_coff, void* stream) {
+  if (N <= 0 || T <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7) || !idx) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dout, d_ld, d_coff, C) || !view_ok(dz, dz_ld, dz_coff, C)) return SFB_ERR_BAD_ARG;
+  View vd{(const __nv_bfloat16*)dout, d_ld, d_coff};
+  ViewW vz{(__nv_bfloat16*)dz, dz_ld, dz_coff};
+  const long long total = (long long)N * T * H * W * (C >> 3);
+  maxpool_bwd_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(vd, idx, N, T, H, W, C, vz);
+  SFB_CHECK_LAUNCH("maxpool_bwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, float* feat, int32_t f_ld,
+                      int32_t f_off, void* stream) {
+  if (N <= 0 || C <= 0 || (C & 7) || kT <= 0 || kH <= 0 || kW <= 0 || kT > T || kH > H || kW > W || !feat) return SFB_ERR_BAD_ARG;
+  if (!view_ok(x, x_ld, x_coff, C) || f_off + C > f_ld || dropout_p < 0.f || dropout_p >= 1.f) return SFB_ERR_BAD_ARG;
+  View vx{(const __nv_bfloat16*)x, x_ld, x_coff};
+  const int total = N * (C >> 3);
+  head_pool_fwd_kernel<<<(total + 63) / 64, 64, 0, (cudaStream_t)stream>>>(vx, N, T, H, W, C, kT, kH, kW, dropout_p, seed,
+                                                                           feat, f_ld, f_off);
+  SFB_CHECK_LAUNCH("head_pool_fwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_head_pool_bwd(const float* dfeat, int32_t f_ld, int32_t f_off, int32_t N, int32_t T, int32_t H, int32_t W,
+                      int32_t C, int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, void* dx,
+                      int32_t dx_ld, int32_t dx_coff, void* stream) {
+  if (N <= 0 || C <= 0 || (C & 7) || kT <= 0 || kH <= 0 || kW <= 0 || kT > T || kH > H || kW > W || !dfeat) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dx, dx_ld, dx_coff, C) || f_off + C > f_ld || dropout_p < 0.f || dropout_p >= 1.f) return SFB_ERR_BAD_ARG;
+  ViewW vx{(__nv_bfloat16*)dx, dx_ld, dx_coff};
+  const long long total = (long long)N * T * H * W * (C >> 3);
+  head_pool_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(dfeat, f_ld, f_off, N, T, H, W, C, kT, kH,
+                                                                               kW, dropout_p, seed, vx);
+  SFB_CHECK_LAUNCH("head_pool_bwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_fc_fwd(const float* feat, const float* w, const float* b, int32_t N, int32_t K, int32_t C, float* logits,
+               void* stream) {
+  if (!feat || !w || !logits || N <= 0 || K <= 0 || C <= 0) return SFB_ERR_BAD_ARG;
+  const long long threads = (long long)N * C * 32;
+  fc_fwd_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(feat, w, b, N, K, C, logits);
+  SFB_CHECK_LAUNCH("fc_fwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_fc_bwd(const float* dlogits, const float* feat, const float* w, int32_t N, int32_t K, int32_t C, float* dfeat,
+               float* dw, float* db, void* stream) {
+  if (!dlogits || !feat || !w || !dfeat || !dw || N <= 0 || K <= 0 || C <= 0) return SFB_ERR_BAD_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  fc_bwd_dfeat_kernel<<<(N * K + 255) / 256, 256, 0, st>>>(dlogits, w, N, K, C, dfeat);
+  SFB_CHECK_LAUNCH("fc_bwd_dfeat_kernel");
+  fc_bwd_dw_kernel<<<(C * K + 255) / 256, 256, 0, st>>>(dlogits, feat, N, K, C, dw, db);
+  SFB_CHECK_LAUNCH("fc_bwd_dw_kernel");
+  return SFB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,187 @@
+"""Tensor-level wrappers over the C ABI (include/sfb200.h).
+
+`Act` is a channel view (buffer, channel offset, channels) of a bf16 NDHWC buffer -- the unit every
+kernel takes as (ptr, ld, coff).  torch owns memory and streams; all arithmetic happens in libsfb200.so.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import _ffi
+from ._ffi import ConvGeom, Epilogue, Prologue, check, lib, ptr, stream_ptr
+
+
+@dataclass
+class Act:
+    buf: torch.Tensor  # (N, T, H, W, ld) bf16 contiguous
+    coff: int
+    C: int
+
+    @property
+    def ld(self):
+        return self.buf.shape[-1]
+
+    @property
+    def dims(self):
+        return tuple(self.buf.shape[:4])
+
+    @property
+    def M(self):
+        n, t, h, w = self.dims
+        return n * t * h * w
+
+    def ptr(self):
+        return self.buf.data_ptr()
+
+    def torch_view(self):
+        return self.buf[..., self.coff:self.coff + self.C]
+
+    @staticmethod
+    def empty(N, T, H, W, ld, device="cuda", coff=0, C=None, zero=False):
+        f = torch.zeros if zero else torch.empty
+        return Act(f((N, T, H, W, ld), dtype=torch.bfloat16, device=device), coff, ld if C is None else C)
+
+    def view(self, coff, C):
+        return Act(self.buf, coff, C)
+
+
+def round_up(x, m):
+    return (x + m - 1) // m * m
+
+
+def conv_out_dims(dims, k, s, p):
+    return tuple((d + 2 * pp - kk) // ss + 1 for d, kk, ss, pp in zip(dims, k, s, p))
+
+
+def layout_input(x: torch.Tensor, ld: int) -> Act:
+    """fp32 (N,C,T,H,W) with arbitrary strides -> bf16 NDHWC buffer with `ld` channels (zero padded)."""
+    assert x.dtype == torch.float32 and x.dim() == 5 and x.is_cuda
+    N, Cc, T, H, W = x.shape
+    out = Act.empty(N, T, H, W, ld, device=x.device, C=ld)
+    sn, sc, st, sh, sw = x.stride()
+    check(lib().sfb_layout_input(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, out.ptr(), ld, stream_ptr()),
+          "sfb_layout_input")
+    return out
+
+
+def pack_weight(w: torch.Tensor, Cg: int, transposed: bool = False, out: Optional[torch.Tensor] = None):
+    """fp32 OIDHW conv weight -> packed bf16 [rows_pad][k_pad] (k = tap*Cg + c)."""
+    assert w.dtype == torch.float32 and w.is_cuda and w.is_contiguous()
+    Co, Ci = w.shape[0], w.shape[1]
+    taps = w[0, 0].numel()
+    rows = Ci if transposed else Co
+    rows_pad, k_pad = _ffi.packed_weight_dims(rows, Cg, taps)
+    if out is None:
+        out = torch.empty((rows_pad, k_pad), dtype=torch.bfloat16, device=w.device)
+    assert tuple(out.shape) == (rows_pad, k_pad)
+    check(lib().sfb_pack_weight(w.data_ptr(), Co, Ci, taps, Cg, int(transposed), out.data_ptr(), rows_pad, k_pad,
+                                stream_ptr()), "sfb_pack_weight")
+    return out
+
+
+def make_geom(x: Act, out: Act, k, s, p, transposed=False) -> ConvGeom:
+    N, Ti, Hi, Wi = x.dims
+    N2, To, Ho, Wo = out.dims
+    assert N == N2
+    return ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, out.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+                    x.ld, x.coff, out.ld, out.coff, int(transposed))
+
+
+def conv_gemm(x: Act, wp: torch.Tensor, out: Act, k, s, p, *, transposed=False,
+              pro: Optional[Tuple[torch.Tensor, torch.Tensor, bool]] = None,
+              epi_affine: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, residual: Optional[Act] = None,
+              relu=False, stats: Optional[torch.Tensor] = None, impl=_ffi.IMPL_TC):
+    g = make_geom(x, out, k, s, p, transposed)
+    pr = Prologue(ptr(pro[0]), ptr(pro[1]), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
+    ep = Epilogue(ptr(epi_affine[0]) if epi_affine else 0, ptr(epi_affine[1]) if epi_affine else 0,
+                  residual.ptr() if residual else 0, residual.ld if residual else 0,
+                  residual.coff if residual else 0, int(relu), ptr(stats))
+    check(lib().sfb_conv_gemm(C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1], out.ptr(),
+                              C.byref(ep), impl, stream_ptr()), "sfb_conv_gemm")
+    return out
+
+
+def conv_wgrad(x: Act, dy: Act, dw: torch.Tensor, k, s, p, *, pro=None, impl=_ffi.IMPL_TC):
+    """dw (fp32, (Co, Ci, kT, kH, kW), contiguous) += wgrad."""
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    g = make_geom(x, dy, k, s, p, False)
+    pr = Prologue(ptr(pro[0]), ptr(pro[1]), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
+    check(lib().sfb_conv_wgrad(C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), dy.ld, dy.coff, dw.data_ptr(),
+                               dw.shape[1], impl, stream_ptr()), "sfb_conv_wgrad")
+    return dw
+
+
+def bn_finalize(stats, count, gamma, beta, eps, momentum, running_mean, running_var, scale, shift, mean, invstd):
+    check(lib().sfb_bn_finalize(stats.data_ptr(), gamma.numel(), count, gamma.data_ptr(), beta.data_ptr(), eps,
+                                momentum, ptr(running_mean), ptr(running_var), scale.data_ptr(), shift.data_ptr(),
+                                mean.data_ptr(), invstd.data_ptr(), stream_ptr()), "sfb_bn_finalize")
+
+
+def bn_fold(gamma, beta, rm, rv, eps, scale, shift):
+    check(lib().sfb_bn_fold(gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(), rv.data_ptr(), eps, gamma.numel(),
+                            scale.data_ptr(), shift.data_ptr(), stream_ptr()), "sfb_bn_fold")
+
+
+def bn_add_relu(y: Act, scale, shift, r: Optional[Act], r_scale, r_shift, out: Act, relu=True):
+    check(lib().sfb_bn_add_relu(y.ptr(), y.ld, y.coff, scale.data_ptr(), shift.data_ptr(),
+                                r.ptr() if r else 0, r.ld if r else 0, r.coff if r else 0, ptr(r_scale), ptr(r_shift),
+                                out.ptr(), out.ld, out.coff, y.M, y.C, int(relu), stream_ptr()), "sfb_bn_add_relu")
+    return out
+
+
+def bn_bwd_reduce(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, relu, dgamma, dbeta):
+    check(lib().sfb_bn_bwd_reduce(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff,
+                                  mask.ptr() if mask else 0, mask.ld if mask else 0, mask.coff if mask else 0,
+                                  ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), int(relu), y.M, y.C,
+                                  dgamma.data_ptr(), dbeta.data_ptr(), stream_ptr()), "sfb_bn_bwd_reduce")
+
+
+def bn_bwd_apply(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, gamma, dgamma, dbeta, relu,
+                 dy: Act, g_out: Optional[Act] = None, g_accumulate=False):
+    check(lib().sfb_bn_bwd_apply(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff,
+                                 mask.ptr() if mask else 0, mask.ld if mask else 0, mask.coff if mask else 0,
+                                 ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                                 dgamma.data_ptr(), dbeta.data_ptr(), int(relu), y.M, y.C, dy.ptr(), dy.ld, dy.coff,
+                                 g_out.ptr() if g_out else 0, g_out.ld if g_out else 0, g_out.coff if g_out else 0,
+                                 int(g_accumulate), stream_ptr()), "sfb_bn_bwd_apply")
+
+
+def maxpool_fwd(y: Act, scale, shift, out: Act, idx: Optional[torch.Tensor]):
+    N, T, H, W = y.dims
+    check(lib().sfb_maxpool_fwd(y.ptr(), y.ld, y.coff, ptr(scale), ptr(shift), N, T, H, W, y.C, out.ptr(), out.ld,
+                                out.coff, ptr(idx), stream_ptr()), "sfb_maxpool_fwd")
+    return out
+
+
+def maxpool_bwd(dout: Act, idx: torch.Tensor, dz: Act):
+    N, T, H, W = dz.dims
+    check(lib().sfb_maxpool_bwd(dout.ptr(), dout.ld, dout.coff, idx.data_ptr(), N, T, H, W, dz.C, dz.ptr(), dz.ld,
+                                dz.coff, stream_ptr()), "sfb_maxpool_bwd")
+    return dz
+
+
+def head_pool_fwd(x: Act, k, dropout_p, seed, feat: torch.Tensor, f_off: int):
+    N, T, H, W = x.dims
+    check(lib().sfb_head_pool_fwd(x.ptr(), x.ld, x.coff, N, T, H, W, x.C, k[0], k[1], k[2], float(dropout_p), seed,
+                                  feat.data_ptr(), feat.shape[1], f_off, stream_ptr()), "sfb_head_pool_fwd")
+
+
+def head_pool_bwd(dfeat: torch.Tensor, f_off: int, k, dropout_p, seed, dx: Act):
+    N, T, H, W = dx.dims
+    check(lib().sfb_head_pool_bwd(dfeat.data_ptr(), dfeat.shape[1], f_off, N, T, H, W, dx.C, k[0], k[1], k[2],
+                                  float(dropout_p), seed, dx.ptr(), dx.ld, dx.coff, stream_ptr()), "sfb_head_pool_bwd")
+
+
+def fc_fwd(feat, w, b, logits):
+    N, K = feat.shape
+    check(lib().sfb_fc_fwd(feat.data_ptr(), w.data_ptr(), ptr(b), N, K, w.shape[0], logits.data_ptr(), stream_ptr()),
+          "sfb_fc_fwd")
+    return logits
+
+
+def fc_bwd(dlogits, feat, w, dfeat, dw, db):
+    N, K = feat.shape
+    check(lib().sfb_fc_bwd(dlogits.data_ptr(), feat.data_ptr(), w.data_ptr(), N, K, w.shape[0], dfeat.data_ptr(),
+                           dw.data_ptr(), ptr(db), stream_ptr()), "sfb_fc_bwd")
