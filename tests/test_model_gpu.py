@@ -1,0 +1,167 @@
+"""End-to-end parity on the B200: the drop-in model (libsfb200 kernels through the C ABI) vs the fp32 oracle on
+identical seeded weights and synthetic clips.  Tolerances are the ones BASELINE.json's north_star states
+(logits rel-err 2e-2, identical top-1, per-layer gradients 3e-2)."""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from oracle import slowfast_oracle as so  # noqa: E402
+from video_classification_b200 import _ffi  # noqa: E402
+
+import parity_utils as pu  # noqa: E402
+
+DEV = "cuda"
+
+
+def _clips(variant, n, size, ts, tf, seed=1):
+    xs, xf = so.synthetic_clips(n, ts, tf, size, seed=seed)
+    return xs.to(DEV), xf.to(DEV)
+
+
+CASES = [
+    # variant, fuse, N, S, Ts, Tf
+    ("REF", True, 4, 64, 8, 8),
+    ("REF", False, 2, 64, 8, 8),
+    ("REF", True, 2, 128, 20, 20),
+    ("HYB", True, 2, 224, 8, 32),
+]
+
+
+@pytest.mark.parametrize("variant,fuse,N,S,Ts,Tf", CASES)
+def test_eval_logits(variant, fuse, N, S, Ts, Tf):
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair(variant, fuse)
+    xs, xf = _clips(variant, N, S, Ts, Tf)
+    oracle.eval()
+    product.eval()
+    with torch.no_grad():
+        ref = oracle([xs, xf])
+        got = product([xs, xf])
+    assert got.shape == ref.shape == (N, 249)
+    err = pu.rel_max(got, ref)
+    assert err <= pu.LOGIT_TOL, f"eval logits rel-err {err:.3e}"
+    assert torch.equal(got.argmax(1), ref.argmax(1)), "top-1 differs"
+
+
+@pytest.mark.parametrize("variant,fuse,N,S,Ts,Tf", CASES)
+def test_train_step_parity(variant, fuse, N, S, Ts, Tf):
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair(variant, fuse)
+    xs, xf = _clips(variant, N, S, Ts, Tf)
+    y = torch.randint(0, 249, (N,), generator=torch.Generator().manual_seed(7)).to(DEV)
+    oracle.train()
+    product.train()
+    ref = oracle([xs, xf])
+    F.cross_entropy(ref, y).backward()
+    got = product([xs, xf])
+    F.cross_entropy(got, y).backward()
+    err = pu.rel_max(got.detach(), ref.detach())
+    assert err <= pu.LOGIT_TOL, f"train logits rel-err {err:.3e}"
+    assert torch.equal(got.argmax(1), ref.argmax(1)), "top-1 differs"
+    ref_grads = {n: p.grad for n, p in oracle.named_parameters()}
+    rep = pu.grad_report(product, ref_grads)
+    worst = sorted(rep, key=lambda t: -t[1])[:5]
+    bad = [(n, e) for n, e in rep if e > pu.GRAD_TOL]
+    assert not bad, f"{len(bad)}/{len(rep)} gradients above {pu.GRAD_TOL}: worst {worst}"
+    # BatchNorm running statistics follow the reference update rule (momentum 0.1, unbiased variance)
+    sd_o, sd_p = oracle.state_dict(), product.state_dict()
+    for k in sd_o:
+        if k.endswith("running_mean") or k.endswith("running_var"):
+            if ".res_unit." in k:
+                continue
+            assert pu.rel_max(sd_p[k].float(), sd_o[k].float()) < 2e-2, k
+        if k.endswith("num_batches_tracked") and ".res_unit." not in k:
+            assert int(sd_p[k]) == int(sd_o[k]), k
+
+
+def test_reference_call_sequence_adam():
+    """train.py:225-231 step order with optim.Adam over ALL parameters (dead ones keep grad=None)."""
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair("REF", True)
+    xs, xf = _clips("REF", 2, 64, 8, 8)
+    y = torch.tensor([3, 200], device=DEV)
+    opt = torch.optim.Adam(product.parameters(), lr=1e-3)
+    losses = []
+    for _ in range(3):
+        product.train()
+        out = product([xs, xf])
+        loss = F.cross_entropy(out, y)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0], losses
+    dead = [n for n, p in product.named_parameters() if p.grad is None]
+    assert len(dead) == 48 and all((".residual." in n or ".res_unit." in n) for n in dead)
+
+
+def test_noncontiguous_inputs_and_time_mismatch():
+    oracle, product = pu.build_pair("REF", True)
+    product.eval()
+    xs, xf = so.synthetic_clips(2, 8, 8, 64)  # non-contiguous views like train.py:136-140
+    assert not xs.is_contiguous()
+    with torch.no_grad():
+        a = product([xs.to(DEV), xf.to(DEV)])
+        b = product([xs.contiguous().to(DEV), xf.contiguous().to(DEV)])
+    assert torch.equal(a, b)
+    with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
+        with torch.no_grad():
+            product([torch.randn(1, 5, 8, 64, 64, device=DEV), torch.randn(1, 15, 32, 64, 64, device=DEV)])
+
+
+def test_simt_impl_matches_tc():
+    """the CUDA-core cross-check kernels and the tcgen05 kernels implement the same contract end to end"""
+    oracle, product = pu.build_pair("REF", True)
+    xs, xf = _clips("REF", 2, 64, 8, 8)
+    product.eval()
+    with torch.no_grad():
+        a = product([xs, xf])
+        product._engine.impl = _ffi.IMPL_SIMT
+        b = product([xs, xf])
+        product._engine.impl = _ffi.IMPL_TC
+    assert pu.rel_max(a, b) < 5e-3
+
+
+@pytest.mark.skipif(not os.path.exists(os.path.join(os.path.dirname(__file__), "golden", "ref_small.pt")),
+                    reason="golden fixture missing")
+@pytest.mark.parametrize("name", ["ref_small", "hyb_small"])
+def test_against_golden_fixture(name):
+    """fixtures were produced by the reference's own model/my_slowfast.py imported verbatim (oracle/make_golden.py)"""
+    path = os.path.join(os.path.dirname(__file__), "golden", name + ".pt")
+    if not os.path.exists(path):
+        pytest.skip("fixture missing")
+    fx = torch.load(path)
+    meta = fx["meta"]
+    oracle, product = pu.build_pair(meta["variant"], True, seed=meta["seed"], bn_seed=meta["bn_seed"])
+    # the regenerated weights must be the ones the fixture was made with
+    chk = sum(float(v.double().abs().sum()) for k, v in oracle.state_dict().items() if v.dtype.is_floating_point)
+    assert abs(chk - meta["weight_checksum"]) <= 1e-6 * meta["weight_checksum"], "seeded weights differ from fixture"
+    xs, xf = so.synthetic_clips(meta["N"], meta["Ts"], meta["Tf"], meta["S"], seed=meta["clip_seed"])
+    xs, xf = xs.to(DEV), xf.to(DEV)
+    y = torch.tensor(meta["labels"], device=DEV)
+    product.eval()
+    with torch.no_grad():
+        got = product([xs, xf])
+    assert pu.rel_max(got.cpu(), fx["eval_logits"]) <= pu.LOGIT_TOL
+    assert torch.equal(got.argmax(1).cpu(), fx["eval_logits"].argmax(1))
+    product.train()
+    out = product([xs, xf])
+    F.cross_entropy(out, y).backward()
+    assert pu.rel_max(out.detach().cpu(), fx["train_logits"]) <= pu.LOGIT_TOL
+    bad = []
+    for n, p in product.named_parameters():
+        if n not in fx["grad_norm"]:
+            assert p.grad is None, n
+            continue
+        g = p.grad.float().cpu().flatten()
+        idx = fx["grad_idx"][n]
+        ref_s, ref_norm = fx["grad_samples"][n], fx["grad_norm"][n]
+        e_norm = abs(float(g.norm()) - ref_norm) / max(ref_norm, 1e-20)
+        e_samp = float((g[idx] - ref_s).norm() / ref_s.norm().clamp_min(1e-20)) if ref_s.numel() > 8 else 0.0
+        if e_norm > pu.GRAD_TOL or e_samp > 2 * pu.GRAD_TOL:
+            bad.append((n, e_norm, e_samp))
+    assert not bad, bad[:8]

@@ -1,0 +1,669 @@
+"""Execution engine of the B200 SlowFast: compiles the parameter tree of my_slowfast.SlowFastB200 into a static
+list of libsfb200 kernel calls (forward, and backward for training) per input shape, with every activation /
+gradient buffer planned up front.
+
+Data flow (training), per conv layer L with BatchNorm:
+    conv_gemm  : raw y_L (bf16 NDHWC) + per-channel sum / sum-of-squares fused in the GEMM epilogue
+    bn_finalize: batch mean/var -> (scale, shift), running-stat update           (tiny)
+    consumer   : applies relu(y*scale+shift) while staging its operand (prologue) -- no standalone BN pass
+    block tail : out = relu(bn_c(y_c) + shortcut)                                  (one fused pass per ResBlock)
+The Fast->Slow lateral conv writes its raw output directly behind the Slow stage output in one
+channel-concatenated buffer (torch.cat of reference model/my_slowfast.py:343 never happens); its BN+ReLU is a
+per-channel prologue of the next stage (identity on the Slow channels).
+Backward mirrors this: bn_bwd_reduce/apply produce dy, conv_wgrad accumulates fp32 weight gradients into one flat
+arena (reverse-forward order, ready for bucketed all-reduce), conv_gemm(transposed) is dgrad.
+"""
+import ctypes as C
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import _ffi
+from ._ffi import ConvGeom, Epilogue, Prologue, lib
+from .ops import Act, conv_out_dims, round_up
+
+
+def _f32(n, dev, zero=False):
+    return (torch.zeros if zero else torch.empty)(n, dtype=torch.float32, device=dev)
+
+
+class BufferPool:
+    """Plan-time recycling of bf16 scratch buffers (ops run in stream order, so static reuse is safe)."""
+
+    def __init__(self, dev):
+        self.dev = dev
+        self.free_list: Dict[int, List[torch.Tensor]] = {}
+        self.total_bytes = 0
+
+    def alloc(self, shape) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= s
+        lst = self.free_list.get(n)
+        if lst:
+            return lst.pop().view(shape)
+        self.total_bytes += n * 2
+        return torch.empty(shape, dtype=torch.bfloat16, device=self.dev)
+
+    def release(self, t: torch.Tensor):
+        self.free_list.setdefault(t.numel(), []).append(t)
+
+
+class ConvL:
+    """One Conv3d (+ its BatchNorm3d) of the graph: parameters, packed bf16 operands, BN scratch, gradient views."""
+
+    def __init__(self, name, conv: nn.Conv3d, bn: nn.BatchNorm3d, needs_dgrad=True):
+        self.name = name
+        self.conv, self.bn = conv, bn
+        self.k = tuple(conv.kernel_size)
+        self.s = tuple(conv.stride)
+        self.p = tuple(conv.padding)
+        self.Ci, self.Co = conv.in_channels, conv.out_channels
+        self.Cg = round_up(self.Ci, 8)
+        self.taps = self.k[0] * self.k[1] * self.k[2]
+        self.needs_dgrad = needs_dgrad
+        self.wp = self.wpt = None
+        self.packed_version = -1
+        # set by the engine
+        self.stats = self.scale = self.shift = self.mean = self.invstd = None
+        self.dw = self.dgamma = self.dbeta = None
+
+
+class FinalAct:
+    """A materialised (post-activation) tensor plus, in training plans, its gradient buffer."""
+
+    def __init__(self, act: Act):
+        self.act = act
+        self.grad: Optional[Act] = None  # allocated at the first gradient contribution (backward plan)
+        self.ginit = False  # has any contribution been written to grad yet (plan-time flag)
+        self.cat = None     # CatInfo when this tensor lives inside a Slow|lateral concat buffer
+
+
+class CatInfo:
+    """Channel-concatenated Slow-stage input: [slow_out (final) | lateral conv output (raw, BN+ReLU lazily applied)]."""
+
+    def __init__(self, cat: Act, c_slow: int):
+        self.cat, self.c_slow = cat, c_slow
+        self.dcat: Optional[Act] = None
+        self.X: Optional[FinalAct] = None         # the whole buffer as the next stage's input
+        self.slow_out: Optional[FinalAct] = None  # channels [0, c_slow)
+
+
+class Plan:
+    def __init__(self):
+        self.fwd: List[Tuple] = []
+        self.bwd: List[Tuple] = []
+        self.keep = []  # ctypes structs / tensors that must outlive the op lists
+        self.x_in: List[Act] = []
+        self.logits = None
+        self.dlogits = None
+        self.act_bytes = 0
+        self.seed_slot = None
+        self.gen = 0  # bumped by every training forward; backward checks it saw the latest one
+
+
+class SlowFastEngine:
+    def __init__(self, model, dry_run: bool = False):
+        """dry_run=True plans on the `meta` device without touching the GPU (host-logic tests only; it cannot
+        execute anything)."""
+        self.model = model
+        cfg = model.graph_cfg
+        self.cfg = cfg
+        self.dry_run = dry_run
+        p0 = next(model.parameters())
+        if not p0.is_cuda and not dry_run:
+            raise _ffi.SfbError("the B200 SlowFast runs on CUDA only: call model.cuda() first (no CPU fallback)")
+        self.dev = torch.device("meta") if dry_run else p0.device
+        self.lib = lib()
+        self.stream = C.c_void_p(0)
+        self.impl = _ffi.IMPL_TC
+        self.plans: Dict[Tuple, Plan] = {}
+        self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
+        self.step_seed = 0
+        self.ddp = None  # set by parallel.attach_ddp
+        self._collect_layers()
+        self._alloc_arenas()
+
+    # ------------------------------------------------------------------ graph description
+    def _collect_layers(self):
+        m = self.model
+        cfg = self.cfg
+        self.fuse = cfg["fuse"]
+        L: List[ConvL] = []
+        self.stems = []
+        for p in range(2):
+            st = m.blocks[0].multipathway_blocks[p]
+            self.stems.append(ConvL(f"blocks.0.multipathway_blocks.{p}", st.conv, st.norm, needs_dgrad=False))
+        L += self.stems
+        self.laterals: List[Optional[ConvL]] = []
+        for si in range(5):
+            fu = m.blocks[si].multipathway_fusion
+            if self.fuse and not isinstance(fu, nn.Identity):
+                self.laterals.append(ConvL(f"blocks.{si}.multipathway_fusion", fu.conv_fast_to_slow[0], fu.norm[0]))
+            else:
+                self.laterals.append(None)
+        self.stages = []  # [stage][pathway] -> list of block dicts
+        for si in range(1, 5):
+            per_path = []
+            for p in range(2):
+                blks = []
+                for bi, rb in enumerate(m.blocks[si].multipathway_blocks[p].res_blocks):
+                    nm = f"blocks.{si}.multipathway_blocks.{p}.res_blocks.{bi}"
+                    b2 = rb.branch2
+                    d = dict(a=ConvL(nm + ".a", b2.conv_a, b2.norm_a), b=ConvL(nm + ".b", b2.conv_b, b2.norm_b),
+                             c=ConvL(nm + ".c", b2.conv_c, b2.norm_c),
+                             s=ConvL(nm + ".s", rb.branch1_conv, rb.branch1_norm) if rb.branch1_conv is not None else None)
+                    blks.append(d)
+                per_path.append(blks)
+            self.stages.append(per_path)
+        # forward order of all conv layers (used for arenas and the reverse-order gradient layout)
+        order: List[ConvL] = list(self.stems)
+        if self.laterals[0] is not None:
+            order.append(self.laterals[0])
+        for si in range(4):
+            for p in range(2):
+                for d in self.stages[si][p]:
+                    if d["s"] is not None:
+                        order.append(d["s"])
+                    order += [d["a"], d["b"], d["c"]]
+            if self.laterals[si + 1] is not None:
+                order.append(self.laterals[si + 1])
+        self.layers = order
+        self.proj = m.blocks[6].proj
+        self.bn_modules = [l.bn for l in self.layers]
+
+    def _alloc_arenas(self):
+        dev = self.dev
+        # ---- BN scratch: [all stats | per layer scale, shift, mean, invstd] ----
+        n_stats = sum(2 * l.Co for l in self.layers)
+        n_rest = sum(4 * l.Co for l in self.layers)
+        self.bn_flat = _f32(n_stats + n_rest, dev, zero=True)
+        self.stats_flat = self.bn_flat[:n_stats]
+        o_s, o_r = 0, n_stats
+        for l in self.layers:
+            c = l.Co
+            l.stats = self.bn_flat[o_s:o_s + 2 * c]
+            o_s += 2 * c
+            l.scale, l.shift = self.bn_flat[o_r:o_r + c], self.bn_flat[o_r + c:o_r + 2 * c]
+            l.mean, l.invstd = self.bn_flat[o_r + 2 * c:o_r + 3 * c], self.bn_flat[o_r + 3 * c:o_r + 4 * c]
+            o_r += 4 * c
+        # ---- concat prologue vectors: identity on the Slow channels, lateral BN on the rest ----
+        self.cat_pro = {}
+        for si, lat in enumerate(self.laterals):
+            if lat is None:
+                continue
+            c_slow = self.cfg["stem_dim_outs"][0] * (1 if si == 0 else 4 * 2 ** (si - 1))
+            tot = c_slow + lat.Co
+            sc, sh = _f32(tot, dev), _f32(tot, dev, zero=True)
+            sc.fill_(1.0)
+            self.cat_pro[si] = (sc, sh, c_slow)
+            lat.scale, lat.shift = sc[c_slow:], sh[c_slow:]  # bn_finalize writes straight into the cat vector
+        # ---- flat gradient arena, reverse forward order (head first) ----
+        live: List[torch.nn.Parameter] = []
+        for l in self.layers:
+            live += [l.conv.weight, l.bn.weight, l.bn.bias]
+        live += [self.proj.weight, self.proj.bias]
+        self.live_params = live
+        offs, o = {}, 0
+        for prm in reversed(live):
+            offs[id(prm)] = o
+            o += round_up(prm.numel(), 8)
+        self.grad_flat = _f32(o, dev, zero=True)
+        self.grad_views = {}
+        for prm in live:
+            st = offs[id(prm)]
+            self.grad_views[id(prm)] = self.grad_flat[st:st + prm.numel()].view(prm.shape)
+        self.grad_offsets = offs
+        for l in self.layers:
+            l.dw = self.grad_views[id(l.conv.weight)]
+            l.dgamma = self.grad_views[id(l.bn.weight)]
+            l.dbeta = self.grad_views[id(l.bn.bias)]
+
+    def invalidate_weights(self):
+        for l in self.layers:
+            l.packed_version = -1
+
+    # ------------------------------------------------------------------ weights
+    def refresh_weights(self, training: bool):
+        """(Re)pack bf16 GEMM operands of every conv whose fp32 master weight changed (optimizer step / load)."""
+        for l in self.layers:
+            w = l.conv.weight
+            if l.packed_version == w._version and l.wp is not None and (l.wpt is not None or not (training and l.needs_dgrad)):
+                continue
+            rp, kp = _ffi.packed_weight_dims(l.Co, l.Cg, l.taps)
+            if l.wp is None:
+                l.wp = torch.empty((rp, kp), dtype=torch.bfloat16, device=self.dev)
+            if self.dry_run:
+                rpt, kpt = _ffi.packed_weight_dims(l.Ci, l.Co, l.taps)
+                l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
+                l.packed_version = w._version
+                continue
+            wd = w.detach()
+            if not wd.is_contiguous():
+                wd = wd.contiguous()
+            _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cg, 0, l.wp.data_ptr(), rp, kp, self.stream),
+                       "sfb_pack_weight")
+            if training and l.needs_dgrad:
+                rpt, kpt = _ffi.packed_weight_dims(l.Ci, l.Co, l.taps)
+                if l.wpt is None:
+                    l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
+                _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Co, 1, l.wpt.data_ptr(), rpt, kpt,
+                                                    self.stream), "sfb_pack_weight(T)")
+            l.packed_version = w._version
+
+    # ------------------------------------------------------------------ op emission helpers
+    def _emit(self, lst, fn, *args):
+        lst.append((fn, args))
+
+    def _conv(self, plan, lst, L: ConvL, x: Act, pro, out: Act, *, stats=False, transposed=False, residual: Act = None,
+              wp=None):
+        k, s, p = L.k, L.s, L.p
+        N, Ti, Hi, Wi = x.dims
+        _, To, Ho, Wo = out.dims
+        g = ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, out.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+                     x.ld, x.coff, out.ld, out.coff, int(transposed))
+        pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
+        ep = Epilogue(0, 0, residual.ptr() if residual else 0, residual.ld if residual else 0,
+                      residual.coff if residual else 0, 0, L.stats.data_ptr() if stats else 0)
+        plan.keep += [g, pr, ep]
+        wp = wp if wp is not None else (L.wpt if transposed else L.wp)
+        self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
+                   out.ptr(), C.byref(ep), self.impl, self.stream)
+
+    def _wgrad(self, plan, lst, L: ConvL, x: Act, pro, dy: Act):
+        k, s, p = L.k, L.s, L.p
+        N, Ti, Hi, Wi = x.dims
+        _, To, Ho, Wo = dy.dims
+        g = ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, dy.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+                     x.ld, x.coff, dy.ld, dy.coff, 0)
+        pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
+        plan.keep += [g, pr]
+        self._emit(lst, self.lib.sfb_conv_wgrad, C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), dy.ld, dy.coff,
+                   L.dw.data_ptr(), L.Ci, self.impl, self.stream)
+        if self.ddp is not None:
+            self.ddp.note_grad_ready(plan, lst, L.conv.weight)
+
+    def _bn_stats_ready(self, plan, lst, L: ConvL, count: int, training: bool):
+        bn = L.bn
+        if training:
+            self._emit(lst, self.lib.sfb_bn_finalize, L.stats.data_ptr(), L.Co, count, bn.weight.data_ptr(), bn.bias.data_ptr(),
+                       float(bn.eps), float(bn.momentum if bn.momentum is not None else 0.1), bn.running_mean.data_ptr(),
+                       bn.running_var.data_ptr(), L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(),
+                       L.invstd.data_ptr(), self.stream)
+        else:
+            self._emit(lst, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                       bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
+
+    def _bn_bwd(self, plan, lst, L: ConvL, dz: Act, y: Act, mask: Optional[Act], dy: Act, g_out: Optional[Act] = None,
+                g_acc=False, do_reduce=True):
+        bn = L.bn
+        m = (mask.ptr(), mask.ld, mask.coff) if mask is not None else (0, 0, 0)
+        if do_reduce:
+            self._emit(lst, self.lib.sfb_bn_bwd_reduce, dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, *m,
+                       L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(), L.invstd.data_ptr(), 1, y.M, y.C,
+                       L.dgamma.data_ptr(), L.dbeta.data_ptr(), self.stream)
+        go = (g_out.ptr(), g_out.ld, g_out.coff) if g_out is not None else (0, 0, 0)
+        self._emit(lst, self.lib.sfb_bn_bwd_apply, dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, *m,
+                   L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(), L.invstd.data_ptr(), bn.weight.data_ptr(),
+                   L.dgamma.data_ptr(), L.dbeta.data_ptr(), 1, y.M, y.C, dy.ptr(), dy.ld, dy.coff, *go, int(g_acc),
+                   self.stream)
+        if self.ddp is not None:
+            self.ddp.note_grad_ready(plan, lst, bn.weight)
+            self.ddp.note_grad_ready(plan, lst, bn.bias)
+
+    # ------------------------------------------------------------------ plan construction
+    def build_plan(self, N, Ts, Tf, H, W, training) -> Plan:
+        cfg = self.cfg
+        dev = self.dev
+        plan = Plan()
+        pool = BufferPool(dev)
+        fwd, bwd_blocks = plan.fwd, []
+
+        def new_act(n, t, h, w, c, zero=False):
+            a = Act.empty(n, t, h, w, c, device=dev, zero=zero)
+            plan.act_bytes += a.buf.numel() * 2
+            return a
+
+        def new_grad(like: Act, C_=None):
+            n, t, h, w = like.dims
+            c = C_ if C_ is not None else like.C
+            return Act(pool.alloc((n, t, h, w, c)), 0, c)
+
+        T_in = (Ts, Tf)
+        # ---------------- stems ----------------
+        stem_rec = []
+        pooled: List[FinalAct] = []
+        cat_bufs = {}  # stage index -> (cat Act, dcat Act|None)
+        c_slow0 = cfg["stem_dim_outs"][0]
+        for p in range(2):
+            L = self.stems[p]
+            x_in = new_act(N, T_in[p], H, W, L.Cg)
+            plan.x_in.append(x_in)
+            To, Ho, Wo = conv_out_dims((T_in[p], H, W), L.k, L.s, L.p)
+            y0 = new_act(N, To, Ho, Wo, L.Co)
+            self._conv(plan, fwd, L, x_in, None, y0, stats=training)
+            self._bn_stats_ready(plan, fwd, L, y0.M, training)
+            Hp, Wp = (Ho - 1) // 2 + 1, (Wo - 1) // 2 + 1
+            if p == 0 and self.laterals[0] is not None:
+                lat = self.laterals[0]
+                ci = CatInfo(new_act(N, To, Hp, Wp, L.Co + lat.Co), L.Co)
+                cat_bufs[0] = ci
+                out = FinalAct(ci.cat.view(0, L.Co))
+                out.cat = ci
+                ci.slow_out = out
+            else:
+                out = FinalAct(new_act(N, To, Hp, Wp, L.Co))
+            idx = torch.empty((N, To, Hp, Wp, L.Co), dtype=torch.uint8, device=dev) if training else None
+            self._emit(fwd, self.lib.sfb_maxpool_fwd, y0.ptr(), y0.ld, y0.coff, L.scale.data_ptr(), L.shift.data_ptr(),
+                       N, To, Ho, Wo, L.Co, out.act.ptr(), out.act.ld, out.act.coff, idx.data_ptr() if training else 0,
+                       self.stream)
+            pooled.append(out)
+            stem_rec.append(dict(L=L, x_in=x_in, y0=y0, out=out, idx=idx))
+
+        # lateral helper -------------------------------------------------
+        lateral_rec = {}
+
+        def do_lateral(si, slow_out: FinalAct, fast_out: FinalAct):
+            """lateral conv after stage-index si (0 = stems); returns the Slow input of the next stage as
+            (Act over the whole cat buffer, prologue, FinalAct-like gradient holder)"""
+            lat = self.laterals[si]
+            ci = cat_bufs[si]
+            sc, sh, c_slow = self.cat_pro[si]
+            assert c_slow == ci.c_slow and slow_out is ci.slow_out
+            ylat = ci.cat.view(c_slow, lat.Co)
+            self._conv(plan, fwd, lat, fast_out.act, None, ylat, stats=training)
+            self._bn_stats_ready(plan, fwd, lat, ylat.M, training)
+            X = FinalAct(ci.cat)
+            X.cat = ci
+            ci.X = X
+            lateral_rec[si] = dict(L=lat, x=fast_out, ylat=ylat, ci=ci)
+            return X, (sc, sh, True)
+
+        # ---------------- residual stages ----------------
+        block_recs = []  # forward order: (stage, pathway, block index, record)
+        cur: List[FinalAct] = pooled
+        cur_pro = [None, None]
+        if self.laterals[0] is not None:
+            X, pro = do_lateral(0, cur[0], cur[1])
+            cur = [X, cur[1]]
+            cur_pro = [pro, None]
+        for si in range(4):
+            nxt: List[FinalAct] = [None, None]
+            for p in (1, 0):  # Fast first: its output feeds the lateral that completes the Slow concat buffer
+                X, Xpro = cur[p], cur_pro[p]
+                blks = self.stages[si][p]
+                for bi, d in enumerate(blks):
+                    a, b, c, s_ = d["a"], d["b"], d["c"], d["s"]
+                    n_, t_, h_, w_ = X.act.dims
+                    ta, ha, wa = conv_out_dims((t_, h_, w_), a.k, a.s, a.p)
+                    ya = new_act(n_, ta, ha, wa, a.Co)
+                    self._conv(plan, fwd, a, X.act, Xpro, ya, stats=training)
+                    self._bn_stats_ready(plan, fwd, a, ya.M, training)
+                    tb, hb, wb = conv_out_dims((ta, ha, wa), b.k, b.s, b.p)
+                    yb = new_act(n_, tb, hb, wb, b.Co)
+                    self._conv(plan, fwd, b, ya, (a.scale, a.shift, True), yb, stats=training)
+                    self._bn_stats_ready(plan, fwd, b, yb.M, training)
+                    yc = new_act(n_, tb, hb, wb, c.Co)
+                    self._conv(plan, fwd, c, yb, (b.scale, b.shift, True), yc, stats=training)
+                    self._bn_stats_ready(plan, fwd, c, yc.M, training)
+                    y1 = None
+                    if s_ is not None:
+                        y1 = new_act(n_, tb, hb, wb, s_.Co)
+                        self._conv(plan, fwd, s_, X.act, Xpro, y1, stats=training)
+                        self._bn_stats_ready(plan, fwd, s_, y1.M, training)
+                    last = bi == len(blks) - 1
+                    if last and p == 0 and self.laterals[si + 1] is not None:
+                        lat = self.laterals[si + 1]
+                        ci = CatInfo(new_act(n_, tb, hb, wb, c.Co + lat.Co), c.Co)
+                        cat_bufs[si + 1] = ci
+                        O = FinalAct(ci.cat.view(0, c.Co))
+                        O.cat = ci
+                        ci.slow_out = O
+                    else:
+                        O = FinalAct(new_act(n_, tb, hb, wb, c.Co))
+                    if y1 is not None:
+                        self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
+                                   y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
+                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream)
+                    else:
+                        assert Xpro is None
+                        self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
+                                   X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
+                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream)
+                    block_recs.append(dict(si=si, p=p, d=d, X=X, Xpro=Xpro, ya=ya, yb=yb, yc=yc, y1=y1, O=O))
+                    X, Xpro = O, None
+                nxt[p] = X
+            cur, cur_pro = nxt, [None, None]
+            if self.laterals[si + 1] is not None:
+                Xs, pro = do_lateral(si + 1, cur[0], cur[1])
+                block_recs.append(dict(lateral=si + 1))
+                cur = [Xs, cur[1]]
+                cur_pro = [pro, None]
+
+        # ---------------- head ----------------
+        feat_dim = cur[0].act.C + cur[1].act.C
+        ncls = self.proj.out_features
+        assert feat_dim == self.proj.in_features
+        feat = _f32(N * feat_dim, dev).view(N, feat_dim)
+        logits = _f32(N * ncls, dev).view(N, ncls)
+        plan.logits = logits
+        hk = cfg["head_pool_kernel_sizes"]
+        drop = float(self.dropout_p) if training else 0.0
+        plan.seed_slot = C.c_uint64(0)
+        f_off = 0
+        for p in range(2):
+            a = cur[p].act
+            n_, t_, h_, w_ = a.dims
+            if hk[p][0] > t_ or hk[p][1] > h_ or hk[p][2] > w_:
+                raise _ffi.SfbError(f"head pool kernel {hk[p]} larger than the final feature map {(t_, h_, w_)} "
+                                    f"(same failure as nn.AvgPool3d in the reference)")
+            self._emit(fwd, self.lib.sfb_head_pool_fwd, a.ptr(), a.ld, a.coff, n_, t_, h_, w_, a.C, hk[p][0], hk[p][1], hk[p][2],
+                       drop, plan.seed_slot, feat.data_ptr(), feat_dim, f_off, self.stream)
+            f_off += a.C
+        self._emit(fwd, self.lib.sfb_fc_fwd, feat.data_ptr(), self.proj.weight.data_ptr(), self.proj.bias.data_ptr(), N,
+                   feat_dim, ncls, logits.data_ptr(), self.stream)
+        plan.keep += [feat, logits]
+        if not training:
+            return plan
+
+        # =============================== backward ===============================
+        bwd = plan.bwd
+        dlogits = _f32(N * ncls, dev).view(N, ncls)
+        dfeat = _f32(N * feat_dim, dev).view(N, feat_dim)
+        plan.dlogits = dlogits
+        plan.keep += [dfeat]
+        self._emit(bwd, self.lib.sfb_fc_bwd, dlogits.data_ptr(), feat.data_ptr(), self.proj.weight.data_ptr(), N, feat_dim, ncls,
+                   dfeat.data_ptr(), self.grad_views[id(self.proj.weight)].data_ptr(),
+                   self.grad_views[id(self.proj.bias)].data_ptr(), self.stream)
+        if self.ddp is not None:
+            self.ddp.note_grad_ready(plan, bwd, self.proj.weight)
+            self.ddp.note_grad_ready(plan, bwd, self.proj.bias)
+
+        def ensure_grad(fa: FinalAct):
+            if fa.grad is not None:
+                return
+            if fa.cat is not None:
+                ci = fa.cat
+                ci.dcat = new_grad(ci.cat)
+                ci.X.grad = ci.dcat
+                ci.slow_out.grad = ci.dcat.view(0, ci.c_slow)
+            else:
+                fa.grad = new_grad(fa.act)
+
+        def lateral_backward(si):
+            lr = lateral_rec[si]
+            lat, ci = lr["L"], lr["ci"]
+            assert ci.X.ginit, "concat buffer without gradient contribution"
+            ci.slow_out.ginit = True  # the Slow channels of dcat are now complete as well
+            dz = ci.dcat.view(ci.c_slow, lat.Co)
+            self._bn_bwd(plan, bwd, lat, dz, lr["ylat"], None, dz)  # in place: dz -> dy
+            self._wgrad(plan, bwd, lat, lr["x"].act, None, dz)
+            dgrad_into(lat, dz, lr["x"])
+
+        f_off = 0
+        for p in range(2):
+            fa = cur[p]
+            ensure_grad(fa)
+            a, ga = fa.act, fa.grad
+            n_, t_, h_, w_ = a.dims
+            self._emit(bwd, self.lib.sfb_head_pool_bwd, dfeat.data_ptr(), feat_dim, f_off, n_, t_, h_, w_, a.C,
+                       hk[p][0], hk[p][1], hk[p][2], drop, plan.seed_slot, ga.ptr(), ga.ld, ga.coff, self.stream)
+            fa.ginit = True
+            f_off += a.C
+
+        def dgrad_into(L: ConvL, dy: Act, X: FinalAct):
+            """dX (+)= conv_transpose(dy, W_L)"""
+            ensure_grad(X)
+            self._conv(plan, bwd, L, dy, None, X.grad, transposed=True, residual=X.grad if X.ginit else None)
+            X.ginit = True
+
+        for rec in reversed(block_recs):
+            if "lateral" in rec:
+                lateral_backward(rec["lateral"])
+                continue
+            d, X, Xpro, O = rec["d"], rec["X"], rec["Xpro"], rec["O"]
+            a, b, c, s_ = d["a"], d["b"], d["c"], d["s"]
+            ya, yb, yc, y1 = rec["ya"], rec["yb"], rec["yc"], rec["y1"]
+            dO = O.grad
+            assert O.ginit, "block output without gradient contribution"
+            dyc = new_grad(yc)
+            if s_ is not None:
+                self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc)
+                dy1 = new_grad(y1)
+                self._bn_bwd(plan, bwd, s_, dO, y1, O.act, dy1)
+            else:
+                # identity shortcut: masked gradient g also flows straight to the block input
+                ensure_grad(X)
+                self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc, g_out=X.grad, g_acc=X.ginit)
+                X.ginit = True
+            self._wgrad(plan, bwd, c, yb, (b.scale, b.shift, True), dyc)
+            dzb = new_grad(yb)
+            self._conv(plan, bwd, c, dyc, None, dzb, transposed=True)
+            pool.release(dyc.buf)
+            self._bn_bwd(plan, bwd, b, dzb, yb, None, dzb)
+            self._wgrad(plan, bwd, b, ya, (a.scale, a.shift, True), dzb)
+            dza = new_grad(ya)
+            self._conv(plan, bwd, b, dzb, None, dza, transposed=True)
+            pool.release(dzb.buf)
+            self._bn_bwd(plan, bwd, a, dza, ya, None, dza)
+            self._wgrad(plan, bwd, a, X.act, Xpro, dza)
+            if s_ is not None:
+                self._wgrad(plan, bwd, s_, X.act, Xpro, dy1)
+                dgrad_into(s_, dy1, X)
+                pool.release(dy1.buf)
+            dgrad_into(a, dza, X)
+            pool.release(dza.buf)
+            pool.release(O.cat.dcat.buf if O.cat is not None else dO.buf)
+
+        if self.laterals[0] is not None:
+            lateral_backward(0)
+        for p in range(2):
+            sr = stem_rec[p]
+            L, y0, out = sr["L"], sr["y0"], sr["out"]
+            assert out.ginit
+            n_, t_, h_, w_ = y0.dims
+            dz0 = new_grad(y0)
+            g = out.grad
+            self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
+                       dz0.ptr(), dz0.ld, dz0.coff, self.stream)
+            self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
+            self._wgrad(plan, bwd, L, sr["x_in"], None, dz0)
+            pool.release(dz0.buf)
+            pool.release(out.cat.dcat.buf if out.cat is not None else g.buf)
+            plan.keep.append(sr["idx"])
+        plan.act_bytes += pool.total_bytes
+        plan.keep.append(pool)
+        return plan
+
+    # ------------------------------------------------------------------ execution
+    def _run(self, ops):
+        for fn, args in ops:
+            rc = fn(*args)
+            if rc:
+                _ffi.check(rc, getattr(fn, "__name__", "libsfb200 call"))
+
+    def get_plan(self, xs, xf, training) -> Plan:
+        N, Cs, Ts, H, W = xs.shape
+        N2, Cf, Tf, H2, W2 = xf.shape
+        if (N2, H2, W2) != (N, H, W):
+            raise ValueError("slow and fast clips must share batch and spatial size")
+        if (Cs, Cf) != tuple(self.cfg["input_channels"]):
+            raise ValueError(f"expected input channels {self.cfg['input_channels']}, got {(Cs, Cf)}")
+        lat_kT, lat_sT = self.cfg["fusion_conv_kernel"][0], self.cfg["fusion_conv_stride"][0]
+        t_lat = (Tf + 2 * (lat_kT // 2) - lat_kT) // lat_sT + 1
+        if self.fuse and t_lat != Ts:
+            raise RuntimeError(f"Sizes of tensors must match except in dimension 1. Expected size {Ts} but got size "
+                               f"{t_lat} (lateral output vs Slow pathway; same failure as torch.cat at reference "
+                               f"model/my_slowfast.py:343)")
+        key = (N, Ts, Tf, H, W, bool(training), self.impl)
+        plan = self.plans.get(key)
+        if plan is None:
+            self.refresh_weights(training)
+            plan = self.build_plan(N, Ts, Tf, H, W, training)
+            self.plans[key] = plan
+        return plan
+
+    def forward(self, xs: torch.Tensor, xf: torch.Tensor, training: bool) -> Tuple[torch.Tensor, Plan]:
+        if xs.dtype != torch.float32 or xf.dtype != torch.float32:
+            raise TypeError("inputs must be float32 (as produced by the reference loader)")
+        if xs.device != self.dev or xf.device != self.dev:
+            raise _ffi.SfbError("inputs must live on the model's CUDA device")
+        self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
+        plan = self.get_plan(xs, xf, training)
+        self.refresh_weights(training)
+        for x, a in zip((xs, xf), plan.x_in):
+            N, Cc, T, H, W = x.shape
+            sn, sc, st, sh, sw = x.stride()
+            _ffi.check(self.lib.sfb_layout_input(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, a.ptr(), a.ld, self.stream),
+                       "sfb_layout_input")
+        if training:
+            plan.gen += 1
+            self.stats_flat.zero_()
+            self.step_seed += 1
+            plan.seed_slot.value = (self.step_seed * 0x9E3779B97F4A7C15 + 12345) & 0xFFFFFFFFFFFFFFFF
+        self._run(plan.fwd)
+        if training:
+            torch._foreach_add_([bn.num_batches_tracked for bn in self.bn_modules], 1)
+        return plan.logits, plan
+
+    def backward(self, plan: Plan, dlogits: torch.Tensor):
+        self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
+        plan.dlogits.copy_(dlogits)
+        self.grad_flat.zero_()
+        if self.ddp is not None:
+            self.ddp.begin_backward(self)
+        self._run(plan.bwd)
+        if self.ddp is not None:
+            self.ddp.finish_backward(self)
+        return [self.grad_views[id(p)] for p in self.live_params]
+
+
+class _SlowFastFn(torch.autograd.Function):
+    """forward + backward of the whole network as ONE autograd node (no per-layer dispatcher overhead)."""
+
+    @staticmethod
+    def forward(ctx, engine: SlowFastEngine, xs, xf, *params):
+        training = engine.model.training
+        logits, plan = engine.forward(xs, xf, training)
+        ctx.engine, ctx.plan, ctx.gen = engine, plan, plan.gen
+        ctx.training = training
+        return logits.clone()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        if not ctx.training:
+            raise RuntimeError("backward through an eval-mode forward of the B200 SlowFast is not supported: "
+                               "call model.train() before the forward pass")
+        if ctx.plan.gen != ctx.gen:
+            raise RuntimeError("a newer training forward of the same shape overwrote the saved activations; "
+                               "run backward before the next forward (one forward in flight per input shape)")
+        grads = ctx.engine.backward(ctx.plan, dlogits.contiguous().float())
+        return (None, None, None) + tuple(grads)
+
+
+def run_model(engine: SlowFastEngine, xs, xf):
+    if torch.is_grad_enabled() and any(p.requires_grad for p in engine.live_params):
+        return _SlowFastFn.apply(engine, xs, xf, *engine.live_params)
+    logits, _ = engine.forward(xs, xf, engine.model.training)
+    return logits.clone()
