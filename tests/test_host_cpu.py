@@ -1,0 +1,118 @@
+"""CPU tests (no GPU, no compute calls): the C-ABI library loads and exports every symbol include/sfb200.h declares,
+argument validation rejects bad requests before any launch, the drop-in keeps the reference's module tree /
+state_dict, and the engine plans a full training step on the meta device."""
+import ctypes as C
+import os
+import re
+
+import pytest
+import torch
+
+from oracle import slowfast_oracle as so
+from video_classification_b200 import _ffi
+from video_classification_b200 import build as sfb_build
+from video_classification_b200.my_slowfast import (FuseFastToSlow, MyFastToSlowFusionBuilder, _MODEL_STAGE_DEPTH,
+                                                   init_my_slowfast)
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    sfb_build.build()
+    return _ffi.lib()
+
+
+def test_header_symbols_all_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "sfb200.h")).read()
+    declared = sorted(set(re.findall(r"\b(sfb_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 20
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/sfb200.h but not exported by libsfb200.so"
+    assert sorted(declared) == _ffi.ALL_SYMBOLS, "ctypes binding and header disagree"
+    assert lib.sfb_version() >= 100
+    assert lib.sfb_strerror(0) == b"ok" and b"bad argument" in lib.sfb_strerror(-1)
+
+
+def test_validation_rejects_before_launch(lib):
+    r, k = C.c_int32(), C.c_int32()
+    assert lib.sfb_packed_weight_dims(64, 8, 49, C.byref(r), C.byref(k)) == 0
+    assert (r.value, k.value) == (64, 448)
+    assert lib.sfb_packed_weight_dims(2048, 1280, 3, C.byref(r), C.byref(k)) == 0
+    assert r.value == 2048 and k.value == 3840
+    assert lib.sfb_packed_weight_dims(64, 5, 49, C.byref(r), C.byref(k)) == -1  # Cg must be a multiple of 8
+    n0 = lib.sfb_launch_count()
+    g = _ffi.ConvGeom(1, 4, 8, 8, 12, 4, 8, 8, 16, 1, 1, 1, 1, 1, 1, 0, 0, 0, 12, 0, 16, 0, 0)  # Cg=12 not /8
+    assert lib.sfb_conv_gemm(C.byref(g), 16, None, 16, 32, 64, 16, None, 0, None) == -1
+    assert lib.sfb_conv_gemm(None, 16, None, 16, 32, 64, 16, None, 0, None) == -1
+    assert lib.sfb_bn_finalize(None, 8, 10, None, None, 1e-5, 0.1, None, None, None, None, None, None, None) == -1
+    assert lib.sfb_fc_fwd(None, None, None, 1, 1, 1, None, None) == -1
+    assert lib.sfb_launch_count() == n0, "a rejected call must not launch anything"
+
+
+def test_missing_library_fails_loudly(monkeypatch):
+    monkeypatch.setattr(_ffi, "_lib", None)
+    monkeypatch.setattr(_ffi, "LIB_PATH", "/nonexistent/libsfb200.so")
+    with pytest.raises(_ffi.SfbError, match="no CPU/PyTorch fallback"):
+        _ffi.lib()
+
+
+def test_dropin_module_tree_matches_reference_contract():
+    torch.manual_seed(0)
+    m = init_my_slowfast(so.make_cfg(249, True), (5, 15), (64, 8))
+    torch.manual_seed(0)
+    o = so.build_oracle()
+    sd_m, sd_o = m.state_dict(), o.state_dict()
+    assert list(sd_m.keys()) == list(sd_o.keys()) and len(sd_m) == 734
+    for k in sd_m:
+        assert sd_m[k].shape == sd_o[k].shape and sd_m[k].dtype == sd_o[k].dtype, k
+        assert torch.equal(sd_m[k], sd_o[k]), f"{k}: initialisation differs from the reference (same seed)"
+    assert sum(p.numel() for p in m.parameters()) == 38077321
+    # the 12 names train.py:94-108 deletes from the canonical checkpoint exist with the reference's shapes
+    for k in ("blocks.0.multipathway_blocks.0.conv.weight", "blocks.0.multipathway_blocks.1.conv.weight",
+              "blocks.6.proj.weight", "blocks.6.proj.bias", "blocks.0.multipathway_fusion.conv_fast_to_slow.0.weight"):
+        assert k in sd_m
+    assert tuple(sd_m["blocks.0.multipathway_blocks.0.conv.weight"].shape) == (64, 5, 1, 7, 7)
+    assert tuple(sd_m["blocks.0.multipathway_fusion.conv_fast_to_slow.0.weight"].shape) == (16, 8, 3, 1, 1)
+    m.load_state_dict(o.state_dict(), strict=True)
+    o.load_state_dict(m.state_dict(), strict=True)
+    assert _MODEL_STAGE_DEPTH[50] == (3, 4, 6, 3)
+    assert isinstance(m.blocks[0].multipathway_fusion, FuseFastToSlow)
+    assert isinstance(MyFastToSlowFusionBuilder.build_fusion_builder(8).create_module(64, 4), torch.nn.Identity)
+    # MODEL.FUSE = False: nn.Identity fusion, 640 fewer... keys as in the reference
+    m2 = init_my_slowfast(so.make_cfg(249, False), (5, 15), (64, 8))
+    assert list(m2.state_dict().keys()) == list(so.build_oracle(fuse=False).state_dict().keys())
+    with pytest.raises(AssertionError):
+        init_my_slowfast(so.make_cfg(), (5,), (64,))
+
+
+def test_cpu_model_refuses_to_run():
+    m = init_my_slowfast(so.make_cfg(), (5, 15), (64, 8))
+    with pytest.raises(_ffi.SfbError, match="no CPU fallback"):
+        m([torch.randn(1, 5, 4, 64, 64), torch.randn(1, 15, 4, 64, 64)])
+
+
+@pytest.mark.parametrize("variant,shape", [("REF", (2, 20, 20, 64, 64)), ("HYB", (2, 8, 32, 224, 224))])
+def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
+    from video_classification_b200.engine import SlowFastEngine
+    kw = {} if variant == "REF" else dict(fusion_conv_stride=(4, 1, 1), head_pool_kernel_sizes=((8, 7, 7), (32, 7, 7)))
+    m = init_my_slowfast(so.make_cfg(), (5, 15), (64, 8), **kw)
+    eng = SlowFastEngine(m, dry_run=True)
+    eng.refresh_weights(True)
+    plan = eng.build_plan(*shape, True)
+    n_conv = len(eng.layers)
+    assert n_conv == 2 + 4 + 16 * 2 * 3 + 4 * 2  # stems, laterals, 16 bottlenecks x 2 pathways x 3, 4 shortcuts x 2
+    convs = [op for op in plan.fwd if op[0] is lib.sfb_conv_gemm]
+    assert len(convs) == n_conv
+    wgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_wgrad]
+    assert len(wgrads) == n_conv
+    dgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_gemm]
+    assert len(dgrads) == n_conv - 2  # the stems need no input gradient
+    assert tuple(plan.logits.shape) == (shape[0], 249)
+    # the lateral output lands behind the Slow stage output in ONE buffer (torch.cat never happens)
+    bufs = eng.tagged_buffers(plan)
+    lat = bufs["blocks.1.multipathway_fusion.conv_fast_to_slow.0.y"]
+    slow = bufs["blocks.1.multipathway_blocks.0.res_blocks.2.O"]
+    assert lat.buf is slow.buf and slow.coff == 0 and lat.coff == slow.C == 256 and lat.buf.shape[-1] == 320
+    with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
+        eng.get_plan(torch.empty(1, 5, 8, 64, 64, device="meta"), torch.empty(1, 15, 32 if variant == "REF" else 8, 64, 64, device="meta"), False)

@@ -19,8 +19,9 @@ S = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 Ts = int(sys.argv[4]) if len(sys.argv) > 4 else 8
 Tf = int(sys.argv[5]) if len(sys.argv) > 5 else Ts
 fuse = (sys.argv[6] != "0") if len(sys.argv) > 6 else True
+twin = (sys.argv[7] == "twin") if len(sys.argv) > 7 else False
 pu.fp32_reference_mode()
-oracle, product = pu.build_pair(variant, fuse)
+oracle, product = pu.build_pair(variant, fuse, twin=twin)
 xs, xf = so.synthetic_clips(N, Ts, Tf, S)
 xs, xf = xs.cuda(), xf.cuda()
 y = torch.randint(0, 249, (N,), generator=torch.Generator().manual_seed(7)).cuda()

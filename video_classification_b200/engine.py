@@ -24,6 +24,11 @@ from ._ffi import ConvGeom, Epilogue, Prologue, lib
 from .ops import Act, conv_out_dims, round_up
 
 
+def _probe():
+    """no-op plan entry: lets a debug capture snapshot a buffer at this point of the op list"""
+    return 0
+
+
 def _f32(n, dev, zero=False):
     return (torch.zeros if zero else torch.empty)(n, dtype=torch.float32, device=dev)
 
@@ -53,8 +58,9 @@ class BufferPool:
 class ConvL:
     """One Conv3d (+ its BatchNorm3d) of the graph: parameters, packed bf16 operands, BN scratch, gradient views."""
 
-    def __init__(self, name, conv: nn.Conv3d, bn: nn.BatchNorm3d, needs_dgrad=True):
+    def __init__(self, name, conv: nn.Conv3d, bn: nn.BatchNorm3d, needs_dgrad=True, conv_name=None):
         self.name = name
+        self.conv_name = conv_name or name  # path of the nn.Conv3d in the module tree (debug captures)
         self.conv, self.bn = conv, bn
         self.k = tuple(conv.kernel_size)
         self.s = tuple(conv.stride)
@@ -122,6 +128,7 @@ class SlowFastEngine:
         self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
         self.step_seed = 0
         self.ddp = None  # set by parallel.attach_ddp
+        self.capture = None  # dict: tools/layer_diag.py sets it to snapshot tagged intermediates (debug only)
         self._collect_layers()
         self._alloc_arenas()
 
@@ -134,13 +141,15 @@ class SlowFastEngine:
         self.stems = []
         for p in range(2):
             st = m.blocks[0].multipathway_blocks[p]
-            self.stems.append(ConvL(f"blocks.0.multipathway_blocks.{p}", st.conv, st.norm, needs_dgrad=False))
+            self.stems.append(ConvL(f"blocks.0.multipathway_blocks.{p}", st.conv, st.norm, needs_dgrad=False,
+                                    conv_name=f"blocks.0.multipathway_blocks.{p}.conv"))
         L += self.stems
         self.laterals: List[Optional[ConvL]] = []
         for si in range(5):
             fu = m.blocks[si].multipathway_fusion
             if self.fuse and not isinstance(fu, nn.Identity):
-                self.laterals.append(ConvL(f"blocks.{si}.multipathway_fusion", fu.conv_fast_to_slow[0], fu.norm[0]))
+                self.laterals.append(ConvL(f"blocks.{si}.multipathway_fusion", fu.conv_fast_to_slow[0], fu.norm[0],
+                                           conv_name=f"blocks.{si}.multipathway_fusion.conv_fast_to_slow.0"))
             else:
                 self.laterals.append(None)
         self.stages = []  # [stage][pathway] -> list of block dicts
@@ -151,9 +160,11 @@ class SlowFastEngine:
                 for bi, rb in enumerate(m.blocks[si].multipathway_blocks[p].res_blocks):
                     nm = f"blocks.{si}.multipathway_blocks.{p}.res_blocks.{bi}"
                     b2 = rb.branch2
-                    d = dict(a=ConvL(nm + ".a", b2.conv_a, b2.norm_a), b=ConvL(nm + ".b", b2.conv_b, b2.norm_b),
-                             c=ConvL(nm + ".c", b2.conv_c, b2.norm_c),
-                             s=ConvL(nm + ".s", rb.branch1_conv, rb.branch1_norm) if rb.branch1_conv is not None else None)
+                    d = dict(a=ConvL(nm + ".a", b2.conv_a, b2.norm_a, conv_name=nm + ".branch2.conv_a"),
+                             b=ConvL(nm + ".b", b2.conv_b, b2.norm_b, conv_name=nm + ".branch2.conv_b"),
+                             c=ConvL(nm + ".c", b2.conv_c, b2.norm_c, conv_name=nm + ".branch2.conv_c"),
+                             s=ConvL(nm + ".s", rb.branch1_conv, rb.branch1_norm, conv_name=nm + ".branch1_conv")
+                             if rb.branch1_conv is not None else None, name=nm)
                     blks.append(d)
                 per_path.append(blks)
             self.stages.append(per_path)
@@ -162,7 +173,7 @@ class SlowFastEngine:
         if self.laterals[0] is not None:
             order.append(self.laterals[0])
         for si in range(4):
-            for p in range(2):
+            for p in (1, 0):  # execution order: Fast first (its output feeds the lateral of the Slow concat buffer)
                 for d in self.stages[si][p]:
                     if d["s"] is not None:
                         order.append(d["s"])
@@ -253,11 +264,12 @@ class SlowFastEngine:
             l.packed_version = w._version
 
     # ------------------------------------------------------------------ op emission helpers
-    def _emit(self, lst, fn, *args):
-        lst.append((fn, args))
+    def _emit(self, lst, fn, *args, tag=None):
+        """tag = (name, Act | tensor): what this op just finished writing (debug captures only)"""
+        lst.append((fn, args, tag))
 
     def _conv(self, plan, lst, L: ConvL, x: Act, pro, out: Act, *, stats=False, transposed=False, residual: Act = None,
-              wp=None):
+              wp=None, tag=None):
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = out.dims
@@ -269,7 +281,8 @@ class SlowFastEngine:
         plan.keep += [g, pr, ep]
         wp = wp if wp is not None else (L.wpt if transposed else L.wp)
         self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
-                   out.ptr(), C.byref(ep), self.impl, self.stream)
+                   out.ptr(), C.byref(ep), self.impl, self.stream,
+                   tag=tag if tag is not None else (None if transposed else (L.conv_name + ".y", out)))
 
     def _wgrad(self, plan, lst, L: ConvL, x: Act, pro, dy: Act):
         k, s, p = L.k, L.s, L.p
@@ -307,7 +320,7 @@ class SlowFastEngine:
         self._emit(lst, self.lib.sfb_bn_bwd_apply, dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, *m,
                    L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(), L.invstd.data_ptr(), bn.weight.data_ptr(),
                    L.dgamma.data_ptr(), L.dbeta.data_ptr(), 1, y.M, y.C, dy.ptr(), dy.ld, dy.coff, *go, int(g_acc),
-                   self.stream)
+                   self.stream, tag=(L.conv_name + ".dy", dy))
         if self.ddp is not None:
             self.ddp.note_grad_ready(plan, lst, bn.weight)
             self.ddp.note_grad_ready(plan, lst, bn.bias)
@@ -357,7 +370,7 @@ class SlowFastEngine:
             idx = torch.empty((N, To, Hp, Wp, L.Co), dtype=torch.uint8, device=dev) if training else None
             self._emit(fwd, self.lib.sfb_maxpool_fwd, y0.ptr(), y0.ld, y0.coff, L.scale.data_ptr(), L.shift.data_ptr(),
                        N, To, Ho, Wo, L.Co, out.act.ptr(), out.act.ld, out.act.coff, idx.data_ptr() if training else 0,
-                       self.stream)
+                       self.stream, tag=(L.name + ".O", out.act))
             pooled.append(out)
             stem_rec.append(dict(L=L, x_in=x_in, y0=y0, out=out, idx=idx))
 
@@ -425,12 +438,12 @@ class SlowFastEngine:
                     if y1 is not None:
                         self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
                                    y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
-                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream)
+                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=(d["name"] + ".O", O.act))
                     else:
                         assert Xpro is None
                         self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
                                    X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
-                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream)
+                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=(d["name"] + ".O", O.act))
                     block_recs.append(dict(si=si, p=p, d=d, X=X, Xpro=Xpro, ya=ya, yb=yb, yc=yc, y1=y1, O=O))
                     X, Xpro = O, None
                 nxt[p] = X
@@ -462,20 +475,23 @@ class SlowFastEngine:
                        drop, plan.seed_slot, feat.data_ptr(), feat_dim, f_off, self.stream)
             f_off += a.C
         self._emit(fwd, self.lib.sfb_fc_fwd, feat.data_ptr(), self.proj.weight.data_ptr(), self.proj.bias.data_ptr(), N,
-                   feat_dim, ncls, logits.data_ptr(), self.stream)
+                   feat_dim, ncls, logits.data_ptr(), self.stream, tag=("logits", logits))
         plan.keep += [feat, logits]
+        plan.feat = feat
         if not training:
             return plan
 
         # =============================== backward ===============================
         bwd = plan.bwd
+        if self.ddp is not None:
+            self.ddp.begin_plan()
         dlogits = _f32(N * ncls, dev).view(N, ncls)
         dfeat = _f32(N * feat_dim, dev).view(N, feat_dim)
         plan.dlogits = dlogits
         plan.keep += [dfeat]
         self._emit(bwd, self.lib.sfb_fc_bwd, dlogits.data_ptr(), feat.data_ptr(), self.proj.weight.data_ptr(), N, feat_dim, ncls,
                    dfeat.data_ptr(), self.grad_views[id(self.proj.weight)].data_ptr(),
-                   self.grad_views[id(self.proj.bias)].data_ptr(), self.stream)
+                   self.grad_views[id(self.proj.bias)].data_ptr(), self.stream, tag=("dfeat", dfeat))
         if self.ddp is not None:
             self.ddp.note_grad_ready(plan, bwd, self.proj.weight)
             self.ddp.note_grad_ready(plan, bwd, self.proj.bias)
@@ -527,6 +543,7 @@ class SlowFastEngine:
             ya, yb, yc, y1 = rec["ya"], rec["yb"], rec["yc"], rec["y1"]
             dO = O.grad
             assert O.ginit, "block output without gradient contribution"
+            self._emit(bwd, _probe, tag=(d["name"] + ".dO", dO))
             dyc = new_grad(yc)
             if s_ is not None:
                 self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc)
@@ -578,10 +595,46 @@ class SlowFastEngine:
 
     # ------------------------------------------------------------------ execution
     def _run(self, ops):
-        for fn, args in ops:
+        cap = self.capture
+        for fn, args, tag in ops:
             rc = fn(*args)
             if rc:
                 _ffi.check(rc, getattr(fn, "__name__", "libsfb200 call"))
+            if cap is not None and tag is not None:
+                t = tag[1]
+                cap[tag[0]] = (t.torch_view() if isinstance(t, Act) else t).float().clone()
+
+    # ------------------------------------------------------------------ debug / test support
+    def tagged_buffers(self, plan: Plan) -> Dict[str, object]:
+        """name -> Act | tensor of every tagged forward intermediate (raw conv outputs `<conv>.y`, block outputs
+        `<block>.O`, stem pool outputs, logits)"""
+        return {tag[0]: tag[1] for _, _, tag in plan.fwd if tag is not None}
+
+    def force_forward_state(self, plan: Plan, tensors: Dict[str, torch.Tensor], feat: Optional[torch.Tensor] = None):
+        """TEST SUPPORT (teacher forcing): overwrite the saved forward state of a training plan with externally
+        computed values -- NDHWC tensors keyed like tagged_buffers(); BatchNorm batch statistics are re-derived
+        from the forced raw conv outputs -- so that a following backward() can be compared with a reference
+        backward evaluated on the very same forward state (no ReLU-mask divergence)."""
+        bufs = self.tagged_buffers(plan)
+        by_conv = {l.conv_name: l for l in self.layers}
+        for name, t in tensors.items():
+            dst = bufs[name]
+            view = dst.torch_view() if isinstance(dst, Act) else dst
+            view.copy_(t.to(view.dtype))
+            if name.endswith(".y"):
+                L = by_conv[name[:-2]]
+                yf = view.float().reshape(-1, L.Co)
+                mean = yf.mean(0)
+                var = yf.var(0, unbiased=False)
+                invstd = torch.rsqrt(var + L.bn.eps)
+                L.mean.copy_(mean)
+                L.invstd.copy_(invstd)
+                L.scale.copy_(L.bn.weight.detach() * invstd)
+                L.shift.copy_(L.bn.bias.detach() - mean * L.bn.weight.detach() * invstd)
+        if feat is not None:
+            plan.feat.copy_(feat)
+        # arg-max indices of the stem pools depend on the forced stem outputs: recompute them
+        self._run([op for op in plan.fwd if op[0] is self.lib.sfb_maxpool_fwd])
 
     def get_plan(self, xs, xf, training) -> Plan:
         N, Cs, Ts, H, W = xs.shape
