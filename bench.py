@@ -1,0 +1,341 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on its config: train clips/s of SlowFast-R50 8x8 (slow 8 / fast 32 frames, alpha=4,
+beta=1/8, 224^2, 5+15 input channels, 249 classes), bf16 storage / fp32 accumulate, batch 64 per GPU, data parallel.
+
+    python bench.py --gpus N --steps K --warmup W          our arm (libsfb200 kernels through the drop-in model)
+    python bench.py --impl reference ...                    the reference's own CPU path (oracle restatement) on host cores
+
+A step is what reference train.py:225-231 does per batch: forward, CrossEntropy, zero_grad, backward (+ bucketed
+gradient all-reduce when N > 1), Adam step.  `value` keeps the clips resident in HBM; `e2e` copies every step's fp32
+clips from pinned host memory (double-buffered on a copy stream) and reads the loss back.  One JSON line on stdout.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# workload constants (SURVEY.md 8d / BASELINE.md 2): algorithmic conv+FC FLOPs per clip, 1 MAC = 2 FLOP
+F_FWD_GF = 100.616
+F_TRAIN_GF = 293.98
+HYB_KW = dict(fusion_conv_stride=(4, 1, 1), head_pool_kernel_sizes=((8, 7, 7), (32, 7, 7)))
+T_SLOW, T_FAST, SIZE, NUM_CLASS = 8, 32, 224, 249
+WORKLOAD = "configs[2]: slowfast-LHand SlowFast-R50 training, slow 5x8x224^2 + fast 15x32x224^2 (alpha=4 lateral), 249 classes"
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], burst=d["bf16_tflops"], sustained=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, burst=1590.0, sustained=1400.0, src="fallback")
+
+
+class ClockSampler(threading.Thread):
+    """samples SM clock / throttle reasons of one GPU with NVML every 200 ms while the timed region runs"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._halt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                 nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self._halt.wait(0.2)
+
+    def stop(self):
+        self._halt.set()
+        if self.is_alive():
+            self.join(timeout=2)
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arm: the reference's own path (fp32 eager PyTorch on host cores).  The reference is pure Python and cannot
+# travel to the GPU box; what is timed is the oracle restatement (oracle/slowfast_oracle.py), which
+# tests/test_oracle.py pins bit-identical to the verbatim import of the reference's model/my_slowfast.py.
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_train_steps(n_clips, steps, warmup, threads=None):
+    """-> (seconds per step, threads used).  One step = train.py:225-231 on a batch of n_clips HYB clips."""
+    import torch
+    import torch.nn.functional as F
+    from oracle import slowfast_oracle as so
+    if threads:
+        torch.set_num_threads(threads)
+    threads = torch.get_num_threads()
+    torch.manual_seed(0)
+    model = so.build_oracle(num_class=NUM_CLASS, fuse=True, **so.VARIANTS["HYB"])
+    so.randomize_bn_(model, 123, 0.1)
+    model.train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    xs, xf = so.synthetic_clips(n_clips, T_SLOW, T_FAST, SIZE, seed=1)
+    y = torch.randint(0, NUM_CLASS, (n_clips,), generator=torch.Generator().manual_seed(7))
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        out = model([xs, xf])
+        loss = F.cross_entropy(out, y)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        float(loss.detach())
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+    return sum(times) / len(times), threads
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # one CPU measurement per box; other ranks exit 0 without work
+    n = args.cpu_clips
+    sec, threads = cpu_train_steps(n, args.steps, max(1, min(args.warmup, 2)))
+    v = n / sec
+    line = {"impl": "reference", "metric": "train clips/sec SlowFast-R50 8x8 224^2", "value": v, "unit": "clips/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": max(1, min(args.warmup, 2)), "ms_per_step": sec * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_step": n, "note": "bounded sample: each step trains on "
+                       f"{n} clips instead of 64 (CPU throughput is batch-insensitive); fwd+CE+bwd+Adam"},
+            "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port",
+                             "sample": f"{args.steps} train steps of {n} HYB clips, fp32 eager PyTorch CPU, oracle "
+                                       "restatement pinned bit-identical to the reference's verbatim my_slowfast.py"},
+            "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    from oracle import slowfast_oracle as so  # only make_cfg (a SimpleNamespace stand-in for the yacs CfgNode)
+    from video_classification_b200 import _ffi
+    from video_classification_b200.my_slowfast import init_my_slowfast
+    from video_classification_b200.parallel import attach_ddp
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    B = args.batch
+    torch.manual_seed(0)
+    model = init_my_slowfast(so.make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **HYB_KW).to(dev)
+    model.train()
+    if world > 1:
+        attach_ddp(model, bucket_mb=args.bucket_mb)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    g = torch.Generator().manual_seed(1000 + rank)
+    # synthetic clips, per-rank seed; resident copies for `value`, a pinned host copy for `e2e`
+    host = [torch.randn((B, 5, T_SLOW, SIZE, SIZE), generator=g).pin_memory(),
+            torch.randn((B, 15, T_FAST, SIZE, SIZE), generator=g).pin_memory()]
+    y = torch.randint(0, NUM_CLASS, (B,), generator=g).to(dev)
+    resident = [h.to(dev) for h in host]
+    h2d_bytes = sum(h.numel() * 4 for h in host)
+
+    def step(xs, xf):
+        out = model([xs, xf])
+        loss = F.cross_entropy(out, y)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _ffi.launch_count()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / steps, _ffi.launch_count() - l0
+
+    # ---- value: inputs resident in HBM ----
+    for _ in range(args.warmup):
+        step(*resident)
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_step, launches = timed(lambda: step(*resident), args.steps)
+    clocks = sampler.stop()
+    loss_val = float(step(*resident).detach())
+
+    # ---- e2e: pinned host -> device every step (double-buffered prefetch on a copy stream) + loss read-back ----
+    copy_stream = torch.cuda.Stream(dev)
+    dbuf = [[torch.empty_like(r) for r in resident] for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    state = {"i": 0}
+
+    def prefetch(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])
+            for d, h in zip(dbuf[slot], host):
+                d.copy_(h, non_blocking=True)
+            ready[slot].record(copy_stream)
+
+    for s_ in range(2):
+        consumed[s_].record()
+
+    def e2e_step():
+        i = state["i"]
+        slot = i & 1
+        if i == 0:
+            prefetch(0)
+        prefetch(slot ^ 1)  # next step's clips travel while this step computes
+        torch.cuda.current_stream().wait_event(ready[slot])
+        loss = step(*dbuf[slot])
+        consumed[slot].record()
+        float(loss.detach())  # device -> host read of the step's result
+        state["i"] = i + 1
+
+    for _ in range(2):
+        e2e_step()
+    e2e_ms, _ = timed(e2e_step, args.steps)
+    return dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
+                e2e_ms=e2e_ms, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B)
+
+
+def profile_kernels(r, peaks, steps=2):
+    """per-plan-entry CUDA-event timing over `steps` extra training steps (events on the launching stream)."""
+    import torch
+    eng = r["model"]._engine
+    eng.prof = []
+    for _ in range(steps):
+        r["step"](*r["resident"])
+    table, flops = eng.profile_summary()
+    if os.environ.get("SFB_DUMP_OPS"):
+        with open(os.environ["SFB_DUMP_OPS"], "w") as f:
+            for name, desc, ms, gf in eng.profile_ops()[: len(eng.prof) // steps]:
+                f.write(f"{ms:9.4f} ms {gf / ms if ms > 0 else 0:9.1f} TF/s {name:20s} {desc}\n")
+    eng.prof = None
+    torch.cuda.synchronize()
+    per_step = {k: {"launches": n // steps, "ms": t / steps} for k, (n, t) in table.items()}
+    for k, f in flops.items():
+        per_step[k]["algorithmic_tflop"] = f / steps / 1e12
+        per_step[k]["tflops"] = f / steps / 1e9 / per_step[k]["ms"]
+    return per_step
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="clips per GPU (BASELINE config: 64)")
+    ap.add_argument("--bucket-mb", type=float, default=25.0)
+    ap.add_argument("--cpu-clips", type=int, default=2, help="clips per CPU step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    args.warmup = max(args.warmup, 3)
+    peaks = load_peaks()
+    r = run_gpu_arm(args)
+    world, B = r["world"], r["B"]
+    kernels = None
+    if not args.no_profile:
+        kernels = profile_kernels(r, peaks)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    if r["rank"] != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    clips_s = world * B / (r["ms_step"] * 1e-3)
+    e2e_clips_s = world * B / (r["e2e_ms"] * 1e-3)
+    tf_gpu = clips_s / world * F_TRAIN_GF / 1e3
+    line = {"metric": "train clips/sec SlowFast-R50 8x8 224^2", "value": clips_s, "unit": "clips/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": world * B,
+                       "step": "fwd + CrossEntropy + bwd + bucketed grad all-reduce + Adam (reference train.py:225-231)",
+                       "parallelism": f"dp{world}", "l2": "working set (>= 30 GB of activations per step) exceeds the 126 MB L2",
+                       "weights": "random init (seed 0)", "loss_after_bench": r["loss"]},
+            "e2e": {"value": e2e_clips_s, "unit": "clips/s", "ms_per_step": r["e2e_ms"],
+                    "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": 4,
+                    "note": "fp32 NCTHW clips from pinned host memory each step (as train.py:136 .cuda()), "
+                            "prefetched on a copy stream; loss.item() each step"},
+            "gpu_launches": r["launches"], "clocks": r["clocks"],
+            "step_tensor_roofline": {"algorithmic_tflop_per_clip": F_TRAIN_GF / 1e3, "achieved_tflops_per_gpu": tf_gpu,
+                                     "peak_sustained": peaks["sustained"], "frac_sustained": tf_gpu / peaks["sustained"],
+                                     "peak_burst": peaks["burst"], "frac_burst": tf_gpu / peaks["burst"],
+                                     "peaks": peaks["src"]}}
+    if kernels:
+        conv = [k for k in kernels if k.startswith("sfb_conv")]
+        dom = max(conv, key=lambda k: kernels[k]["ms"])
+        d = kernels[dom]
+        line["roofline"] = {"kernel": dom, "bound": "tensor", "achieved": d["tflops"], "peak": peaks["sustained"],
+                            "unit": "TFLOP/s", "frac": d["tflops"] / peaks["sustained"], "traffic": None,
+                            "launches_per_step": d["launches"], "ms_per_step": d["ms"],
+                            "algorithmic_tflop_per_step": d["algorithmic_tflop"],
+                            "peak_source": f"{peaks['src']} bf16_tflops_sustained (kernel timed inside a long step)",
+                            "share_of_step": d["ms"] / sum(v["ms"] for v in kernels.values())}
+        line["kernel_breakdown_ms_per_step"] = {k: round(v["ms"], 3) for k, v in sorted(kernels.items(), key=lambda t: -t[1]["ms"])}
+        line["kernel_tflops"] = {k: round(v["tflops"], 1) for k, v in kernels.items() if "tflops" in v}
+    if world == 1 and not args.no_cpu_baseline:
+        n = args.cpu_clips
+        sec, threads = cpu_train_steps(n, 2, 1)
+        line["cpu_baseline"] = {"value": n / sec, "unit": "clips/s", "cores": threads, "kind": "port",
+                                "sample": f"2 train steps (after 1 warm-up) of {n} HYB clips, fp32 eager PyTorch on the "
+                                          "host cores; oracle restatement of the reference path"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

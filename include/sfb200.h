@@ -14,8 +14,9 @@
  *     the Slow stage output share ONE buffer (torch.cat at my_slowfast.py:343 becomes a no-op).
  *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden syncs.
  *   - return value: 0 on success, negative SfbStatus otherwise; sfb_strerror() explains.
- *   - `impl`: SFB_IMPL_TC = tcgen05/TMEM tensor-core kernel, SFB_IMPL_SIMT = plain CUDA-core
- *     kernel with the same contract (kept as an on-device cross-check; never a CPU path).
+ *   - `impl`: SFB_IMPL_TC = tcgen05/TMEM tensor-core kernels (persistent TMA-fed kernel where the geometry
+ *     allows, else the register-gather kernel); SFB_IMPL_TC_GATHER = force the register-gather tcgen05 kernel;
+ *     SFB_IMPL_SIMT = plain CUDA-core kernel with the same contract (on-device cross-check; never a CPU path).
  */
 #ifndef SFB200_H
 #define SFB200_H
@@ -34,7 +35,7 @@ typedef enum SfbStatus {
   SFB_ERR_DRIVER = -4        /* could not resolve cuTensorMapEncodeTiled from the driver */
 } SfbStatus;
 
-enum { SFB_IMPL_TC = 0, SFB_IMPL_SIMT = 1 };
+enum { SFB_IMPL_TC = 0, SFB_IMPL_SIMT = 1, SFB_IMPL_TC_GATHER = 2 };
 
 /* Geometry of one implicit-GEMM convolution pass.
  *   fprop   (transposed=0): out[m, co] = sum_{tap,c} G[in(m,tap), c] * Wp[co][tap*Cg + c]

@@ -46,6 +46,14 @@ CONV_CASES = [
     ("fast_1x3x3_16_16", 2, 8, 12, 12, 16, 16, (1, 3, 3), (1, 1, 1)),
     ("lateral_3x1x1_32_64_s4", 2, 16, 8, 8, 32, 64, (3, 1, 1), (4, 1, 1)),
     ("1x1x1_512_2048", 1, 4, 7, 7, 512, 2048, (1, 1, 1), (1, 1, 1)),
+    # larger / odd shapes: several persistent waves, partial patches, every A-box width of the TMA kernel
+    ("big_1x3x3_64_64", 3, 8, 56, 56, 64, 64, (1, 3, 3), (1, 1, 1)),
+    ("big_1x1x1_320_128", 2, 8, 56, 56, 320, 128, (1, 1, 1), (1, 1, 1)),
+    ("big_3x1x1_640_256", 2, 8, 14, 14, 640, 256, (3, 1, 1), (1, 1, 1)),
+    ("odd_1x3x3_32_32", 2, 5, 13, 11, 32, 32, (1, 3, 3), (1, 1, 1)),
+    ("odd_3x1x1_16_48", 1, 7, 9, 10, 16, 48, (3, 1, 1), (1, 1, 1)),
+    ("stem_slow_16_64", 2, 2, 64, 64, 16, 64, (1, 7, 7), (1, 2, 2)),
+    ("ref_1x3x3_512_512_2x2", 2, 20, 2, 2, 512, 512, (1, 3, 3), (1, 1, 1)),
 ]
 
 

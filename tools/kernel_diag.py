@@ -15,7 +15,7 @@ def child(kind):
     import torch
     import kernel_cases as kc
     from video_classification_b200 import _ffi
-    for impl_name, impl in (("simt", _ffi.IMPL_SIMT), ("tc", _ffi.IMPL_TC)):
+    for impl_name, impl in (("simt", _ffi.IMPL_SIMT), ("tc", _ffi.IMPL_TC)) if kind == "wgrad" else (("tc", _ffi.IMPL_TC),):
         for case in kc.CONV_CASES:
             variants = {"fprop": ["plain"], "fused": ["pro", "epi", "stats"], "dgrad": ["d", "dacc"], "wgrad": ["w", "wpro"]}[kind]
             for v in variants:
@@ -28,7 +28,7 @@ def child(kind):
                     elif kind == "dgrad":
                         r = kc.run_dgrad_case(case, impl, accumulate=(v == "dacc"))
                     else:
-                        ci_real = {"stem_slow_8_64": 5, "stem_fast_16_8": 15}.get(case[0])
+                        ci_real = {"stem_slow_8_64": 5, "stem_fast_16_8": 15, "stem_slow_16_64": 5}.get(case[0])
                         r = kc.run_wgrad_case(case, impl, pro=(v == "wpro"), ci_real=ci_real)
                     flag = "OK " if r["err"] < 2e-2 else "BAD"
                     print(f"{flag} {kind:6s} {impl_name:4s} {v:5s} {case[0]:28s} " +

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libsfb200.so")
 
 IMPL_TC = 0
 IMPL_SIMT = 1
+IMPL_TC_GATHER = 2
 
 
 class SfbError(RuntimeError):

@@ -1,0 +1,303 @@
+// conv_tma.cuh -- persistent, warp-specialised implicit-GEMM Conv3d for sm_100a (fprop, and dgrad of stride-1 convs).
+//
+//   A operand : NDHWC bf16 activation, fetched by TMA as shifted 5-D boxes.  An M tile is a rectangular patch of
+//               Wt x Ht x Tt output pixels (<= 128) of one clip; filter tap (kt,kh,kw) of that tile is ONE box
+//               [box_k channels][Wt*sW][Ht*sH][Tt*sT][1] whose origin is the patch origin shifted by the tap
+//               (traversal strides = conv strides), so zero padding and partial edge tiles are TMA out-of-bounds
+//               zero fill -- no index arithmetic, no register staging.  box_k = 64 / 32 / 16 channels lands in the
+//               SWIZZLE_128B / 64B / 32B K-major layouts tcgen05.mma reads directly.
+//   B operand : packed bf16 weights [rows_pad][k_pad] (k = tap*Cg + c), 2-D TMA, SWIZZLE_128B, 64-wide K chunks.
+//   D         : fp32 in TMEM, two accumulator buffers so the epilogue of tile i overlaps the MMAs of tile i+1.
+//   roles     : warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 = epilogue (tcgen05.ld -> affine / residual /
+//               ReLU -> bf16 stores; per-channel sum and sum-of-squares for training BatchNorm kept in shared memory
+//               across all tiles of the CTA and flushed with one atomic per channel per CTA).
+//   schedule  : persistent, grid = #SMs, static round-robin over (pixel patch, N tile) with the N tile fastest.
+//
+// Replaces cuDNN fprop / bwd-data behind nn.Conv3d in the reference graph (model/my_slowfast.py:94-125).
+#pragma once
+#include "common.cuh"
+#include "../../include/sfb200.h"
+#include <cuda.h>
+
+namespace sfb {
+
+__device__ __forceinline__ void tma_load_5d(uint32_t smem_dst, const void* tmap, uint64_t* bar, int32_t c0, int32_t c1,
+                                            int32_t c2, int32_t c3, int32_t c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
+      "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_u32(uint32_t smem_dst, const void* tmap, uint64_t* bar, int32_t x, int32_t y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
+}
+
+// K-major shared-memory operand descriptor for a swizzle span of `span` bytes (128 / 64 / 32):
+// rows are `span` bytes apart, 8-row atoms are 8*span bytes apart (SBO); layout type 2 / 4 / 6.
+__device__ __forceinline__ uint64_t umma_smem_desc_kmajor(uint32_t smem_addr, uint32_t span) {
+  const uint64_t layout = span == 128 ? 2ull : (span == 64 ? 4ull : 6ull);
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;                                   // LBO (unused for swizzled K-major): 16 bytes
+  d |= (uint64_t)(((8u * span) >> 4) & 0x3FFF) << 32;       // SBO
+  d |= (uint64_t)1 << 46;                                   // descriptor version (sm_100)
+  d |= layout << 61;
+  return d;
+}
+
+struct ConvTmaParams {
+  int N, To, Ho, Wo;           // output tensor (rows of the GEMM)
+  int Co, o_ld, o_coff;
+  int kT, kH, kW, sT, sH, sW, pT, pH, pW;
+  int transposed;              // dgrad of a stride-1 conv: tap shifts are mirrored
+  int Cg;                      // channels of the gathered view
+  int box_k;                   // channels per A box: 64, 32 or 16
+  int cchunks;                 // 64-channel chunks per tap (Cg > 64), else 1
+  int taps, Ktot, nk;          // Ktot = taps*Cg ; nk = number of 64-wide K chunks of the packed weights
+  int Wt, Ht, Tt;              // output patch of one M tile; Wt*Ht*Tt <= 128
+  int tilesW, tilesH, tilesT;
+  int n_tiles;                 // ceil(Co / BN)
+  int total_tiles;             // N*tilesT*tilesH*tilesW*n_tiles
+  __nv_bfloat16* out;
+  const float* epi_scale;
+  const float* epi_shift;
+  const __nv_bfloat16* res;
+  int res_ld, res_coff;
+  int epi_relu;
+  float* stats;                // [2*Co] or null
+};
+
+template <int BN>
+struct ConvTmaCfg {
+  static constexpr int kStages = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kAStage = 128 * 128;  // 16 KB: 128 rows x (64 | 2x32 | 4x16) channels
+  static constexpr int kBStage = BN * 128;
+  static constexpr int kStage = kAStage + kBStage;
+  static constexpr int kBarOff = kStages * kStage;                    // full[S], empty[S], tfull[2], tempty[2]
+  static constexpr int kHolderOff = kBarOff + (2 * kStages + 4) * 8;
+  static constexpr int kStatsOff = kHolderOff + 16;
+  static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  static size_t smem_bytes(int Co, bool stats) { return 1024 + kStatsOff + (stats ? (size_t)Co * 8 : 0); }
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                const ConvTmaParams p) {
+  using L = ConvTmaCfg<BN>;
+  constexpr int S = L::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tfull_bar = empty_bar + S;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kHolderOff);
+  float* s_stats = reinterpret_cast<float*>(smem + L::kStatsOff);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull_bar[b], 1);
+      mbar_init(&tempty_bar[b], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_w);
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_holder, L::kTmemCols);
+    tmem_relinquish();
+  }
+  if (p.stats) {
+    for (int i = tid; i < 2 * p.Co; i += blockDim.x) s_stats[i] = 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const int rows = p.Wt * p.Ht * p.Tt;
+  const uint32_t box_bytes = (uint32_t)(rows * p.box_k * 2);
+  const int bpc = p.Cg >= 64 ? 1 : 64 / p.box_k;  // A boxes per 64-wide K chunk
+  const uint32_t sub_stride = (uint32_t)(128 * p.box_k * 2);
+  const int khw = p.kH * p.kW;
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int nt = tile % p.n_tiles;
+        int q = tile / p.n_tiles;
+        const int tw = q % p.tilesW; q /= p.tilesW;
+        const int th = q % p.tilesH; q /= p.tilesH;
+        const int tt = q % p.tilesT;
+        const int n = q / p.tilesT;
+        const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
+        for (int kc = 0; kc < p.nk; ++kc, ++g) {
+          const int s = g % S;
+          const uint32_t par = ((g / S) & 1) ^ 1;
+          mbar_wait(&empty_bar[s], par, 11);
+          int nbox = 1, tap0, c0 = 0;
+          if (p.Cg >= 64) {
+            tap0 = kc / p.cchunks;
+            c0 = (kc - tap0 * p.cchunks) * 64;
+          } else {
+            tap0 = kc * bpc;
+            nbox = min(bpc, p.taps - tap0);
+          }
+          mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nbox * box_bytes + (uint32_t)L::kBStage);
+          const uint32_t sa = smem_u32(smem + s * L::kStage);
+          for (int b = 0; b < nbox; ++b) {
+            const int tap = tap0 + b;
+            const int kt = tap / khw;
+            const int r2 = tap - kt * khw;
+            const int kh = r2 / p.kW;
+            const int kw = r2 - kh * p.kW;
+            int cw, ch, ct;
+            if (!p.transposed) {
+              cw = w0 * p.sW + kw - p.pW; ch = h0 * p.sH + kh - p.pH; ct = t0 * p.sT + kt - p.pT;
+            } else {
+              cw = w0 + p.pW - kw; ch = h0 + p.pH - kh; ct = t0 + p.pT - kt;
+            }
+            tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], c0, cw, ch, ct, n);
+          }
+          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], kc * 64, nt * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+      const uint32_t span = (uint32_t)(p.box_k * 2);
+      uint32_t g = 0;
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+        for (int kc = 0; kc < p.nk; ++kc, ++g) {
+          const int s = g % S;
+          mbar_wait(&full_bar[s], (g / S) & 1, 13);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * L::kStage);
+          const uint32_t sb = sa + L::kAStage;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const int k = kc * 64 + kk * 16;
+            if (k < p.Ktot) {
+              const int koff = kk * 16;
+              const int sub = koff / p.box_k;
+              const int within = koff - sub * p.box_k;
+              const uint64_t ad = umma_smem_desc_kmajor(sa + sub * sub_stride + within * 2, span);
+              const uint64_t bd = umma_smem_desc_kmajor(sb + kk * 32, 128);
+              umma_bf16(d_tmem, ad, bd, idesc, (kc | kk) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(&empty_bar[s]);
+        }
+        umma_commit(&tfull_bar[buf]);
+      }
+    }
+  } else {
+    // ======================= epilogue (warps 2..5; TMEM lanes 32*(warp&3)..) =======================
+    const int q4 = warp & 3;
+    const int r = q4 * 32 + lane;
+    const int ww = r % p.Wt;
+    const int hh = (r / p.Wt) % p.Ht;
+    const int tq = r / (p.Wt * p.Ht);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const int nt = tile % p.n_tiles;
+      int q = tile / p.n_tiles;
+      const int tw = q % p.tilesW; q /= p.tilesW;
+      const int th = q % p.tilesH; q /= p.tilesH;
+      const int tt = q % p.tilesT;
+      const int n = q / p.tilesT;
+      const int wo = tw * p.Wt + ww, ho = th * p.Ht + hh, to = tt * p.Tt + tq;
+      const bool mv = r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
+      const long long m = mv ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
+      const int n0 = nt * BN;
+      const int buf = it & 1;
+      mbar_wait(&tfull_bar[buf], (uint32_t)((it >> 1) & 1), 14);
+      tc_fence_after();
+      __nv_bfloat16* orow = p.out + (size_t)m * p.o_ld + p.o_coff;
+      const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
+#pragma unroll 1
+      for (int cc = 0; cc < BN / 32; ++cc) {
+        if (n0 + cc * 32 >= p.Co) break;
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + cc * 32), v);
+        tmem_ld_wait();
+        const int nb = n0 + cc * 32;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int nn = nb + j * 8;
+          if (nn < p.Co) {
+            float* f = v + j * 8;
+            if (p.epi_scale) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+            }
+            if (rrow && mv) {
+              float rf[8];
+              unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] += rf[i];
+            }
+            if (p.epi_relu) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+            }
+            if (mv) *reinterpret_cast<uint4*>(orow + nn) = pack8(f);
+          }
+        }
+        if (p.stats) {
+          float sq[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            v[i] = mv ? v[i] : 0.f;
+            sq[i] = v[i] * v[i];
+          }
+          const float s1 = warp_colsum32(v, lane);
+          const float s2 = warp_colsum32(sq, lane);
+          if (nb + lane < p.Co) {
+            atomicAdd(&s_stats[nb + lane], s1);
+            atomicAdd(&s_stats[p.Co + nb + lane], s2);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+    }
+    if (p.stats) {
+      named_bar_sync(1, 128);
+      for (int i = tid - 64; i < 2 * p.Co; i += 128) {
+        const float v = s_stats[i];
+        if (v != 0.f) atomicAdd(p.stats + i, v);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, L::kTmemCols);
+}
+
+}  // namespace sfb

@@ -2,8 +2,10 @@
 // cache, kernel dispatch.  Single translation unit; links only cudart (static).  The driver entry point
 // cuTensorMapEncodeTiled is resolved at run time so the library also loads on a box without a GPU.
 #include "conv_simt.cuh"
+#include "conv_tma.cuh"
 #include "elementwise.cuh"
 
+#include <array>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -101,6 +103,119 @@ int check_geom(const SfbConvGeom* g) {
   const long long Pin = (long long)g->N * g->Ti * g->Hi * g->Wi;
   if (M >= (1ll << 31) - 256 || Pin >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
   return SFB_OK;
+}
+
+// ---- 5-D activation tensor maps (C, W, H, T, N) with traversal strides = conv strides ----
+std::map<std::array<long long, 16>, CUtensorMap> g_act_tmaps;
+
+int ensure_encode() {
+  if (g_encode) return SFB_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cudaGetDriverEntryPoint(cuTensorMapEncodeTiled) failed");
+    return SFB_ERR_DRIVER;
+  }
+  g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  return SFB_OK;
+}
+
+int get_act_tmap(const void* base, int C, int W, int H, int T, int N, int ld, int box_c, int bw, int bh, int bt, int sW,
+                 int sH, int sT, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  std::array<long long, 16> key = {(long long)(uintptr_t)base, C, W, H, T, N, ld, box_c, bw, bh, bt, sW, sH, sT, 0, 0};
+  auto it = g_act_tmaps.find(key);
+  if (it != g_act_tmaps.end()) {
+    *out = it->second;
+    return SFB_OK;
+  }
+  int rc = ensure_encode();
+  if (rc) return rc;
+  CUtensorMap tm;
+  cuuint64_t gdim[5] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)T, (cuuint64_t)N};
+  cuuint64_t gstr[4] = {(cuuint64_t)ld * 2, (cuuint64_t)W * ld * 2, (cuuint64_t)H * W * ld * 2,
+                        (cuuint64_t)T * H * W * ld * 2};
+  cuuint32_t box[5] = {(cuuint32_t)box_c, (cuuint32_t)(bw * sW), (cuuint32_t)(bh * sH), (cuuint32_t)(bt * sT), 1};
+  cuuint32_t estr[5] = {1, (cuuint32_t)sW, (cuuint32_t)sH, (cuuint32_t)sT, 1};
+  const CUtensorMapSwizzle sw = box_c == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                            : (box_c == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(5d act C=%d W=%d H=%d T=%d N=%d ld=%d box=%d,%d,%d,%d) failed: %d",
+             C, W, H, T, N, ld, box_c, bw * sW, bh * sH, bt * sT, (int)r);
+    return SFB_ERR_DRIVER;
+  }
+  if (g_act_tmaps.size() > 8192) g_act_tmaps.clear();
+  g_act_tmaps[key] = tm;
+  *out = tm;
+  return SFB_OK;
+}
+
+int g_num_sms = 0;
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    g_num_sms = n > 0 ? n : 148;
+  }
+  return g_num_sms;
+}
+
+// output patch (Wt, Ht, Tt) with Wt*Ht*Tt <= 128 that wastes the fewest MMA rows; ties -> longest W run
+void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht, int* Tt) {
+  double best = -1.0;
+  int bw = 1, bh = 1, bt = 1;
+  for (int w = 1; w <= Wo && w <= 128 && w * sW <= 256; ++w) {
+    const int tw = (Wo + w - 1) / w;
+    for (int h = 1; h <= Ho && w * h <= 128 && h * sH <= 256; ++h) {
+      const int th = (Ho + h - 1) / h;
+      int t = 128 / (w * h);
+      if (t > To) t = To;
+      while (t * sT > 256) --t;
+      // prefer a Tt that divides To
+      int tbest = t;
+      for (int c = t; c >= 1 && c > t / 2; --c)
+        if (To % c == 0) { tbest = c; break; }
+      for (int pass = 0; pass < 2; ++pass) {
+        const int tcur = pass == 0 ? t : tbest;
+        const int ttiles = (To + tcur - 1) / tcur;
+        const double util = (double)Wo * Ho * To / ((double)tw * th * ttiles * 128.0);
+        const double score = util + 1e-4 * w / 128.0;
+        if (score > best) { best = score; bw = w; bh = h; bt = tcur; }
+      }
+    }
+  }
+  *Wt = bw; *Ht = bh; *Tt = bt;
+}
+
+template <int BN>
+int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const ConvTmaParams& p, cudaStream_t st) {
+  using L = ConvTmaCfg<BN>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)L::smem_bytes(2048, true));
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
+    attr_done = true;
+  }
+  int grid = num_sms();
+  if (grid > p.total_tiles) grid = p.total_tiles;
+  conv_tma_kernel<BN><<<grid, 192, L::smem_bytes(p.Co, p.stats != nullptr), st>>>(ta, tw, p);
+  SFB_CHECK_LAUNCH("conv_tma_kernel");
+  return SFB_OK;
+}
+
+// Can the TMA kernel take this conv?  (everything else stays on the register-gather kernel)
+bool tma_eligible(const SfbConvGeom* g, int taps) {
+  if (g->Cg % 16) return false;
+  if (g->Cg > 64 && (g->Cg % 64) && taps != 1) return false;
+  if (g->Cg < 64 && g->Cg != 16 && g->Cg != 32) return false;
+  if (g->transposed && !(g->sT == 1 && g->sH == 1 && g->sW == 1)) return false;
+  if (g->Co > 2048) return false;
+  return true;
 }
 
 template <int BN, int STAGES>
@@ -209,13 +324,55 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     SFB_CHECK_LAUNCH("conv_gemm_simt_kernel");
     return SFB_OK;
   }
-  if (impl != SFB_IMPL_TC) return SFB_ERR_BAD_ARG;
+  if (impl != SFB_IMPL_TC && impl != SFB_IMPL_TC_GATHER) return SFB_ERR_BAD_ARG;
   if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
   const int bn = pick_bn(geom->Co);
   if (rows_pad % bn) return SFB_ERR_BAD_ARG;
   CUtensorMap tm;
   rc = get_weight_tmap(wp, rows_pad, k_pad, bn, &tm);
   if (rc) return rc;
+  if (impl == SFB_IMPL_TC && !p.pro_scale && tma_eligible(geom, taps)) {
+    // ---- persistent TMA / tcgen05 kernel ----
+    ConvTmaParams q;
+    memset(&q, 0, sizeof(q));
+    const bool pointwise = taps == 1 && geom->sT == 1 && geom->sH == 1 && geom->sW == 1 && geom->pT == 0 &&
+                           geom->pH == 0 && geom->pW == 0;
+    int gW = geom->Wi, gH = geom->Hi, gT = geom->Ti, gN = geom->N;
+    q.N = geom->N; q.To = geom->To; q.Ho = geom->Ho; q.Wo = geom->Wo;
+    if (pointwise) {  // a 1x1x1 stride-1 conv is a plain GEMM over the flattened pixel list: full 128-row tiles
+      gW = geom->N * geom->Ti * geom->Hi * geom->Wi; gH = gT = gN = 1;
+      q.N = 1; q.To = 1; q.Ho = 1; q.Wo = p.M;
+    }
+    q.Co = geom->Co; q.o_ld = geom->o_ld; q.o_coff = geom->o_coff;
+    q.kT = geom->kT; q.kH = geom->kH; q.kW = geom->kW;
+    q.sT = geom->sT; q.sH = geom->sH; q.sW = geom->sW;
+    q.pT = geom->pT; q.pH = geom->pH; q.pW = geom->pW;
+    q.transposed = geom->transposed;
+    q.Cg = geom->Cg;
+    q.box_k = geom->Cg >= 64 ? 64 : geom->Cg;
+    q.cchunks = geom->Cg >= 64 ? (geom->Cg + 63) / 64 : 1;
+    q.taps = taps; q.Ktot = p.Ktot; q.nk = p.nk;
+    if (geom->Cg >= 64 && q.cchunks * taps != q.nk) return SFB_ERR_BAD_ARG;
+    pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt);
+    q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
+    q.n_tiles = (geom->Co + bn - 1) / bn;
+    const long long tt = (long long)q.N * q.tilesT * q.tilesH * q.tilesW * q.n_tiles;
+    if (tt >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+    q.total_tiles = (int)tt;
+    q.out = p.out; q.epi_scale = p.epi_scale; q.epi_shift = p.epi_shift; q.res = p.res; q.res_ld = p.res_ld;
+    q.res_coff = p.res_coff; q.epi_relu = p.epi_relu; q.stats = p.stats;
+    CUtensorMap ta;
+    const int sW = geom->transposed ? 1 : q.sW, sH = geom->transposed ? 1 : q.sH, sT = geom->transposed ? 1 : q.sT;
+    rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,
+                      q.Tt, sW, sH, sT, &ta);
+    if (rc) return rc;
+    switch (bn) {
+      case 32: return launch_conv_tma<32>(ta, tm, q, st);
+      case 64: return launch_conv_tma<64>(ta, tm, q, st);
+      case 128: return launch_conv_tma<128>(ta, tm, q, st);
+      default: return launch_conv_tma<256>(ta, tm, q, st);
+    }
+  }
   switch (bn) {
     case 32: return launch_conv_tc<32, 4>(tm, p, st);
     case 64: return launch_conv_tc<64, 4>(tm, p, st);

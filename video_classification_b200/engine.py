@@ -128,6 +128,7 @@ class SlowFastEngine:
         self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
         self.step_seed = 0
         self.ddp = None  # set by parallel.attach_ddp
+        self.prof = None     # list: bench.py sets it to time every plan entry with CUDA events
         self.capture = None  # dict: tools/layer_diag.py sets it to snapshot tagged intermediates (debug only)
         self._collect_layers()
         self._alloc_arenas()
@@ -278,6 +279,8 @@ class SlowFastEngine:
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
         ep = Epilogue(0, 0, residual.ptr() if residual else 0, residual.ld if residual else 0,
                       residual.coff if residual else 0, 0, L.stats.data_ptr() if stats else 0)
+        g.real_k = (L.Co if transposed else L.Ci) * L.taps  # algorithmic reduction length (no channel padding)
+        g.real_n = L.Ci if transposed else L.Co
         plan.keep += [g, pr, ep]
         wp = wp if wp is not None else (L.wpt if transposed else L.wp)
         self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
@@ -291,6 +294,7 @@ class SlowFastEngine:
         g = ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, dy.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
                      x.ld, x.coff, dy.ld, dy.coff, 0)
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
+        g.real_k, g.real_n = L.Ci * L.taps, L.Co
         plan.keep += [g, pr]
         self._emit(lst, self.lib.sfb_conv_wgrad, C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), dy.ld, dy.coff,
                    L.dw.data_ptr(), L.Ci, self.impl, self.stream)
@@ -596,6 +600,8 @@ class SlowFastEngine:
     # ------------------------------------------------------------------ execution
     def _run(self, ops):
         cap = self.capture
+        if self.prof is not None:
+            return self._run_profiled(ops)
         for fn, args, tag in ops:
             rc = fn(*args)
             if rc:
@@ -603,6 +609,55 @@ class SlowFastEngine:
             if cap is not None and tag is not None:
                 t = tag[1]
                 cap[tag[0]] = (t.torch_view() if isinstance(t, Act) else t).float().clone()
+
+    def _run_profiled(self, ops):
+        """bench support: CUDA events around every plan entry (on the launching stream); self.prof collects
+        (entry name, start event, end event, op args) -- resolved to milliseconds by profile_summary()"""
+        st = torch.cuda.current_stream(self.dev)
+        for fn, args, tag in ops:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(st)
+            rc = fn(*args)
+            e1.record(st)
+            if rc:
+                _ffi.check(rc, getattr(fn, "__name__", "libsfb200 call"))
+            self.prof.append((getattr(fn, "__name__", "op"), e0, e1, args))
+
+    def profile_ops(self):
+        """-> list of (entry name, layer description, ms, algorithmic GFLOP) per recorded plan entry"""
+        torch.cuda.synchronize(self.dev)
+        rows = []
+        for name, e0, e1, args in self.prof:
+            desc, gf = "", 0.0
+            if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
+                g = args[0]._obj
+                kind = "wgrad" if name == "sfb_conv_wgrad" else ("dgrad" if g.transposed else "fprop")
+                M = g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo
+                gf = 2.0 * M * g.real_n * g.real_k / 1e9
+                desc = (f"{kind} in({g.Ti},{g.Hi},{g.Wi})x{g.Cg} out({g.To},{g.Ho},{g.Wo})x{g.Co} "
+                        f"k({g.kT},{g.kH},{g.kW}) s({g.sT},{g.sH},{g.sW})")
+            rows.append((name, desc, e0.elapsed_time(e1), gf))
+        return rows
+
+    def profile_summary(self):
+        """-> {entry name: (launches, total ms)}, plus conv FLOPs per class, from the events in self.prof"""
+        torch.cuda.synchronize(self.dev)
+        out, flops = {}, {}
+        for name, e0, e1, args in self.prof:
+            ms = e0.elapsed_time(e1)
+            key = name
+            if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
+                g = args[0]._obj
+                if name == "sfb_conv_gemm" and g.transposed:
+                    key = "sfb_conv_gemm[dgrad]"
+                elif name == "sfb_conv_gemm":
+                    key = "sfb_conv_gemm[fprop]"
+                # algorithmic work: rows of the forward conv's OUTPUT (for dgrad that is the gathered tensor dY)
+                M = g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo
+                flops[key] = flops.get(key, 0.0) + 2.0 * M * g.real_n * g.real_k
+            n, t = out.get(key, (0, 0.0))
+            out[key] = (n + 1, t + ms)
+        return out, flops
 
     # ------------------------------------------------------------------ debug / test support
     def tagged_buffers(self, plan: Plan) -> Dict[str, object]:
