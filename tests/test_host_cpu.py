@@ -111,7 +111,7 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     assert tuple(plan.logits.shape) == (shape[0], 249)
     # the lateral output lands behind the Slow stage output in ONE buffer (torch.cat never happens)
     bufs = eng.tagged_buffers(plan)
-    lat = bufs["blocks.1.multipathway_fusion.conv_fast_to_slow.0.y"]
+    lat = bufs["blocks.1.multipathway_fusion.conv_fast_to_slow.0.z"]
     slow = bufs["blocks.1.multipathway_blocks.0.res_blocks.2.O"]
     assert lat.buf is slow.buf and slow.coff == 0 and lat.coff == slow.C == 256 and lat.buf.shape[-1] == 320
     with pytest.raises(RuntimeError, match="Sizes of tensors must match"):

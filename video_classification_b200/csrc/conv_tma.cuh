@@ -60,8 +60,9 @@ struct ConvTmaParams {
   int taps, Ktot, nk;          // Ktot = taps*Cg ; nk = number of 64-wide K chunks of the packed weights
   int Wt, Ht, Tt;              // output patch of one M tile; Wt*Ht*Tt <= 128
   int tilesW, tilesH, tilesT;
-  int n_tiles;                 // ceil(Co / BN)
-  int total_tiles;             // N*tilesT*tilesH*tilesW*n_tiles
+  int n_tiles;                 // ceil(Co / BN); a CTA works on ONE N tile: blockIdx.x % n_tiles
+  int total_patches;           // N*tilesT*tilesH*tilesW
+  int ocols;                   // channels per output store box: min(64, Co) rounded to 8/16/32/64
   __nv_bfloat16* out;
   const float* epi_scale;
   const float* epi_shift;
@@ -71,23 +72,43 @@ struct ConvTmaParams {
   float* stats;                // [2*Co] or null
 };
 
+__device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int32_t c0, int32_t c1, int32_t c2,
+                                             int32_t c3, int32_t c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+      ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+
 template <int BN>
 struct ConvTmaCfg {
   static constexpr int kStages = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kAStage = 128 * 128;  // 16 KB: 128 rows x (64 | 2x32 | 4x16) channels
   static constexpr int kBStage = BN * 128;
   static constexpr int kStage = kAStage + kBStage;
-  static constexpr int kBarOff = kStages * kStage;                    // full[S], empty[S], tfull[2], tempty[2]
+  static constexpr int kChunk = BN < 128 ? BN : 128;                  // output columns staged per pass
+  static constexpr int kChunks = BN / kChunk;
+  static constexpr int kStagingOff = kStages * kStage;
+  static constexpr int kStagingBytes = 128 * kChunk * 2;
+  static constexpr int kBarOff = kStagingOff + kStagingBytes;          // full[S], empty[S], tfull[2], tempty[2]
   static constexpr int kHolderOff = kBarOff + (2 * kStages + 4) * 8;
-  static constexpr int kStatsOff = kHolderOff + 16;
+  static constexpr int kEnd = kHolderOff + 16;
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
-  static size_t smem_bytes(int Co, bool stats) { return 1024 + kStatsOff + (stats ? (size_t)Co * 8 : 0); }
+  static size_t smem_bytes() { return 1024 + kEnd; }
 };
 
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                const ConvTmaParams p) {
+                const __grid_constant__ CUtensorMap tmap_o, const ConvTmaParams p) {
   using L = ConvTmaCfg<BN>;
   constexpr int S = L::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -97,7 +118,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   uint64_t* tfull_bar = empty_bar + S;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kHolderOff);
-  float* s_stats = reinterpret_cast<float*>(smem + L::kStatsOff);
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5;
@@ -117,13 +137,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_w);
+    tma_prefetch_desc(&tmap_o);
   }
   if (warp == 2) {
     tmem_alloc(tmem_holder, L::kTmemCols);
     tmem_relinquish();
-  }
-  if (p.stats) {
-    for (int i = tid; i < 2 * p.Co; i += blockDim.x) s_stats[i] = 0.f;
   }
   tc_fence_before();
   __syncthreads();
@@ -134,14 +152,18 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const int bpc = p.Cg >= 64 ? 1 : 64 / p.box_k;  // A boxes per 64-wide K chunk
   const uint32_t sub_stride = (uint32_t)(128 * p.box_k * 2);
   const int khw = p.kH * p.kW;
+  // this CTA's N tile and its walk over the pixel patches
+  const int nt = blockIdx.x % p.n_tiles;
+  const int patch0 = blockIdx.x / p.n_tiles;
+  const int patch_step = gridDim.x / p.n_tiles;
+  const int n0 = nt * BN;
 
   if (warp == 0) {
     // ======================= TMA producer =======================
     if (lane == 0) {
       uint32_t g = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const int nt = tile % p.n_tiles;
-        int q = tile / p.n_tiles;
+      for (int patch = patch0; patch < p.total_patches; patch += patch_step) {
+        int q = patch;
         const int tw = q % p.tilesW; q /= p.tilesW;
         const int th = q % p.tilesH; q /= p.tilesH;
         const int tt = q % p.tilesT;
@@ -175,7 +197,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
             tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], c0, cw, ch, ct, n);
           }
-          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], kc * 64, nt * BN);
+          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], kc * 64, n0);
         }
       }
     }
@@ -186,7 +208,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const uint32_t span = (uint32_t)(p.box_k * 2);
       uint32_t g = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
         const int buf = it & 1;
         mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
         tc_fence_after();
@@ -216,81 +238,138 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
   } else {
     // ======================= epilogue (warps 2..5; TMEM lanes 32*(warp&3)..) =======================
+    // TMEM -> registers -> (affine, residual, ReLU) -> bf16 -> swizzled staging tile in shared memory -> TMA store.
+    // BatchNorm statistics are column sums of the staged (bf16-rounded) tile, kept in registers across all tiles.
+    constexpr int CH = L::kChunk;
+    constexpr int NCH = L::kChunks;
+    constexpr int PAIRS = CH / 2;        // bf16x2 column pairs per staged chunk
+    constexpr int TPP = 128 / PAIRS;     // threads sharing one column pair (they split the rows)
     const int q4 = warp & 3;
     const int r = q4 * 32 + lane;
+    const int te = tid - 64;
     const int ww = r % p.Wt;
     const int hh = (r / p.Wt) % p.Ht;
     const int tq = r / (p.Wt * p.Ht);
+    const int ocols = p.ocols;
+    const uint32_t rb = (uint32_t)(ocols * 2);
+    const uint32_t swz = rb == 128 ? 7u : (rb == 64 ? 3u : (rb == 32 ? 1u : 0u));
+    const uint32_t stg = smem_u32(smem + L::kStagingOff);
+    const uint32_t sub_bytes = 128u * rb;
+    const int my_pair = te % PAIRS;
+    const int rpart = te / PAIRS;
+    const int last_ch = min(NCH, (p.Co - n0 + CH - 1) / CH) - 1;
+    float ssum[NCH][2], ssq[NCH][2];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) { ssum[c][0] = ssum[c][1] = ssq[c][0] = ssq[c][1] = 0.f; }
+    bool store_pending = false;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
-      const int nt = tile % p.n_tiles;
-      int q = tile / p.n_tiles;
+    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
+      int q = patch;
       const int tw = q % p.tilesW; q /= p.tilesW;
       const int th = q % p.tilesH; q /= p.tilesH;
       const int tt = q % p.tilesT;
       const int n = q / p.tilesT;
-      const int wo = tw * p.Wt + ww, ho = th * p.Ht + hh, to = tt * p.Tt + tq;
+      const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
+      const int wo = w0 + ww, ho = h0 + hh, to = t0 + tq;
       const bool mv = r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
       const long long m = mv ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
-      const int n0 = nt * BN;
+      const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
       const int buf = it & 1;
       mbar_wait(&tfull_bar[buf], (uint32_t)((it >> 1) & 1), 14);
       tc_fence_after();
-      __nv_bfloat16* orow = p.out + (size_t)m * p.o_ld + p.o_coff;
-      const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        if (ch <= last_ch) {
+          const int col0 = n0 + ch * CH;
+          // (A) the previous TMA store must have finished reading the staging tile
+          if (te == 0 && store_pending) tma_store_wait_read();
+          named_bar_sync(1, 128);
+          // (B) accumulator -> staging
 #pragma unroll 1
-      for (int cc = 0; cc < BN / 32; ++cc) {
-        if (n0 + cc * 32 >= p.Co) break;
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + cc * 32), v);
-        tmem_ld_wait();
-        const int nb = n0 + cc * 32;
+          for (int cc = 0; cc < CH / 32; ++cc) {
+            const int nb = col0 + cc * 32;
+            if (nb >= p.Co) break;
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cc * 32), v);
+            tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int nn = nb + j * 8;
-          if (nn < p.Co) {
-            float* f = v + j * 8;
-            if (p.epi_scale) {
+            for (int j = 0; j < 4; ++j) {
+              const int nn = nb + j * 8;
+              if (nn < p.Co) {
+                float* f = v + j * 8;
+                if (p.epi_scale) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+                  for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+                }
+                if (rrow && mv) {
+                  float rf[8];
+                  unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) f[i] += rf[i];
+                }
+                if (p.epi_relu) {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+                }
+                uint4 pk = pack8(f);
+                if (!mv) pk = make_uint4(0, 0, 0, 0);
+                const int cl = cc * 32 + j * 8;            // column inside the chunk
+                const int gsub = cl / ocols;
+                uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl - gsub * ocols) * 2);
+                addr ^= ((addr >> 7) & swz) << 4;
+                sts_v4(addr, pk);
+              }
             }
-            if (rrow && mv) {
-              float rf[8];
-              unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] += rf[i];
-            }
-            if (p.epi_relu) {
-#pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
-            }
-            if (mv) *reinterpret_cast<uint4*>(orow + nn) = pack8(f);
           }
-        }
-        if (p.stats) {
-          float sq[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            v[i] = mv ? v[i] : 0.f;
-            sq[i] = v[i] * v[i];
+          // (C) last chunk read: hand the accumulator buffer back to the MMA warp
+          if (ch == last_ch) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
           }
-          const float s1 = warp_colsum32(v, lane);
-          const float s2 = warp_colsum32(sq, lane);
-          if (nb + lane < p.Co) {
-            atomicAdd(&s_stats[nb + lane], s1);
-            atomicAdd(&s_stats[p.Co + nb + lane], s2);
+          // (D) staged tile -> global memory (TMA clips rows/columns outside the tensor)
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (te == 0) {
+            const int nsub = (min(CH, p.Co - col0) + ocols - 1) / ocols;
+            for (int gsub = 0; gsub < nsub; ++gsub)
+              tma_store_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
+            tma_store_commit();
+            store_pending = true;
+          }
+          // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros)
+          if (p.stats) {
+            const int cl = my_pair * 2;
+            if (col0 + cl < p.Co) {
+              const int gsub = cl / ocols;
+              const uint32_t base = stg + gsub * sub_bytes + (uint32_t)((cl - gsub * ocols) * 2);
+              float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll 4
+              for (int rr = rpart; rr < 128; rr += TPP) {
+                uint32_t addr = base + (uint32_t)rr * rb;
+                addr ^= ((addr >> 7) & swz) << 4;
+                const uint32_t w = lds_u32(addr);
+                const float x0 = bf16lo_to_f32(w), x1 = bf16hi_to_f32(w);
+                a0 += x0; a1 += x1;
+                b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
+              }
+              ssum[ch][0] += a0; ssum[ch][1] += a1; ssq[ch][0] += b0; ssq[ch][1] += b1;
+            }
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
     }
+    if (te == 0 && store_pending) tma_store_wait_all();
     if (p.stats) {
-      named_bar_sync(1, 128);
-      for (int i = tid - 64; i < 2 * p.Co; i += 128) {
-        const float v = s_stats[i];
-        if (v != 0.f) atomicAdd(p.stats + i, v);
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        const int col = n0 + ch * CH + my_pair * 2;
+        if (ch <= last_ch && col < p.Co) {
+          atomicAdd(p.stats + col, ssum[ch][0]);
+          atomicAdd(p.stats + col + 1, ssum[ch][1]);
+          atomicAdd(p.stats + p.Co + col, ssq[ch][0]);
+          atomicAdd(p.stats + p.Co + col + 1, ssq[ch][1]);
+        }
       }
     }
   }

@@ -3,6 +3,7 @@
 // cuTensorMapEncodeTiled is resolved at run time so the library also loads on a box without a GPU.
 #include "conv_simt.cuh"
 #include "conv_tma.cuh"
+#include "wgrad_tma.cuh"
 #include "elementwise.cuh"
 
 #include <array>
@@ -139,7 +140,8 @@ int get_act_tmap(const void* base, int C, int W, int H, int T, int N, int ld, in
   cuuint32_t box[5] = {(cuuint32_t)box_c, (cuuint32_t)(bw * sW), (cuuint32_t)(bh * sH), (cuuint32_t)(bt * sT), 1};
   cuuint32_t estr[5] = {1, (cuuint32_t)sW, (cuuint32_t)sH, (cuuint32_t)sT, 1};
   const CUtensorMapSwizzle sw = box_c == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
-                                            : (box_c == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+                                            : (box_c == 32 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                           : (box_c == 16 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE));
   CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), gdim, gstr, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -165,14 +167,14 @@ int num_sms() {
 }
 
 // output patch (Wt, Ht, Tt) with Wt*Ht*Tt <= 128 that wastes the fewest MMA rows; ties -> longest W run
-void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht, int* Tt) {
+void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht, int* Tt, int max_rows = 128) {
   double best = -1.0;
   int bw = 1, bh = 1, bt = 1;
-  for (int w = 1; w <= Wo && w <= 128 && w * sW <= 256; ++w) {
+  for (int w = 1; w <= Wo && w <= max_rows && w * sW <= 256; ++w) {
     const int tw = (Wo + w - 1) / w;
-    for (int h = 1; h <= Ho && w * h <= 128 && h * sH <= 256; ++h) {
+    for (int h = 1; h <= Ho && w * h <= max_rows && h * sH <= 256; ++h) {
       const int th = (Ho + h - 1) / h;
-      int t = 128 / (w * h);
+      int t = max_rows / (w * h);
       if (t > To) t = To;
       while (t * sT > 256) --t;
       // prefer a Tt that divides To
@@ -182,8 +184,8 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
       for (int pass = 0; pass < 2; ++pass) {
         const int tcur = pass == 0 ? t : tbest;
         const int ttiles = (To + tcur - 1) / tcur;
-        const double util = (double)Wo * Ho * To / ((double)tw * th * ttiles * 128.0);
-        const double score = util + 1e-4 * w / 128.0;
+        const double util = (double)Wo * Ho * To / ((double)tw * th * ttiles * (double)max_rows);
+        const double score = util + 1e-4 * w / (double)max_rows;
         if (score > best) { best = score; bw = w; bh = h; bt = tcur; }
       }
     }
@@ -192,18 +194,22 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
 }
 
 template <int BN>
-int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const ConvTmaParams& p, cudaStream_t st) {
+int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
+                    cudaStream_t st) {
   using L = ConvTmaCfg<BN>;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)L::smem_bytes(2048, true));
+                                         (int)L::smem_bytes());
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
     attr_done = true;
   }
-  int grid = num_sms();
-  if (grid > p.total_tiles) grid = p.total_tiles;
-  conv_tma_kernel<BN><<<grid, 192, L::smem_bytes(p.Co, p.stats != nullptr), st>>>(ta, tw, p);
+  // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
+  long long per_nt = num_sms() / p.n_tiles;
+  if (per_nt < 1) per_nt = 1;
+  if (per_nt > p.total_patches) per_nt = p.total_patches;
+  const int grid = (int)per_nt * p.n_tiles;
+  conv_tma_kernel<BN><<<grid, 192, L::smem_bytes(), st>>>(ta, tw, to, p);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
@@ -356,9 +362,10 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt);
     q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
     q.n_tiles = (geom->Co + bn - 1) / bn;
-    const long long tt = (long long)q.N * q.tilesT * q.tilesH * q.tilesW * q.n_tiles;
+    const long long tt = (long long)q.N * q.tilesT * q.tilesH * q.tilesW;
     if (tt >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
-    q.total_tiles = (int)tt;
+    q.total_patches = (int)tt;
+    q.ocols = geom->Co >= 64 ? 64 : (geom->Co >= 32 ? 32 : (geom->Co >= 16 ? 16 : 8));
     q.out = p.out; q.epi_scale = p.epi_scale; q.epi_shift = p.epi_shift; q.res = p.res; q.res_ld = p.res_ld;
     q.res_coff = p.res_coff; q.epi_relu = p.epi_relu; q.stats = p.stats;
     CUtensorMap ta;
@@ -366,11 +373,15 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,
                       q.Tt, sW, sH, sT, &ta);
     if (rc) return rc;
+    CUtensorMap to;
+    rc = get_act_tmap((const __nv_bfloat16*)out + geom->o_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, geom->o_ld, q.ocols, q.Wt,
+                      q.Ht, q.Tt, 1, 1, 1, &to);
+    if (rc) return rc;
     switch (bn) {
-      case 32: return launch_conv_tma<32>(ta, tm, q, st);
-      case 64: return launch_conv_tma<64>(ta, tm, q, st);
-      case 128: return launch_conv_tma<128>(ta, tm, q, st);
-      default: return launch_conv_tma<256>(ta, tm, q, st);
+      case 32: return launch_conv_tma<32>(ta, tm, to, q, st);
+      case 64: return launch_conv_tma<64>(ta, tm, to, q, st);
+      case 128: return launch_conv_tma<128>(ta, tm, to, q, st);
+      default: return launch_conv_tma<256>(ta, tm, to, q, st);
     }
   }
   switch (bn) {
@@ -417,8 +428,61 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     SFB_CHECK_LAUNCH("conv_wgrad_simt_kernel");
     return SFB_OK;
   }
-  if (impl != SFB_IMPL_TC) return SFB_ERR_BAD_ARG;
+  if (impl != SFB_IMPL_TC && impl != SFB_IMPL_TC_GATHER) return SFB_ERR_BAD_ARG;
   if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
+  if (impl == SFB_IMPL_TC && !p.pro_scale && (geom->Cg % 16) == 0) {
+    // ---- TMA-fed tcgen05 kernel ----
+    WgradTmaParams q;
+    memset(&q, 0, sizeof(q));
+    q.N = geom->N; q.To = geom->To; q.Ho = geom->Ho; q.Wo = geom->Wo;
+    q.Co = geom->Co; q.Cg = geom->Cg; q.Ci_real = Ci_real; q.taps = p.taps;
+    q.kT = geom->kT; q.kH = geom->kH; q.kW = geom->kW; q.sT = geom->sT; q.sH = geom->sH; q.sW = geom->sW;
+    q.pT = geom->pT; q.pH = geom->pH; q.pW = geom->pW;
+    q.box_k = geom->Cg >= 64 ? 64 : geom->Cg;
+    if (q.box_k != 64 && q.box_k != 32 && q.box_k != 16) q.box_k = 16;  // Cg = 48: three 16-channel... (not used)
+    q.cchunks = geom->Cg >= 64 ? (geom->Cg + 63) / 64 : geom->Cg / q.box_k;
+    q.n_units = p.taps * q.cchunks;
+    q.upc = 256 / q.box_k;
+    if (q.upc > q.n_units) q.upc = q.n_units;
+    int gW = geom->Wi, gH = geom->Hi, gT = geom->Ti, gN = geom->N;
+    const bool pointwise = p.taps == 1 && geom->sT == 1 && geom->sH == 1 && geom->sW == 1 && geom->pT == 0 &&
+                           geom->pH == 0 && geom->pW == 0;
+    if (pointwise) {
+      gW = p.M; gH = gT = gN = 1;
+      q.N = 1; q.To = 1; q.Ho = 1; q.Wo = p.M;
+    }
+    pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt, kWtRows);
+    q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
+    const long long tp = (long long)q.N * q.tilesT * q.tilesH * q.tilesW;
+    if (tp >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+    q.total_patches = (int)tp;
+    q.dW = dw;
+    const int gx = (q.n_units + q.upc - 1) / q.upc;
+    const int gy = (geom->Co + 127) / 128;
+    long long splits = (2ll * num_sms() + gx * gy - 1) / (gx * gy);
+    if (splits < 1) splits = 1;
+    if (splits > q.total_patches) splits = q.total_patches;
+    q.patches_per_split = (int)((q.total_patches + splits - 1) / splits);
+    splits = (q.total_patches + q.patches_per_split - 1) / q.patches_per_split;
+    CUtensorMap tx, tdy;
+    // X boxes: when Cg < 64 a "64-channel chunk" is a box_k-channel chunk at channel offset chunk*box_k
+    rc = get_act_tmap((const __nv_bfloat16*)x + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,
+                      q.Tt, q.sW, q.sH, q.sT, &tx);
+    if (rc) return rc;
+    rc = get_act_tmap((const __nv_bfloat16*)dy + dy_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, dy_ld, 64, q.Wt, q.Ht, q.Tt, 1, 1,
+                      1, &tdy);
+    if (rc) return rc;
+    static bool attr_done2 = false;
+    if (!attr_done2) {
+      cudaError_t e = cudaFuncSetAttribute(wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWtSmem);
+      if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tma)");
+      attr_done2 = true;
+    }
+    dim3 grid(gx, gy, (unsigned)splits);
+    wgrad_tma_kernel<<<grid, 192, kWtSmem, st>>>(tx, tdy, q);
+    SFB_CHECK_LAUNCH("wgrad_tma_kernel");
+    return SFB_OK;
+  }
   const int kpad = (p.Ktot + 63) / 64 * 64;
   const int gx = (kpad + 255) / 256;
   const int gy = (geom->Co + 127) / 128;

@@ -1,0 +1,189 @@
+// wgrad_tma.cuh -- Conv3d weight gradient on tcgen05, operands fetched by TMA (sm_100a).
+//
+//   dW[co][(tap, c)] = sum over output pixels m of  dY[m][co] * X[in(m, tap)][c]
+//
+//   The reduction runs over pixels, so both MMA operands are "MN-major": a shared-memory row is one pixel, its 128 /
+//   64 / 32 bytes are consecutive channels -- exactly what a TMA box of an NDHWC tensor produces.
+//     A = dY patch  : [R pixels][128 co]  two SWIZZLE_128B blocks of 64 channels (TMA zero-fills co >= Co)
+//     B = X  patch  : per unit u = (tap, 64-channel chunk) one shifted box [R pixels][box_k channels]
+//                     (the same shifted-box im2col as conv_tma.cuh); UPC units side by side = N of the MMA
+//   D[128 co][UPC*box_k] lives in TMEM for the whole kernel; a CTA walks its share of the pixel patches
+//   (split over blockIdx.z), then adds its partial sums into the fp32 OIDHW gradient with atomics.
+//   R <= 64 pixels per stage; stages are zeroed once so the rows a box never writes (R not a multiple of 16) add 0.
+//
+// Replaces cuDNN bwd-filter behind nn.Conv3d (reference model/my_slowfast.py:94-125 via autograd).
+#pragma once
+#include "conv_tma.cuh"
+
+namespace sfb {
+
+struct WgradTmaParams {
+  int N, To, Ho, Wo;
+  int Co, Cg, Ci_real, taps;
+  int kT, kH, kW, sT, sH, sW, pT, pH, pW;
+  int box_k, cchunks;          // channels per X box (64/32/16); 64-channel chunks per tap
+  int n_units;                 // taps * cchunks
+  int upc;                     // units per CTA (upc * box_k <= 256)
+  int Wt, Ht, Tt, tilesW, tilesH, tilesT, total_patches;
+  int patches_per_split;
+  float* dW;
+};
+
+constexpr int kWtStages = 4;
+constexpr int kWtRows = 64;
+constexpr int kWtABytes = 2 * kWtRows * 128;          // 16 KB: two [64 px][64 co] blocks
+constexpr int kWtBBytes = 4 * kWtRows * 128;          // 32 KB: up to 256 columns
+constexpr int kWtStage = kWtABytes + kWtBBytes;       // 48 KB
+constexpr int kWtBarOff = kWtStages * kWtStage;
+constexpr int kWtHolderOff = kWtBarOff + (2 * kWtStages + 1) * 8;
+constexpr int kWtSmem = 1024 + kWtHolderOff + 16;
+
+// MN-major operand descriptor: rows (K) are `span` bytes, 8-row groups SBO = 8*span apart, the next block of
+// span/2 MN-elements is `lbo` bytes away.
+__device__ __forceinline__ uint64_t umma_smem_desc_mnmajor(uint32_t smem_addr, uint32_t span, uint32_t lbo) {
+  const uint64_t layout = span == 128 ? 2ull : (span == 64 ? 4ull : 6ull);
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)(((8u * span) >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= layout << 61;
+  return d;
+}
+
+__global__ void __launch_bounds__(192, 1)
+wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dy,
+                 const WgradTmaParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kWtBarOff);
+  uint64_t* empty_bar = full_bar + kWtStages;
+  uint64_t* done_bar = empty_bar + kWtStages;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + kWtHolderOff);
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5;
+  const int lane = tid & 31;
+  const int u0 = blockIdx.x * p.upc;                       // first unit of this CTA
+  const int nu = min(p.upc, p.n_units - u0);               // live units
+  const int co0 = blockIdx.y * 128;
+  const int patch_begin = blockIdx.z * p.patches_per_split;
+  const int patch_end = min(p.total_patches, patch_begin + p.patches_per_split);
+  const int rows = p.Wt * p.Ht * p.Tt;
+  const int ksteps = (rows + 15) >> 4;
+  const uint32_t span = (uint32_t)(p.box_k * 2);
+  const uint32_t bblock = (uint32_t)kWtRows * span;        // bytes of one unit block
+  const int nblk_a = min(2, (p.Co - co0 + 63) / 64);
+  constexpr uint32_t kTmemCols = 256;
+
+  if (tid == 0) {
+    for (int s = 0; s < kWtStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(done_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_x);
+    tma_prefetch_desc(&tmap_dy);
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_holder, kTmemCols);
+    tmem_relinquish();
+  }
+  // zero the operand stages once: rows a box never writes must contribute 0 (and never NaN)
+  for (int i = tid; i < kWtStages * kWtStage / 16; i += blockDim.x)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const int khw = p.kH * p.kW;
+
+  if (patch_end > patch_begin) {
+    if (warp == 0) {
+      if (lane == 0) {
+        const uint32_t tx = (uint32_t)(nblk_a * rows * 128 + nu * rows * (int)span);
+        uint32_t g = 0;
+        for (int patch = patch_begin; patch < patch_end; ++patch, ++g) {
+          int q = patch;
+          const int tw = q % p.tilesW; q /= p.tilesW;
+          const int th = q % p.tilesH; q /= p.tilesH;
+          const int tt = q % p.tilesT;
+          const int n = q / p.tilesT;
+          const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
+          const int s = g % kWtStages;
+          mbar_wait(&empty_bar[s], ((g / kWtStages) & 1) ^ 1, 21);
+          mbar_arrive_expect_tx(&full_bar[s], tx);
+          const uint32_t sa = smem_u32(smem + s * kWtStage);
+          for (int b = 0; b < nblk_a; ++b)
+            tma_load_5d(sa + b * (kWtRows * 128), &tmap_dy, &full_bar[s], co0 + b * 64, w0, h0, t0, n);
+          const uint32_t sb = sa + kWtABytes;
+          for (int u = 0; u < nu; ++u) {
+            const int unit = u0 + u;
+            const int tap = unit / p.cchunks;
+            const int c0 = (unit - tap * p.cchunks) * p.box_k;
+            const int kt = tap / khw;
+            const int r2 = tap - kt * khw;
+            const int kh = r2 / p.kW;
+            const int kw = r2 - kh * p.kW;
+            tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], c0, w0 * p.sW + kw - p.pW, h0 * p.sH + kh - p.pH,
+                        t0 * p.sT + kt - p.pT, n);
+          }
+        }
+      }
+    } else if (warp == 1) {
+      if (lane == 0) {
+        const int ncols = ((nu * p.box_k + 15) >> 4) << 4;
+        const uint32_t idesc = umma_idesc_bf16(128, ncols, 1, 1);
+        uint32_t g = 0;
+        for (int patch = patch_begin; patch < patch_end; ++patch, ++g) {
+          const int s = g % kWtStages;
+          mbar_wait(&full_bar[s], (g / kWtStages) & 1, 22);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + s * kWtStage);
+          const uint32_t sb = sa + kWtABytes;
+          for (int kk = 0; kk < ksteps; ++kk) {
+            const uint64_t ad = umma_smem_desc_mnmajor(sa + kk * (16 * 128), 128, kWtRows * 128);
+            const uint64_t bd = umma_smem_desc_mnmajor(sb + kk * 16 * span, span, bblock);
+            umma_bf16(tmem_base, ad, bd, idesc, (g | (uint32_t)kk) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+        }
+        umma_commit(done_bar);
+      }
+    } else {
+      // ---------------- epilogue: TMEM lane = co, columns = (unit, channel) ----------------
+      const int q4 = warp & 3;
+      mbar_wait(done_bar, 0, 23);
+      tc_fence_after();
+      const int co = co0 + q4 * 32 + lane;
+      const bool cov = co < p.Co;
+      float* dwrow = p.dW + (size_t)(cov ? co : 0) * p.Ci_real * p.taps;
+      const int ncols = nu * p.box_k;
+#pragma unroll 1
+      for (int cc = 0; cc * 32 < ncols; ++cc) {
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int col = cc * 32 + i;
+          const int u = col / p.box_k;
+          const int unit = u0 + u;
+          const int tap = unit / p.cchunks;
+          const int c = (unit - tap * p.cchunks) * p.box_k + (col - u * p.box_k);
+          if (cov && col < ncols && c < p.Ci_real) atomicAdd(dwrow + (size_t)c * p.taps + tap, v[i]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+}  // namespace sfb

@@ -66,7 +66,8 @@ class ConvL:
         self.s = tuple(conv.stride)
         self.p = tuple(conv.padding)
         self.Ci, self.Co = conv.in_channels, conv.out_channels
-        self.Cg = round_up(self.Ci, 8)
+        self.Cg = round_up(self.Ci, 16)    # gathered-operand width: TMA boxes / MMA K steps are 16 channels
+        self.Cgt = round_up(self.Co, 16)   # same for the dgrad operand (dY)
         self.taps = self.k[0] * self.k[1] * self.k[2]
         self.needs_dgrad = needs_dgrad
         self.wp = self.wpt = None
@@ -200,17 +201,6 @@ class SlowFastEngine:
             l.scale, l.shift = self.bn_flat[o_r:o_r + c], self.bn_flat[o_r + c:o_r + 2 * c]
             l.mean, l.invstd = self.bn_flat[o_r + 2 * c:o_r + 3 * c], self.bn_flat[o_r + 3 * c:o_r + 4 * c]
             o_r += 4 * c
-        # ---- concat prologue vectors: identity on the Slow channels, lateral BN on the rest ----
-        self.cat_pro = {}
-        for si, lat in enumerate(self.laterals):
-            if lat is None:
-                continue
-            c_slow = self.cfg["stem_dim_outs"][0] * (1 if si == 0 else 4 * 2 ** (si - 1))
-            tot = c_slow + lat.Co
-            sc, sh = _f32(tot, dev), _f32(tot, dev, zero=True)
-            sc.fill_(1.0)
-            self.cat_pro[si] = (sc, sh, c_slow)
-            lat.scale, lat.shift = sc[c_slow:], sh[c_slow:]  # bn_finalize writes straight into the cat vector
         # ---- flat gradient arena, reverse forward order (head first) ----
         live: List[torch.nn.Parameter] = []
         for l in self.layers:
@@ -247,7 +237,7 @@ class SlowFastEngine:
             if l.wp is None:
                 l.wp = torch.empty((rp, kp), dtype=torch.bfloat16, device=self.dev)
             if self.dry_run:
-                rpt, kpt = _ffi.packed_weight_dims(l.Ci, l.Co, l.taps)
+                rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
                 l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
                 l.packed_version = w._version
                 continue
@@ -257,10 +247,10 @@ class SlowFastEngine:
             _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cg, 0, l.wp.data_ptr(), rp, kp, self.stream),
                        "sfb_pack_weight")
             if training and l.needs_dgrad:
-                rpt, kpt = _ffi.packed_weight_dims(l.Ci, l.Co, l.taps)
+                rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
                 if l.wpt is None:
                     l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
-                _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Co, 1, l.wpt.data_ptr(), rpt, kpt,
+                _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cgt, 1, l.wpt.data_ptr(), rpt, kpt,
                                                     self.stream), "sfb_pack_weight(T)")
             l.packed_version = w._version
 
@@ -270,15 +260,22 @@ class SlowFastEngine:
         lst.append((fn, args, tag))
 
     def _conv(self, plan, lst, L: ConvL, x: Act, pro, out: Act, *, stats=False, transposed=False, residual: Act = None,
-              wp=None, tag=None):
+              wp=None, tag=None, epi=None):
+        """x is gathered with its channel count rounded up to 16 (the pad lanes of every buffer are zero); a dgrad
+        (transposed) writes the full padded width of its output so those lanes stay zero in recycled buffers.
+        epi = (scale, shift, relu): folded-BatchNorm epilogue (eval mode)."""
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = out.dims
-        g = ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, out.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+        cg = round_up(x.C, 16)
+        co = round_up(out.C, 16) if transposed else out.C
+        assert x.coff + cg <= x.ld and out.coff + co <= out.ld
+        g = ConvGeom(N, Ti, Hi, Wi, cg, To, Ho, Wo, co, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
                      x.ld, x.coff, out.ld, out.coff, int(transposed))
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
-        ep = Epilogue(0, 0, residual.ptr() if residual else 0, residual.ld if residual else 0,
-                      residual.coff if residual else 0, 0, L.stats.data_ptr() if stats else 0)
+        ep = Epilogue(epi[0].data_ptr() if epi else 0, epi[1].data_ptr() if epi else 0,
+                      residual.ptr() if residual else 0, residual.ld if residual else 0,
+                      residual.coff if residual else 0, int(epi[2]) if epi else 0, L.stats.data_ptr() if stats else 0)
         g.real_k = (L.Co if transposed else L.Ci) * L.taps  # algorithmic reduction length (no channel padding)
         g.real_n = L.Ci if transposed else L.Co
         plan.keep += [g, pr, ep]
@@ -291,7 +288,7 @@ class SlowFastEngine:
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = dy.dims
-        g = ConvGeom(N, Ti, Hi, Wi, x.C, To, Ho, Wo, dy.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+        g = ConvGeom(N, Ti, Hi, Wi, round_up(x.C, 16), To, Ho, Wo, dy.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
                      x.ld, x.coff, dy.ld, dy.coff, 0)
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
         g.real_k, g.real_n = L.Ci * L.taps, L.Co
@@ -329,36 +326,66 @@ class SlowFastEngine:
             self.ddp.note_grad_ready(plan, lst, bn.weight)
             self.ddp.note_grad_ready(plan, lst, bn.bias)
 
+    def _apply(self, lst, L: ConvL, y: Act, out: Act, tag=None):
+        """out = relu(y * scale_L + shift_L)   (training: BatchNorm needs the batch statistics of the whole tensor
+        before it can normalise, so the activated operand of the next conv is materialised by one HBM-bound pass)"""
+        self._emit(lst, self.lib.sfb_bn_add_relu, y.ptr(), y.ld, y.coff, L.scale.data_ptr(), L.shift.data_ptr(), 0, 0, 0, 0, 0,
+                   out.ptr(), out.ld, out.coff, y.M, y.C, 1, self.stream, tag=tag)
+
     # ------------------------------------------------------------------ plan construction
     def build_plan(self, N, Ts, Tf, H, W, training) -> Plan:
         cfg = self.cfg
         dev = self.dev
         plan = Plan()
         pool = BufferPool(dev)
-        fwd, bwd_blocks = plan.fwd, []
+        fwd = plan.fwd
 
-        def new_act(n, t, h, w, c, zero=False):
-            a = Act.empty(n, t, h, w, c, device=dev, zero=zero)
+        def new_act(n, t, h, w, c, pad=True):
+            """activation buffer; channel counts that are not a multiple of 16 get zeroed pad lanes (TMA operand width)"""
+            ld = round_up(c, 16) if pad else c
+            a = Act.empty(n, t, h, w, ld, device=dev, C=c, zero=(ld != c))
             plan.act_bytes += a.buf.numel() * 2
             return a
 
-        def new_grad(like: Act, C_=None):
+        def new_grad(like: Act):
             n, t, h, w = like.dims
-            c = C_ if C_ is not None else like.C
-            return Act(pool.alloc((n, t, h, w, c)), 0, c)
+            return Act(pool.alloc((n, t, h, w, like.ld)), like.coff, like.C)
+
+        def fold(L):
+            bn = L.bn
+            self._emit(fwd, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                       bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
+
+        def conv_bn_act(L, x: Act, out_z: Optional[Act], *, relu=True, residual=None, keep_raw=True):
+            """conv + BatchNorm (+ReLU).  training: raw y (+ fused statistics) -> finalize -> [apply -> z];
+            eval: folded BatchNorm (+residual, ReLU) in the GEMM epilogue, nothing else.
+            returns (y_raw | None, z | None)"""
+            n_, t_, h_, w_ = x.dims
+            to, ho, wo = conv_out_dims((t_, h_, w_), L.k, L.s, L.p)
+            if training:
+                y = new_act(n_, to, ho, wo, L.Co)
+                self._conv(plan, fwd, L, x, None, y, stats=True)
+                self._bn_stats_ready(plan, fwd, L, y.M, True)
+                if out_z is not None:
+                    self._apply(fwd, L, y, out_z, tag=(L.conv_name + ".z", out_z))
+                return y, out_z
+            fold(L)
+            assert out_z is not None
+            self._conv(plan, fwd, L, x, None, out_z, epi=(L.scale, L.shift, relu), residual=residual,
+                       tag=(L.conv_name + ".z", out_z))
+            return None, out_z
 
         T_in = (Ts, Tf)
         # ---------------- stems ----------------
         stem_rec = []
         pooled: List[FinalAct] = []
-        cat_bufs = {}  # stage index -> (cat Act, dcat Act|None)
-        c_slow0 = cfg["stem_dim_outs"][0]
+        cat_bufs = {}
         for p in range(2):
             L = self.stems[p]
-            x_in = new_act(N, T_in[p], H, W, L.Cg)
+            x_in = new_act(N, T_in[p], H, W, L.Ci)
             plan.x_in.append(x_in)
             To, Ho, Wo = conv_out_dims((T_in[p], H, W), L.k, L.s, L.p)
-            y0 = new_act(N, To, Ho, Wo, L.Co)
+            y0 = new_act(N, To, Ho, Wo, L.Co, pad=False)  # biggest tensors of the net: consumed by the pool only
             self._conv(plan, fwd, L, x_in, None, y0, stats=training)
             self._bn_stats_ready(plan, fwd, L, y0.M, training)
             Hp, Wp = (Ho - 1) // 2 + 1, (Wo - 1) // 2 + 1
@@ -378,57 +405,41 @@ class SlowFastEngine:
             pooled.append(out)
             stem_rec.append(dict(L=L, x_in=x_in, y0=y0, out=out, idx=idx))
 
-        # lateral helper -------------------------------------------------
         lateral_rec = {}
 
         def do_lateral(si, slow_out: FinalAct, fast_out: FinalAct):
-            """lateral conv after stage-index si (0 = stems); returns the Slow input of the next stage as
-            (Act over the whole cat buffer, prologue, FinalAct-like gradient holder)"""
+            """lateral conv after stage index si (0 = stems): relu(bn(conv(fast))) lands behind the Slow tensor in
+            the concat buffer (torch.cat of reference model/my_slowfast.py:343 never happens)"""
             lat = self.laterals[si]
             ci = cat_bufs[si]
-            sc, sh, c_slow = self.cat_pro[si]
-            assert c_slow == ci.c_slow and slow_out is ci.slow_out
-            ylat = ci.cat.view(c_slow, lat.Co)
-            self._conv(plan, fwd, lat, fast_out.act, None, ylat, stats=training)
-            self._bn_stats_ready(plan, fwd, lat, ylat.M, training)
+            assert slow_out is ci.slow_out
+            zlat = ci.cat.view(ci.c_slow, lat.Co)
+            ylat, _ = conv_bn_act(lat, fast_out.act, zlat)
             X = FinalAct(ci.cat)
             X.cat = ci
             ci.X = X
-            lateral_rec[si] = dict(L=lat, x=fast_out, ylat=ylat, ci=ci)
-            return X, (sc, sh, True)
+            lateral_rec[si] = dict(L=lat, x=fast_out, ylat=ylat, zlat=zlat, ci=ci)
+            return X
 
         # ---------------- residual stages ----------------
-        block_recs = []  # forward order: (stage, pathway, block index, record)
+        block_recs = []
         cur: List[FinalAct] = pooled
-        cur_pro = [None, None]
         if self.laterals[0] is not None:
-            X, pro = do_lateral(0, cur[0], cur[1])
-            cur = [X, cur[1]]
-            cur_pro = [pro, None]
+            cur = [do_lateral(0, cur[0], cur[1]), cur[1]]
         for si in range(4):
             nxt: List[FinalAct] = [None, None]
             for p in (1, 0):  # Fast first: its output feeds the lateral that completes the Slow concat buffer
-                X, Xpro = cur[p], cur_pro[p]
+                X = cur[p]
                 blks = self.stages[si][p]
                 for bi, d in enumerate(blks):
                     a, b, c, s_ = d["a"], d["b"], d["c"], d["s"]
                     n_, t_, h_, w_ = X.act.dims
                     ta, ha, wa = conv_out_dims((t_, h_, w_), a.k, a.s, a.p)
-                    ya = new_act(n_, ta, ha, wa, a.Co)
-                    self._conv(plan, fwd, a, X.act, Xpro, ya, stats=training)
-                    self._bn_stats_ready(plan, fwd, a, ya.M, training)
+                    za = new_act(n_, ta, ha, wa, a.Co)
+                    ya, _ = conv_bn_act(a, X.act, za)
                     tb, hb, wb = conv_out_dims((ta, ha, wa), b.k, b.s, b.p)
-                    yb = new_act(n_, tb, hb, wb, b.Co)
-                    self._conv(plan, fwd, b, ya, (a.scale, a.shift, True), yb, stats=training)
-                    self._bn_stats_ready(plan, fwd, b, yb.M, training)
-                    yc = new_act(n_, tb, hb, wb, c.Co)
-                    self._conv(plan, fwd, c, yb, (b.scale, b.shift, True), yc, stats=training)
-                    self._bn_stats_ready(plan, fwd, c, yc.M, training)
-                    y1 = None
-                    if s_ is not None:
-                        y1 = new_act(n_, tb, hb, wb, s_.Co)
-                        self._conv(plan, fwd, s_, X.act, Xpro, y1, stats=training)
-                        self._bn_stats_ready(plan, fwd, s_, y1.M, training)
+                    zb = new_act(n_, tb, hb, wb, b.Co)
+                    yb, _ = conv_bn_act(b, za, zb)
                     last = bi == len(blks) - 1
                     if last and p == 0 and self.laterals[si + 1] is not None:
                         lat = self.laterals[si + 1]
@@ -439,24 +450,37 @@ class SlowFastEngine:
                         ci.slow_out = O
                     else:
                         O = FinalAct(new_act(n_, tb, hb, wb, c.Co))
-                    if y1 is not None:
-                        self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
-                                   y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
-                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=(d["name"] + ".O", O.act))
+                    otag = (d["name"] + ".O", O.act)
+                    yc = y1 = None
+                    if training:
+                        yc, _ = conv_bn_act(c, zb, None)
+                        if s_ is not None:
+                            y1, _ = conv_bn_act(s_, X.act, None)
+                            self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
+                                       c.shift.data_ptr(), y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
+                                       O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=otag)
+                        else:
+                            self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
+                                       c.shift.data_ptr(), X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
+                                       O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=otag)
                     else:
-                        assert Xpro is None
-                        self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(), c.shift.data_ptr(),
-                                   X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
-                                   O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=(d["name"] + ".O", O.act))
-                    block_recs.append(dict(si=si, p=p, d=d, X=X, Xpro=Xpro, ya=ya, yb=yb, yc=yc, y1=y1, O=O))
-                    X, Xpro = O, None
+                        # eval: shortcut = folded-BN conv (no ReLU) or X itself; conv_c adds it and applies the ReLU
+                        if s_ is not None:
+                            S = new_act(n_, tb, hb, wb, s_.Co)
+                            conv_bn_act(s_, X.act, S, relu=False)
+                            res = S
+                        else:
+                            res = X.act
+                        fold(c)
+                        self._conv(plan, fwd, c, zb, None, O.act, epi=(c.scale, c.shift, True), residual=res, tag=otag)
+                    block_recs.append(dict(si=si, p=p, d=d, X=X, ya=ya, za=za, yb=yb, zb=zb, yc=yc, y1=y1, O=O))
+                    X = O
                 nxt[p] = X
-            cur, cur_pro = nxt, [None, None]
+            cur = nxt
             if self.laterals[si + 1] is not None:
-                Xs, pro = do_lateral(si + 1, cur[0], cur[1])
+                Xs = do_lateral(si + 1, cur[0], cur[1])
                 block_recs.append(dict(lateral=si + 1))
                 cur = [Xs, cur[1]]
-                cur_pro = [pro, None]
 
         # ---------------- head ----------------
         feat_dim = cur[0].act.C + cur[1].act.C
@@ -511,13 +535,19 @@ class SlowFastEngine:
             else:
                 fa.grad = new_grad(fa.act)
 
+        def dgrad_into(L: ConvL, dy: Act, X: FinalAct):
+            """dX (+)= conv_transpose(dy, W_L)"""
+            ensure_grad(X)
+            self._conv(plan, bwd, L, dy, None, X.grad, transposed=True, residual=X.grad if X.ginit else None)
+            X.ginit = True
+
         def lateral_backward(si):
             lr = lateral_rec[si]
             lat, ci = lr["L"], lr["ci"]
             assert ci.X.ginit, "concat buffer without gradient contribution"
             ci.slow_out.ginit = True  # the Slow channels of dcat are now complete as well
             dz = ci.dcat.view(ci.c_slow, lat.Co)
-            self._bn_bwd(plan, bwd, lat, dz, lr["ylat"], None, dz)  # in place: dz -> dy
+            self._bn_bwd(plan, bwd, lat, dz, lr["ylat"], lr["zlat"], dz)  # in place: dz -> dy
             self._wgrad(plan, bwd, lat, lr["x"].act, None, dz)
             dgrad_into(lat, dz, lr["x"])
 
@@ -532,19 +562,13 @@ class SlowFastEngine:
             fa.ginit = True
             f_off += a.C
 
-        def dgrad_into(L: ConvL, dy: Act, X: FinalAct):
-            """dX (+)= conv_transpose(dy, W_L)"""
-            ensure_grad(X)
-            self._conv(plan, bwd, L, dy, None, X.grad, transposed=True, residual=X.grad if X.ginit else None)
-            X.ginit = True
-
         for rec in reversed(block_recs):
             if "lateral" in rec:
                 lateral_backward(rec["lateral"])
                 continue
-            d, X, Xpro, O = rec["d"], rec["X"], rec["Xpro"], rec["O"]
+            d, X, O = rec["d"], rec["X"], rec["O"]
             a, b, c, s_ = d["a"], d["b"], d["c"], d["s"]
-            ya, yb, yc, y1 = rec["ya"], rec["yb"], rec["yc"], rec["y1"]
+            ya, za, yb, zb, yc, y1 = rec["ya"], rec["za"], rec["yb"], rec["zb"], rec["yc"], rec["y1"]
             dO = O.grad
             assert O.ginit, "block output without gradient contribution"
             self._emit(bwd, _probe, tag=(d["name"] + ".dO", dO))
@@ -554,23 +578,23 @@ class SlowFastEngine:
                 dy1 = new_grad(y1)
                 self._bn_bwd(plan, bwd, s_, dO, y1, O.act, dy1)
             else:
-                # identity shortcut: masked gradient g also flows straight to the block input
+                # identity shortcut: the masked gradient g also flows straight to the block input
                 ensure_grad(X)
                 self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc, g_out=X.grad, g_acc=X.ginit)
                 X.ginit = True
-            self._wgrad(plan, bwd, c, yb, (b.scale, b.shift, True), dyc)
+            self._wgrad(plan, bwd, c, zb, None, dyc)
             dzb = new_grad(yb)
             self._conv(plan, bwd, c, dyc, None, dzb, transposed=True)
             pool.release(dyc.buf)
-            self._bn_bwd(plan, bwd, b, dzb, yb, None, dzb)
-            self._wgrad(plan, bwd, b, ya, (a.scale, a.shift, True), dzb)
+            self._bn_bwd(plan, bwd, b, dzb, yb, zb, dzb)
+            self._wgrad(plan, bwd, b, za, None, dzb)
             dza = new_grad(ya)
             self._conv(plan, bwd, b, dzb, None, dza, transposed=True)
             pool.release(dzb.buf)
-            self._bn_bwd(plan, bwd, a, dza, ya, None, dza)
-            self._wgrad(plan, bwd, a, X.act, Xpro, dza)
+            self._bn_bwd(plan, bwd, a, dza, ya, za, dza)
+            self._wgrad(plan, bwd, a, X.act, None, dza)
             if s_ is not None:
-                self._wgrad(plan, bwd, s_, X.act, Xpro, dy1)
+                self._wgrad(plan, bwd, s_, X.act, None, dy1)
                 dgrad_into(s_, dy1, X)
                 pool.release(dy1.buf)
             dgrad_into(a, dza, X)
@@ -688,8 +712,10 @@ class SlowFastEngine:
                 L.shift.copy_(L.bn.bias.detach() - mean * L.bn.weight.detach() * invstd)
         if feat is not None:
             plan.feat.copy_(feat)
-        # arg-max indices of the stem pools depend on the forced stem outputs: recompute them
-        self._run([op for op in plan.fwd if op[0] is self.lib.sfb_maxpool_fwd])
+        # activated operands (z = relu(bn(y))) and the stem pools (+ arg-max indices) derive from the forced raw
+        # outputs: recompute them with the engine's own kernels
+        self._run([op for op in plan.fwd if op[0] is self.lib.sfb_maxpool_fwd or
+                   (op[0] is self.lib.sfb_bn_add_relu and op[2] is not None and op[2][0].endswith(".z"))])
 
     def get_plan(self, xs, xf, training) -> Plan:
         N, Cs, Ts, H, W = xs.shape
