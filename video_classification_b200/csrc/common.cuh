@@ -41,13 +41,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: ~2^31 cycles (about a second) then flag + trap, so a protocol bug fails the launch
+// Bounded wait: ~2^34 cycles (about 9 s; long enough for instrumented ncu replays) then flag + trap, so a protocol bug fails the launch
 // instead of hanging the GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int site) {
   if (mbar_try_wait(bar, parity)) return;
   long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > (1ll << 31)) {
+    if (clock64() - t0 > (1ll << 34)) {
       atomicExch(&g_dev_error, 0x1000u | (unsigned)site);
       __trap();
     }

@@ -547,7 +547,7 @@ class SlowFastEngine:
             assert ci.X.ginit, "concat buffer without gradient contribution"
             ci.slow_out.ginit = True  # the Slow channels of dcat are now complete as well
             dz = ci.dcat.view(ci.c_slow, lat.Co)
-            self._bn_bwd(plan, bwd, lat, dz, lr["ylat"], lr["zlat"], dz)  # in place: dz -> dy
+            self._bn_bwd(plan, bwd, lat, dz, lr["ylat"], None, dz)  # in place: dz -> dy; ReLU mask recomputed from y
             self._wgrad(plan, bwd, lat, lr["x"].act, None, dz)
             dgrad_into(lat, dz, lr["x"])
 
@@ -586,12 +586,12 @@ class SlowFastEngine:
             dzb = new_grad(yb)
             self._conv(plan, bwd, c, dyc, None, dzb, transposed=True)
             pool.release(dyc.buf)
-            self._bn_bwd(plan, bwd, b, dzb, yb, zb, dzb)
+            self._bn_bwd(plan, bwd, b, dzb, yb, None, dzb)  # mask = (y*scale+shift > 0), recomputed: one tensor read less
             self._wgrad(plan, bwd, b, za, None, dzb)
             dza = new_grad(ya)
             self._conv(plan, bwd, b, dzb, None, dza, transposed=True)
             pool.release(dzb.buf)
-            self._bn_bwd(plan, bwd, a, dza, ya, za, dza)
+            self._bn_bwd(plan, bwd, a, dza, ya, None, dza)
             self._wgrad(plan, bwd, a, X.act, None, dza)
             if s_ is not None:
                 self._wgrad(plan, bwd, s_, X.act, None, dy1)
