@@ -108,6 +108,28 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
                    const void* dy, int32_t dy_ld, int32_t dy_coff,
                    float* dw, int32_t Ci_real, int32_t impl, void* stream);
 
+
+/* ---- stem convolution (1,7,7)/s(1,2,2)/p(0,3,3) in space-to-depth form -------------------------------------------
+ * replaces: ResNetBasicStem.conv of both pathways (reference model/my_slowfast.py:63-68: kernel (1,7,7), stride
+ * (1,2,2), padding (0,3,3); pytorchvideo create_res_basic_stem) and its weight gradient.  The clip is laid out
+ * "s2d": [N][T][H/2][W/2][Cs] bf16 with channel (sh*2+sw)*C + c = input channel c of sub-pixel (sh, sw) of the 2x2
+ * block, zero padded to Cs = sfb_stem_s2d_channels(C) (32 or 64).  The conv is then a stride-1 4x4 conv whose input
+ * rows are staged once in shared memory and reused by every tap (csrc/stem_win.cuh).  H and W must be even,
+ * W/2 <= 125, 4*C <= 64, Co <= 64; anything else: use sfb_layout_input + sfb_conv_gemm / sfb_conv_wgrad. */
+int sfb_stem_s2d_channels(int32_t C);
+/* replaces: train.py:136-140 (_prepare_slowfast_data) feeding the stem: fp32 strided NCTHW -> s2d bf16 */
+int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw,
+                         int32_t N, int32_t C, int32_t T, int32_t H, int32_t W, void* out, int32_t Cs, void* stream);
+/* fp32 (Co, Ci, 1, 7, 7) -> bf16 [rows_pad][16*Cs]; rows_pad = 16 / 32 / 64 (Co rounded up) */
+int sfb_pack_weight_stem(const float* w, int32_t Co, int32_t Ci, int32_t Cs, void* wp, int32_t rows_pad, void* stream);
+/* y[N,T,H2,W2,Co] (view o_ld/o_coff) = conv(x) ; stats as in SfbEpilogue.stats (may be NULL) */
+int sfb_stem_conv_fprop(const void* xs2d, int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs,
+                        const void* wp, int32_t rows_pad, void* out, int32_t o_ld, int32_t o_coff, int32_t Co,
+                        float* stats, void* stream);
+/* dw (fp32, (Co, Ci, 1, 7, 7), accumulated) += wgrad */
+int sfb_stem_conv_wgrad(const void* xs2d, int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs,
+                        const void* dy, int32_t dy_ld, int32_t dy_coff, int32_t Co, float* dw, void* stream);
+
 /* replaces: nn.BatchNorm3d training statistics finalisation + running-stat update.
  * stats = [sum(C), sumsq(C)] over `count` elements per channel.
  * scale = gamma*invstd, shift = beta - mean*scale; save_mean/save_invstd kept for backward;

@@ -102,10 +102,11 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     plan = eng.build_plan(*shape, True)
     n_conv = len(eng.layers)
     assert n_conv == 2 + 4 + 16 * 2 * 3 + 4 * 2  # stems, laterals, 16 bottlenecks x 2 pathways x 3, 4 shortcuts x 2
+    # the two stems run as space-to-depth row-window kernels, everything else as the generic implicit GEMM
     convs = [op for op in plan.fwd if op[0] is lib.sfb_conv_gemm]
-    assert len(convs) == n_conv
+    assert len(convs) == n_conv - 2 and len([op for op in plan.fwd if op[0] is lib.sfb_stem_conv_fprop]) == 2
     wgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_wgrad]
-    assert len(wgrads) == n_conv
+    assert len(wgrads) == n_conv - 2 and len([op for op in plan.bwd if op[0] is lib.sfb_stem_conv_wgrad]) == 2
     dgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_gemm]
     assert len(dgrads) == n_conv - 2  # the stems need no input gradient
     assert tuple(plan.logits.shape) == (shape[0], 249)

@@ -227,6 +227,70 @@ def test_conv_wgrad(case, impl_name, impl):
     assert r["err"] < 2e-2, r
 
 
+# ------------------------------------------------------------------ stem (1,7,7)/s(1,2,2) in space-to-depth form
+# N, T, H, W, Ci, Co
+STEM_CASES = [
+    (1, 2, 32, 32, 5, 64),      # slow stem, REF 64^2 crop
+    (2, 3, 64, 64, 15, 8),      # fast stem
+    (1, 2, 224, 224, 15, 8),    # headline size: 112 output pixels per row
+    (1, 1, 128, 128, 5, 64),
+    (1, 3, 48, 250, 3, 16),     # widest supported row (125 pixels), CANON channel count
+    (3, 1, 20, 36, 2, 24),      # reference's (5, 2) channel variant (new_feature_test.py:715)
+]
+
+
+def _stem_inputs(N, T, H, W, Ci, Co, seed=0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    base = torch.randn((N, T, Ci + 3, H, W), device=DEV, generator=g)
+    x = base.permute(0, 2, 1, 3, 4)[:, 2:2 + Ci]  # non-contiguous NCTHW view like train.py:136-140
+    w = torch.randn((Co, Ci, 1, 7, 7), device=DEV, generator=g) / (Ci * 49) ** 0.5
+    return x, w
+
+
+@pytest.mark.parametrize("N,T,H,W,Ci,Co", STEM_CASES)
+def test_stem_s2d_layout_and_fprop(N, T, H, W, Ci, Co):
+    x, w = _stem_inputs(N, T, H, W, Ci, Co)
+    assert ops.stem_s2d_eligible(Ci, Co, (1, 7, 7), (1, 2, 2), (0, 3, 3), H, W)
+    xs = ops.layout_input_s2d(x)
+    cs = xs.shape[-1]
+    # layout: channel (sh*2+sw)*Ci + c of s2d pixel (h, w) = x[c, 2h+sh, 2w+sw]
+    ref_l = torch.zeros_like(xs, dtype=torch.float32)
+    for sh in range(2):
+        for sw in range(2):
+            q = sh * 2 + sw
+            ref_l[..., q * Ci:(q + 1) * Ci] = x[:, :, :, sh::2, sw::2].permute(0, 2, 3, 4, 1).bfloat16().float()
+    assert torch.equal(xs.float(), ref_l)
+    wp = ops.pack_weight_stem(w.contiguous())
+    out = Act.empty(N, T, H // 2, W // 2, Co + 16, coff=8, C=Co, zero=True)
+    stats = torch.zeros(2 * Co, device=DEV)
+    ops.stem_conv_fprop(xs, Ci, wp, out, stats)
+    torch.cuda.synchronize()
+    ref = F.conv3d(x.bfloat16().float(), w.bfloat16().float(), stride=(1, 2, 2), padding=(0, 3, 3))
+    got = kc.from_act(out)
+    assert kc.relerr(got, ref) < 1e-2
+    assert float(out.buf[..., :8].abs().max()) == 0.0 and float(out.buf[..., 8 + Co:].abs().max()) == 0.0
+    cnt = ref.numel() / Co
+    gq = got  # statistics are taken from the stored (bf16-rounded) values
+    torch.testing.assert_close(stats[:Co] / cnt, gq.mean(dim=(0, 2, 3, 4)), rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(stats[Co:] / cnt, (gq * gq).mean(dim=(0, 2, 3, 4)), rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("N,T,H,W,Ci,Co", STEM_CASES)
+def test_stem_s2d_wgrad(N, T, H, W, Ci, Co):
+    x, w = _stem_inputs(N, T, H, W, Ci, Co, seed=1)
+    xs = ops.layout_input_s2d(x)
+    g = torch.Generator(device=DEV).manual_seed(5)
+    dy = torch.randn((N, Co, T, H // 2, W // 2), device=DEV, generator=g)
+    dya = kc.to_act(dy, ld=Co + 8, coff=8)
+    wz = torch.zeros_like(w, requires_grad=True)
+    F.conv3d(x.bfloat16().float(), wz, stride=(1, 2, 2), padding=(0, 3, 3)).backward(kc.from_act(dya))
+    dw = torch.zeros_like(w)
+    ops.stem_conv_wgrad(xs, Ci, dya, dw)
+    ops.stem_conv_wgrad(xs, Ci, dya, dw)  # accumulates
+    torch.cuda.synchronize()
+    assert kc.relerr(dw, 2 * wz.grad) < 2e-2
+
+
 def test_bad_args_rejected():
     x = Act.empty(1, 2, 4, 4, 12)  # 12 channels: not a multiple of 8
     w = torch.empty(64, 64, dtype=torch.bfloat16, device=DEV)

@@ -26,6 +26,10 @@ LAYERS = [
     ("stem_fast", "wgrad", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
     ("stem_slow", "fprop_stats", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
     ("stem_slow", "wgrad", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
+    ("stem_fast", "s2d_fprop", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
+    ("stem_fast", "s2d_wgrad", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
+    ("stem_slow", "s2d_fprop", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
+    ("stem_slow", "s2d_wgrad", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
     ("slow_res2_c_64_256", "fprop_stats", 8, 56, 56, 64, 256, (1, 1, 1), (1, 1, 1)),
     ("slow_res2_c_64_256", "dgrad", 8, 56, 56, 64, 256, (1, 1, 1), (1, 1, 1)),
     ("slow_res2_c_64_256", "wgrad", 8, 56, 56, 64, 256, (1, 1, 1), (1, 1, 1)),
@@ -70,7 +74,20 @@ def run_layer(N, spec, reps):
     flops = 2.0 * M * Co * Ci * taps
     in_b, out_b = N * T * H * W * Ci * 2, M * Co * 2
     xg = Act(x.buf, 0, r16(Ci))
-    if kind in ("fprop", "fprop_stats"):
+    if kind in ("s2d_fprop", "s2d_wgrad"):
+        xf = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
+        xs = ops.layout_input_s2d(xf)
+        del xf
+        yv = Act(y.buf[..., :Co].contiguous(), 0, Co)  # the engine keeps the stem output unpadded (ld = Co)
+        if kind == "s2d_fprop":
+            wp = ops.pack_weight_stem(w)
+            stats = torch.zeros(2 * Co, device=DEV)
+            fn = lambda: ops.stem_conv_fprop(xs, Ci, wp, yv, stats)
+        else:
+            dw = torch.zeros((Co, Ci) + k, device=DEV)
+            fn = lambda: ops.stem_conv_wgrad(xs, Ci, yv, dw)
+        bytes_ = in_b + out_b
+    elif kind in ("fprop", "fprop_stats"):
         wp = ops.pack_weight(w, xg.C)
         stats = torch.zeros(2 * Co, device=DEV) if kind == "fprop_stats" else None
         fn = lambda: ops.conv_gemm(xg, wp, y, k, s, p, stats=stats)

@@ -54,12 +54,17 @@ SIGNATURES = {
     "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
     "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_fc_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
+    "sfb_layout_input_s2d": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
+    "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
+    "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
+    "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
 }
 _SPECIAL = {
     "sfb_strerror": ([_i32], C.c_char_p),
     "sfb_last_cuda_error": ([], C.c_char_p),
     "sfb_version": ([], _i32),
     "sfb_launch_count": ([], _i64),
+    "sfb_stem_s2d_channels": ([_i32], _i32),
 }
 ALL_SYMBOLS = sorted(list(SIGNATURES) + list(_SPECIAL))
 

@@ -70,12 +70,20 @@ struct ConvTmaParams {
   int res_ld, res_coff;
   int epi_relu;
   float* stats;                // [2*Co] or null
+  int reduce_add;              // 1: the TMA store is a reduce-add into the output (in-place gradient accumulation)
 };
 
 __device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int32_t c0, int32_t c1, int32_t c2,
                                              int32_t c3, int32_t c4) {
   asm volatile(
       "cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+      ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_5d(const void* tmap, uint32_t smem_src, int32_t c0, int32_t c1, int32_t c2,
+                                                  int32_t c3, int32_t c4) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.5d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
       ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
@@ -102,11 +110,16 @@ struct ConvTmaCfg {
   static constexpr int kHolderOff = kBarOff + (2 * kStages + 4) * 8;
   static constexpr int kEnd = kHolderOff + 16;
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  // epilogue warps: one per (TMEM lane quadrant, 32-column slice of a staged chunk).  With a single warp per SM
+  // sub-partition the epilogue was dependency-stall bound (ncu r1b: 38 % "wait", 21 % issuing, 1 warp / scheduler).
+  static constexpr int kEpiWarps = kChunk / 8;        // 16 (BN >= 128), 8 (BN = 64), 4 (BN = 32)
+  static constexpr int kEpiThreads = 32 * kEpiWarps;
+  static constexpr int kThreads = 64 + kEpiThreads;
   static size_t smem_bytes() { return 1024 + kEnd; }
 };
 
 template <int BN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(ConvTmaCfg<BN>::kThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                 const __grid_constant__ CUtensorMap tmap_o, const ConvTmaParams p) {
   using L = ConvTmaCfg<BN>;
@@ -130,7 +143,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull_bar[b], 1);
-      mbar_init(&tempty_bar[b], 4);
+      mbar_init(&tempty_bar[b], L::kEpiWarps);
     }
     mbar_fence_init();
   }
@@ -242,11 +255,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     // BatchNorm statistics are column sums of the staged (bf16-rounded) tile, kept in registers across all tiles.
     constexpr int CH = L::kChunk;
     constexpr int NCH = L::kChunks;
+    constexpr int ET = L::kEpiThreads;
     constexpr int PAIRS = CH / 2;        // bf16x2 column pairs per staged chunk
-    constexpr int TPP = 128 / PAIRS;     // threads sharing one column pair (they split the rows)
-    const int q4 = warp & 3;
-    const int r = q4 * 32 + lane;
+    constexpr int TPP = ET / PAIRS;      // threads sharing one column pair (they split the rows)
+    const int q4 = warp & 3;             // TMEM lane quadrant this warp may read
     const int te = tid - 64;
+    const int cslice = (warp - 2) >> 2;  // 32-column slice of the chunk
+    const int r = q4 * 32 + lane;
     const int ww = r % p.Wt;
     const int hh = (r / p.Wt) % p.Ht;
     const int tq = r / (p.Wt * p.Ht);
@@ -283,41 +298,41 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int col0 = n0 + ch * CH;
           // (A) the previous TMA store must have finished reading the staging tile
           if (te == 0 && store_pending) tma_store_wait_read();
-          named_bar_sync(1, 128);
-          // (B) accumulator -> staging
-#pragma unroll 1
-          for (int cc = 0; cc < CH / 32; ++cc) {
-            const int nb = col0 + cc * 32;
-            if (nb >= p.Co) break;
-            float v[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cc * 32), v);
-            tmem_ld_wait();
+          named_bar_sync(1, ET);
+          // (B) accumulator -> staging: this warp's 32-column slice
+          {
+            const int nb = col0 + cslice * 32;
+            if (nb < p.Co) {
+              float v[32];
+              tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
+              tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int nn = nb + j * 8;
-              if (nn < p.Co) {
-                float* f = v + j * 8;
-                if (p.epi_scale) {
+              for (int j = 0; j < 4; ++j) {
+                const int nn = nb + j * 8;
+                if (nn < p.Co) {
+                  float* f = v + j * 8;
+                  if (p.epi_scale) {
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+                    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+                  }
+                  if (rrow && mv) {
+                    float rf[8];
+                    unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] += rf[i];
+                  }
+                  if (p.epi_relu) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+                  }
+                  uint4 pk = pack8(f);
+                  if (!mv) pk = make_uint4(0, 0, 0, 0);
+                  const int cl = cslice * 32 + j * 8;        // column inside the chunk
+                  const int gsub = cl / ocols;
+                  uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl - gsub * ocols) * 2);
+                  addr ^= ((addr >> 7) & swz) << 4;
+                  sts_v4(addr, pk);
                 }
-                if (rrow && mv) {
-                  float rf[8];
-                  unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
-#pragma unroll
-                  for (int i = 0; i < 8; ++i) f[i] += rf[i];
-                }
-                if (p.epi_relu) {
-#pragma unroll
-                  for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
-                }
-                uint4 pk = pack8(f);
-                if (!mv) pk = make_uint4(0, 0, 0, 0);
-                const int cl = cc * 32 + j * 8;            // column inside the chunk
-                const int gsub = cl / ocols;
-                uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl - gsub * ocols) * 2);
-                addr ^= ((addr >> 7) & swz) << 4;
-                sts_v4(addr, pk);
               }
             }
           }
@@ -329,11 +344,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           }
           // (D) staged tile -> global memory (TMA clips rows/columns outside the tensor)
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(1, ET);
           if (te == 0) {
             const int nsub = (min(CH, p.Co - col0) + ocols - 1) / ocols;
-            for (int gsub = 0; gsub < nsub; ++gsub)
-              tma_store_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
+            for (int gsub = 0; gsub < nsub; ++gsub) {
+              if (p.reduce_add) tma_reduce_add_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
+              else tma_store_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
+            }
             tma_store_commit();
             store_pending = true;
           }

@@ -4,11 +4,13 @@
 #include "conv_simt.cuh"
 #include "conv_tma.cuh"
 #include "wgrad_tma.cuh"
+#include "stem_win.cuh"
 #include "elementwise.cuh"
 
 #include <array>
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -23,6 +25,7 @@ std::atomic<long long> g_launches{0};
 
 int cuda_fail(cudaError_t e, const char* where) {
   snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", where, cudaGetErrorString(e));
+  (void)cudaGetLastError();  // non-sticky errors must not leak into the next call's launch check
   return SFB_ERR_CUDA;
 }
 #define SFB_CHECK_LAUNCH(where)                         \
@@ -156,6 +159,88 @@ int get_act_tmap(const void* base, int C, int W, int H, int T, int N, int ld, in
   return SFB_OK;
 }
 
+
+// ---- generic tiled tensor map (rank <= 5, element strides 1), cached ----
+std::map<std::array<long long, 20>, CUtensorMap> g_gen_tmaps;
+int get_tmap_generic(const void* base, int rank, const long long* dims, const long long* strides_bytes, const int* box,
+                     int swizzle_bytes, CUtensorMap* out) {
+  std::lock_guard<std::mutex> lk(g_mu);
+  std::array<long long, 20> key;
+  key.fill(0);
+  key[0] = (long long)(uintptr_t)base; key[1] = rank; key[2] = swizzle_bytes;
+  for (int i = 0; i < rank; ++i) { key[3 + i] = dims[i]; key[8 + i] = i + 1 < rank ? strides_bytes[i] : 0; key[13 + i] = box[i]; }
+  auto it = g_gen_tmaps.find(key);
+  if (it != g_gen_tmaps.end()) { *out = it->second; return SFB_OK; }
+  int rc = ensure_encode();
+  if (rc) return rc;
+  cuuint64_t gdim[5]; cuuint64_t gstr[4]; cuuint32_t bx[5]; cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = (cuuint64_t)dims[i]; bx[i] = (cuuint32_t)box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = (cuuint64_t)strides_bytes[i];
+  const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUtensorMap tm;
+  CUresult r = g_encode(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "cuTensorMapEncodeTiled(generic rank %d, box0 %d, swizzle %d) failed: %d", rank,
+             box[0], swizzle_bytes, (int)r);
+    return SFB_ERR_DRIVER;
+  }
+  if (g_gen_tmaps.size() > 4096) g_gen_tmaps.clear();
+  g_gen_tmaps[key] = tm;
+  *out = tm;
+  return SFB_OK;
+}
+
+constexpr size_t kMaxSmem = 227 * 1024;
+int stem_bn(int Co) { return Co <= 16 ? 16 : (Co <= 32 ? 32 : 64); }
+// Measured on B200 (tests/test_kernels_gpu.py::test_stem_s2d_*): tcgen05.mma applies the 32/64/128-byte swizzle XOR
+// to ABSOLUTE shared-memory address bits, so a window whose start is shifted by whole pixels (not a multiple of the
+// 8-row swizzle period) needs NO descriptor "base offset"; setting base_offset = (addr >> 7) & 7 gives wrong results.
+int stem_base_off_mode() { return 0; }
+
+template <int BN, int CS>
+int launch_stem_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const StemParams& p, int grid, cudaStream_t st) {
+  const size_t smem = StemFpropCfg<BN>::smem_bytes(p.Cs);
+  if (smem > kMaxSmem) return SFB_ERR_UNSUPPORTED;
+  static size_t attr_bytes = 0;
+  if (smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(stem_fprop_kernel<BN, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(stem_fprop)");
+    attr_bytes = smem;
+  }
+  stem_fprop_kernel<BN, CS><<<grid, 192, smem, st>>>(tx, tw, p);
+  SFB_CHECK_LAUNCH("stem_fprop_kernel");
+  return SFB_OK;
+}
+
+template <int BN, int CS>
+int launch_stem_wgrad(const CUtensorMap& tx, const CUtensorMap& tdy, const StemParams& p, int grid, cudaStream_t st) {
+  const size_t smem = 1024 + (size_t)kStemSlots * 128 * p.Cs * 2 + 1024 + (size_t)kStemDySlots * 128 * BN * 2 + 512;
+  if (smem > kMaxSmem || 4 * (p.Cs / 32) * BN > 512) return SFB_ERR_UNSUPPORTED;
+  static size_t attr_bytes = 0;
+  if (smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(stem_wgrad_kernel<BN, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(stem_wgrad)");
+    attr_bytes = smem;
+  }
+  stem_wgrad_kernel<BN, CS><<<grid, 192, smem, st>>>(tx, tdy, p);
+  SFB_CHECK_LAUNCH("stem_wgrad_kernel");
+  return SFB_OK;
+}
+
+int stem_check(int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs, int32_t Co) {
+  if (N <= 0 || T <= 0 || H2 <= 0 || W2 <= 0 || Ci <= 0 || Co <= 0 || (Co & 7)) return SFB_ERR_BAD_ARG;
+  if (Cs != 32 && Cs != 64) return SFB_ERR_BAD_ARG;
+  if (4 * Ci > Cs) return SFB_ERR_BAD_ARG;
+  if (W2 > 125 || Co > 64) return SFB_ERR_UNSUPPORTED;
+  if (Cs == 64 && Co > 32) return SFB_ERR_UNSUPPORTED;  // ring + weights would not fit 227 KB of shared memory
+  if ((long long)N * T * H2 >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+  return SFB_OK;
+}
+
 int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms == 0) {
@@ -209,7 +294,7 @@ int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensor
   if (per_nt < 1) per_nt = 1;
   if (per_nt > p.total_patches) per_nt = p.total_patches;
   const int grid = (int)per_nt * p.n_tiles;
-  conv_tma_kernel<BN><<<grid, 192, L::smem_bytes(), st>>>(ta, tw, to, p);
+  conv_tma_kernel<BN><<<grid, L::kThreads, L::smem_bytes(), st>>>(ta, tw, to, p);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
@@ -292,6 +377,110 @@ int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t
   return SFB_OK;
 }
 
+
+int sfb_stem_s2d_channels(int32_t Ci) {
+  if (Ci <= 0 || 4 * Ci > 64) return SFB_ERR_UNSUPPORTED;
+  return 4 * Ci <= 32 ? 32 : 64;
+}
+
+int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw, int32_t N, int32_t C,
+                         int32_t T, int32_t H, int32_t W, void* out, int32_t Cs, void* stream) {
+  if (!x || !out || N <= 0 || C <= 0 || T <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1) || !aligned16(out)) return SFB_ERR_BAD_ARG;
+  if ((Cs != 32 && Cs != 64) || 4 * C > Cs) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)N * T * (H / 2) * (W / 2) * (Cs / 8);
+  layout_input_s2d_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(
+      x, sn, sc, st, sh, sw, N, C, T, H / 2, W / 2, (__nv_bfloat16*)out, Cs);
+  SFB_CHECK_LAUNCH("layout_input_s2d_kernel");
+  return SFB_OK;
+}
+
+int sfb_pack_weight_stem(const float* w, int32_t Co, int32_t Ci, int32_t Cs, void* wp, int32_t rows_pad, void* stream) {
+  if (!w || !wp || Co <= 0 || Ci <= 0 || (Cs != 32 && Cs != 64) || 4 * Ci > Cs || rows_pad < Co) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)rows_pad * 16 * Cs;
+  pack_weight_stem_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, Co, Ci, Cs, (__nv_bfloat16*)wp, rows_pad);
+  SFB_CHECK_LAUNCH("pack_weight_stem_kernel");
+  return SFB_OK;
+}
+
+int sfb_stem_conv_fprop(const void* xs2d, int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs,
+                        const void* wp, int32_t rows_pad, void* out, int32_t o_ld, int32_t o_coff, int32_t Co,
+                        float* stats, void* stream) {
+  int rc = stem_check(N, T, H2, W2, Ci, Cs, Co);
+  if (rc) return rc;
+  if (!xs2d || !wp || !out || !aligned16(xs2d) || !aligned16(wp) || !aligned16(out)) return SFB_ERR_BAD_ARG;
+  if ((o_ld & 7) || (o_coff & 7) || o_coff + Co > o_ld) return SFB_ERR_BAD_ARG;
+  const int bn = stem_bn(Co);
+  if (rows_pad != bn) return SFB_ERR_BAD_ARG;
+  const long long F = (long long)N * T;
+  CUtensorMap tx, tw;
+  const long long xd[4] = {Cs, W2, H2, F};
+  const long long xs[3] = {(long long)Cs * 2, (long long)W2 * Cs * 2, (long long)H2 * W2 * Cs * 2};
+  const int xb[4] = {Cs, 128, 1, 1};
+  rc = get_tmap_generic(xs2d, 4, xd, xs, xb, Cs * 2, &tx);
+  if (rc) return rc;
+  const long long wd[2] = {16ll * Cs, bn};
+  const long long ws[1] = {16ll * Cs * 2};
+  const int wb[2] = {64, bn};
+  rc = get_tmap_generic(wp, 2, wd, ws, wb, 128, &tw);
+  if (rc) return rc;
+  StemParams p;
+  memset(&p, 0, sizeof(p));
+  p.F = (int)F; p.Ho = H2; p.Wo = W2; p.Cs = Cs; p.Co = Co; p.o_ld = o_ld; p.o_coff = o_coff; p.Ci = Ci;
+  p.total_tiles = (int)(F * H2);
+  int grid = num_sms();
+  if (grid > p.total_tiles) grid = p.total_tiles;
+  p.tiles_per_cta = (p.total_tiles + grid - 1) / grid;
+  grid = (p.total_tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;
+  p.base_off_mode = stem_base_off_mode();
+  p.out = (__nv_bfloat16*)out; p.stats = stats;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (Cs == 64) return bn == 16 ? launch_stem_fprop<16, 64>(tx, tw, p, grid, st) : launch_stem_fprop<32, 64>(tx, tw, p, grid, st);
+  switch (bn) {
+    case 16: return launch_stem_fprop<16, 32>(tx, tw, p, grid, st);
+    case 32: return launch_stem_fprop<32, 32>(tx, tw, p, grid, st);
+    default: return launch_stem_fprop<64, 32>(tx, tw, p, grid, st);
+  }
+}
+
+int sfb_stem_conv_wgrad(const void* xs2d, int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs,
+                        const void* dy, int32_t dy_ld, int32_t dy_coff, int32_t Co, float* dw, void* stream) {
+  int rc = stem_check(N, T, H2, W2, Ci, Cs, Co);
+  if (rc) return rc;
+  if (!xs2d || !dy || !dw || !aligned16(xs2d) || !aligned16(dy)) return SFB_ERR_BAD_ARG;
+  if ((dy_ld & 7) || (dy_coff & 7) || dy_coff + Co > dy_ld) return SFB_ERR_BAD_ARG;
+  const int bn = stem_bn(Co);
+  const long long F = (long long)N * T;
+  CUtensorMap tx, tdy;
+  const long long xd[4] = {Cs, W2, H2, F};
+  const long long xs[3] = {(long long)Cs * 2, (long long)W2 * Cs * 2, (long long)H2 * W2 * Cs * 2};
+  const int xb[4] = {Cs, 128, 1, 1};
+  rc = get_tmap_generic(xs2d, 4, xd, xs, xb, Cs * 2, &tx);
+  if (rc) return rc;
+  const long long dd[4] = {Co, W2, H2, F};
+  const long long ds[3] = {(long long)dy_ld * 2, (long long)W2 * dy_ld * 2, (long long)H2 * W2 * dy_ld * 2};
+  const int db[4] = {bn, 128, 1, 1};
+  rc = get_tmap_generic((const __nv_bfloat16*)dy + dy_coff, 4, dd, ds, db, bn * 2, &tdy);
+  if (rc) return rc;
+  StemParams p;
+  memset(&p, 0, sizeof(p));
+  p.F = (int)F; p.Ho = H2; p.Wo = W2; p.Cs = Cs; p.Co = Co; p.Ci = Ci;
+  p.total_tiles = (int)(F * H2);
+  int grid = num_sms();
+  if (grid > p.total_tiles) grid = p.total_tiles;
+  p.tiles_per_cta = (p.total_tiles + grid - 1) / grid;
+  grid = (p.total_tiles + p.tiles_per_cta - 1) / p.tiles_per_cta;
+  p.ksteps = (W2 + 15) / 16;
+  p.base_off_mode = stem_base_off_mode();
+  p.dW = dw;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (Cs == 64) return bn == 16 ? launch_stem_wgrad<16, 64>(tx, tdy, p, grid, st) : launch_stem_wgrad<32, 64>(tx, tdy, p, grid, st);
+  switch (bn) {
+    case 16: return launch_stem_wgrad<16, 32>(tx, tdy, p, grid, st);
+    case 32: return launch_stem_wgrad<32, 32>(tx, tdy, p, grid, st);
+    default: return launch_stem_wgrad<64, 32>(tx, tdy, p, grid, st);
+  }
+}
+
 int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro, const void* wp, int32_t rows_pad,
                   int32_t k_pad, void* out, const SfbEpilogue* epi, int32_t impl, void* stream) {
   int rc = check_geom(geom);
@@ -368,6 +557,11 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     q.ocols = geom->Co >= 64 ? 64 : (geom->Co >= 32 ? 32 : (geom->Co >= 16 ? 16 : 8));
     q.out = p.out; q.epi_scale = p.epi_scale; q.epi_shift = p.epi_shift; q.res = p.res; q.res_ld = p.res_ld;
     q.res_coff = p.res_coff; q.epi_relu = p.epi_relu; q.stats = p.stats;
+    // in-place accumulation (dX += dgrad): no residual read in the SM, the TMA store becomes a bf16 reduce-add in L2
+    if (q.res == p.out && q.res_ld == geom->o_ld && q.res_coff == geom->o_coff && !q.epi_scale && !q.epi_relu && !q.stats) {
+      q.reduce_add = 1;
+      q.res = nullptr;
+    }
     CUtensorMap ta;
     const int sW = geom->transposed ? 1 : q.sW, sH = geom->transposed ? 1 : q.sH, sT = geom->transposed ? 1 : q.sT;
     rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,

@@ -21,6 +21,7 @@ import torch.nn as nn
 
 from . import _ffi
 from ._ffi import ConvGeom, Epilogue, Prologue, lib
+from . import ops as _ops
 from .ops import Act, conv_out_dims, round_up
 
 
@@ -71,6 +72,8 @@ class ConvL:
         self.taps = self.k[0] * self.k[1] * self.k[2]
         self.needs_dgrad = needs_dgrad
         self.wp = self.wpt = None
+        self.wps = None  # stems: space-to-depth packing for the row-window kernels (csrc/stem_win.cuh)
+        self.is_stem = False
         self.packed_version = -1
         # set by the engine
         self.stats = self.scale = self.shift = self.mean = self.invstd = None
@@ -145,6 +148,8 @@ class SlowFastEngine:
             st = m.blocks[0].multipathway_blocks[p]
             self.stems.append(ConvL(f"blocks.0.multipathway_blocks.{p}", st.conv, st.norm, needs_dgrad=False,
                                     conv_name=f"blocks.0.multipathway_blocks.{p}.conv"))
+        for st_ in self.stems:
+            st_.is_stem = True
         L += self.stems
         self.laterals: List[Optional[ConvL]] = []
         for si in range(5):
@@ -236,6 +241,11 @@ class SlowFastEngine:
             rp, kp = _ffi.packed_weight_dims(l.Co, l.Cg, l.taps)
             if l.wp is None:
                 l.wp = torch.empty((rp, kp), dtype=torch.bfloat16, device=self.dev)
+            s2d_ok = l.is_stem and l.k == (1, 7, 7) and l.s == (1, 2, 2) and l.p == (0, 3, 3) and \
+                _ops.stem_s2d_eligible(l.Ci, l.Co, l.k, l.s, l.p, 2, 2)
+            if s2d_ok and l.wps is None:
+                cs = 32 if 4 * l.Ci <= 32 else 64
+                l.wps = torch.empty((_ops.stem_rows_pad(l.Co), 16 * cs), dtype=torch.bfloat16, device=self.dev)
             if self.dry_run:
                 rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
                 l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
@@ -246,6 +256,9 @@ class SlowFastEngine:
                 wd = wd.contiguous()
             _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cg, 0, l.wp.data_ptr(), rp, kp, self.stream),
                        "sfb_pack_weight")
+            if l.wps is not None:
+                _ffi.check(self.lib.sfb_pack_weight_stem(wd.data_ptr(), l.Co, l.Ci, l.wps.shape[1] // 16, l.wps.data_ptr(),
+                                                         l.wps.shape[0], self.stream), "sfb_pack_weight_stem")
             if training and l.needs_dgrad:
                 rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
                 if l.wpt is None:
@@ -382,11 +395,21 @@ class SlowFastEngine:
         cat_bufs = {}
         for p in range(2):
             L = self.stems[p]
-            x_in = new_act(N, T_in[p], H, W, L.Ci)
-            plan.x_in.append(x_in)
             To, Ho, Wo = conv_out_dims((T_in[p], H, W), L.k, L.s, L.p)
             y0 = new_act(N, To, Ho, Wo, L.Co, pad=False)  # biggest tensors of the net: consumed by the pool only
-            self._conv(plan, fwd, L, x_in, None, y0, stats=training)
+            if L.wps is not None and _ops.stem_s2d_eligible(L.Ci, L.Co, L.k, L.s, L.p, H, W):
+                # space-to-depth clip + row-window kernel: every input row is staged once for all 49 taps
+                cs = L.wps.shape[1] // 16
+                x_in = torch.empty((N, T_in[p], H // 2, W // 2, cs), dtype=torch.bfloat16, device=dev)
+                plan.act_bytes += x_in.numel() * 2
+                plan.x_in.append(x_in)
+                self._emit(fwd, self.lib.sfb_stem_conv_fprop, x_in.data_ptr(), N, T_in[p], H // 2, W // 2, L.Ci, cs,
+                           L.wps.data_ptr(), L.wps.shape[0], y0.ptr(), y0.ld, y0.coff, L.Co,
+                           L.stats.data_ptr() if training else 0, self.stream, tag=(L.conv_name + ".y", y0))
+            else:
+                x_in = new_act(N, T_in[p], H, W, L.Ci)
+                plan.x_in.append(x_in)
+                self._conv(plan, fwd, L, x_in, None, y0, stats=training)
             self._bn_stats_ready(plan, fwd, L, y0.M, training)
             Hp, Wp = (Ho - 1) // 2 + 1, (Wo - 1) // 2 + 1
             if p == 0 and self.laterals[0] is not None:
@@ -613,7 +636,14 @@ class SlowFastEngine:
             self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
                        dz0.ptr(), dz0.ld, dz0.coff, self.stream)
             self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
-            self._wgrad(plan, bwd, L, sr["x_in"], None, dz0)
+            if isinstance(sr["x_in"], Act):
+                self._wgrad(plan, bwd, L, sr["x_in"], None, dz0)
+            else:
+                xs2 = sr["x_in"]
+                self._emit(bwd, self.lib.sfb_stem_conv_wgrad, xs2.data_ptr(), xs2.shape[0], xs2.shape[1], xs2.shape[2],
+                           xs2.shape[3], L.Ci, xs2.shape[4], dz0.ptr(), dz0.ld, dz0.coff, L.Co, L.dw.data_ptr(), self.stream)
+                if self.ddp is not None:
+                    self.ddp.note_grad_ready(plan, bwd, L.conv.weight)
             pool.release(dz0.buf)
             pool.release(out.cat.dcat.buf if out.cat is not None else g.buf)
             plan.keep.append(sr["idx"])
@@ -660,6 +690,10 @@ class SlowFastEngine:
                 gf = 2.0 * M * g.real_n * g.real_k / 1e9
                 desc = (f"{kind} in({g.Ti},{g.Hi},{g.Wi})x{g.Cg} out({g.To},{g.Ho},{g.Wo})x{g.Co} "
                         f"k({g.kT},{g.kH},{g.kW}) s({g.sT},{g.sH},{g.sW})")
+            if name in ("sfb_stem_conv_fprop", "sfb_stem_conv_wgrad"):
+                ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])
+                gf = 2.0 * args[1] * args[2] * args[3] * args[4] * co * ci * 49 / 1e9
+                desc = f"stem s2d in({args[2]},{2 * args[3]},{2 * args[4]})x{ci} out x{co} k(1,7,7) s(1,2,2)"
             rows.append((name, desc, e0.elapsed_time(e1), gf))
         return rows
 
@@ -679,6 +713,9 @@ class SlowFastEngine:
                 # algorithmic work: rows of the forward conv's OUTPUT (for dgrad that is the gathered tensor dY)
                 M = g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo
                 flops[key] = flops.get(key, 0.0) + 2.0 * M * g.real_n * g.real_k
+            if name in ("sfb_stem_conv_fprop", "sfb_stem_conv_wgrad"):
+                ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])
+                flops[name] = flops.get(name, 0.0) + 2.0 * args[1] * args[2] * args[3] * args[4] * co * ci * 49
             n, t = out.get(key, (0, 0.0))
             out[key] = (n + 1, t + ms)
         return out, flops
@@ -749,8 +786,12 @@ class SlowFastEngine:
         for x, a in zip((xs, xf), plan.x_in):
             N, Cc, T, H, W = x.shape
             sn, sc, st, sh, sw = x.stride()
-            _ffi.check(self.lib.sfb_layout_input(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, a.ptr(), a.ld, self.stream),
-                       "sfb_layout_input")
+            if isinstance(a, Act):
+                _ffi.check(self.lib.sfb_layout_input(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, a.ptr(), a.ld, self.stream),
+                           "sfb_layout_input")
+            else:
+                _ffi.check(self.lib.sfb_layout_input_s2d(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, a.data_ptr(),
+                                                         a.shape[4], self.stream), "sfb_layout_input_s2d")
         if training:
             plan.gen += 1
             self.stats_flat.zero_()

@@ -81,6 +81,60 @@ def pack_weight(w: torch.Tensor, Cg: int, transposed: bool = False, out: Optiona
     return out
 
 
+def stem_s2d_eligible(C_in, C_out, k, s, p, H, W) -> bool:
+    """can the (1,7,7)/s(1,2,2)/p(0,3,3) stem take the space-to-depth row-window kernels (csrc/stem_win.cuh)?"""
+    return (tuple(k) == (1, 7, 7) and tuple(s) == (1, 2, 2) and tuple(p) == (0, 3, 3) and H % 2 == 0 and W % 2 == 0
+            and W // 2 <= 125 and 4 * C_in <= 64 and C_out <= (64 if 4 * C_in <= 32 else 32) and C_out % 8 == 0)
+
+
+def stem_s2d_channels(C_in: int) -> int:
+    cs = lib().sfb_stem_s2d_channels(C_in)
+    if cs < 0:
+        check(cs, "sfb_stem_s2d_channels")
+    return cs
+
+
+def stem_rows_pad(C_out: int) -> int:
+    return 16 if C_out <= 16 else (32 if C_out <= 32 else 64)
+
+
+def layout_input_s2d(x: torch.Tensor) -> torch.Tensor:
+    """fp32 (N,C,T,H,W), arbitrary strides -> s2d bf16 (N,T,H/2,W/2,Cs)"""
+    assert x.dtype == torch.float32 and x.dim() == 5 and x.is_cuda
+    N, Cc, T, H, W = x.shape
+    cs = stem_s2d_channels(Cc)
+    out = torch.empty((N, T, H // 2, W // 2, cs), dtype=torch.bfloat16, device=x.device)
+    sn, sc, st, sh, sw = x.stride()
+    check(lib().sfb_layout_input_s2d(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, out.data_ptr(), cs, stream_ptr()),
+          "sfb_layout_input_s2d")
+    return out
+
+
+def pack_weight_stem(w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert w.dtype == torch.float32 and w.is_cuda and w.is_contiguous() and tuple(w.shape[2:]) == (1, 7, 7)
+    Co, Ci = w.shape[0], w.shape[1]
+    cs, rp = stem_s2d_channels(Ci), stem_rows_pad(Co)
+    if out is None:
+        out = torch.empty((rp, 16 * cs), dtype=torch.bfloat16, device=w.device)
+    check(lib().sfb_pack_weight_stem(w.data_ptr(), Co, Ci, cs, out.data_ptr(), rp, stream_ptr()), "sfb_pack_weight_stem")
+    return out
+
+
+def stem_conv_fprop(xs2d: torch.Tensor, Ci: int, wp: torch.Tensor, out: Act, stats: Optional[torch.Tensor] = None):
+    N, T, H2, W2, cs = xs2d.shape
+    check(lib().sfb_stem_conv_fprop(xs2d.data_ptr(), N, T, H2, W2, Ci, cs, wp.data_ptr(), wp.shape[0], out.ptr(), out.ld,
+                                    out.coff, out.C, ptr(stats), stream_ptr()), "sfb_stem_conv_fprop")
+    return out
+
+
+def stem_conv_wgrad(xs2d: torch.Tensor, Ci: int, dy: Act, dw: torch.Tensor):
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    N, T, H2, W2, cs = xs2d.shape
+    check(lib().sfb_stem_conv_wgrad(xs2d.data_ptr(), N, T, H2, W2, Ci, cs, dy.ptr(), dy.ld, dy.coff, dy.C, dw.data_ptr(),
+                                    stream_ptr()), "sfb_stem_conv_wgrad")
+    return dw
+
+
 def make_geom(x: Act, out: Act, k, s, p, transposed=False) -> ConvGeom:
     N, Ti, Hi, Wi = x.dims
     N2, To, Ho, Wo = out.dims
