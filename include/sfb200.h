@@ -90,6 +90,17 @@ int sfb_packed_weight_dims(int32_t Co, int32_t Cg, int32_t taps, int32_t* rows_p
 int sfb_pack_weight(const float* w, int32_t Co, int32_t Ci, int32_t taps, int32_t Cg,
                     int32_t transposed, void* wp, int32_t rows_pad, int32_t k_pad, void* stream);
 
+
+/* Operand of the input-gradient GEMM (sfb_conv_gemm with transposed=1, impl SFB_IMPL_TC).  A convolution with stride
+ * s splits its input gradient into s_T*s_H*s_W parity classes, each a stride-1 transposed conv over a subset of the
+ * taps (csrc/elementwise.cuh, DgradClass); the packed matrix is [rows_pad >= Ci][k_pad] with one contiguous,
+ * 64-padded K range per class (column = k0(class) + tap_in_class*Cg + co).  For stride 1 this is the layout of
+ * sfb_pack_weight(transposed=1).  SFB_IMPL_SIMT / SFB_IMPL_TC_GATHER keep taking sfb_pack_weight's tap-major layout. */
+int sfb_packed_weight_dims_dgrad(int32_t Ci, int32_t Cg, int32_t kT, int32_t kH, int32_t kW, int32_t sT, int32_t sH,
+                                 int32_t sW, int32_t* rows_pad, int32_t* k_pad);
+int sfb_pack_weight_dgrad(const float* w, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t sT,
+                          int32_t sH, int32_t sW, int32_t Cg, void* wp, int32_t rows_pad, int32_t k_pad, void* stream);
+
 /* replaces: train.py:136-140 (_prepare_slowfast_data permute + channel slices) feeding Conv3d.
  * fp32 tensor with arbitrary element strides (n,c,t,h,w) -> bf16 NDHWC, channels zero-padded to ld. */
 int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw,

@@ -54,6 +54,12 @@ CONV_CASES = [
     ("odd_3x1x1_16_48", 1, 7, 9, 10, 16, 48, (3, 1, 1), (1, 1, 1)),
     ("stem_slow_16_64", 2, 2, 64, 64, 16, 64, (1, 7, 7), (1, 2, 2)),
     ("ref_1x3x3_512_512_2x2", 2, 20, 2, 2, 512, 512, (1, 3, 3), (1, 1, 1)),
+    # strided convs of the Fast pathway / first lateral (16- and 32-channel dgrad operands) and odd sizes
+    ("fast_1x3x3_16_16_s2", 2, 8, 14, 14, 16, 16, (1, 3, 3), (1, 2, 2)),
+    ("fast_1x3x3_32_32_s2", 2, 4, 14, 14, 32, 32, (1, 3, 3), (1, 2, 2)),
+    ("lateral0_3x1x1_8_16_s4", 2, 16, 6, 6, 8, 16, (3, 1, 1), (4, 1, 1)),
+    ("odd_1x3x3_64_64_s2", 1, 3, 13, 11, 64, 64, (1, 3, 3), (1, 2, 2)),
+    ("fast_1x1x1_32_64_s2", 2, 4, 14, 14, 32, 64, (1, 1, 1), (1, 2, 2)),
 ]
 
 
@@ -119,7 +125,9 @@ def run_dgrad_case(case, impl, seed=0, accumulate=False):
     x = torch.zeros((N, Ci, T, H, W), device=DEV, requires_grad=True)
     F.conv3d(x, wq, stride=s, padding=p).backward(from_act(dya))
     ref = x.grad
-    wpt = ops.pack_weight(w.contiguous(), Co, transposed=True)
+    # the tensor-core path takes the class-major operand (one K range per stride parity class); the SIMT / gather
+    # cross-check kernels keep the tap-major layout
+    wpt = ops.pack_weight_dgrad(w.contiguous(), Co, s) if impl == _ffi.IMPL_TC else ops.pack_weight(w.contiguous(), Co, transposed=True)
     dx = Act.empty(N, T, H, W, Ci, zero=True)
     kw = {}
     if accumulate:

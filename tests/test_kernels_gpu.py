@@ -212,7 +212,7 @@ def test_conv_fprop_fused(case, variant, impl_name, impl):
 @pytest.mark.parametrize("impl_name,impl", IMPLS)
 @pytest.mark.parametrize("case", [c for c in kc.CONV_CASES if not c[0].startswith("stem")], ids=lambda c: c[0])
 def test_conv_dgrad(case, impl_name, impl):
-    r = kc.run_dgrad_case(case, impl, accumulate=(case[0] in ("1x1x1_64_256", "1x3x3_128_128_s2")))
+    r = kc.run_dgrad_case(case, impl, accumulate=(case[0] in ("1x1x1_64_256", "1x3x3_128_128_s2", "lateral0_3x1x1_8_16_s4", "fast_1x1x1_32_64_s2")))
     assert r["err"] < 1e-2, r
 
 

@@ -94,7 +94,7 @@ def run_layer(N, spec, reps):
         bytes_ = in_b + out_b
     elif kind in ("dgrad", "dgrad_acc"):
         yg = Act(y.buf, 0, r16(Co))
-        wpt = ops.pack_weight(w, yg.C, transposed=True)
+        wpt = ops.pack_weight_dgrad(w, yg.C, s)
         res = xg if kind == "dgrad_acc" else None
         fn = lambda: ops.conv_gemm(yg, wpt, xg, k, s, p, transposed=True, residual=res)
         bytes_ = in_b * (2 if res is not None else 1) + out_b

@@ -54,6 +54,8 @@ SIGNATURES = {
     "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
     "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_fc_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
+    "sfb_packed_weight_dims_dgrad": [_i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
+    "sfb_pack_weight_dgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_layout_input_s2d": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
@@ -108,6 +110,13 @@ def packed_weight_dims(Co, Cg, taps):
     r, k = _i32(), _i32()
     check(lib().sfb_packed_weight_dims(Co, Cg, taps, C.byref(r), C.byref(k)), "sfb_packed_weight_dims")
     return r.value, k.value
+
+
+def packed_weight_dims_dgrad(Ci, Cg, k, s):
+    r, kp = _i32(), _i32()
+    check(lib().sfb_packed_weight_dims_dgrad(Ci, Cg, k[0], k[1], k[2], s[0], s[1], s[2], C.byref(r), C.byref(kp)),
+          "sfb_packed_weight_dims_dgrad")
+    return r.value, kp.value
 
 
 def launch_count():

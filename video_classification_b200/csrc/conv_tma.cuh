@@ -58,6 +58,7 @@ struct ConvTmaParams {
   int box_k;                   // channels per A box: 64, 32 or 16
   int cchunks;                 // 64-channel chunks per tap (Cg > 64), else 1
   int taps, Ktot, nk;          // Ktot = taps*Cg ; nk = number of 64-wide K chunks of the packed weights
+  int wk0;                     // first K column of this launch inside the packed weights (strided-dgrad classes)
   int Wt, Ht, Tt;              // output patch of one M tile; Wt*Ht*Tt <= 128
   int tilesW, tilesH, tilesT;
   int n_tiles;                 // ceil(Co / BN); a CTA works on ONE N tile: blockIdx.x % n_tiles
@@ -210,7 +211,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
             tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], c0, cw, ch, ct, n);
           }
-          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], kc * 64, n0);
+          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
         }
       }
     }

@@ -72,6 +72,58 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, 
   }
 }
 
+
+// ---- strided dgrad: parity classes -----------------------------------------------------------------------
+// dX[o] = sum_k dY[(o + p - k)/s] W[k] over the taps with (o + p - k) % s == 0.  Per dimension the outputs split into
+// s classes r = (o + p) % s; class r uses taps k = r + s*j and is a STRIDE-1 transposed conv in a = (o + p - r)/s:
+// dX[s*a + r - p] = sum_j dY[a - j] W[r + s*j].  The packed dgrad operand is class-major so each class is one
+// contiguous K range (padded to 64) of the same matrix.
+struct DgradClass {
+  int r[3], nj[3], amin[3], na[3];
+  int k0, taps;
+};
+struct DgradClassTable {
+  int n;
+  int s[3], k[3];
+  DgradClass c[16];
+};
+
+// fp32 OIDHW (Co, Ci, kT,kH,kW) -> bf16 [rows_pad (>= Ci)][k_pad], column = class k0 + tap_in_class*Cg + co
+__global__ void pack_weight_dgrad_kernel(const float* __restrict__ w, int Co, int Ci, int Cg, DgradClassTable tb,
+                                         __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+  const long long total = (long long)rows_pad * k_pad;
+  const int taps_all = tb.k[0] * tb.k[1] * tb.k[2];
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int col = (int)(idx % k_pad);
+    const int row = (int)(idx / k_pad);
+    float v = 0.f;
+    for (int ci = 0; ci < tb.n; ++ci) {
+      const DgradClass& c = tb.c[ci];
+      const int rel = col - c.k0;
+      if (rel >= 0 && rel < c.taps * Cg) {
+        const int tap = rel / Cg, co = rel - tap * Cg;
+        const int jw = tap % c.nj[2];
+        const int jh = (tap / c.nj[2]) % c.nj[1];
+        const int jt = tap / (c.nj[2] * c.nj[1]);
+        const int kt = c.r[0] + tb.s[0] * jt, kh = c.r[1] + tb.s[1] * jh, kw = c.r[2] + tb.s[2] * jw;
+        const int otap = (kt * tb.k[1] + kh) * tb.k[2] + kw;
+        if (row < Ci && co < Co) v = w[((size_t)co * Ci + row) * taps_all + otap];
+        break;
+      }
+    }
+    wp[idx] = __float2bfloat16_rn(v);
+  }
+}
+
+__global__ void zero_view_kernel(ViewW v, long long M, int C) {
+  const int CV = C >> 3;
+  const long long total = M * CV;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x)
+    vstore(v, idx / CV, (int)(idx % CV) << 3, make_uint4(0, 0, 0, 0));
+}
+
 // ---- BatchNorm finalize / fold ---------------------------------------------------------------------
 __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double inv_count, double unbias,
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
@@ -141,34 +193,44 @@ __global__ void bn_add_relu_kernel(View y, const float* __restrict__ scale, cons
 }
 
 // ---- BatchNorm(+ReLU) backward ----------------------------------------------------------------------
-// masked gradient g for 8 channels of row m
-__device__ __forceinline__ void bn_bwd_load(const View& dz, const View& y, const View& msk, const float* scale,
-                                            const float* shift, const float* mean, const float* invstd, int relu,
-                                            long long m, int c, float* g, float* xhat) {
-  float yv[8], mu[8], is[8];
-  unpack8(vload(dz, m, c), g);
-  unpack8(vload(y, m, c), yv);
-  load8f(mean + c, mu);
-  load8f(invstd + c, is);
+constexpr int kRedThreads = 256;
+constexpr int kBnUnroll = 4;  // independent 16-byte loads in flight per thread and tensor (HBM latency hiding)
+
+// raw operands of kBnUnroll rows (loads issued back to back), then the masked gradient / xhat per row
+struct BnBwdRaw {
+  uint4 dz[kBnUnroll], y[kBnUnroll], mk[kBnUnroll];
+};
+__device__ __forceinline__ void bn_bwd_fetch(const View& dz, const View& y, const View& msk, int relu, const long long* m,
+                                             const bool* ok, int c, BnBwdRaw& r) {
+#pragma unroll
+  for (int u = 0; u < kBnUnroll; ++u) {
+    if (ok[u]) {
+      r.dz[u] = vload(dz, m[u], c);
+      r.y[u] = vload(y, m[u], c);
+      if (relu && msk.p) r.mk[u] = vload(msk, m[u], c);
+    }
+  }
+}
+__device__ __forceinline__ void bn_bwd_math(const BnBwdRaw& r, int u, bool has_mask, int relu, const float* s, const float* b,
+                                            const float* mu, const float* is, float* g, float* xhat) {
+  float yv[8];
+  unpack8(r.dz[u], g);
+  unpack8(r.y[u], yv);
 #pragma unroll
   for (int i = 0; i < 8; ++i) xhat[i] = (yv[i] - mu[i]) * is[i];
   if (relu) {
-    if (msk.p) {
+    if (has_mask) {
       float mv[8];
-      unpack8(vload(msk, m, c), mv);
+      unpack8(r.mk[u], mv);
 #pragma unroll
       for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
     } else {
-      float s[8], b[8];
-      load8f(scale + c, s);
-      load8f(shift + c, b);
 #pragma unroll
       for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], s[i], b[i]) > 0.f ? g[i] : 0.f;
     }
   }
 }
 
-constexpr int kRedThreads = 256;
 // block = (CV channel-vectors) x (RL row lanes); grid.x strides over row groups
 __global__ void __launch_bounds__(kRedThreads)
 bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale, const float* __restrict__ shift,
@@ -184,11 +246,28 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale,
 #pragma unroll
   for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
   if (ty < RL) {
-    for (long long m = (long long)blockIdx.x * RL + ty; m < M; m += (long long)gridDim.x * RL) {
-      float g[8], xh[8];
-      bn_bwd_load(dz, y, msk, scale, shift, mean, invstd, relu, m, c, g, xh);
+    float sc[8], sh[8], mu[8], is[8];
+    const bool has_mask = msk.p != nullptr;
+    if (relu && !has_mask) { load8f(scale + c, sc); load8f(shift + c, sh); }
+    load8f(mean + c, mu);
+    load8f(invstd + c, is);
+    const long long stride = (long long)gridDim.x * RL;
+    for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kBnUnroll) {
+      long long m[kBnUnroll];
+      bool ok[kBnUnroll];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], xh[i], s2[i]); }
+      for (int u = 0; u < kBnUnroll; ++u) { m[u] = m0 + u * stride; ok[u] = m[u] < M; }
+      BnBwdRaw r;
+      bn_bwd_fetch(dz, y, msk, relu, m, ok, c, r);
+#pragma unroll
+      for (int u = 0; u < kBnUnroll; ++u) {
+        if (ok[u]) {
+          float g[8], xh[8];
+          bn_bwd_math(r, u, has_mask, relu, sc, sh, mu, is, g, xh);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], xh[i], s2[i]); }
+        }
+      }
     }
   }
 #pragma unroll
@@ -207,35 +286,83 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale,
   }
 }
 
-__global__ void bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
-                                    const float* __restrict__ shift, const float* __restrict__ mean,
-                                    const float* __restrict__ invstd, const float* __restrict__ gamma,
-                                    const float* __restrict__ dgamma, const float* __restrict__ dbeta, int relu,
-                                    long long M, int C, float invM, ViewW dy, ViewW gout, int g_accumulate) {
+// block = (CV channel-vectors) x (RL row lanes) like the reduction, so the per-channel constants are loaded once
+template <bool MASK, bool GOUT>
+__global__ void __launch_bounds__(kRedThreads, 2)
+bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
+                    const float* __restrict__ shift, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ dgamma, const float* __restrict__ dbeta, int relu,
+                    long long M, int C, float invM, ViewW dy, ViewW gout, int g_accumulate) {
   const int CV = C >> 3;
-  const long long total = M * CV;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(idx % CV) << 3;
-    const long long m = idx / CV;
-    float g[8], xh[8], ga[8], is[8], dg[8], db[8], o[8];
-    bn_bwd_load(dz, y, msk, scale, shift, mean, invstd, relu, m, c, g, xh);
-    load8f(gamma + c, ga);
+  const int RL = kRedThreads / CV;
+  const int tx = threadIdx.x % CV;
+  const int ty = threadIdx.x / CV;
+  if (ty >= RL) return;
+  const int c = tx << 3;
+  // dy = gamma*invstd*(g - dbeta/M - xhat*dgamma/M) = k0*g - ka*y + kb   (xhat = (y-mean)*invstd folded in)
+  float sc[8], sh[8], k0[8], ka[8], kb[8];
+  constexpr bool has_mask = MASK;
+  if (relu && !has_mask) { load8f(scale + c, sc); load8f(shift + c, sh); }
+  {
+    float ga[8], dg[8], db[8], mu[8], is[8];
+    load8f(mean + c, mu);
     load8f(invstd + c, is);
+    load8f(gamma + c, ga);
     load8f(dgamma + c, dg);
     load8f(dbeta + c, db);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) o[i] = ga[i] * is[i] * (g[i] - db[i] * invM - xh[i] * dg[i] * invM);
-    vstore(dy, m, c, pack8(o));
-    if (gout.p) {
-      if (g_accumulate) {
-        float old[8];
-        View gv{gout.p, gout.ld, gout.coff};
-        unpack8(vload(gv, m, c), old);
+    for (int i = 0; i < 8; ++i) {
+      k0[i] = ga[i] * is[i];
+      ka[i] = k0[i] * dg[i] * invM * is[i];
+      kb[i] = ka[i] * mu[i] - k0[i] * db[i] * invM;
+    }
+  }
+  const View gv{gout.p, gout.ld, gout.coff};
+  const long long stride = (long long)gridDim.x * RL;
+  for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kBnUnroll) {
+    long long m[kBnUnroll];
+    bool ok[kBnUnroll];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) g[i] += old[i];
+    for (int u = 0; u < kBnUnroll; ++u) { m[u] = m0 + u * stride; ok[u] = m[u] < M; }
+    BnBwdRaw r;
+    bn_bwd_fetch(dz, y, has_mask ? msk : View{nullptr, 0, 0}, relu, m, ok, c, r);
+    uint4 old[kBnUnroll];
+    if (GOUT && g_accumulate) {
+#pragma unroll
+      for (int u = 0; u < kBnUnroll; ++u)
+        if (ok[u]) old[u] = vload(gv, m[u], c);
+    }
+#pragma unroll
+    for (int u = 0; u < kBnUnroll; ++u) {
+      if (ok[u]) {
+        float g[8], yv[8], o[8];
+        unpack8(r.dz[u], g);
+        unpack8(r.y[u], yv);
+        if (relu) {
+          if (has_mask) {
+            float mv[8];
+            unpack8(r.mk[u], mv);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], sc[i], sh[i]) > 0.f ? g[i] : 0.f;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaf(k0[i], g[i], fmaf(-ka[i], yv[i], kb[i]));
+        vstore(dy, m[u], c, pack8(o));
+        if (GOUT) {
+          if (g_accumulate) {
+            float of[8];
+            unpack8(old[u], of);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] += of[i];
+          }
+          vstore(gout, m[u], c, pack8(g));
+        }
       }
-      vstore(gout, m, c, pack8(g));
     }
   }
 }

@@ -241,6 +241,39 @@ int stem_check(int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t
   return SFB_OK;
 }
 
+
+// ---- strided dgrad classes (see elementwise.cuh) ----
+// k/s/p in (T,H,W) order; O = dX dims (only needed for amin / na; pass nullptr when packing)
+int build_dgrad_classes(const int* k, const int* s, const int* p, const int* O, int Cg, DgradClassTable* tb, int* k_pad) {
+  if (s[0] * s[1] * s[2] > 16) return SFB_ERR_UNSUPPORTED;
+  memset(tb, 0, sizeof(*tb));
+  for (int d = 0; d < 3; ++d) { tb->s[d] = s[d]; tb->k[d] = k[d]; }
+  int k0 = 0;
+  for (int rt = 0; rt < s[0]; ++rt)
+    for (int rh = 0; rh < s[1]; ++rh)
+      for (int rw = 0; rw < s[2]; ++rw) {
+        DgradClass& c = tb->c[tb->n++];
+        const int r[3] = {rt, rh, rw};
+        c.taps = 1;
+        for (int d = 0; d < 3; ++d) {
+          c.r[d] = r[d];
+          c.nj[d] = r[d] < k[d] ? (k[d] - r[d] + s[d] - 1) / s[d] : 0;
+          c.taps *= c.nj[d];
+          if (p && O) {
+            const int num = p[d] - r[d];
+            c.amin[d] = num > 0 ? (num + s[d] - 1) / s[d] : 0;
+            const int top = O[d] - 1 + p[d] - r[d];
+            c.na[d] = top >= 0 ? top / s[d] - c.amin[d] + 1 : 0;
+            if (c.na[d] < 0) c.na[d] = 0;
+          }
+        }
+        c.k0 = k0;
+        k0 += (c.taps * Cg + 63) / 64 * 64;
+      }
+  if (k_pad) *k_pad = k0 > 0 ? k0 : 64;
+  return SFB_OK;
+}
+
 int g_num_sms = 0;
 int num_sms() {
   if (g_num_sms == 0) {
@@ -377,6 +410,38 @@ int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t
   return SFB_OK;
 }
 
+
+
+int sfb_packed_weight_dims_dgrad(int32_t Ci, int32_t Cg, int32_t kT, int32_t kH, int32_t kW, int32_t sT, int32_t sH,
+                                 int32_t sW, int32_t* rows_pad, int32_t* k_pad) {
+  if (Ci <= 0 || Cg <= 0 || (Cg & 7) || kT <= 0 || kH <= 0 || kW <= 0 || sT <= 0 || sH <= 0 || sW <= 0 || !rows_pad || !k_pad)
+    return SFB_ERR_BAD_ARG;
+  const int k[3] = {kT, kH, kW}, s[3] = {sT, sH, sW};
+  DgradClassTable tb;
+  int kp = 0;
+  int rc = build_dgrad_classes(k, s, nullptr, nullptr, Cg, &tb, &kp);
+  if (rc) return rc;
+  const int bn = pick_bn(Ci);
+  *rows_pad = (Ci + bn - 1) / bn * bn;
+  *k_pad = kp;
+  return SFB_OK;
+}
+
+int sfb_pack_weight_dgrad(const float* w, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t sT,
+                          int32_t sH, int32_t sW, int32_t Cg, void* wp, int32_t rows_pad, int32_t k_pad, void* stream) {
+  if (!w || !wp || Co <= 0 || Ci <= 0 || (Cg & 7) || Cg < Co || rows_pad < Ci) return SFB_ERR_BAD_ARG;
+  const int k[3] = {kT, kH, kW}, s[3] = {sT, sH, sW};
+  DgradClassTable tb;
+  int kp = 0;
+  int rc = build_dgrad_classes(k, s, nullptr, nullptr, Cg, &tb, &kp);
+  if (rc) return rc;
+  if (k_pad != kp) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)rows_pad * k_pad;
+  pack_weight_dgrad_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, Co, Ci, Cg, tb, (__nv_bfloat16*)wp,
+                                                                                   rows_pad, k_pad);
+  SFB_CHECK_LAUNCH("pack_weight_dgrad_kernel");
+  return SFB_OK;
+}
 
 int sfb_stem_s2d_channels(int32_t Ci) {
   if (Ci <= 0 || 4 * Ci > 64) return SFB_ERR_UNSUPPORTED;
@@ -526,6 +591,78 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
   CUtensorMap tm;
   rc = get_weight_tmap(wp, rows_pad, k_pad, bn, &tm);
   if (rc) return rc;
+  const bool strided_dgrad = geom->transposed && (geom->sT != 1 || geom->sH != 1 || geom->sW != 1);
+  if (impl == SFB_IMPL_TC && strided_dgrad) {
+    // ---- strided dgrad: one stride-1 launch of the persistent TMA kernel per parity class; the operand `wp` must be
+    //      the class-major packing of sfb_pack_weight_dgrad ----
+    if (p.pro_scale || p.epi_scale || p.epi_relu || p.stats) return SFB_ERR_UNSUPPORTED;
+    if ((geom->Cg % 16) || (geom->Cg > 64 && (geom->Cg % 64)) || (geom->Cg < 64 && geom->Cg != 16 && geom->Cg != 32) ||
+        geom->Co > 2048)
+      return SFB_ERR_UNSUPPORTED;
+    const bool accumulate = p.res != nullptr;
+    if (accumulate && !(p.res == p.out && p.res_ld == geom->o_ld && p.res_coff == geom->o_coff)) return SFB_ERR_UNSUPPORTED;
+    const int k[3] = {geom->kT, geom->kH, geom->kW}, s[3] = {geom->sT, geom->sH, geom->sW};
+    const int pd[3] = {geom->pT, geom->pH, geom->pW}, O[3] = {geom->To, geom->Ho, geom->Wo};
+    DgradClassTable tb;
+    int kp = 0;
+    rc = build_dgrad_classes(k, s, pd, O, geom->Cg, &tb, &kp);
+    if (rc) return rc;
+    if (kp != k_pad) return SFB_ERR_BAD_ARG;
+    bool any_empty = false;
+    for (int ci = 0; ci < tb.n; ++ci) any_empty |= tb.c[ci].taps == 0;
+    if (any_empty && !accumulate) {
+      ViewW vo{p.out, geom->o_ld, geom->o_coff};
+      zero_view_kernel<<<grid_for((long long)p.M * (geom->Co >> 3), 256), 256, 0, st>>>(vo, p.M, geom->Co);
+      SFB_CHECK_LAUNCH("zero_view_kernel");
+    }
+    CUtensorMap ta;
+    for (int ci = 0; ci < tb.n; ++ci) {
+      const DgradClass& c = tb.c[ci];
+      if (c.taps == 0 || c.na[0] <= 0 || c.na[1] <= 0 || c.na[2] <= 0) continue;
+      ConvTmaParams q;
+      memset(&q, 0, sizeof(q));
+      q.N = geom->N; q.To = c.na[0]; q.Ho = c.na[1]; q.Wo = c.na[2];
+      q.Co = geom->Co; q.o_ld = geom->o_ld; q.o_coff = geom->o_coff;
+      q.kT = c.nj[0]; q.kH = c.nj[1]; q.kW = c.nj[2];
+      q.sT = q.sH = q.sW = 1;
+      q.pT = c.amin[0]; q.pH = c.amin[1]; q.pW = c.amin[2];  // transposed box origin = a0 + amin - j
+      q.transposed = 1;
+      q.Cg = geom->Cg;
+      q.box_k = geom->Cg >= 64 ? 64 : geom->Cg;
+      q.cchunks = geom->Cg >= 64 ? geom->Cg / 64 : 1;
+      q.taps = c.taps; q.Ktot = c.taps * geom->Cg; q.nk = (q.Ktot + 63) / 64; q.wk0 = c.k0;
+      pick_patch(q.Wo, q.Ho, q.To, 1, 1, 1, &q.Wt, &q.Ht, &q.Tt);
+      q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
+      q.n_tiles = (geom->Co + bn - 1) / bn;
+      q.total_patches = q.N * q.tilesT * q.tilesH * q.tilesW;
+      q.ocols = geom->Co >= 64 ? 64 : (geom->Co >= 32 ? 32 : (geom->Co >= 16 ? 16 : 8));
+      q.out = p.out;
+      q.reduce_add = accumulate ? 1 : 0;
+      rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, geom->Wi, geom->Hi, geom->Ti, geom->N, geom->g_ld,
+                        q.box_k, q.Wt, q.Ht, q.Tt, 1, 1, 1, &ta);
+      if (rc) return rc;
+      // output: the class's sub-lattice of dX as a strided 5-D tensor
+      const int o0[3] = {s[0] * c.amin[0] + c.r[0] - pd[0], s[1] * c.amin[1] + c.r[1] - pd[1], s[2] * c.amin[2] + c.r[2] - pd[2]};
+      const long long ld2 = (long long)geom->o_ld * 2;
+      const __nv_bfloat16* obase = (const __nv_bfloat16*)out + geom->o_coff +
+                                   (((long long)o0[0] * geom->Ho + o0[1]) * geom->Wo + o0[2]) * geom->o_ld;
+      const long long od[5] = {geom->Co, c.na[2], c.na[1], c.na[0], geom->N};
+      const long long os[4] = {s[2] * ld2, (long long)s[1] * geom->Wo * ld2, (long long)s[0] * geom->Ho * geom->Wo * ld2,
+                               (long long)geom->To * geom->Ho * geom->Wo * ld2};
+      const int ob[5] = {q.ocols, q.Wt, q.Ht, q.Tt, 1};
+      CUtensorMap to;
+      rc = get_tmap_generic(obase, 5, od, os, ob, q.ocols * 2 >= 128 ? 128 : q.ocols * 2, &to);
+      if (rc) return rc;
+      switch (bn) {
+        case 32: rc = launch_conv_tma<32>(ta, tm, to, q, st); break;
+        case 64: rc = launch_conv_tma<64>(ta, tm, to, q, st); break;
+        case 128: rc = launch_conv_tma<128>(ta, tm, to, q, st); break;
+        default: rc = launch_conv_tma<256>(ta, tm, to, q, st); break;
+      }
+      if (rc) return rc;
+    }
+    return SFB_OK;
+  }
   if (impl == SFB_IMPL_TC && !p.pro_scale && tma_eligible(geom, taps)) {
     // ---- persistent TMA / tcgen05 kernel ----
     ConvTmaParams q;
@@ -753,7 +890,7 @@ int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff, const void
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
   const int RL = kRedThreads / (C >> 3);
-  const int grid = grid_for((M + RL - 1) / RL, 1, 148 * 4);
+  const int grid = grid_for((M + (long long)RL * kBnUnroll - 1) / ((long long)RL * kBnUnroll), 1, 148 * 8);
   bn_bwd_reduce_kernel<<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, vy, vm, scale, shift, mean, invstd, relu, M,
                                                                        C, dgamma, dbeta);
   SFB_CHECK_LAUNCH("bn_bwd_reduce_kernel");
@@ -765,7 +902,7 @@ int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void*
                      const float* mean, const float* invstd, const float* gamma, const float* dgamma,
                      const float* dbeta, int32_t relu, int64_t M, int32_t C, void* dy, int32_t dy_ld, int32_t dy_coff,
                      void* g_out, int32_t g_ld, int32_t g_coff, int32_t g_accumulate, void* stream) {
-  if (M <= 0 || C <= 0 || (C & 7) || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
+  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
   if (!view_ok(dz, dz_ld, dz_coff, C) || !view_ok(y, y_ld, y_coff, C) || !view_ok(dy, dy_ld, dy_coff, C))
     return SFB_ERR_BAD_ARG;
   if (mask_src && !view_ok(mask_src, m_ld, m_coff, C)) return SFB_ERR_BAD_ARG;
@@ -776,8 +913,15 @@ int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void*
   View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
   ViewW vdy{(__nv_bfloat16*)dy, dy_ld, dy_coff};
   ViewW vg{(__nv_bfloat16*)g_out, g_ld, g_coff};
-  bn_bwd_apply_kernel<<<grid_for(M * (C >> 3), 256), 256, 0, (cudaStream_t)stream>>>(
-      vdz, vy, vm, scale, shift, mean, invstd, gamma, dgamma, dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, g_accumulate);
+  const int RLa = kRedThreads / (C >> 3);
+  const int grid_a = grid_for((M + (long long)RLa * kBnUnroll - 1) / ((long long)RLa * kBnUnroll), 1, 148 * 8);
+  const bool hm = relu && mask_src != nullptr, hg = g_out != nullptr;
+#define SFB_APPLY(MK, GO) bn_bwd_apply_kernel<MK, GO><<<grid_a, kRedThreads, 0, (cudaStream_t)stream>>>(       vdz, vy, vm, scale, shift, mean, invstd, gamma, dgamma, dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, g_accumulate)
+  if (hm && hg) SFB_APPLY(true, true);
+  else if (hm) SFB_APPLY(true, false);
+  else if (hg) SFB_APPLY(false, true);
+  else SFB_APPLY(false, false);
+#undef SFB_APPLY
   SFB_CHECK_LAUNCH("bn_bwd_apply_kernel");
   return SFB_OK;
 }

@@ -236,8 +236,10 @@ class SlowFastEngine:
         """(Re)pack bf16 GEMM operands of every conv whose fp32 master weight changed (optimizer step / load)."""
         for l in self.layers:
             w = l.conv.weight
-            if l.packed_version == w._version and l.wp is not None and (l.wpt is not None or not (training and l.needs_dgrad)):
+            if l.packed_version == w._version and l.wp is not None and getattr(l, "packed_impl", None) == self.impl and \
+                    (l.wpt is not None or not (training and l.needs_dgrad)):
                 continue
+            l.packed_impl = self.impl
             rp, kp = _ffi.packed_weight_dims(l.Co, l.Cg, l.taps)
             if l.wp is None:
                 l.wp = torch.empty((rp, kp), dtype=torch.bfloat16, device=self.dev)
@@ -247,7 +249,7 @@ class SlowFastEngine:
                 cs = 32 if 4 * l.Ci <= 32 else 64
                 l.wps = torch.empty((_ops.stem_rows_pad(l.Co), 16 * cs), dtype=torch.bfloat16, device=self.dev)
             if self.dry_run:
-                rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
+                rpt, kpt = _ffi.packed_weight_dims_dgrad(l.Ci, l.Cgt, l.k, l.s)
                 l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
                 l.packed_version = w._version
                 continue
@@ -260,11 +262,20 @@ class SlowFastEngine:
                 _ffi.check(self.lib.sfb_pack_weight_stem(wd.data_ptr(), l.Co, l.Ci, l.wps.shape[1] // 16, l.wps.data_ptr(),
                                                          l.wps.shape[0], self.stream), "sfb_pack_weight_stem")
             if training and l.needs_dgrad:
-                rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
-                if l.wpt is None:
-                    l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
-                _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cgt, 1, l.wpt.data_ptr(), rpt, kpt,
-                                                    self.stream), "sfb_pack_weight(T)")
+                if self.impl == _ffi.IMPL_TC:
+                    # class-major operand: strided convs back-propagate as one stride-1 launch per parity class
+                    rpt, kpt = _ffi.packed_weight_dims_dgrad(l.Ci, l.Cgt, l.k, l.s)
+                    if l.wpt is None or tuple(l.wpt.shape) != (rpt, kpt):
+                        l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
+                    _ffi.check(self.lib.sfb_pack_weight_dgrad(wd.data_ptr(), l.Co, l.Ci, l.k[0], l.k[1], l.k[2], l.s[0], l.s[1],
+                                                              l.s[2], l.Cgt, l.wpt.data_ptr(), rpt, kpt, self.stream),
+                               "sfb_pack_weight_dgrad")
+                else:
+                    rpt, kpt = _ffi.packed_weight_dims(l.Cg, l.Cgt, l.taps)
+                    if l.wpt is None or tuple(l.wpt.shape) != (rpt, kpt):
+                        l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
+                    _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cgt, 1, l.wpt.data_ptr(), rpt, kpt,
+                                                        self.stream), "sfb_pack_weight(T)")
             l.packed_version = w._version
 
     # ------------------------------------------------------------------ op emission helpers
@@ -616,12 +627,14 @@ class SlowFastEngine:
             pool.release(dzb.buf)
             self._bn_bwd(plan, bwd, a, dza, ya, None, dza)
             self._wgrad(plan, bwd, a, X.act, None, dza)
+            # conv_a (stride 1) writes every pixel of dX first; the strided shortcut then only touches its own
+            # sub-lattice with a reduce-add (no zero fill of the pixels a stride-2 conv never reads)
+            dgrad_into(a, dza, X)
+            pool.release(dza.buf)
             if s_ is not None:
                 self._wgrad(plan, bwd, s_, X.act, None, dy1)
                 dgrad_into(s_, dy1, X)
                 pool.release(dy1.buf)
-            dgrad_into(a, dza, X)
-            pool.release(dza.buf)
             pool.release(O.cat.dcat.buf if O.cat is not None else dO.buf)
 
         if self.laterals[0] is not None:

@@ -81,6 +81,20 @@ def pack_weight(w: torch.Tensor, Cg: int, transposed: bool = False, out: Optiona
     return out
 
 
+def pack_weight_dgrad(w: torch.Tensor, Cg: int, stride, out: Optional[torch.Tensor] = None):
+    """fp32 OIDHW conv weight -> class-major packed bf16 operand of the tensor-core input-gradient GEMM."""
+    assert w.dtype == torch.float32 and w.is_cuda and w.is_contiguous()
+    Co, Ci = w.shape[0], w.shape[1]
+    k = tuple(w.shape[2:])
+    rows_pad, k_pad = _ffi.packed_weight_dims_dgrad(Ci, Cg, k, stride)
+    if out is None:
+        out = torch.empty((rows_pad, k_pad), dtype=torch.bfloat16, device=w.device)
+    assert tuple(out.shape) == (rows_pad, k_pad)
+    check(lib().sfb_pack_weight_dgrad(w.data_ptr(), Co, Ci, k[0], k[1], k[2], stride[0], stride[1], stride[2], Cg,
+                                      out.data_ptr(), rows_pad, k_pad, stream_ptr()), "sfb_pack_weight_dgrad")
+    return out
+
+
 def stem_s2d_eligible(C_in, C_out, k, s, p, H, W) -> bool:
     """can the (1,7,7)/s(1,2,2)/p(0,3,3) stem take the space-to-depth row-window kernels (csrc/stem_win.cuh)?"""
     return (tuple(k) == (1, 7, 7) and tuple(s) == (1, 2, 2) and tuple(p) == (0, 3, 3) and H % 2 == 0 and W % 2 == 0
