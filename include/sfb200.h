@@ -120,6 +120,21 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
                    float* dw, int32_t Ci_real, int32_t impl, void* stream);
 
 
+
+/* ---- pixel folding for narrow-channel layers (Fast pathway: 8..32 channels) ------------------------------------
+ * A stride-1 conv over a dense NDHWC tensor may be run on the SAME memory viewed as (N,T,H,W/f,f*ld): f neighbouring
+ * pixels become one pixel with f*ld channels (128-byte rows for TMA instead of 32/64-byte ones) and the weight
+ * becomes block-banded (csrc/elementwise.cuh).  These translate between the reference layout and the folded one:
+ *   sfb_fold_weight : fp32 (Co,Ci,kT,kH,kW) -> fp32 (f*ldo, f*ldi, kT, kH, kW') , kW' = 1 (kW = 1) or 3 (kW = 3);
+ *                     feed the result to sfb_pack_weight / sfb_pack_weight_dgrad with Co' = f*ldo, Ci' = f*ldi
+ *   sfb_unfold_wgrad: dw (Co,Ci,kT,kH,kW) += band sums of the folded weight gradient produced by sfb_conv_wgrad
+ *   sfb_unfold_stats: stats[2*C] += column-group sums of the folded BatchNorm statistics [2*f*ld] */
+int sfb_fold_weight(const float* w, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
+                    int32_t ldi, float* wf, void* stream);
+int sfb_unfold_wgrad(const float* dwf, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
+                     int32_t ldi, float* dw, void* stream);
+int sfb_unfold_stats(const float* stats_folded, int32_t f, int32_t ld, int32_t C, float* stats, void* stream);
+
 /* ---- stem convolution (1,7,7)/s(1,2,2)/p(0,3,3) in space-to-depth form -------------------------------------------
  * replaces: ResNetBasicStem.conv of both pathways (reference model/my_slowfast.py:63-68: kernel (1,7,7), stride
  * (1,2,2), padding (0,3,3); pytorchvideo create_res_basic_stem) and its weight gradient.  The clip is laid out

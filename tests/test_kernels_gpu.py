@@ -291,6 +291,74 @@ def test_stem_s2d_wgrad(N, T, H, W, Ci, Co):
     assert kc.relerr(dw, 2 * wz.grad) < 2e-2
 
 
+# ------------------------------------------------------------------ pixel folding of narrow-channel layers
+# N, T, H, W, Ci, Co, k
+FOLD_CASES = [
+    (2, 4, 12, 16, 8, 8, (1, 3, 3)),     # fast res2 conv_b
+    (2, 6, 10, 12, 32, 8, (3, 1, 1)),    # fast res2 conv_a
+    (2, 4, 10, 12, 8, 32, (1, 1, 1)),    # fast res2 conv_c
+    (1, 4, 9, 8, 64, 16, (3, 1, 1)),     # fast res3 conv_a
+    (2, 3, 7, 14, 32, 32, (1, 3, 3)),    # fast res4 conv_b (f = 2)
+    (1, 3, 7, 14, 32, 128, (1, 1, 1)),   # fast res4 conv_c (f = 2)
+]
+
+
+@pytest.mark.parametrize("N,T,H,W,Ci,Co,k", FOLD_CASES)
+def test_folded_conv_matches_reference(N, T, H, W, Ci, Co, k):
+    """fprop (+ BatchNorm statistics), dgrad and wgrad run on the folded view of the same buffers"""
+    g = torch.Generator(device=DEV).manual_seed(3)
+    ldi, ldo = kc.ops.round_up(Ci, 16), kc.ops.round_up(Co, 16)
+    s1, p = (1, 1, 1), tuple(kk // 2 for kk in k)
+    f = ops.fold_factor(ldi, ldo, k, s1, W)
+    assert f >= 2
+    x = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
+    w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Ci * k[0] * k[1] * k[2]) ** 0.5
+    xa = Act.empty(N, T, H, W, ldi, C=Ci, zero=True)
+    xa.torch_view().copy_(x.permute(0, 2, 3, 4, 1))
+    xq, wq = kc.from_act(xa), w.bfloat16().float()
+    kf = (k[0], k[1], 1 if k[2] == 1 else 3)
+    pf = tuple(kk // 2 for kk in kf)
+    wf = ops.fold_weight(w.contiguous(), f, ldo, ldi)
+    # ---- fprop + stats
+    out = Act.empty(N, T, H, W, ldo, C=Co, zero=True)
+    sf = torch.zeros(2 * f * ldo, device=DEV)
+    ops.conv_gemm(ops.folded(xa, f), ops.pack_weight(wf, f * ldi), ops.folded(out, f), kf, s1, pf, stats=sf)
+    stats = torch.zeros(2 * Co, device=DEV)
+    ops.unfold_stats(sf, f, ldo, Co, stats)
+    ref = F.conv3d(xq, wq, padding=p)
+    got = kc.from_act(out)
+    assert kc.relerr(got, ref) < 1e-2
+    assert float(out.buf[..., Co:].abs().max()) == 0.0 if ldo > Co else True
+    cnt = ref.numel() / Co
+    torch.testing.assert_close(stats[:Co] / cnt, got.mean(dim=(0, 2, 3, 4)), rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(stats[Co:] / cnt, (got * got).mean(dim=(0, 2, 3, 4)), rtol=1e-3, atol=1e-4)
+    # ---- dgrad (accumulating on top of a base gradient)
+    dy = torch.randn((N, Co, T, H, W), device=DEV, generator=g)
+    dya = Act.empty(N, T, H, W, ldo, C=Co, zero=True)
+    dya.torch_view().copy_(dy.permute(0, 2, 3, 4, 1))
+    dyq = kc.from_act(dya)
+    xz = torch.zeros_like(xq, requires_grad=True)
+    wz = torch.zeros_like(wq, requires_grad=True)
+    F.conv3d(xz, wq, padding=p).backward(dyq)
+    F.conv3d(xq, wz, padding=p).backward(dyq)
+    base = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
+    dxa = Act.empty(N, T, H, W, ldi, C=Ci, zero=True)
+    dxa.torch_view().copy_(base.permute(0, 2, 3, 4, 1))
+    ref_dx = xz.grad + kc.from_act(dxa)
+    dxf = ops.folded(dxa, f)
+    ops.conv_gemm(ops.folded(dya, f), ops.pack_weight_dgrad(wf, f * ldo, s1), dxf, kf, s1, pf, transposed=True, residual=dxf)
+    torch.cuda.synchronize()
+    assert kc.relerr(kc.from_act(dxa), ref_dx) < 1.5e-2
+    assert float(dxa.buf[..., Ci:].abs().max()) == 0.0 if ldi > Ci else True
+    # ---- wgrad through the folded gradient
+    dwf = torch.zeros_like(wf)
+    ops.conv_wgrad(ops.folded(xa, f), ops.folded(dya, f), dwf, kf, s1, pf)
+    dw = torch.zeros_like(w)
+    ops.unfold_wgrad(dwf, f, ldo, ldi, dw)
+    torch.cuda.synchronize()
+    assert kc.relerr(dw, wz.grad) < 2e-2
+
+
 def test_bad_args_rejected():
     x = Act.empty(1, 2, 4, 4, 12)  # 12 channels: not a multiple of 8
     w = torch.empty(64, 64, dtype=torch.bfloat16, device=DEV)

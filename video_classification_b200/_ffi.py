@@ -56,6 +56,9 @@ SIGNATURES = {
     "sfb_fc_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
     "sfb_packed_weight_dims_dgrad": [_i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
     "sfb_pack_weight_dgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
+    "sfb_fold_weight": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
+    "sfb_unfold_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
+    "sfb_unfold_stats": [_vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_layout_input_s2d": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],

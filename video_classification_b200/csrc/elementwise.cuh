@@ -124,6 +124,71 @@ __global__ void zero_view_kernel(ViewW v, long long M, int C) {
     vstore(v, idx / CV, (int)(idx % CV) << 3, make_uint4(0, 0, 0, 0));
 }
 
+
+// ---- pixel folding for narrow-channel layers -------------------------------------------------------------
+// A stride-1 conv over a dense NDHWC tensor with C < 64 channels moves 16/32-channel (32/64-byte) rows, which
+// bounds TMA by its request rate, not by bytes.  Viewing f consecutive W pixels as ONE pixel with f*C channels is the
+// same memory; the conv becomes a conv with a block-banded weight
+//   Wf[(j,co)][(j',c)][kt][kh][kw'] = W[co][c][kt][kh][kw],  kw = f*(kw' - kW'/2) + j' - j + kW/2   (0 outside [0,kW))
+// (kW' = 1 for kW = 1, 3 for kW = 3).  The heavy kernels run unchanged on 128-byte rows; these three small kernels
+// translate weights, BatchNorm statistics and weight gradients between the folded and the reference layout.
+__global__ void fold_weight_kernel(const float* __restrict__ w, int Co, int Ci, int kT, int kH, int kW, int f, int ldo,
+                                   int ldi, float* __restrict__ wf) {
+  const int kWf = kW == 1 ? 1 : 3;
+  const int Cof = f * ldo, Cif = f * ldi;
+  const long long total = (long long)Cof * Cif * kT * kH * kWf;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    long long q = idx;
+    const int kwf = (int)(q % kWf); q /= kWf;
+    const int kh = (int)(q % kH); q /= kH;
+    const int kt = (int)(q % kT); q /= kT;
+    const int cif = (int)(q % Cif);
+    const int cof = (int)(q / Cif);
+    const int j = cof / ldo, co = cof - j * ldo;
+    const int jp = cif / ldi, c = cif - jp * ldi;
+    const int kw = f * (kwf - kWf / 2) + jp - j + kW / 2;
+    float v = 0.f;
+    if (co < Co && c < Ci && kw >= 0 && kw < kW) v = w[((((size_t)co * Ci + c) * kT + kt) * kH + kh) * kW + kw];
+    wf[idx] = v;
+  }
+}
+
+// dW[co][c][kt][kh][kw] += sum over (j, j', kw') mapping to kw of dWf[(j,co)][(j',c)][kt][kh][kw']
+__global__ void unfold_wgrad_kernel(const float* __restrict__ dwf, int Co, int Ci, int kT, int kH, int kW, int f, int ldo,
+                                    int ldi, float* __restrict__ dw) {
+  const int kWf = kW == 1 ? 1 : 3;
+  const int Cif = f * ldi;
+  const long long total = (long long)Co * Ci * kT * kH * kW;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    long long q = idx;
+    const int kw = (int)(q % kW); q /= kW;
+    const int kh = (int)(q % kH); q /= kH;
+    const int kt = (int)(q % kT); q /= kT;
+    const int c = (int)(q % Ci);
+    const int co = (int)(q / Ci);
+    float acc = 0.f;
+    for (int j = 0; j < f; ++j)
+      for (int kwf = 0; kwf < kWf; ++kwf) {
+        const int jp = kw - kW / 2 + j - f * (kwf - kWf / 2);
+        if (jp < 0 || jp >= f) continue;
+        acc += dwf[((((size_t)(j * ldo + co) * Cif + (jp * ldi + c)) * kT + kt) * kH + kh) * kWf + kwf];
+      }
+    dw[idx] += acc;
+  }
+}
+
+// stats[c] += sum_j sf[j*ld + c] ; stats[C + c] += sum_j sf[f*ld + j*ld + c]
+__global__ void unfold_stats_kernel(const float* __restrict__ sf, int f, int ld, int C, float* __restrict__ stats) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a = 0.f, b = 0.f;
+  for (int j = 0; j < f; ++j) { a += sf[j * ld + c]; b += sf[f * ld + j * ld + c]; }
+  stats[c] += a;
+  stats[C + c] += b;
+}
+
 // ---- BatchNorm finalize / fold ---------------------------------------------------------------------
 __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double inv_count, double unbias,
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,

@@ -443,6 +443,37 @@ int sfb_pack_weight_dgrad(const float* w, int32_t Co, int32_t Ci, int32_t kT, in
   return SFB_OK;
 }
 
+
+static bool fold_args_ok(int Co, int Ci, int kT, int kH, int kW, int f, int ldo, int ldi) {
+  return Co > 0 && Ci > 0 && kT > 0 && kH > 0 && (kW == 1 || kW == 3) && f >= 2 && f <= 8 && ldo >= Co && ldi >= Ci &&
+         !(ldo & 7) && !(ldi & 7);
+}
+
+int sfb_fold_weight(const float* w, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
+                    int32_t ldi, float* wf, void* stream) {
+  if (!w || !wf || !fold_args_ok(Co, Ci, kT, kH, kW, f, ldo, ldi)) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)f * ldo * f * ldi * kT * kH * (kW == 1 ? 1 : 3);
+  fold_weight_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, Co, Ci, kT, kH, kW, f, ldo, ldi, wf);
+  SFB_CHECK_LAUNCH("fold_weight_kernel");
+  return SFB_OK;
+}
+
+int sfb_unfold_wgrad(const float* dwf, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
+                     int32_t ldi, float* dw, void* stream) {
+  if (!dwf || !dw || !fold_args_ok(Co, Ci, kT, kH, kW, f, ldo, ldi)) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)Co * Ci * kT * kH * kW;
+  unfold_wgrad_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(dwf, Co, Ci, kT, kH, kW, f, ldo, ldi, dw);
+  SFB_CHECK_LAUNCH("unfold_wgrad_kernel");
+  return SFB_OK;
+}
+
+int sfb_unfold_stats(const float* stats_folded, int32_t f, int32_t ld, int32_t C, float* stats, void* stream) {
+  if (!stats_folded || !stats || f < 2 || f > 8 || C <= 0 || ld < C) return SFB_ERR_BAD_ARG;
+  unfold_stats_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats_folded, f, ld, C, stats);
+  SFB_CHECK_LAUNCH("unfold_stats_kernel");
+  return SFB_OK;
+}
+
 int sfb_stem_s2d_channels(int32_t Ci) {
   if (Ci <= 0 || 4 * Ci > 64) return SFB_ERR_UNSUPPORTED;
   return 4 * Ci <= 32 ? 32 : 64;

@@ -73,6 +73,12 @@ class ConvL:
         self.needs_dgrad = needs_dgrad
         self.wp = self.wpt = None
         self.wps = None  # stems: space-to-depth packing for the row-window kernels (csrc/stem_win.cuh)
+        # pixel folding (narrow-channel layers, csrc/elementwise.cuh): f W-neighbouring pixels viewed as one
+        self.fold_f = 1
+        self.ldi, self.ldo = round_up(self.Ci, 16), round_up(self.Co, 16)
+        self.kf = (self.k[0], self.k[1], 1 if self.k[2] == 1 else 3)
+        self.pf = tuple(v // 2 for v in self.kf)
+        self.wf = self.wpf = self.wptf = self.dwf = self.sf = None
         self.is_stem = False
         self.packed_version = -1
         # set by the engine
@@ -188,13 +194,18 @@ class SlowFastEngine:
             if self.laterals[si + 1] is not None:
                 order.append(self.laterals[si + 1])
         self.layers = order
+        import os as _os
+        if not _os.environ.get("SFB_NO_FOLD"):
+            for l in order:
+                if not l.is_stem:
+                    l.fold_f = _ops.fold_factor(l.ldi, l.ldo, l.k, l.s, 8)
         self.proj = m.blocks[6].proj
         self.bn_modules = [l.bn for l in self.layers]
 
     def _alloc_arenas(self):
         dev = self.dev
         # ---- BN scratch: [all stats | per layer scale, shift, mean, invstd] ----
-        n_stats = sum(2 * l.Co for l in self.layers)
+        n_stats = sum(2 * l.Co + (2 * l.fold_f * l.ldo if l.fold_f > 1 else 0) for l in self.layers)
         n_rest = sum(4 * l.Co for l in self.layers)
         self.bn_flat = _f32(n_stats + n_rest, dev, zero=True)
         self.stats_flat = self.bn_flat[:n_stats]
@@ -203,6 +214,9 @@ class SlowFastEngine:
             c = l.Co
             l.stats = self.bn_flat[o_s:o_s + 2 * c]
             o_s += 2 * c
+            if l.fold_f > 1:
+                l.sf = self.bn_flat[o_s:o_s + 2 * l.fold_f * l.ldo]
+                o_s += 2 * l.fold_f * l.ldo
             l.scale, l.shift = self.bn_flat[o_r:o_r + c], self.bn_flat[o_r + c:o_r + 2 * c]
             l.mean, l.invstd = self.bn_flat[o_r + 2 * c:o_r + 3 * c], self.bn_flat[o_r + 3 * c:o_r + 4 * c]
             o_r += 4 * c
@@ -216,7 +230,18 @@ class SlowFastEngine:
         for prm in reversed(live):
             offs[id(prm)] = o
             o += round_up(prm.numel(), 8)
+        # folded weight gradients (scratch behind the parameters: zeroed with the arena, outside every DDP bucket)
+        fold_offs = {}
+        for l in self.layers:
+            if l.fold_f > 1:
+                n = l.fold_f * l.ldo * l.fold_f * l.ldi * l.kf[0] * l.kf[1] * l.kf[2]
+                fold_offs[id(l)] = (o, n)
+                o += round_up(n, 8)
         self.grad_flat = _f32(o, dev, zero=True)
+        for l in self.layers:
+            if l.fold_f > 1:
+                st, n = fold_offs[id(l)]
+                l.dwf = self.grad_flat[st:st + n].view(l.fold_f * l.ldo, l.fold_f * l.ldi, *l.kf)
         self.grad_views = {}
         for prm in live:
             st = offs[id(prm)]
@@ -248,6 +273,13 @@ class SlowFastEngine:
             if s2d_ok and l.wps is None:
                 cs = 32 if 4 * l.Ci <= 32 else 64
                 l.wps = torch.empty((_ops.stem_rows_pad(l.Co), 16 * cs), dtype=torch.bfloat16, device=self.dev)
+            if l.fold_f > 1 and l.wf is None:
+                f_, tf_ = l.fold_f, l.kf[0] * l.kf[1] * l.kf[2]
+                l.wf = torch.empty((f_ * l.ldo, f_ * l.ldi) + l.kf, dtype=torch.float32, device=self.dev)
+                rpf, kpf = _ffi.packed_weight_dims(f_ * l.ldo, f_ * l.ldi, tf_)
+                l.wpf = torch.empty((rpf, kpf), dtype=torch.bfloat16, device=self.dev)
+                rpt_, kpt_ = _ffi.packed_weight_dims_dgrad(f_ * l.ldi, f_ * l.ldo, l.kf, (1, 1, 1))
+                l.wptf = torch.empty((rpt_, kpt_), dtype=torch.bfloat16, device=self.dev)
             if self.dry_run:
                 rpt, kpt = _ffi.packed_weight_dims_dgrad(l.Ci, l.Cgt, l.k, l.s)
                 l.wpt = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
@@ -258,6 +290,27 @@ class SlowFastEngine:
                 wd = wd.contiguous()
             _ffi.check(self.lib.sfb_pack_weight(wd.data_ptr(), l.Co, l.Ci, l.taps, l.Cg, 0, l.wp.data_ptr(), rp, kp, self.stream),
                        "sfb_pack_weight")
+            if l.fold_f > 1:
+                f = l.fold_f
+                tf = l.kf[0] * l.kf[1] * l.kf[2]
+                _ffi.check(self.lib.sfb_fold_weight(wd.data_ptr(), l.Co, l.Ci, l.k[0], l.k[1], l.k[2], f, l.ldo, l.ldi,
+                                                    l.wf.data_ptr(), self.stream), "sfb_fold_weight")
+                _ffi.check(self.lib.sfb_pack_weight(l.wf.data_ptr(), f * l.ldo, f * l.ldi, tf, f * l.ldi, 0, l.wpf.data_ptr(),
+                                                    l.wpf.shape[0], l.wpf.shape[1], self.stream), "sfb_pack_weight(folded)")
+                if training and l.needs_dgrad:
+                    if self.impl == _ffi.IMPL_TC:
+                        rpt, kpt = _ffi.packed_weight_dims_dgrad(f * l.ldi, f * l.ldo, l.kf, (1, 1, 1))
+                    else:
+                        rpt, kpt = _ffi.packed_weight_dims(f * l.ldi, f * l.ldo, tf)
+                    if l.wptf is None or tuple(l.wptf.shape) != (rpt, kpt):
+                        l.wptf = torch.empty((rpt, kpt), dtype=torch.bfloat16, device=self.dev)
+                    if self.impl == _ffi.IMPL_TC:
+                        _ffi.check(self.lib.sfb_pack_weight_dgrad(l.wf.data_ptr(), f * l.ldo, f * l.ldi, l.kf[0], l.kf[1], l.kf[2],
+                                                                  1, 1, 1, f * l.ldo, l.wptf.data_ptr(), rpt, kpt, self.stream),
+                                   "sfb_pack_weight_dgrad(folded)")
+                    else:
+                        _ffi.check(self.lib.sfb_pack_weight(l.wf.data_ptr(), f * l.ldo, f * l.ldi, tf, f * l.ldo, 1,
+                                                            l.wptf.data_ptr(), rpt, kpt, self.stream), "sfb_pack_weight(T, folded)")
             if l.wps is not None:
                 _ffi.check(self.lib.sfb_pack_weight_stem(wd.data_ptr(), l.Co, l.Ci, l.wps.shape[1] // 16, l.wps.data_ptr(),
                                                          l.wps.shape[0], self.stream), "sfb_pack_weight_stem")
@@ -291,27 +344,66 @@ class SlowFastEngine:
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = out.dims
-        cg = round_up(x.C, 16)
-        co = round_up(out.C, 16) if transposed else out.C
-        assert x.coff + cg <= x.ld and out.coff + co <= out.ld
-        g = ConvGeom(N, Ti, Hi, Wi, cg, To, Ho, Wo, co, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
-                     x.ld, x.coff, out.ld, out.coff, int(transposed))
+        f = self._fold_of(L, x, out, transposed) if (wp is None and pro is None and epi is None) else 1
+        if f > 1:
+            # the same buffers seen as (N,T,H,W/f,f*ld): 128-byte rows for TMA, block-banded weights
+            k, p = L.kf, L.pf
+            cg, co = f * x.ld, f * out.ld
+            g = ConvGeom(N, Ti, Hi, Wi // f, cg, To, Ho, Wo // f, co, k[0], k[1], k[2], 1, 1, 1, p[0], p[1], p[2],
+                         cg, 0, co, 0, int(transposed))
+            assert residual is None or (residual.buf is out.buf and residual.coff == 0)
+            ep = Epilogue(0, 0, out.ptr() if residual else 0, co if residual else 0, 0, 0, L.sf.data_ptr() if stats else 0)
+            wp = L.wptf if transposed else L.wpf
+        else:
+            cg = round_up(x.C, 16)
+            co = round_up(out.C, 16) if transposed else out.C
+            assert x.coff + cg <= x.ld and out.coff + co <= out.ld
+            g = ConvGeom(N, Ti, Hi, Wi, cg, To, Ho, Wo, co, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
+                         x.ld, x.coff, out.ld, out.coff, int(transposed))
+            ep = Epilogue(epi[0].data_ptr() if epi else 0, epi[1].data_ptr() if epi else 0,
+                          residual.ptr() if residual else 0, residual.ld if residual else 0,
+                          residual.coff if residual else 0, int(epi[2]) if epi else 0, L.stats.data_ptr() if stats else 0)
+            wp = wp if wp is not None else (L.wpt if transposed else L.wp)
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
-        ep = Epilogue(epi[0].data_ptr() if epi else 0, epi[1].data_ptr() if epi else 0,
-                      residual.ptr() if residual else 0, residual.ld if residual else 0,
-                      residual.coff if residual else 0, int(epi[2]) if epi else 0, L.stats.data_ptr() if stats else 0)
         g.real_k = (L.Co if transposed else L.Ci) * L.taps  # algorithmic reduction length (no channel padding)
         g.real_n = L.Ci if transposed else L.Co
+        g.real_m = N * Ti * Hi * Wi if transposed else N * To * Ho * Wo  # rows of the forward conv's output
         plan.keep += [g, pr, ep]
-        wp = wp if wp is not None else (L.wpt if transposed else L.wp)
         self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
                    out.ptr(), C.byref(ep), self.impl, self.stream,
                    tag=tag if tag is not None else (None if transposed else (L.conv_name + ".y", out)))
+        if f > 1 and stats:
+            self._emit(lst, self.lib.sfb_unfold_stats, L.sf.data_ptr(), f, L.ldo, L.Co, L.stats.data_ptr(), self.stream)
+
+    def _fold_of(self, L: ConvL, x: Act, out: Act, transposed: bool) -> int:
+        """fold factor to run this conv pass with (1 = unfolded): needs whole dense buffers on both sides"""
+        f = L.fold_f
+        if f <= 1:
+            return 1
+        a, b = (out, x) if transposed else (x, out)  # a = conv input side, b = conv output side
+        if a.coff or b.coff or a.ld != L.ldi or b.ld != L.ldo or a.dims != b.dims or a.dims[3] % f:
+            return 1
+        return f
 
     def _wgrad(self, plan, lst, L: ConvL, x: Act, pro, dy: Act):
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = dy.dims
+        f = self._fold_of(L, x, dy, False) if pro is None else 1
+        if f > 1:
+            k, p = L.kf, L.pf
+            g = ConvGeom(N, Ti, Hi, Wi // f, f * x.ld, To, Ho, Wo // f, f * dy.ld, k[0], k[1], k[2], 1, 1, 1, p[0], p[1], p[2],
+                         f * x.ld, 0, f * dy.ld, 0, 0)
+            g.real_k, g.real_n, g.real_m = L.Ci * L.taps, L.Co, N * To * Ho * Wo
+            pr = Prologue(0, 0, 0)
+            plan.keep += [g, pr]
+            self._emit(lst, self.lib.sfb_conv_wgrad, C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), f * dy.ld, 0,
+                       L.dwf.data_ptr(), f * x.ld, self.impl, self.stream)
+            self._emit(lst, self.lib.sfb_unfold_wgrad, L.dwf.data_ptr(), L.Co, L.Ci, L.k[0], L.k[1], L.k[2], f, L.ldo, L.ldi,
+                       L.dw.data_ptr(), self.stream)
+            if self.ddp is not None:
+                self.ddp.note_grad_ready(plan, lst, L.conv.weight)
+            return
         g = ConvGeom(N, Ti, Hi, Wi, round_up(x.C, 16), To, Ho, Wo, dy.C, k[0], k[1], k[2], s[0], s[1], s[2], p[0], p[1], p[2],
                      x.ld, x.coff, dy.ld, dy.coff, 0)
         pr = Prologue(pro[0].data_ptr(), pro[1].data_ptr(), int(pro[2])) if pro is not None else Prologue(0, 0, 0)
@@ -699,7 +791,7 @@ class SlowFastEngine:
             if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
                 g = args[0]._obj
                 kind = "wgrad" if name == "sfb_conv_wgrad" else ("dgrad" if g.transposed else "fprop")
-                M = g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo
+                M = getattr(g, "real_m", None) or (g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo)
                 gf = 2.0 * M * g.real_n * g.real_k / 1e9
                 desc = (f"{kind} in({g.Ti},{g.Hi},{g.Wi})x{g.Cg} out({g.To},{g.Ho},{g.Wo})x{g.Co} "
                         f"k({g.kT},{g.kH},{g.kW}) s({g.sT},{g.sH},{g.sW})")
@@ -724,7 +816,7 @@ class SlowFastEngine:
                 elif name == "sfb_conv_gemm":
                     key = "sfb_conv_gemm[fprop]"
                 # algorithmic work: rows of the forward conv's OUTPUT (for dgrad that is the gathered tensor dY)
-                M = g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo
+                M = getattr(g, "real_m", None) or (g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo)
                 flops[key] = flops.get(key, 0.0) + 2.0 * M * g.real_n * g.real_k
             if name in ("sfb_stem_conv_fprop", "sfb_stem_conv_wgrad"):
                 ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])

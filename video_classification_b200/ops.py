@@ -95,6 +95,47 @@ def pack_weight_dgrad(w: torch.Tensor, Cg: int, stride, out: Optional[torch.Tens
     return out
 
 
+# ---------------------------------------------------------------- pixel folding (narrow-channel layers)
+def fold_factor(ld_in: int, ld_out: int, k, s, W: int) -> int:
+    """how many W-neighbouring pixels to view as one (1 = do not fold): rows of >= 128 bytes for TMA on both sides"""
+    if tuple(s) != (1, 1, 1) or k[2] not in (1, 3):
+        return 1
+    m = min(ld_in, ld_out)
+    if m >= 64:
+        return 1
+    f = 64 // m
+    while f > 1 and (W % f or f * max(ld_in, ld_out) > 512):
+        f //= 2
+    return f
+
+
+def folded(a: Act, f: int) -> Act:
+    """the same memory with f neighbouring W pixels as one pixel of f*ld channels (a must be a whole dense buffer)"""
+    N, T, H, W = a.dims
+    assert a.coff == 0 and W % f == 0
+    return Act(a.buf.view(N, T, H, W // f, f * a.ld), 0, f * a.ld)
+
+
+def fold_weight(w: torch.Tensor, f: int, ldo: int, ldi: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    Co, Ci, kT, kH, kW = w.shape
+    kWf = 1 if kW == 1 else 3
+    if out is None:
+        out = torch.empty((f * ldo, f * ldi, kT, kH, kWf), dtype=torch.float32, device=w.device)
+    check(lib().sfb_fold_weight(w.data_ptr(), Co, Ci, kT, kH, kW, f, ldo, ldi, out.data_ptr(), stream_ptr()), "sfb_fold_weight")
+    return out
+
+
+def unfold_wgrad(dwf: torch.Tensor, f: int, ldo: int, ldi: int, dw: torch.Tensor):
+    Co, Ci, kT, kH, kW = dw.shape
+    check(lib().sfb_unfold_wgrad(dwf.data_ptr(), Co, Ci, kT, kH, kW, f, ldo, ldi, dw.data_ptr(), stream_ptr()), "sfb_unfold_wgrad")
+    return dw
+
+
+def unfold_stats(sf: torch.Tensor, f: int, ld: int, C_: int, stats: torch.Tensor):
+    check(lib().sfb_unfold_stats(sf.data_ptr(), f, ld, C_, stats.data_ptr(), stream_ptr()), "sfb_unfold_stats")
+    return stats
+
+
 def stem_s2d_eligible(C_in, C_out, k, s, p, H, W) -> bool:
     """can the (1,7,7)/s(1,2,2)/p(0,3,3) stem take the space-to-depth row-window kernels (csrc/stem_win.cuh)?"""
     return (tuple(k) == (1, 7, 7) and tuple(s) == (1, 2, 2) and tuple(p) == (0, 3, 3) and H % 2 == 0 and W % 2 == 0
