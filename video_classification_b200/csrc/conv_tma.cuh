@@ -97,33 +97,37 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
   return v;
 }
 
-template <int BN>
+// BRES: the CTA's whole weight slice [BN][Ktot] stays resident in shared memory (loaded once; a persistent CTA works
+// on one N tile for its whole life), so a pipeline stage carries the activation boxes only.  Small-K layers were bound
+// by L2->SM traffic, of which the per-tile weight re-fetch was 1/3 (64->64 (1,3,3)) to 2/3 (64->256 pointwise).
+template <int BN, bool BRES = false>
 struct ConvTmaCfg {
-  static constexpr int kStages = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kStages = BRES ? (BN >= 128 ? 6 : 8) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8));
   static constexpr int kAStage = 128 * 128;  // 16 KB: 128 rows x (64 | 2x32 | 4x16) channels
-  static constexpr int kBStage = BN * 128;
+  static constexpr int kBStage = BRES ? 0 : BN * 128;
   static constexpr int kStage = kAStage + kBStage;
   static constexpr int kChunk = BN < 128 ? BN : 128;                  // output columns staged per pass
   static constexpr int kChunks = BN / kChunk;
   static constexpr int kStagingOff = kStages * kStage;
   static constexpr int kStagingBytes = 128 * kChunk * 2;
   static constexpr int kBarOff = kStagingOff + kStagingBytes;          // full[S], empty[S], tfull[2], tempty[2]
-  static constexpr int kHolderOff = kBarOff + (2 * kStages + 4) * 8;
+  static constexpr int kHolderOff = kBarOff + (2 * kStages + 5) * 8;   // + bres
   static constexpr int kEnd = kHolderOff + 16;
+  static constexpr int kBResOff = (kEnd + 1023) / 1024 * 1024;        // resident weights: nk blocks of [BN][128 B]
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
   // epilogue warps: one per (TMEM lane quadrant, 32-column slice of a staged chunk).  With a single warp per SM
   // sub-partition the epilogue was dependency-stall bound (ncu r1b: 38 % "wait", 21 % issuing, 1 warp / scheduler).
   static constexpr int kEpiWarps = kChunk / 8;        // 16 (BN >= 128), 8 (BN = 64), 4 (BN = 32)
   static constexpr int kEpiThreads = 32 * kEpiWarps;
   static constexpr int kThreads = 64 + kEpiThreads;
-  static size_t smem_bytes() { return 1024 + kEnd; }
+  static size_t smem_bytes(int nk = 0) { return 1024 + (BRES ? (size_t)kBResOff + (size_t)nk * BN * 128 : (size_t)kEnd); }
 };
 
-template <int BN>
-__global__ void __launch_bounds__(ConvTmaCfg<BN>::kThreads, 1)
+template <int BN, bool BRES = false>
+__global__ void __launch_bounds__(ConvTmaCfg<BN, BRES>::kThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                 const __grid_constant__ CUtensorMap tmap_o, const ConvTmaParams p) {
-  using L = ConvTmaCfg<BN>;
+  using L = ConvTmaCfg<BN, BRES>;
   constexpr int S = L::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -131,6 +135,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   uint64_t* empty_bar = full_bar + S;
   uint64_t* tfull_bar = empty_bar + S;
   uint64_t* tempty_bar = tfull_bar + 2;
+  uint64_t* bres_bar = tempty_bar + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kHolderOff);
 
   const int tid = threadIdx.x;
@@ -146,6 +151,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       mbar_init(&tfull_bar[b], 1);
       mbar_init(&tempty_bar[b], L::kEpiWarps);
     }
+    mbar_init(bres_bar, 1);
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) {
@@ -174,44 +180,49 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   if (warp == 0) {
     // ======================= TMA producer =======================
+    // One thread feeds the whole pipeline, so its per-chunk instruction count is on the critical path of every
+    // small-K / small-N layer: taps and stages advance with counters, no division inside the chunk loop.
     if (lane == 0) {
-      uint32_t g = 0;
+      if (BRES && patch0 < p.total_patches) {
+        mbar_arrive_expect_tx(bres_bar, (uint32_t)(p.nk * BN * 128));
+        for (int kc = 0; kc < p.nk; ++kc)
+          tma_load_2d_u32(smem_u32(smem + L::kBResOff) + kc * (BN * 128), &tmap_w, bres_bar, p.wk0 + kc * 64, n0);
+      }
+      const int sgn = p.transposed ? -1 : 1;
+      const uint32_t smem0 = smem_u32(smem);
+      int s = 0;
+      uint32_t ph = 1;  // parity to wait on for "stage s is free"
       for (int patch = patch0; patch < p.total_patches; patch += patch_step) {
         int q = patch;
         const int tw = q % p.tilesW; q /= p.tilesW;
         const int th = q % p.tilesH; q /= p.tilesH;
         const int tt = q % p.tilesT;
         const int n = q / p.tilesT;
-        const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
-        for (int kc = 0; kc < p.nk; ++kc, ++g) {
-          const int s = g % S;
-          const uint32_t par = ((g / S) & 1) ^ 1;
-          mbar_wait(&empty_bar[s], par, 11);
-          int nbox = 1, tap0, c0 = 0;
+        const int bw = p.transposed ? tw * p.Wt + p.pW : tw * p.Wt * p.sW - p.pW;
+        const int bh = p.transposed ? th * p.Ht + p.pH : th * p.Ht * p.sH - p.pH;
+        const int bt = p.transposed ? tt * p.Tt + p.pT : tt * p.Tt * p.sT - p.pT;
+        int kt = 0, kh = 0, kw = 0, cc = 0, tap = 0;
+        for (int kc = 0; kc < p.nk; ++kc) {
+          mbar_wait(&empty_bar[s], ph, 11);
+          const uint32_t sa = smem0 + (uint32_t)s * L::kStage;
           if (p.Cg >= 64) {
-            tap0 = kc / p.cchunks;
-            c0 = (kc - tap0 * p.cchunks) * 64;
-          } else {
-            tap0 = kc * bpc;
-            nbox = min(bpc, p.taps - tap0);
-          }
-          mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nbox * box_bytes + (uint32_t)L::kBStage);
-          const uint32_t sa = smem_u32(smem + s * L::kStage);
-          for (int b = 0; b < nbox; ++b) {
-            const int tap = tap0 + b;
-            const int kt = tap / khw;
-            const int r2 = tap - kt * khw;
-            const int kh = r2 / p.kW;
-            const int kw = r2 - kh * p.kW;
-            int cw, ch, ct;
-            if (!p.transposed) {
-              cw = w0 * p.sW + kw - p.pW; ch = h0 * p.sH + kh - p.pH; ct = t0 * p.sT + kt - p.pT;
-            } else {
-              cw = w0 + p.pW - kw; ch = h0 + p.pH - kh; ct = t0 + p.pT - kt;
+            mbar_arrive_expect_tx(&full_bar[s], box_bytes + (uint32_t)L::kBStage);
+            tma_load_5d(sa, &tmap_a, &full_bar[s], cc * 64, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
+            if (++cc == p.cchunks) {
+              cc = 0;
+              if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
             }
-            tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], c0, cw, ch, ct, n);
+          } else {
+            const int nbox = min(bpc, p.taps - tap);
+            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nbox * box_bytes + (uint32_t)L::kBStage);
+            for (int b = 0; b < nbox; ++b) {
+              tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], 0, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
+              if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
+            }
+            tap += nbox;
           }
-          tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
+          if (!BRES) tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
+          if (++s == S) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -220,32 +231,38 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
       const uint32_t span = (uint32_t)(p.box_k * 2);
-      uint32_t g = 0;
+      // descriptors = constant + offset in the 14-bit start-address field: one add per operand per MMA
+      const uint64_t adesc0 = umma_smem_desc_kmajor(smem_u32(smem), span);
+      const uint64_t bdesc0 = umma_smem_desc_kmajor(BRES ? smem_u32(smem + L::kBResOff) : smem_u32(smem) + L::kAStage, 128);
+      uint32_t aoff[4];
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const int koff = kk * 16;
+        const int sub = koff / p.box_k;
+        aoff[kk] = (uint32_t)((sub * sub_stride + (koff - sub * p.box_k) * 2) >> 4);
+      }
+      const int n_last = (p.Ktot - (p.nk - 1) * 64 + 15) >> 4;  // 16-wide K steps of the last chunk
+      int s = 0;
+      uint32_t ph = 0;
       int it = 0;
+      if (BRES && patch0 < p.total_patches) mbar_wait(bres_bar, 0, 15);
       for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
         const int buf = it & 1;
         mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
-        for (int kc = 0; kc < p.nk; ++kc, ++g) {
-          const int s = g % S;
-          mbar_wait(&full_bar[s], (g / S) & 1, 13);
+        for (int kc = 0; kc < p.nk; ++kc) {
+          mbar_wait(&full_bar[s], ph, 13);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * L::kStage);
-          const uint32_t sb = sa + L::kAStage;
+          const uint64_t ad0 = adesc0 + (uint64_t)(((uint32_t)s * L::kStage) >> 4);
+          const uint64_t bd0 = bdesc0 + (uint64_t)((BRES ? (uint32_t)kc * (BN * 128) : (uint32_t)s * L::kStage) >> 4);
+          const int nkk = kc == p.nk - 1 ? n_last : 4;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
-            const int k = kc * 64 + kk * 16;
-            if (k < p.Ktot) {
-              const int koff = kk * 16;
-              const int sub = koff / p.box_k;
-              const int within = koff - sub * p.box_k;
-              const uint64_t ad = umma_smem_desc_kmajor(sa + sub * sub_stride + within * 2, span);
-              const uint64_t bd = umma_smem_desc_kmajor(sb + kk * 32, 128);
-              umma_bf16(d_tmem, ad, bd, idesc, (kc | kk) != 0 ? 1u : 0u);
-            }
+            if (kk < nkk) umma_bf16(d_tmem, ad0 + aoff[kk], bd0 + (uint64_t)(kk * 2), idesc, (kc | kk) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);
+          if (++s == S) { s = 0; ph ^= 1; }
         }
         umma_commit(&tfull_bar[buf]);
       }

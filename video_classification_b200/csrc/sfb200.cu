@@ -311,25 +311,33 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
   *Wt = bw; *Ht = bh; *Tt = bt;
 }
 
-template <int BN>
-int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
-                    cudaStream_t st) {
-  using L = ConvTmaCfg<BN>;
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)L::smem_bytes());
+template <int BN, bool BRES>
+int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
+                         cudaStream_t st) {
+  using L = ConvTmaCfg<BN, BRES>;
+  const size_t smem = L::smem_bytes(p.nk);
+  static size_t attr_bytes = 0;
+  if (smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
-    attr_done = true;
+    attr_bytes = smem;
   }
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
   long long per_nt = num_sms() / p.n_tiles;
   if (per_nt < 1) per_nt = 1;
   if (per_nt > p.total_patches) per_nt = p.total_patches;
   const int grid = (int)per_nt * p.n_tiles;
-  conv_tma_kernel<BN><<<grid, L::kThreads, L::smem_bytes(), st>>>(ta, tw, to, p);
+  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem, st>>>(ta, tw, to, p);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
+}
+
+template <int BN>
+int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
+                    cudaStream_t st) {
+  // weights resident in shared memory when the CTA's [BN][Ktot] slice fits next to the pipeline (see ConvTmaCfg)
+  if (ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024) return launch_conv_tma_impl<BN, true>(ta, tw, to, p, st);
+  return launch_conv_tma_impl<BN, false>(ta, tw, to, p, st);
 }
 
 // Can the TMA kernel take this conv?  (everything else stays on the register-gather kernel)

@@ -36,7 +36,8 @@ constexpr int kWtBBytes = 4 * kWtRows * 128;          // 32 KB: up to 256 column
 constexpr int kWtStage = kWtABytes + kWtBBytes;       // 48 KB
 constexpr int kWtBarOff = kWtStages * kWtStage;
 constexpr int kWtHolderOff = kWtBarOff + (2 * kWtStages + 1) * 8;
-constexpr int kWtSmem = 1024 + kWtHolderOff + 16;
+constexpr int kWtUnitOff = (kWtHolderOff + 16 + 15) / 16 * 16;         // int4 per unit: (c0, kw - pW, kh - pH, kt - pT), <= 16 units
+constexpr int kWtSmem = 1024 + kWtUnitOff + 16 * 16;
 
 // MN-major operand descriptor: rows (K) are `span` bytes, 8-row groups SBO = 8*span apart, the next block of
 // span/2 MN-elements is `lbo` bytes away.
@@ -92,6 +93,16 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     tmem_alloc(tmem_holder, kTmemCols);
     tmem_relinquish();
   }
+  if (tid < nu) {  // per-unit box offsets, computed once (the producer thread must not divide per box)
+    const int khw = p.kH * p.kW;
+    const int unit = u0 + tid;
+    const int tap = unit / p.cchunks;
+    const int kt = tap / khw;
+    const int r2 = tap - kt * khw;
+    const int kh = r2 / p.kW;
+    reinterpret_cast<int4*>(smem + kWtUnitOff)[tid] =
+        make_int4((unit - tap * p.cchunks) * p.box_k, r2 - kh * p.kW - p.pW, kh - p.pH, kt - p.pT);
+  }
   // zero the operand stages once: rows a box never writes must contribute 0 (and never NaN)
   for (int i = tid; i < kWtStages * kWtStage / 16; i += blockDim.x)
     reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
@@ -100,57 +111,59 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
-  const int khw = p.kH * p.kW;
+  const int4* unit_tab = reinterpret_cast<const int4*>(smem + kWtUnitOff);
 
   if (patch_end > patch_begin) {
     if (warp == 0) {
       if (lane == 0) {
         const uint32_t tx = (uint32_t)(nblk_a * rows * 128 + nu * rows * (int)span);
-        uint32_t g = 0;
-        for (int patch = patch_begin; patch < patch_end; ++patch, ++g) {
-          int q = patch;
-          const int tw = q % p.tilesW; q /= p.tilesW;
-          const int th = q % p.tilesH; q /= p.tilesH;
-          const int tt = q % p.tilesT;
-          const int n = q / p.tilesT;
+        const uint32_t smem0 = smem_u32(smem);
+        int s = 0;
+        uint32_t ph = 1;
+        int q = patch_begin;
+        int tw = q % p.tilesW; q /= p.tilesW;
+        int th = q % p.tilesH; q /= p.tilesH;
+        int tt = q % p.tilesT;
+        int n = q / p.tilesT;
+        for (int patch = patch_begin; patch < patch_end; ++patch) {
           const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
-          const int s = g % kWtStages;
-          mbar_wait(&empty_bar[s], ((g / kWtStages) & 1) ^ 1, 21);
+          mbar_wait(&empty_bar[s], ph, 21);
           mbar_arrive_expect_tx(&full_bar[s], tx);
-          const uint32_t sa = smem_u32(smem + s * kWtStage);
+          const uint32_t sa = smem0 + (uint32_t)s * kWtStage;
           for (int b = 0; b < nblk_a; ++b)
             tma_load_5d(sa + b * (kWtRows * 128), &tmap_dy, &full_bar[s], co0 + b * 64, w0, h0, t0, n);
           const uint32_t sb = sa + kWtABytes;
+          const int xw = w0 * p.sW, xh = h0 * p.sH, xt = t0 * p.sT;
           for (int u = 0; u < nu; ++u) {
-            const int unit = u0 + u;
-            const int tap = unit / p.cchunks;
-            const int c0 = (unit - tap * p.cchunks) * p.box_k;
-            const int kt = tap / khw;
-            const int r2 = tap - kt * khw;
-            const int kh = r2 / p.kW;
-            const int kw = r2 - kh * p.kW;
-            tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], c0, w0 * p.sW + kw - p.pW, h0 * p.sH + kh - p.pH,
-                        t0 * p.sT + kt - p.pT, n);
+            const int4 ut = unit_tab[u];
+            tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], ut.x, xw + ut.y, xh + ut.z, xt + ut.w, n);
           }
+          if (++s == kWtStages) { s = 0; ph ^= 1; }
+          if (++tw == p.tilesW) { tw = 0; if (++th == p.tilesH) { th = 0; if (++tt == p.tilesT) { tt = 0; ++n; } } }
         }
       }
     } else if (warp == 1) {
       if (lane == 0) {
         const int ncols = ((nu * p.box_k + 15) >> 4) << 4;
         const uint32_t idesc = umma_idesc_bf16(128, ncols, 1, 1);
-        uint32_t g = 0;
-        for (int patch = patch_begin; patch < patch_end; ++patch, ++g) {
-          const int s = g % kWtStages;
-          mbar_wait(&full_bar[s], (g / kWtStages) & 1, 22);
+        const uint64_t adesc0 = umma_smem_desc_mnmajor(smem_u32(smem), 128, kWtRows * 128);
+        const uint64_t bdesc0 = umma_smem_desc_mnmajor(smem_u32(smem) + kWtABytes, span, bblock);
+        const uint32_t bstep = (16 * span) >> 4;
+        int s = 0;
+        uint32_t ph = 0, first = 1;
+        for (int patch = patch_begin; patch < patch_end; ++patch) {
+          mbar_wait(&full_bar[s], ph, 22);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + s * kWtStage);
-          const uint32_t sb = sa + kWtABytes;
+          uint64_t ad = adesc0 + (uint64_t)(((uint32_t)s * kWtStage) >> 4);
+          uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * kWtStage) >> 4);
           for (int kk = 0; kk < ksteps; ++kk) {
-            const uint64_t ad = umma_smem_desc_mnmajor(sa + kk * (16 * 128), 128, kWtRows * 128);
-            const uint64_t bd = umma_smem_desc_mnmajor(sb + kk * 16 * span, span, bblock);
-            umma_bf16(tmem_base, ad, bd, idesc, (g | (uint32_t)kk) != 0 ? 1u : 0u);
+            umma_bf16(tmem_base, ad, bd, idesc, first ? 0u : 1u);
+            first = 0;
+            ad += (16 * 128) >> 4;
+            bd += bstep;
           }
           umma_commit(&empty_bar[s]);
+          if (++s == kWtStages) { s = 0; ph ^= 1; }
         }
         umma_commit(done_bar);
       }
