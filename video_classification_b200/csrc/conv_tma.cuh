@@ -91,6 +91,11 @@ __device__ __forceinline__ void tma_reduce_add_5d(const void* tmap, uint32_t sme
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds_v4(uint32_t saddr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(saddr));
+  return v;
+}
 __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
@@ -274,8 +279,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     constexpr int CH = L::kChunk;
     constexpr int NCH = L::kChunks;
     constexpr int ET = L::kEpiThreads;
-    constexpr int PAIRS = CH / 2;        // bf16x2 column pairs per staged chunk
-    constexpr int TPP = ET / PAIRS;      // threads sharing one column pair (they split the rows)
     const int q4 = warp & 3;             // TMEM lane quadrant this warp may read
     const int te = tid - 64;
     const int cslice = (warp - 2) >> 2;  // 32-column slice of the chunk
@@ -283,17 +286,19 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int ww = r % p.Wt;
     const int hh = (r / p.Wt) % p.Ht;
     const int tq = r / (p.Wt * p.Ht);
-    const int ocols = p.ocols;
+    const int ocols = p.ocols;                       // 8, 16, 32 or 64
+    const int olog = 31 - __clz(ocols);
     const uint32_t rb = (uint32_t)(ocols * 2);
     const uint32_t swz = rb == 128 ? 7u : (rb == 64 ? 3u : (rb == 32 ? 1u : 0u));
     const uint32_t stg = smem_u32(smem + L::kStagingOff);
     const uint32_t sub_bytes = 128u * rb;
-    const int my_pair = te % PAIRS;
-    const int rpart = te / PAIRS;
     const int last_ch = min(NCH, (p.Co - n0 + CH - 1) / CH) - 1;
-    float ssum[NCH][2], ssq[NCH][2];
+    float ssum[NCH][8], ssq[NCH][8];
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) { ssum[c][0] = ssum[c][1] = ssq[c][0] = ssq[c][1] = 0.f; }
+    for (int c = 0; c < NCH; ++c) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { ssum[c][i] = 0.f; ssq[c][i] = 0.f; }
+    }
     bool store_pending = false;
     int it = 0;
     for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
@@ -346,8 +351,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                   uint4 pk = pack8(f);
                   if (!mv) pk = make_uint4(0, 0, 0, 0);
                   const int cl = cslice * 32 + j * 8;        // column inside the chunk
-                  const int gsub = cl / ocols;
-                  uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl - gsub * ocols) * 2);
+                  const int gsub = cl >> olog;
+                  uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl & (ocols - 1)) * 2);
                   addr ^= ((addr >> 7) & swz) << 4;
                   sts_v4(addr, pk);
                 }
@@ -364,7 +369,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           fence_proxy_async_smem();
           named_bar_sync(1, ET);
           if (te == 0) {
-            const int nsub = (min(CH, p.Co - col0) + ocols - 1) / ocols;
+            const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
             for (int gsub = 0; gsub < nsub; ++gsub) {
               if (p.reduce_add) tma_reduce_add_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
               else tma_store_5d(&tmap_o, stg + gsub * sub_bytes, col0 + gsub * ocols, w0, h0, t0, n);
@@ -372,23 +377,24 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             tma_store_commit();
             store_pending = true;
           }
-          // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros)
+          // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros): epilogue
+          //     warp e owns the 8-column group e of the chunk, its lanes split the 128 rows (16-byte reads)
           if (p.stats) {
-            const int cl = my_pair * 2;
+            const int cl = (warp - 2) * 8;
             if (col0 + cl < p.Co) {
-              const int gsub = cl / ocols;
-              const uint32_t base = stg + gsub * sub_bytes + (uint32_t)((cl - gsub * ocols) * 2);
-              float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-#pragma unroll 4
-              for (int rr = rpart; rr < 128; rr += TPP) {
-                uint32_t addr = base + (uint32_t)rr * rb;
+              const uint32_t base = stg + (cl >> olog) * sub_bytes + (uint32_t)((cl & (ocols - 1)) * 2);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                uint32_t addr = base + (uint32_t)(lane + 32 * i) * rb;
                 addr ^= ((addr >> 7) & swz) << 4;
-                const uint32_t w = lds_u32(addr);
-                const float x0 = bf16lo_to_f32(w), x1 = bf16hi_to_f32(w);
-                a0 += x0; a1 += x1;
-                b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
+                float x[8];
+                unpack8(lds_v4(addr), x);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                  ssum[ch][c] += x[c];
+                  ssq[ch][c] = fmaf(x[c], x[c], ssq[ch][c]);
+                }
               }
-              ssum[ch][0] += a0; ssum[ch][1] += a1; ssq[ch][0] += b0; ssq[ch][1] += b1;
             }
           }
         }
@@ -398,12 +404,19 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (p.stats) {
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {
-        const int col = n0 + ch * CH + my_pair * 2;
-        if (ch <= last_ch && col < p.Co) {
-          atomicAdd(p.stats + col, ssum[ch][0]);
-          atomicAdd(p.stats + col + 1, ssum[ch][1]);
-          atomicAdd(p.stats + p.Co + col, ssq[ch][0]);
-          atomicAdd(p.stats + p.Co + col + 1, ssq[ch][1]);
+        const int col = n0 + ch * CH + (warp - 2) * 8;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float a = ssum[ch][c], b = ssq[ch][c];
+#pragma unroll
+          for (int off = 16; off >= 1; off >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, off);
+            b += __shfl_xor_sync(0xffffffffu, b, off);
+          }
+          if (lane == c && ch <= last_ch && col < p.Co) {
+            atomicAdd(p.stats + col + c, a);
+            atomicAdd(p.stats + p.Co + col + c, b);
+          }
         }
       }
     }

@@ -491,8 +491,8 @@ int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int
                          int32_t T, int32_t H, int32_t W, void* out, int32_t Cs, void* stream) {
   if (!x || !out || N <= 0 || C <= 0 || T <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1) || !aligned16(out)) return SFB_ERR_BAD_ARG;
   if ((Cs != 32 && Cs != 64) || 4 * C > Cs) return SFB_ERR_BAD_ARG;
-  const long long total = (long long)N * T * (H / 2) * (W / 2) * (Cs / 8);
-  layout_input_s2d_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(
+  const long long total = (long long)N * T * (H / 2) * (W / 2);
+  layout_input_s2d_kernel<<<grid_for(total, 128, 148 * 64), 128, 0, (cudaStream_t)stream>>>(
       x, sn, sc, st, sh, sw, N, C, T, H / 2, W / 2, (__nv_bfloat16*)out, Cs);
   SFB_CHECK_LAUNCH("layout_input_s2d_kernel");
   return SFB_OK;
@@ -828,7 +828,8 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     q.total_patches = (int)tp;
     q.dW = dw;
     const int gx = (q.n_units + q.upc - 1) / q.upc;
-    const int gy = (geom->Co + 127) / 128;
+    q.mh = geom->Co > 128 ? 2 : 1;
+    const int gy = (geom->Co + 128 * q.mh - 1) / (128 * q.mh);
     long long splits = (2ll * num_sms() + gx * gy - 1) / (gx * gy);
     if (splits < 1) splits = 1;
     if (splits > q.total_patches) splits = q.total_patches;

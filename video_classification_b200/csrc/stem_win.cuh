@@ -424,28 +424,30 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 __global__ void layout_input_s2d_kernel(const float* __restrict__ x, long long sn, long long sc, long long st,
                                         long long sh, long long sw, int N, int C, int T, int H2, int W2,
                                         __nv_bfloat16* __restrict__ out, int Cs) {
+  // one thread per s2d pixel: for a fixed (channel, sub-pixel) the lanes of a warp read consecutive W positions of one
+  // fp32 plane (coalesced through L1; the other sub-pixel of the pair hits the same lines), and write 16 B each
   const int CV = Cs >> 3;
-  const long long total = (long long)N * T * H2 * W2 * CV;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int cv = (int)(idx % CV);
-    long long pix = idx / CV;
+  const long long total = (long long)N * T * H2 * W2;
+  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < total;
+       pix += (long long)gridDim.x * blockDim.x) {
     const int w = (int)(pix % W2);
     long long q = pix / W2;
     const int h = (int)(q % H2);
     q /= H2;
     const int t = (int)(q % T);
     const int n = (int)(q / T);
-    const float* src = x + n * sn + t * st;
-    float f[8];
+    const float* src = x + n * sn + t * st + (long long)(2 * h) * sh + (long long)(2 * w) * sw;
+    __nv_bfloat16* dst = out + (size_t)pix * Cs;
+    int quad = 0, c = 0;
+    for (int cv = 0; cv < CV; ++cv) {
+      float f[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int ch = cv * 8 + i;
-      const int quad = ch / C, c = ch - quad * C;
-      f[i] = quad < 4 ? __ldg(src + (long long)c * sc + (long long)(2 * h + (quad >> 1)) * sh + (long long)(2 * w + (quad & 1)) * sw)
-                      : 0.f;
+      for (int i = 0; i < 8; ++i) {
+        f[i] = quad < 4 ? __ldg(src + (long long)c * sc + (long long)(quad >> 1) * sh + (long long)(quad & 1) * sw) : 0.f;
+        if (++c == C) { c = 0; ++quad; }
+      }
+      *reinterpret_cast<uint4*>(dst + cv * 8) = pack8(f);
     }
-    *reinterpret_cast<uint4*>(out + (size_t)pix * Cs + cv * 8) = pack8(f);
   }
 }
 

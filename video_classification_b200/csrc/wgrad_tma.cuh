@@ -26,6 +26,7 @@ struct WgradTmaParams {
   int upc;                     // units per CTA (upc * box_k <= 256)
   int Wt, Ht, Tt, tilesW, tilesH, tilesT, total_patches;
   int patches_per_split;
+  int mh;                      // 128-channel halves of dY per CTA: 2 when Co > 128 (two TMEM accumulators share the X boxes)
   float* dW;
 };
 
@@ -67,15 +68,22 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   const int lane = tid & 31;
   const int u0 = blockIdx.x * p.upc;                       // first unit of this CTA
   const int nu = min(p.upc, p.n_units - u0);               // live units
-  const int co0 = blockIdx.y * 128;
+  // With one 128 x 256 accumulator a stage moves 48 KB for 4 MMAs (94 B/clk at the tensor floor, twice what TMA
+  // sustains per SM); a second accumulator (co0+128..) reuses the 32 KB of X boxes: 64 KB for 8 MMAs.
+  const int mh = p.mh;
+  const int n_stages = mh == 2 ? 3 : kWtStages;
+  const uint32_t stage_bytes = mh == 2 ? 4 * kWtRows * 128 + kWtBBytes : kWtStage;   // 64 KB | 48 KB
+  const uint32_t a_bytes = (uint32_t)mh * kWtABytes;
+  const int co0 = blockIdx.y * 128 * mh;
   const int patch_begin = blockIdx.z * p.patches_per_split;
   const int patch_end = min(p.total_patches, patch_begin + p.patches_per_split);
   const int rows = p.Wt * p.Ht * p.Tt;
   const int ksteps = (rows + 15) >> 4;
   const uint32_t span = (uint32_t)(p.box_k * 2);
   const uint32_t bblock = (uint32_t)kWtRows * span;        // bytes of one unit block
-  const int nblk_a = min(2, (p.Co - co0 + 63) / 64);
-  constexpr uint32_t kTmemCols = 256;
+  const int nblk_a = min(2 * mh, (p.Co - co0 + 63) / 64);
+  const int halves = (nblk_a + 1) >> 1;
+  constexpr uint32_t kTmemCols = 512;
 
   if (tid == 0) {
     for (int s = 0; s < kWtStages; ++s) {
@@ -129,16 +137,16 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
           const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
           mbar_wait(&empty_bar[s], ph, 21);
           mbar_arrive_expect_tx(&full_bar[s], tx);
-          const uint32_t sa = smem0 + (uint32_t)s * kWtStage;
+          const uint32_t sa = smem0 + (uint32_t)s * stage_bytes;
           for (int b = 0; b < nblk_a; ++b)
             tma_load_5d(sa + b * (kWtRows * 128), &tmap_dy, &full_bar[s], co0 + b * 64, w0, h0, t0, n);
-          const uint32_t sb = sa + kWtABytes;
+          const uint32_t sb = sa + a_bytes;
           const int xw = w0 * p.sW, xh = h0 * p.sH, xt = t0 * p.sT;
           for (int u = 0; u < nu; ++u) {
             const int4 ut = unit_tab[u];
             tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], ut.x, xw + ut.y, xh + ut.z, xt + ut.w, n);
           }
-          if (++s == kWtStages) { s = 0; ph ^= 1; }
+          if (++s == n_stages) { s = 0; ph ^= 1; }
           if (++tw == p.tilesW) { tw = 0; if (++th == p.tilesH) { th = 0; if (++tt == p.tilesT) { tt = 0; ++n; } } }
         }
       }
@@ -147,23 +155,24 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         const int ncols = ((nu * p.box_k + 15) >> 4) << 4;
         const uint32_t idesc = umma_idesc_bf16(128, ncols, 1, 1);
         const uint64_t adesc0 = umma_smem_desc_mnmajor(smem_u32(smem), 128, kWtRows * 128);
-        const uint64_t bdesc0 = umma_smem_desc_mnmajor(smem_u32(smem) + kWtABytes, span, bblock);
+        const uint64_t bdesc0 = umma_smem_desc_mnmajor(smem_u32(smem) + a_bytes, span, bblock);
         const uint32_t bstep = (16 * span) >> 4;
         int s = 0;
         uint32_t ph = 0, first = 1;
         for (int patch = patch_begin; patch < patch_end; ++patch) {
           mbar_wait(&full_bar[s], ph, 22);
           tc_fence_after();
-          uint64_t ad = adesc0 + (uint64_t)(((uint32_t)s * kWtStage) >> 4);
-          uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * kWtStage) >> 4);
+          uint64_t ad = adesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
+          uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
           for (int kk = 0; kk < ksteps; ++kk) {
             umma_bf16(tmem_base, ad, bd, idesc, first ? 0u : 1u);
+            if (halves == 2) umma_bf16(tmem_base + 256, ad + (uint64_t)(kWtABytes >> 4), bd, idesc, first ? 0u : 1u);
             first = 0;
             ad += (16 * 128) >> 4;
             bd += bstep;
           }
           umma_commit(&empty_bar[s]);
-          if (++s == kWtStages) { s = 0; ph ^= 1; }
+          if (++s == n_stages) { s = 0; ph ^= 1; }
         }
         umma_commit(done_bar);
       }
@@ -172,14 +181,16 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
       const int q4 = warp & 3;
       mbar_wait(done_bar, 0, 23);
       tc_fence_after();
-      const int co = co0 + q4 * 32 + lane;
-      const bool cov = co < p.Co;
-      float* dwrow = p.dW + (size_t)(cov ? co : 0) * p.Ci_real * p.taps;
       const int ncols = nu * p.box_k;
 #pragma unroll 1
-      for (int cc = 0; cc * 32 < ncols; ++cc) {
+      for (int hc = 0; hc * 32 < halves * 256; ++hc) {
+        const int h = hc >> 3, cc = hc & 7;
+        if (cc * 32 >= ncols) continue;
+        const int co = co0 + h * 128 + q4 * 32 + lane;
+        const bool cov = co < p.Co;
+        float* dwrow = p.dW + (size_t)(cov ? co : 0) * p.Ci_real * p.taps;
         float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cc * 32), v);
+        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(h * 256 + cc * 32), v);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
