@@ -828,7 +828,8 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     q.total_patches = (int)tp;
     q.dW = dw;
     const int gx = (q.n_units + q.upc - 1) / q.upc;
-    q.mh = geom->Co > 128 ? 2 : 1;
+    // second accumulator only where the X boxes dominate the stage traffic (many tap/channel units) and enough CTAs remain
+    q.mh = (geom->Co > 128 && q.n_units >= 2 * q.upc) ? 2 : 1;
     const int gy = (geom->Co + 128 * q.mh - 1) / (128 * q.mh);
     long long splits = (2ll * num_sms() + gx * gy - 1) / (gx * gy);
     if (splits < 1) splits = 1;
@@ -845,12 +846,14 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     if (rc) return rc;
     static bool attr_done2 = false;
     if (!attr_done2) {
-      cudaError_t e = cudaFuncSetAttribute(wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWtSmem);
+      cudaError_t e = cudaFuncSetAttribute(wgrad_tma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWtSmem);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(wgrad_tma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kWtSmem);
       if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(wgrad_tma)");
       attr_done2 = true;
     }
     dim3 grid(gx, gy, (unsigned)splits);
-    wgrad_tma_kernel<<<grid, 192, kWtSmem, st>>>(tx, tdy, q);
+    if (q.mh == 2) wgrad_tma_kernel<2><<<grid, 192, kWtSmem, st>>>(tx, tdy, q);
+    else wgrad_tma_kernel<1><<<grid, 192, kWtSmem, st>>>(tx, tdy, q);
     SFB_CHECK_LAUNCH("wgrad_tma_kernel");
     return SFB_OK;
   }

@@ -53,6 +53,7 @@ __device__ __forceinline__ uint64_t umma_smem_desc_mnmajor(uint32_t smem_addr, u
   return d;
 }
 
+template <int MH>
 __global__ void __launch_bounds__(192, 1)
 wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dy,
                  const WgradTmaParams p) {
@@ -70,10 +71,10 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   const int nu = min(p.upc, p.n_units - u0);               // live units
   // With one 128 x 256 accumulator a stage moves 48 KB for 4 MMAs (94 B/clk at the tensor floor, twice what TMA
   // sustains per SM); a second accumulator (co0+128..) reuses the 32 KB of X boxes: 64 KB for 8 MMAs.
-  const int mh = p.mh;
-  const int n_stages = mh == 2 ? 3 : kWtStages;
-  const uint32_t stage_bytes = mh == 2 ? 4 * kWtRows * 128 + kWtBBytes : kWtStage;   // 64 KB | 48 KB
-  const uint32_t a_bytes = (uint32_t)mh * kWtABytes;
+  constexpr int mh = MH;
+  constexpr int n_stages = MH == 2 ? 3 : kWtStages;
+  constexpr uint32_t stage_bytes = MH == 2 ? 4 * kWtRows * 128 + kWtBBytes : kWtStage;   // 64 KB | 48 KB
+  constexpr uint32_t a_bytes = (uint32_t)MH * kWtABytes;
   const int co0 = blockIdx.y * 128 * mh;
   const int patch_begin = blockIdx.z * p.patches_per_split;
   const int patch_end = min(p.total_patches, patch_begin + p.patches_per_split);
@@ -82,8 +83,8 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   const uint32_t span = (uint32_t)(p.box_k * 2);
   const uint32_t bblock = (uint32_t)kWtRows * span;        // bytes of one unit block
   const int nblk_a = min(2 * mh, (p.Co - co0 + 63) / 64);
-  const int halves = (nblk_a + 1) >> 1;
-  constexpr uint32_t kTmemCols = 512;
+  const int halves = MH == 2 ? (nblk_a + 1) >> 1 : 1;
+  constexpr uint32_t kTmemCols = 256 * MH;
 
   if (tid == 0) {
     for (int s = 0; s < kWtStages; ++s) {
@@ -166,7 +167,7 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
           uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
           for (int kk = 0; kk < ksteps; ++kk) {
             umma_bf16(tmem_base, ad, bd, idesc, first ? 0u : 1u);
-            if (halves == 2) umma_bf16(tmem_base + 256, ad + (uint64_t)(kWtABytes >> 4), bd, idesc, first ? 0u : 1u);
+            if (MH == 2 && halves == 2) umma_bf16(tmem_base + 256, ad + (uint64_t)(kWtABytes >> 4), bd, idesc, first ? 0u : 1u);
             first = 0;
             ad += (16 * 128) >> 4;
             bd += bstep;
