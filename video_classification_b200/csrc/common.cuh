@@ -54,6 +54,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int si
   }
 }
 
+// ---- warp-uniform role code --------------------------------------------------------------------
+// tcgen05.mma / TMA take their descriptors, coordinates and addresses from UNIFORM registers.  A role written as
+// `if (lane == 0) { loop }` is divergent code to the compiler: it keeps the operands in vector registers and wraps
+// every issue in an elect/broadcast "waterfall" loop (15 SASS instructions per MMA; ncu r1g: the one issuing thread of
+// the stem kernels was instruction-bound, 5.5 k cycles per 64-MMA tile).  Roles therefore run their loops in all 32
+// lanes with values the compiler can prove uniform (warp index through a shuffle) and predicate only the issue itself
+// on one elected lane.
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+__device__ __forceinline__ uint32_t uniform_u32(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // generic-proxy smem writes -> visible to the async proxy (TMA / tcgen05 operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");

@@ -144,7 +144,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kHolderOff);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = tid & 31;
 
   if (tid == 0) {
@@ -171,7 +171,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tmem_base = uniform_u32(*tmem_holder);
   const int rows = p.Wt * p.Ht * p.Tt;
   const uint32_t box_bytes = (uint32_t)(rows * p.box_k * 2);
   const int bpc = p.Cg >= 64 ? 1 : 64 / p.box_k;  // A boxes per 64-wide K chunk
@@ -185,92 +185,99 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   if (warp == 0) {
     // ======================= TMA producer =======================
-    // One thread feeds the whole pipeline, so its per-chunk instruction count is on the critical path of every
-    // small-K / small-N layer: taps and stages advance with counters, no division inside the chunk loop.
-    if (lane == 0) {
-      if (BRES && patch0 < p.total_patches) {
-        mbar_arrive_expect_tx(bres_bar, (uint32_t)(p.nk * BN * 128));
-        for (int kc = 0; kc < p.nk; ++kc)
-          tma_load_2d_u32(smem_u32(smem + L::kBResOff) + kc * (BN * 128), &tmap_w, bres_bar, p.wk0 + kc * 64, n0);
-      }
-      const int sgn = p.transposed ? -1 : 1;
-      const uint32_t smem0 = smem_u32(smem);
-      int s = 0;
-      uint32_t ph = 1;  // parity to wait on for "stage s is free"
-      for (int patch = patch0; patch < p.total_patches; patch += patch_step) {
-        int q = patch;
-        const int tw = q % p.tilesW; q /= p.tilesW;
-        const int th = q % p.tilesH; q /= p.tilesH;
-        const int tt = q % p.tilesT;
-        const int n = q / p.tilesT;
-        const int bw = p.transposed ? tw * p.Wt + p.pW : tw * p.Wt * p.sW - p.pW;
-        const int bh = p.transposed ? th * p.Ht + p.pH : th * p.Ht * p.sH - p.pH;
-        const int bt = p.transposed ? tt * p.Tt + p.pT : tt * p.Tt * p.sT - p.pT;
-        int kt = 0, kh = 0, kw = 0, cc = 0, tap = 0;
-        for (int kc = 0; kc < p.nk; ++kc) {
-          mbar_wait(&empty_bar[s], ph, 11);
-          const uint32_t sa = smem0 + (uint32_t)s * L::kStage;
-          if (p.Cg >= 64) {
+    // One instruction stream feeds the whole pipeline, so its per-chunk instruction count is on the critical path of
+    // every small-K / small-N layer: the loop is warp-uniform (operands in uniform registers, one elected lane
+    // issues), taps and stages advance with counters, no division inside the chunk loop.
+    const bool leader = elect_one();
+    if (BRES && patch0 < p.total_patches && leader) {
+      mbar_arrive_expect_tx(bres_bar, (uint32_t)(p.nk * BN * 128));
+      for (int kc = 0; kc < p.nk; ++kc)
+        tma_load_2d_u32(smem_u32(smem + L::kBResOff) + kc * (BN * 128), &tmap_w, bres_bar, p.wk0 + kc * 64, n0);
+    }
+    const int sgn = p.transposed ? -1 : 1;
+    const uint32_t smem0 = smem_u32(smem);
+    int s = 0;
+    uint32_t ph = 1;  // parity to wait on for "stage s is free"
+    for (int patch = patch0; patch < p.total_patches; patch += patch_step) {
+      int q = patch;
+      const int tw = q % p.tilesW; q /= p.tilesW;
+      const int th = q % p.tilesH; q /= p.tilesH;
+      const int tt = q % p.tilesT;
+      const int n = q / p.tilesT;
+      const int bw = p.transposed ? tw * p.Wt + p.pW : tw * p.Wt * p.sW - p.pW;
+      const int bh = p.transposed ? th * p.Ht + p.pH : th * p.Ht * p.sH - p.pH;
+      const int bt = p.transposed ? tt * p.Tt + p.pT : tt * p.Tt * p.sT - p.pT;
+      int kt = 0, kh = 0, kw = 0, cc = 0, tap = 0;
+      for (int kc = 0; kc < p.nk; ++kc) {
+        mbar_wait(&empty_bar[s], ph, 11);
+        const uint32_t sa = smem0 + (uint32_t)s * L::kStage;
+        if (p.Cg >= 64) {
+          if (leader) {
             mbar_arrive_expect_tx(&full_bar[s], box_bytes + (uint32_t)L::kBStage);
             tma_load_5d(sa, &tmap_a, &full_bar[s], cc * 64, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
-            if (++cc == p.cchunks) {
-              cc = 0;
-              if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
-            }
-          } else {
-            const int nbox = min(bpc, p.taps - tap);
-            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nbox * box_bytes + (uint32_t)L::kBStage);
-            for (int b = 0; b < nbox; ++b) {
-              tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], 0, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
-              if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
-            }
-            tap += nbox;
           }
-          if (!BRES) tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
-          if (++s == S) { s = 0; ph ^= 1; }
+          if (++cc == p.cchunks) {
+            cc = 0;
+            if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
+          }
+        } else {
+          const int nbox = min(bpc, p.taps - tap);
+          if (leader) mbar_arrive_expect_tx(&full_bar[s], (uint32_t)nbox * box_bytes + (uint32_t)L::kBStage);
+          for (int b = 0; b < nbox; ++b) {
+            if (leader)
+              tma_load_5d(sa + b * sub_stride, &tmap_a, &full_bar[s], 0, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
+            if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
+          }
+          tap += nbox;
         }
+        if (!BRES && leader) tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
-    // ======================= MMA issuer =======================
-    if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
-      const uint32_t span = (uint32_t)(p.box_k * 2);
-      // descriptors = constant + offset in the 14-bit start-address field: one add per operand per MMA
-      const uint64_t adesc0 = umma_smem_desc_kmajor(smem_u32(smem), span);
-      const uint64_t bdesc0 = umma_smem_desc_kmajor(BRES ? smem_u32(smem + L::kBResOff) : smem_u32(smem) + L::kAStage, 128);
-      uint32_t aoff[4];
+    // ======================= MMA issuer (warp-uniform loop, one elected lane issues) =======================
+    const bool leader = elect_one();
+    const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+    const uint32_t span = (uint32_t)(p.box_k * 2);
+    // descriptors = constant + offset in the 14-bit start-address field: one add per operand per MMA
+    const uint64_t adesc0 = umma_smem_desc_kmajor(smem_u32(smem), span);
+    const uint64_t bdesc0 = umma_smem_desc_kmajor(BRES ? smem_u32(smem + L::kBResOff) : smem_u32(smem) + L::kAStage, 128);
+    uint32_t aoff[4];
 #pragma unroll
-      for (int kk = 0; kk < 4; ++kk) {
-        const int koff = kk * 16;
-        const int sub = koff / p.box_k;
-        aoff[kk] = (uint32_t)((sub * sub_stride + (koff - sub * p.box_k) * 2) >> 4);
-      }
-      const int n_last = (p.Ktot - (p.nk - 1) * 64 + 15) >> 4;  // 16-wide K steps of the last chunk
-      int s = 0;
-      uint32_t ph = 0;
-      int it = 0;
-      if (BRES && patch0 < p.total_patches) mbar_wait(bres_bar, 0, 15);
-      for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
-        const int buf = it & 1;
-        mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
+    for (int kk = 0; kk < 4; ++kk) {
+      const int koff = kk * 16;
+      const int sub = koff / p.box_k;
+      aoff[kk] = (uint32_t)((sub * sub_stride + (koff - sub * p.box_k) * 2) >> 4);
+    }
+    const int n_last = (p.Ktot - (p.nk - 1) * 64 + 15) >> 4;  // 16-wide K steps of the last chunk
+    int s = 0;
+    uint32_t ph = 0;
+    int it = 0;
+    if (BRES && patch0 < p.total_patches) mbar_wait(bres_bar, 0, 15);
+    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
+      const int buf = it & 1;
+      mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+      for (int kc = 0; kc < p.nk; ++kc) {
+        mbar_wait(&full_bar[s], ph, 13);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
-        for (int kc = 0; kc < p.nk; ++kc) {
-          mbar_wait(&full_bar[s], ph, 13);
-          tc_fence_after();
-          const uint64_t ad0 = adesc0 + (uint64_t)(((uint32_t)s * L::kStage) >> 4);
-          const uint64_t bd0 = bdesc0 + (uint64_t)((BRES ? (uint32_t)kc * (BN * 128) : (uint32_t)s * L::kStage) >> 4);
-          const int nkk = kc == p.nk - 1 ? n_last : 4;
+        const uint64_t ad0 = adesc0 + (uint64_t)(((uint32_t)s * L::kStage) >> 4);
+        const uint64_t bd0 = bdesc0 + (uint64_t)((BRES ? (uint32_t)kc * (BN * 128) : (uint32_t)s * L::kStage) >> 4);
+        const int nkk = kc == p.nk - 1 ? n_last : 4;
+        if (leader) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             if (kk < nkk) umma_bf16(d_tmem, ad0 + aoff[kk], bd0 + (uint64_t)(kk * 2), idesc, (kc | kk) != 0 ? 1u : 0u);
           }
           umma_commit(&empty_bar[s]);
-          if (++s == S) { s = 0; ph ^= 1; }
         }
-        umma_commit(&tfull_bar[buf]);
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1; }
       }
+      if (leader) umma_commit(&tfull_bar[buf]);
+      __syncwarp();
     }
   } else {
     // ======================= epilogue (warps 2..5; TMEM lanes 32*(warp&3)..) =======================

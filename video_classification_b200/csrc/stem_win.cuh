@@ -115,7 +115,7 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   uint64_t* b_bar = tempty_bar + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(b_bar + 1);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = uniform_warp_idx(), lane = tid & 31;
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
@@ -131,44 +131,52 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tmem_base = uniform_u32(*tmem_holder);
   const int g0 = blockIdx.x * p.tiles_per_cta;
   const int g1 = min(p.total_tiles, g0 + p.tiles_per_cta);
   const uint32_t ring0 = smem_u32(smem);
 
   if (warp == 0) {
-    if (lane == 0 && g0 < g1) {
-      mbar_arrive_expect_tx(b_bar, (uint32_t)(BN * Ktot * 2));
-      for (int kc = 0; kc < nk; ++kc) tma_load_2d_u32(smem_u32(bsm) + kc * (BN * 128), &tmap_w, b_bar, kc * 64, 0);
+    // TMA producer: the loop runs warp-uniform, one elected lane issues (see common.cuh)
+    if (g0 < g1) {
+      const bool leader = elect_one();
+      if (leader) {
+        mbar_arrive_expect_tx(b_bar, (uint32_t)(BN * Ktot * 2));
+        for (int kc = 0; kc < nk; ++kc) tma_load_2d_u32(smem_u32(bsm) + kc * (BN * 128), &tmap_w, b_bar, kc * 64, 0);
+      }
       uint32_t L = 0;
-      int prev_frame = -1;
+      int frame = g0 / p.Ho, ho = g0 - frame * p.Ho;
+      bool fresh = true;  // first tile of a frame (or of the CTA): the whole 4-row window is loaded
       for (int g = g0; g < g1; ++g) {
-        const int frame = g / p.Ho, ho = g - frame * p.Ho;
-        const int r_first = frame != prev_frame ? ho - 2 : ho + 1;
-        prev_frame = frame;
-        for (int r = r_first; r <= ho + 1; ++r, ++L) {
+        for (int r = fresh ? ho - 2 : ho + 1; r <= ho + 1; ++r, ++L) {
           const int s = L % NS;
           mbar_wait(&empty_bar[s], ((L / NS) & 1) ^ 1, 31);
-          mbar_arrive_expect_tx(&full_bar[s], slot_bytes);
-          tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, r, frame);
+          if (leader) {
+            mbar_arrive_expect_tx(&full_bar[s], slot_bytes);
+            tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, r, frame);
+          }
+          __syncwarp();
         }
+        fresh = false;
+        if (++ho == p.Ho) { ho = 0; ++frame; fresh = true; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && g0 < g1) {
+    // MMA issuer: warp-uniform loop, one elected lane issues
+    if (g0 < g1) {
+      const bool leader = elect_one();
       const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
       constexpr int KS = CS / 16;
-      // One thread issues 16*KS MMAs per output row: descriptors are a constant plus a compile-time offset in the
-      // 14-bit start-address field (everything lives below 256 KB, no carry), i.e. one integer add per operand.
+      // 16*KS MMAs per output row: descriptors are a constant plus a compile-time offset in the 14-bit start-address
+      // field (everything lives below 256 KB, no carry), i.e. one integer add per operand.
       const uint64_t adesc0 = umma_smem_desc_kmajor(ring0, span);
       const uint64_t bdesc0 = umma_smem_desc_kmajor(smem_u32(bsm), 128);
       mbar_wait(b_bar, 0, 32);
       uint32_t L = 0;
-      int prev_frame = -1, it = 0;
+      int ho = g0 % p.Ho, it = 0;
+      bool fresh = true;
       for (int g = g0; g < g1; ++g, ++it) {
-        const int frame = g / p.Ho;
-        L += frame != prev_frame ? 4 : 1;
-        prev_frame = frame;
+        L += fresh ? 4 : 1;
         const int buf = it & 1;
         mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 33);
         tc_fence_after();
@@ -180,26 +188,33 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
           mbar_wait(&full_bar[s], (l / NS) & 1, 34);
           tc_fence_after();
           const uint64_t ad_slot = adesc0 + (uint64_t)((s * slot_bytes) >> 4);
+          if (leader) {
 #pragma unroll
-          for (int dw = 0; dw < 4; ++dw) {
+            for (int dw = 0; dw < 4; ++dw) {
 #pragma unroll
-            for (int ks = 0; ks < KS; ++ks) {
-              constexpr int dummy = 0; (void)dummy;
-              const int kidx = (dh * 4 + dw) * CS + ks * 16;
-              const uint32_t b_off = (uint32_t)((kidx >> 6) * (BN * 128) + (kidx & 63) * 2);
-              const uint64_t ad = ad_slot + (uint64_t)((dw * span + ks * 32) >> 4);
-              const uint64_t bd = bdesc0 + (uint64_t)(b_off >> 4);
-              umma_bf16(d_tmem, ad, bd, idesc, (dh | dw | ks) != 0 ? 1u : 0u);
+              for (int ks = 0; ks < KS; ++ks) {
+                const int kidx = (dh * 4 + dw) * CS + ks * 16;
+                const uint32_t b_off = (uint32_t)((kidx >> 6) * (BN * 128) + (kidx & 63) * 2);
+                const uint64_t ad = ad_slot + (uint64_t)((dw * span + ks * 32) >> 4);
+                const uint64_t bd = bdesc0 + (uint64_t)(b_off >> 4);
+                umma_bf16(d_tmem, ad, bd, idesc, (dh | dw | ks) != 0 ? 1u : 0u);
+              }
             }
           }
+          __syncwarp();
         }
-        const bool last_of_run = (g + 1 == g1) || ((g + 1) / p.Ho != frame);
-        if (last_of_run) {
-          for (int dh = 0; dh < 4; ++dh) umma_commit(&empty_bar[(L - 4 + dh) % NS]);
-        } else {
-          umma_commit(&empty_bar[(L - 4) % NS]);
+        fresh = false;
+        if (++ho == p.Ho) { ho = 0; fresh = true; }
+        const bool last_of_run = (g + 1 == g1) || fresh;
+        if (leader) {
+          if (last_of_run) {
+            for (int dh = 0; dh < 4; ++dh) umma_commit(&empty_bar[(L - 4 + dh) % NS]);
+          } else {
+            umma_commit(&empty_bar[(L - 4) % NS]);
+          }
+          umma_commit(&tfull_bar[buf]);
         }
-        umma_commit(&tfull_bar[buf]);
+        __syncwarp();
       }
     }
   } else {
@@ -296,7 +311,7 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   uint64_t* done_bar = bempty_bar + NB;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(done_bar + 1);
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = uniform_warp_idx(), lane = tid & 31;
   if (tid == 0) {
     for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int s = 0; s < NB; ++s) { mbar_init(&bfull_bar[s], 1); mbar_init(&bempty_bar[s], 1); }
@@ -314,7 +329,7 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tmem_base = uniform_u32(*tmem_holder);
   const int g0 = blockIdx.x * p.tiles_per_cta;
   const int g1 = min(p.total_tiles, g0 + p.tiles_per_cta);
   const uint32_t ring0 = smem_u32(smem);
@@ -322,46 +337,53 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
   if (g0 < g1) {
     if (warp == 0) {
-      if (lane == 0) {
-        uint32_t L = 0, it = 0;
-        int prev_frame = -1;
-        for (int g = g0; g < g1; ++g, ++it) {
-          const int frame = g / p.Ho, ho = g - frame * p.Ho;
-          const int r_first = frame != prev_frame ? ho - 2 : ho + 1;
-          prev_frame = frame;
-          for (int r = r_first; r <= ho + 1; ++r, ++L) {
-            const int s = L % NS;
-            mbar_wait(&empty_bar[s], ((L / NS) & 1) ^ 1, 41);
+      // TMA producer: warp-uniform loop, one elected lane issues (see common.cuh)
+      const bool leader = elect_one();
+      uint32_t L = 0, it = 0;
+      int frame = g0 / p.Ho, ho = g0 - frame * p.Ho;
+      bool fresh = true;
+      for (int g = g0; g < g1; ++g, ++it) {
+        for (int r = fresh ? ho - 2 : ho + 1; r <= ho + 1; ++r, ++L) {
+          const int s = L % NS;
+          mbar_wait(&empty_bar[s], ((L / NS) & 1) ^ 1, 41);
+          if (leader) {
             mbar_arrive_expect_tx(&full_bar[s], slot_bytes);
             tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, r, frame);
           }
-          const int sb = it % NB;
-          mbar_wait(&bempty_bar[sb], ((it / NB) & 1) ^ 1, 42);
+          __syncwarp();
+        }
+        const int sb = it % NB;
+        mbar_wait(&bempty_bar[sb], ((it / NB) & 1) ^ 1, 42);
+        if (leader) {
           mbar_arrive_expect_tx(&bfull_bar[sb], bslot_bytes);
           tma_load_4d(bring0 + sb * bslot_bytes, &tmap_dy, &bfull_bar[sb], 0, 0, ho, frame);
         }
+        __syncwarp();
+        fresh = false;
+        if (++ho == p.Ho) { ho = 0; ++frame; fresh = true; }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        const uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
-        const uint64_t adesc0 = umma_smem_desc_mnmajor(ring0, span, span);       // next M block = next pixel (dw tap)
-        const uint64_t bdesc0 = umma_smem_desc_mnmajor(bring0, span_b, bslot_bytes);
-        uint32_t L = 0, it = 0;
-        int prev_frame = -1;
-        for (int g = g0; g < g1; ++g, ++it) {
-          const int frame = g / p.Ho;
-          L += frame != prev_frame ? 4 : 1;
-          prev_frame = frame;
-          const int sb = it % NB;
-          mbar_wait(&bfull_bar[sb], (it / NB) & 1, 43);
-          const uint64_t bd_slot = bdesc0 + (uint64_t)((sb * bslot_bytes) >> 4);
+      // MMA issuer: warp-uniform loop, one elected lane issues
+      const bool leader = elect_one();
+      const uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
+      const uint64_t adesc0 = umma_smem_desc_mnmajor(ring0, span, span);       // next M block = next pixel (dw tap)
+      const uint64_t bdesc0 = umma_smem_desc_mnmajor(bring0, span_b, bslot_bytes);
+      uint32_t L = 0, it = 0;
+      int ho = g0 % p.Ho;
+      bool fresh = true;
+      for (int g = g0; g < g1; ++g, ++it) {
+        L += fresh ? 4 : 1;
+        const int sb = it % NB;
+        mbar_wait(&bfull_bar[sb], (it / NB) & 1, 43);
+        const uint64_t bd_slot = bdesc0 + (uint64_t)((sb * bslot_bytes) >> 4);
 #pragma unroll
-          for (int dh = 0; dh < 4; ++dh) {
-            const uint32_t l = L - 4 + dh;
-            const int s = l % NS;
-            mbar_wait(&full_bar[s], (l / NS) & 1, 44);
-            tc_fence_after();
-            const uint64_t ad_slot = adesc0 + (uint64_t)((s * slot_bytes) >> 4);
+        for (int dh = 0; dh < 4; ++dh) {
+          const uint32_t l = L - 4 + dh;
+          const int s = l % NS;
+          mbar_wait(&full_bar[s], (l / NS) & 1, 44);
+          tc_fence_after();
+          const uint64_t ad_slot = adesc0 + (uint64_t)((s * slot_bytes) >> 4);
+          if (leader) {
 #pragma unroll
             for (int gi = 0; gi < G; ++gi) {
               const uint32_t d_tmem = tmem_base + (uint32_t)((dh * G + gi) * BN);
@@ -374,7 +396,12 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
               }
             }
           }
-          const bool last_of_run = (g + 1 == g1) || ((g + 1) / p.Ho != frame);
+          __syncwarp();
+        }
+        fresh = false;
+        if (++ho == p.Ho) { ho = 0; fresh = true; }
+        const bool last_of_run = (g + 1 == g1) || fresh;
+        if (leader) {
           if (last_of_run) {
             for (int dh = 0; dh < 4; ++dh) umma_commit(&empty_bar[(L - 4 + dh) % NS]);
           } else {
@@ -382,8 +409,10 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
           }
           umma_commit(&bempty_bar[sb]);
         }
-        umma_commit(done_bar);
+        __syncwarp();
       }
+      if (leader) umma_commit(done_bar);
+      __syncwarp();
     } else {
       // epilogue: TMEM lane m = (dw block j, s2d channel cs); columns = co, per (dh, group)
       const int q4 = warp & 3;

@@ -37,8 +37,7 @@ constexpr int kWtBBytes = 4 * kWtRows * 128;          // 32 KB: up to 256 column
 constexpr int kWtStage = kWtABytes + kWtBBytes;       // 48 KB
 constexpr int kWtBarOff = kWtStages * kWtStage;
 constexpr int kWtHolderOff = kWtBarOff + (2 * kWtStages + 1) * 8;
-constexpr int kWtUnitOff = (kWtHolderOff + 16 + 15) / 16 * 16;         // int4 per unit: (c0, kw - pW, kh - pH, kt - pT), <= 16 units
-constexpr int kWtSmem = 1024 + kWtUnitOff + 16 * 16;
+constexpr int kWtSmem = 1024 + kWtHolderOff + 16;
 
 // MN-major operand descriptor: rows (K) are `span` bytes, 8-row groups SBO = 8*span apart, the next block of
 // span/2 MN-elements is `lbo` bytes away.
@@ -65,7 +64,7 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + kWtHolderOff);
 
   const int tid = threadIdx.x;
-  const int warp = tid >> 5;
+  const int warp = uniform_warp_idx();
   const int lane = tid & 31;
   const int u0 = blockIdx.x * p.upc;                       // first unit of this CTA
   const int nu = min(p.upc, p.n_units - u0);               // live units
@@ -102,16 +101,6 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
     tmem_alloc(tmem_holder, kTmemCols);
     tmem_relinquish();
   }
-  if (tid < nu) {  // per-unit box offsets, computed once (the producer thread must not divide per box)
-    const int khw = p.kH * p.kW;
-    const int unit = u0 + tid;
-    const int tap = unit / p.cchunks;
-    const int kt = tap / khw;
-    const int r2 = tap - kt * khw;
-    const int kh = r2 / p.kW;
-    reinterpret_cast<int4*>(smem + kWtUnitOff)[tid] =
-        make_int4((unit - tap * p.cchunks) * p.box_k, r2 - kh * p.kW - p.pW, kh - p.pH, kt - p.pT);
-  }
   // zero the operand stages once: rows a box never writes must contribute 0 (and never NaN)
   for (int i = tid; i < kWtStages * kWtStage / 16; i += blockDim.x)
     reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
@@ -119,52 +108,61 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_holder;
-  const int4* unit_tab = reinterpret_cast<const int4*>(smem + kWtUnitOff);
+  const uint32_t tmem_base = uniform_u32(*tmem_holder);
 
   if (patch_end > patch_begin) {
     if (warp == 0) {
-      if (lane == 0) {
-        const uint32_t tx = (uint32_t)(nblk_a * rows * 128 + nu * rows * (int)span);
-        const uint32_t smem0 = smem_u32(smem);
-        int s = 0;
-        uint32_t ph = 1;
-        int q = patch_begin;
-        int tw = q % p.tilesW; q /= p.tilesW;
-        int th = q % p.tilesH; q /= p.tilesH;
-        int tt = q % p.tilesT;
-        int n = q / p.tilesT;
-        for (int patch = patch_begin; patch < patch_end; ++patch) {
-          const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
-          mbar_wait(&empty_bar[s], ph, 21);
+      // TMA producer: warp-uniform loop (operands in uniform registers), one elected lane issues; taps and patches
+      // advance with counters -- no division and no table lookup per box.
+      const bool leader = elect_one();
+      const uint32_t tx = (uint32_t)(nblk_a * rows * 128 + nu * rows * (int)span);
+      const uint32_t smem0 = smem_u32(smem);
+      const int khw = p.kH * p.kW;
+      const int tap0 = u0 / p.cchunks, cc0 = u0 - tap0 * p.cchunks;
+      const int kt0 = tap0 / khw, kh0 = (tap0 - kt0 * khw) / p.kW, kw0 = tap0 - kt0 * khw - kh0 * p.kW;
+      int s = 0;
+      uint32_t ph = 1;
+      int q = patch_begin;
+      int tw = q % p.tilesW; q /= p.tilesW;
+      int th = q % p.tilesH; q /= p.tilesH;
+      int tt = q % p.tilesT;
+      int n = q / p.tilesT;
+      for (int patch = patch_begin; patch < patch_end; ++patch) {
+        const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
+        mbar_wait(&empty_bar[s], ph, 21);
+        const uint32_t sa = smem0 + (uint32_t)s * stage_bytes;
+        if (leader) {
           mbar_arrive_expect_tx(&full_bar[s], tx);
-          const uint32_t sa = smem0 + (uint32_t)s * stage_bytes;
           for (int b = 0; b < nblk_a; ++b)
             tma_load_5d(sa + b * (kWtRows * 128), &tmap_dy, &full_bar[s], co0 + b * 64, w0, h0, t0, n);
-          const uint32_t sb = sa + a_bytes;
-          const int xw = w0 * p.sW, xh = h0 * p.sH, xt = t0 * p.sT;
-          for (int u = 0; u < nu; ++u) {
-            const int4 ut = unit_tab[u];
-            tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], ut.x, xw + ut.y, xh + ut.z, xt + ut.w, n);
-          }
-          if (++s == n_stages) { s = 0; ph ^= 1; }
-          if (++tw == p.tilesW) { tw = 0; if (++th == p.tilesH) { th = 0; if (++tt == p.tilesT) { tt = 0; ++n; } } }
         }
+        const uint32_t sb = sa + a_bytes;
+        const int xw = w0 * p.sW - p.pW, xh = h0 * p.sH - p.pH, xt = t0 * p.sT - p.pT;
+        int cc = cc0, kw = kw0, kh = kh0, kt = kt0;
+        for (int u = 0; u < nu; ++u) {
+          if (leader) tma_load_5d(sb + u * bblock, &tmap_x, &full_bar[s], cc * p.box_k, xw + kw, xh + kh, xt + kt, n);
+          if (++cc == p.cchunks) { cc = 0; if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } } }
+        }
+        __syncwarp();
+        if (++s == n_stages) { s = 0; ph ^= 1; }
+        if (++tw == p.tilesW) { tw = 0; if (++th == p.tilesH) { th = 0; if (++tt == p.tilesT) { tt = 0; ++n; } } }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        const int ncols = ((nu * p.box_k + 15) >> 4) << 4;
-        const uint32_t idesc = umma_idesc_bf16(128, ncols, 1, 1);
-        const uint64_t adesc0 = umma_smem_desc_mnmajor(smem_u32(smem), 128, kWtRows * 128);
-        const uint64_t bdesc0 = umma_smem_desc_mnmajor(smem_u32(smem) + a_bytes, span, bblock);
-        const uint32_t bstep = (16 * span) >> 4;
-        int s = 0;
-        uint32_t ph = 0, first = 1;
-        for (int patch = patch_begin; patch < patch_end; ++patch) {
-          mbar_wait(&full_bar[s], ph, 22);
-          tc_fence_after();
-          uint64_t ad = adesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
-          uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
+      // MMA issuer: warp-uniform loop, one elected lane issues
+      const bool leader = elect_one();
+      const int ncols = ((nu * p.box_k + 15) >> 4) << 4;
+      const uint32_t idesc = umma_idesc_bf16(128, ncols, 1, 1);
+      const uint64_t adesc0 = umma_smem_desc_mnmajor(smem_u32(smem), 128, kWtRows * 128);
+      const uint64_t bdesc0 = umma_smem_desc_mnmajor(smem_u32(smem) + a_bytes, span, bblock);
+      const uint32_t bstep = (16 * span) >> 4;
+      int s = 0;
+      uint32_t ph = 0, first = 1;
+      for (int patch = patch_begin; patch < patch_end; ++patch) {
+        mbar_wait(&full_bar[s], ph, 22);
+        tc_fence_after();
+        uint64_t ad = adesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
+        uint64_t bd = bdesc0 + (uint64_t)(((uint32_t)s * stage_bytes) >> 4);
+        if (leader) {
           for (int kk = 0; kk < ksteps; ++kk) {
             umma_bf16(tmem_base, ad, bd, idesc, first ? 0u : 1u);
             if (MH == 2 && halves == 2) umma_bf16(tmem_base + 256, ad + (uint64_t)(kWtABytes >> 4), bd, idesc, first ? 0u : 1u);
@@ -173,10 +171,13 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
             bd += bstep;
           }
           umma_commit(&empty_bar[s]);
-          if (++s == n_stages) { s = 0; ph ^= 1; }
         }
-        umma_commit(done_bar);
+        first = 0;
+        __syncwarp();
+        if (++s == n_stages) { s = 0; ph ^= 1; }
       }
+      if (leader) umma_commit(done_bar);
+      __syncwarp();
     } else {
       // ---------------- epilogue: TMEM lane = co, columns = (unit, channel) ----------------
       const int q4 = warp & 3;
