@@ -40,6 +40,14 @@ LAYERS = [
     ("slow_res2_b_64_64", "wgrad", 8, 56, 56, 64, 64, (1, 3, 3), (1, 1, 1)),
     ("slow_res4_a_1280_256", "fprop_stats", 8, 14, 14, 1280, 256, (3, 1, 1), (1, 1, 1)),
     ("slow_res4_a_1280_256", "wgrad", 8, 14, 14, 1280, 256, (3, 1, 1), (1, 1, 1)),
+    ("slow_res4_a_1024_256", "wgrad", 8, 14, 14, 1024, 256, (3, 1, 1), (1, 1, 1)),
+    ("slow_res4_b_256_256", "wgrad", 8, 14, 14, 256, 256, (1, 3, 3), (1, 1, 1)),
+    ("slow_res4_b_256_256", "fprop_stats", 8, 14, 14, 256, 256, (1, 3, 3), (1, 1, 1)),
+    ("slow_res4_c_256_1024", "wgrad", 8, 14, 14, 256, 1024, (1, 1, 1), (1, 1, 1)),
+    ("slow_res4_c_256_1024", "fprop_stats", 8, 14, 14, 256, 1024, (1, 1, 1), (1, 1, 1)),
+    ("slow_res5_c_512_2048", "wgrad", 8, 7, 7, 512, 2048, (1, 1, 1), (1, 1, 1)),
+    ("slow_res3_c_128_512", "fprop_stats", 8, 28, 28, 128, 512, (1, 1, 1), (1, 1, 1)),
+    ("slow_res3_c_128_512", "dgrad", 8, 28, 28, 128, 512, (1, 1, 1), (1, 1, 1)),
     ("slow_res3_b_128_128_s2", "dgrad", 8, 56, 56, 128, 128, (1, 3, 3), (1, 2, 2)),
     ("slow_res3_s_320_512_s2", "dgrad_acc", 8, 56, 56, 320, 512, (1, 1, 1), (1, 2, 2)),
     ("fast_res2_b_8_8", "fprop_stats", 32, 56, 56, 8, 8, (1, 3, 3), (1, 1, 1)),

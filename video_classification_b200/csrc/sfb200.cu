@@ -814,6 +814,7 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     q.n_units = p.taps * q.cchunks;
     q.upc = 256 / q.box_k;
     if (q.upc > q.n_units) q.upc = q.n_units;
+    q.upc = (q.n_units + (q.n_units + q.upc - 1) / q.upc - 1) / ((q.n_units + q.upc - 1) / q.upc);  // same CTA count, even split (9 units: 3+3+3, not 4+4+1)
     int gW = geom->Wi, gH = geom->Hi, gT = geom->Ti, gN = geom->N;
     const bool pointwise = p.taps == 1 && geom->sT == 1 && geom->sH == 1 && geom->sW == 1 && geom->pT == 0 &&
                            geom->pH == 0 && geom->pW == 0;
@@ -831,7 +832,8 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     // second accumulator only where the X boxes dominate the stage traffic (many tap/channel units) and enough CTAs remain
     q.mh = (geom->Co > 128 && q.n_units >= 2 * q.upc) ? 2 : 1;
     const int gy = (geom->Co + 128 * q.mh - 1) / (128 * q.mh);
-    long long splits = (2ll * num_sms() + gx * gy - 1) / (gx * gy);
+    static const int waves_x2 = getenv("SFB_WGRAD_WAVES_X2") ? atoi(getenv("SFB_WGRAD_WAVES_X2")) : 4;  // tuning knob: CTAs per SM, in halves
+    long long splits = ((long long)waves_x2 * num_sms() / 2 + gx * gy - 1) / (gx * gy);
     if (splits < 1) splits = 1;
     if (splits > q.total_patches) splits = q.total_patches;
     q.patches_per_split = (int)((q.total_patches + splits - 1) / splits);

@@ -180,29 +180,42 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
       __syncwarp();
     } else {
       // ---------------- epilogue: TMEM lane = co, columns = (unit, channel) ----------------
+      // A thread reads one co row of the accumulator, but in the OIDHW gradient consecutive addresses run along
+      // (channel, tap) of ONE co: adding straight from the TMEM layout makes every lane of an atomic hit its own
+      // line (32 sectors per instruction; the tail of 65 k scattered atomics per CTA was longer than the MMA phase
+      // of the small-map layers).  Each warp therefore transposes its 32 x 32 block through shared memory (the
+      // operand stages are idle by now) and adds with lane = channel: `taps` floats apart, 1 (pointwise) to 9 lines.
       const int q4 = warp & 3;
       mbar_wait(done_bar, 0, 23);
       tc_fence_after();
       const int ncols = nu * p.box_k;
+      float* scratch = reinterpret_cast<float*>(smem) + (warp - 2) * (32 * 33);
+      const size_t co_stride = (size_t)p.Ci_real * p.taps;
 #pragma unroll 1
       for (int hc = 0; hc * 32 < halves * 256; ++hc) {
         const int h = hc >> 3, cc = hc & 7;
         if (cc * 32 >= ncols) continue;
-        const int co = co0 + h * 128 + q4 * 32 + lane;
-        const bool cov = co < p.Co;
-        float* dwrow = p.dW + (size_t)(cov ? co : 0) * p.Ci_real * p.taps;
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(h * 256 + cc * 32), v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int col = cc * 32 + i;
-          const int u = col / p.box_k;
-          const int unit = u0 + u;
-          const int tap = unit / p.cchunks;
-          const int c = (unit - tap * p.cchunks) * p.box_k + (col - u * p.box_k);
-          if (cov && col < ncols && c < p.Ci_real) atomicAdd(dwrow + (size_t)c * p.taps + tap, v[i]);
+        for (int i = 0; i < 32; ++i) scratch[lane * 33 + i] = v[i];
+        __syncwarp();
+        // this lane's column of the block -> (tap, channel) of the gradient
+        const int col = cc * 32 + lane;
+        const int u = col / p.box_k;
+        const int unit = u0 + u;
+        const int tap = unit / p.cchunks;
+        const int c = (unit - tap * p.cchunks) * p.box_k + (col - u * p.box_k);
+        const bool cv = col < ncols && c < p.Ci_real;
+        const int co_b = co0 + h * 128 + q4 * 32;
+        float* dst = p.dW + (size_t)co_b * co_stride + (size_t)(cv ? c : 0) * p.taps + tap;
+        const int nrows = min(32, p.Co - co_b);
+        if (cv) {
+#pragma unroll 4
+          for (int rr = 0; rr < nrows; ++rr) atomicAdd(dst + (size_t)rr * co_stride, scratch[rr * 33 + lane]);
         }
+        __syncwarp();
       }
     }
   }
