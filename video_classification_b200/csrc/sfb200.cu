@@ -7,6 +7,7 @@
 #include "stem_win.cuh"
 #include "elementwise.cuh"
 
+#include <algorithm>
 #include <array>
 #include <atomic>
 #include <cstdio>
@@ -832,10 +833,19 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     // second accumulator only where the X boxes dominate the stage traffic (many tap/channel units) and enough CTAs remain
     q.mh = (geom->Co > 128 && q.n_units >= 2 * q.upc) ? 2 : 1;
     const int gy = (geom->Co + 128 * q.mh - 1) / (128 * q.mh);
-    static const int waves_x2 = getenv("SFB_WGRAD_WAVES_X2") ? atoi(getenv("SFB_WGRAD_WAVES_X2")) : 4;  // tuning knob: CTAs per SM, in halves
-    long long splits = ((long long)waves_x2 * num_sms() / 2 + gx * gy - 1) / (gx * gy);
-    if (splits < 1) splits = 1;
-    if (splits > q.total_patches) splits = q.total_patches;
+    // Split of the pixel reduction over blockIdx.z: one CTA per SM at a time, so the launch runs in
+    // rounds = ceil(CTAs / SMs) and every CTA pays a fixed cost (operand-stage zeroing, TMEM allocation, pipeline fill,
+    // the atomic epilogue ~ `fixed` patches of MMA time).  Pick the split with the least rounds * (patches + fixed).
+    const int fixed = q.mh == 2 ? 32 : 48;  // measured insensitive between 16 and 96
+    const int gxy = gx * gy;
+    long long splits = 1;
+    double best_cost = 1e30;
+    const int max_splits = (int)std::min<long long>(q.total_patches, (4ll * num_sms() + gxy - 1) / gxy);
+    for (int sp = 1; sp <= max_splits; ++sp) {
+      const long long rounds = ((long long)gxy * sp + num_sms() - 1) / num_sms();
+      const double cost = (double)rounds * ((double)((q.total_patches + sp - 1) / sp) + fixed);
+      if (cost < best_cost) { best_cost = cost; splits = sp; }
+    }
     q.patches_per_split = (int)((q.total_patches + splits - 1) / splits);
     splits = (q.total_patches + q.patches_per_split - 1) / q.patches_per_split;
     CUtensorMap tx, tdy;
