@@ -172,14 +172,17 @@ int sfb_bn_fold(const float* gamma, const float* beta, const float* running_mean
  * shortcut = r*r_scale + r_shift when r_scale != NULL (branch1_conv+branch1_norm), else r. */
 int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift,
                     const void* r, int32_t r_ld, int32_t r_coff, const float* r_scale, const float* r_shift,
-                    void* out, int32_t o_ld, int32_t o_coff, int64_t M, int32_t C, int32_t relu, void* stream);
+                    void* out, int32_t o_ld, int32_t o_coff, uint8_t* mask_bits, int64_t M, int32_t C, int32_t relu,
+                    void* stream);
 
 /* BatchNorm3d(+ReLU) backward, phase 1: per-channel reductions accumulated (atomically) into
  * dgamma/dbeta:  g = dz * [relu ? (y*scale+shift > 0) : 1] ;  dbeta += sum g ; dgamma += sum g*xhat.
- * mask_src: optional bf16 tensor whose sign gives the ReLU mask instead (block output O). */
+ * mask_src: optional bf16 tensor whose sign gives the ReLU mask instead (block output O).
+ * mask_bits: optional packed mask [M][C/8] written by sfb_bn_add_relu (bit i of byte cv = channel 8*cv+i); wins over
+ * mask_src: the residual tail's backward then reads one byte per 8 channels instead of the block output. */
 int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff,
                       const void* y, int32_t y_ld, int32_t y_coff,
-                      const void* mask_src, int32_t m_ld, int32_t m_coff,
+                      const void* mask_src, int32_t m_ld, int32_t m_coff, const uint8_t* mask_bits,
                       const float* scale, const float* shift, const float* mean, const float* invstd,
                       int32_t relu, int64_t M, int32_t C, float* dgamma, float* dbeta, void* stream);
 
@@ -187,7 +190,7 @@ int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff,
  * If g_out != NULL also writes g (masked dz) there (identity-shortcut gradient). */
 int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff,
                      const void* y, int32_t y_ld, int32_t y_coff,
-                     const void* mask_src, int32_t m_ld, int32_t m_coff,
+                     const void* mask_src, int32_t m_ld, int32_t m_coff, const uint8_t* mask_bits,
                      const float* scale, const float* shift, const float* mean, const float* invstd,
                      const float* gamma, const float* dgamma, const float* dbeta,
                      int32_t relu, int64_t M, int32_t C,

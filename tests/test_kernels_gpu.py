@@ -77,7 +77,8 @@ def test_bn_add_relu(C_, with_rbn):
     s, b = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)
     rs, rb = (torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)) if with_rbn else (None, None)
     out = Act.empty(2, 3, 6, 6, C_ + 16, coff=16, C=C_, zero=True)
-    ops.bn_add_relu(ya, s, b, ra, rs, rb, out)
+    bits = torch.zeros(2 * 3 * 6 * 6, C_ // 8, dtype=torch.uint8, device=DEV)
+    ops.bn_add_relu(ya, s, b, ra, rs, rb, out, mask_bits=bits)
     bc = lambda t: t.view(1, -1, 1, 1, 1)
     rr = kc.from_act(ra)
     if with_rbn:
@@ -85,9 +86,14 @@ def test_bn_add_relu(C_, with_rbn):
     ref = torch.relu(kc.from_act(ya) * bc(s) + bc(b) + rr)
     assert kc.relerr(kc.from_act(out), ref) < 6e-3
     assert out.buf[..., :16].abs().max() == 0
+    # packed ReLU mask: bit i of byte cv = (out[..., 8*cv+i] > 0), exactly
+    o = out.torch_view().reshape(-1, C_ // 8, 8) > 0
+    w = (2 ** torch.arange(8, device=DEV, dtype=torch.int32)).view(1, 1, 8)
+    assert torch.equal(bits, (o.to(torch.int32) * w).sum(-1).to(torch.uint8))
 
 
-@pytest.mark.parametrize("C_,relu,use_mask", [(64, True, False), (256, True, True), (8, False, False), (1280, True, False)])
+@pytest.mark.parametrize("C_,relu,use_mask", [(64, True, False), (256, True, True), (8, False, False), (1280, True, False),
+                                              (256, True, "bits"), (32, True, "bits")])
 def test_bn_bwd(C_, relu, use_mask):
     N, T, H, W = 2, 3, 6, 6
     y = (torch.randn(N, C_, T, H, W, device=DEV) * 1.5 + 0.3)
@@ -105,12 +111,17 @@ def test_bn_bwd(C_, relu, use_mask):
     mean, var, invstd = _bn_ref(yq.detach(), gamma, beta)
     scale = (gamma * invstd).detach()
     shift = (beta - mean * gamma * invstd).detach()
-    mask = kc.to_act(z.detach()) if use_mask else None
+    mask = kc.to_act(z.detach()) if use_mask is True else None
+    bits = None
+    if use_mask == "bits":  # packed mask as the forward residual tail writes it
+        o = z.detach().permute(0, 2, 3, 4, 1).reshape(-1, C_ // 8, 8) > 0
+        w = (2 ** torch.arange(8, device=DEV, dtype=torch.int32)).view(1, 1, 8)
+        bits = (o.to(torch.int32) * w).sum(-1).to(torch.uint8).contiguous()
     dgamma, dbeta = torch.zeros(C_, device=DEV), torch.zeros(C_, device=DEV)
-    ops.bn_bwd_reduce(dza, ya, mask, scale, shift, mean, invstd, relu, dgamma, dbeta)
+    ops.bn_bwd_reduce(dza, ya, mask, scale, shift, mean, invstd, relu, dgamma, dbeta, mask_bits=bits)
     dy = Act.empty(N, T, H, W, C_)
     gout = Act.empty(N, T, H, W, C_)
-    ops.bn_bwd_apply(dza, ya, mask, scale, shift, mean, invstd, gamma.detach(), dgamma, dbeta, relu, dy, gout)
+    ops.bn_bwd_apply(dza, ya, mask, scale, shift, mean, invstd, gamma.detach(), dgamma, dbeta, relu, dy, gout, mask_bits=bits)
     torch.cuda.synchronize()
     assert kc.relerr(dgamma, gamma.grad) < 1e-2
     assert kc.relerr(dbeta, beta.grad) < 1e-2

@@ -60,6 +60,8 @@ LAYERS = [
     ("lateral1_32_64_s4", "dgrad_acc", 32, 56, 56, 32, 64, (3, 1, 1), (4, 1, 1)),
     ("bn_bwd_256", "bn_bwd", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
     ("bn_apply_256", "bn_apply", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
+    ("bn_tail_256", "bn_tail", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
+    ("bn_tail_bwd_256", "bn_tail_bwd", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
 ]
 
 
@@ -124,6 +126,30 @@ def run_layer(N, spec, reps):
             ops.bn_bwd_reduce(dz, y, None, sc, sh, mean, inv, True, dga, dbe)
             ops.bn_bwd_apply(dz, y, None, sc, sh, mean, inv, gam, dga, dbe, True, dy)
         flops, bytes_ = 0.0, 5 * out_b  # reduce reads dz,y ; apply reads dz,y writes dy
+    elif kind in ("bn_tail", "bn_tail_bwd"):
+        # residual tail O = relu(bn(yc) + X) with the packed ReLU mask, and its backward (reduce + apply with g_out)
+        C_ = Co
+        sc, sh = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)
+        mean, inv = torch.randn(C_, device=DEV), torch.rand(C_, device=DEV) + 0.5
+        gam = torch.rand(C_, device=DEV) + 0.5
+        dga, dbe = torch.zeros(C_, device=DEV), torch.zeros(C_, device=DEV)
+        X = Act.empty(N, To, Ho, Wo, C_)
+        X.buf.normal_()
+        O = Act.empty(N, To, Ho, Wo, C_)
+        bits = torch.zeros(M * C_ // 8, dtype=torch.uint8, device=DEV)
+        if kind == "bn_tail":
+            fn = lambda: ops.bn_add_relu(y, sc, sh, X, None, None, O, mask_bits=bits)
+            flops, bytes_ = 0.0, 3 * out_b
+        else:
+            ops.bn_add_relu(y, sc, sh, X, None, None, O, mask_bits=bits)
+            dO = X  # any gradient-like tensor
+            dy = Act.empty(N, To, Ho, Wo, C_)
+            gX = Act.empty(N, To, Ho, Wo, C_)
+
+            def fn():
+                ops.bn_bwd_reduce(dO, y, None, sc, sh, mean, inv, True, dga, dbe, mask_bits=bits)
+                ops.bn_bwd_apply(dO, y, None, sc, sh, mean, inv, gam, dga, dbe, True, dy, gX, mask_bits=bits)
+            flops, bytes_ = 0.0, 6 * out_b  # reduce reads dO,yc ; apply reads dO,yc writes dyc,gX
     elif kind == "bn_apply":
         C_ = Co
         sc, sh = torch.rand(C_, device=DEV) + 0.5, torch.randn(C_, device=DEV)

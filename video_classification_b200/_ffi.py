@@ -44,9 +44,9 @@ SIGNATURES = {
     "sfb_conv_wgrad": [C.POINTER(ConvGeom), _vp, C.POINTER(Prologue), _vp, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_bn_finalize": [_vp, _i32, _i64, _vp, _vp, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "sfb_bn_fold": [_vp, _vp, _vp, _vp, _f32, _i32, _vp, _vp, _vp],
-    "sfb_bn_add_relu": [_vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _i64, _i32, _i32, _vp],
-    "sfb_bn_bwd_reduce": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _vp, _vp],
-    "sfb_bn_bwd_apply": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+    "sfb_bn_add_relu": [_vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp, _i32, _i32, _vp, _i64, _i32, _i32, _vp],
+    "sfb_bn_bwd_reduce": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _vp, _vp],
+    "sfb_bn_bwd_apply": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                          _i32, _i64, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp],
     "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
     "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],

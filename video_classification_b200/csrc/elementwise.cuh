@@ -222,38 +222,73 @@ __global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __r
 }
 
 // ---- residual tail: out = relu(y*s+b + (r*rs+rb | r)) -------------------------------------------------
-__global__ void bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, View r,
-                                   const float* __restrict__ r_scale, const float* __restrict__ r_shift, ViewW out,
-                                   long long M, int C, int relu) {
+// block = (CV channel-vectors) x (RL row lanes): a thread keeps its 8 channels' constants in registers and has
+// kTailUnroll rows of every operand in flight (one 16-byte load per row and tensor was latency-bound at 75 % of HBM).
+// mask_bits (optional, [M][C/8] bytes, bit i = channel 8*cv+i): the ReLU mask of `out`, so that the backward pass
+// reads one byte instead of 16 to know where the gradient passes.
+constexpr int kTailThreads = 256;
+constexpr int kTailUnroll = 4;
+__global__ void __launch_bounds__(kTailThreads)
+bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, View r,
+                   const float* __restrict__ r_scale, const float* __restrict__ r_shift, ViewW out,
+                   uint8_t* __restrict__ mask_bits, long long M, int C, int relu) {
   const int CV = C >> 3;
-  const long long total = M * CV;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(idx % CV) << 3;
-    const long long m = idx / CV;
-    float f[8], s[8], b[8];
-    unpack8(vload(y, m, c), f);
-    load8f(scale + c, s);
-    load8f(shift + c, b);
+  const int RL = kTailThreads / CV;
+  const int tx = threadIdx.x % CV;
+  const int ty = threadIdx.x / CV;
+  if (ty >= RL) return;
+  const int c = tx << 3;
+  float s[8], b[8], rs[8], rb[8];
+  load8f(scale + c, s);
+  load8f(shift + c, b);
+  const bool has_r = r.p != nullptr, r_bn = r_scale != nullptr;
+  if (r_bn) { load8f(r_scale + c, rs); load8f(r_shift + c, rb); }
+  const long long stride = (long long)gridDim.x * RL;
+  for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kTailUnroll) {
+    uint4 qy[kTailUnroll], qr[kTailUnroll];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], s[i], b[i]);
-    if (r.p) {
-      float rf[8];
-      unpack8(vload(r, m, c), rf);
-      if (r_scale) {
-        load8f(r_scale + c, s);
-        load8f(r_shift + c, b);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) rf[i] = fmaf(rf[i], s[i], b[i]);
+    for (int u = 0; u < kTailUnroll; ++u) {
+      const long long m = m0 + u * stride;
+      if (m < M) {
+        qy[u] = vload(y, m, c);
+        if (has_r) qr[u] = vload(r, m, c);
       }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) f[i] += rf[i];
     }
-    if (relu) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+    for (int u = 0; u < kTailUnroll; ++u) {
+      const long long m = m0 + u * stride;
+      if (m < M) {
+        float f[8];
+        unpack8(qy[u], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], s[i], b[i]);
+        if (has_r) {
+          float rf[8];
+          unpack8(qr[u], rf);
+          if (r_bn) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) rf[i] = fmaf(rf[i], rs[i], rb[i]);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] += rf[i];
+        }
+        if (relu) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = fmaxf(f[i], 0.f);
+        }
+        const uint4 q = pack8(f);
+        vstore(out, m, c, q);
+        if (mask_bits) {
+          // from the bf16-rounded output, i.e. exactly (out > 0) as the backward would have recomputed it
+          float o[8];
+          unpack8(q, o);
+          uint32_t bits = 0;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) bits |= (o[i] > 0.f ? 1u : 0u) << i;
+          mask_bits[m * CV + tx] = (uint8_t)bits;
+        }
+      }
     }
-    vstore(out, m, c, pack8(f));
   }
 }
 
@@ -265,42 +300,50 @@ constexpr int kBnUnroll = 4;  // independent 16-byte loads in flight per thread 
 struct BnBwdRaw {
   uint4 dz[kBnUnroll], y[kBnUnroll], mk[kBnUnroll];
 };
-__device__ __forceinline__ void bn_bwd_fetch(const View& dz, const View& y, const View& msk, int relu, const long long* m,
-                                             const bool* ok, int c, BnBwdRaw& r) {
+// ReLU mask source: 0 = recomputed from y (scale*y+shift > 0), 1 = sign of a bf16 tensor, 2 = packed bits [M][C/8]
+__device__ __forceinline__ void bn_bwd_fetch(const View& dz, const View& y, const View& msk, const uint8_t* bits, int CV,
+                                             int mode, const long long* m, const bool* ok, int c, BnBwdRaw& r) {
 #pragma unroll
   for (int u = 0; u < kBnUnroll; ++u) {
     if (ok[u]) {
       r.dz[u] = vload(dz, m[u], c);
       r.y[u] = vload(y, m[u], c);
-      if (relu && msk.p) r.mk[u] = vload(msk, m[u], c);
+      if (mode == 1) r.mk[u] = vload(msk, m[u], c);
+      else if (mode == 2) r.mk[u].x = bits[m[u] * CV + (c >> 3)];
     }
   }
 }
-__device__ __forceinline__ void bn_bwd_math(const BnBwdRaw& r, int u, bool has_mask, int relu, const float* s, const float* b,
+__device__ __forceinline__ void bn_apply_mask(const BnBwdRaw& r, int u, int mode, const float* yv, const float* s,
+                                              const float* b, float* g) {
+  if (mode == 1) {
+    float mv[8];
+    unpack8(r.mk[u], mv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
+  } else if (mode == 2) {
+    const uint32_t bits = r.mk[u].x;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = (bits >> i) & 1u ? g[i] : 0.f;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], s[i], b[i]) > 0.f ? g[i] : 0.f;
+  }
+}
+__device__ __forceinline__ void bn_bwd_math(const BnBwdRaw& r, int u, int mode, int relu, const float* s, const float* b,
                                             const float* mu, const float* is, float* g, float* xhat) {
   float yv[8];
   unpack8(r.dz[u], g);
   unpack8(r.y[u], yv);
 #pragma unroll
   for (int i = 0; i < 8; ++i) xhat[i] = (yv[i] - mu[i]) * is[i];
-  if (relu) {
-    if (has_mask) {
-      float mv[8];
-      unpack8(r.mk[u], mv);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], s[i], b[i]) > 0.f ? g[i] : 0.f;
-    }
-  }
+  if (relu) bn_apply_mask(r, u, mode, yv, s, b, g);
 }
 
 // block = (CV channel-vectors) x (RL row lanes); grid.x strides over row groups
 __global__ void __launch_bounds__(kRedThreads)
-bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale, const float* __restrict__ shift,
-                     const float* __restrict__ mean, const float* __restrict__ invstd, int relu, long long M, int C,
-                     float* dgamma, float* dbeta) {
+bn_bwd_reduce_kernel(View dz, View y, View msk, const uint8_t* __restrict__ mask_bits, const float* __restrict__ scale,
+                     const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
+                     int relu, long long M, int C, float* dgamma, float* dbeta) {
   __shared__ float red[kRedThreads * 16];
   const int CV = C >> 3;
   const int RL = kRedThreads / CV;  // >= 1 (C <= 2048)
@@ -312,8 +355,8 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale,
   for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
   if (ty < RL) {
     float sc[8], sh[8], mu[8], is[8];
-    const bool has_mask = msk.p != nullptr;
-    if (relu && !has_mask) { load8f(scale + c, sc); load8f(shift + c, sh); }
+    const int mode = !relu ? 3 : (mask_bits ? 2 : (msk.p ? 1 : 0));
+    if (mode == 0) { load8f(scale + c, sc); load8f(shift + c, sh); }
     load8f(mean + c, mu);
     load8f(invstd + c, is);
     const long long stride = (long long)gridDim.x * RL;
@@ -323,12 +366,12 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale,
 #pragma unroll
       for (int u = 0; u < kBnUnroll; ++u) { m[u] = m0 + u * stride; ok[u] = m[u] < M; }
       BnBwdRaw r;
-      bn_bwd_fetch(dz, y, msk, relu, m, ok, c, r);
+      bn_bwd_fetch(dz, y, msk, mask_bits, CV, mode, m, ok, c, r);
 #pragma unroll
       for (int u = 0; u < kBnUnroll; ++u) {
         if (ok[u]) {
           float g[8], xh[8];
-          bn_bwd_math(r, u, has_mask, relu, sc, sh, mu, is, g, xh);
+          bn_bwd_math(r, u, mode, relu, sc, sh, mu, is, g, xh);
 #pragma unroll
           for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], xh[i], s2[i]); }
         }
@@ -352,9 +395,9 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const float* __restrict__ scale,
 }
 
 // block = (CV channel-vectors) x (RL row lanes) like the reduction, so the per-channel constants are loaded once
-template <bool MASK, bool GOUT>
+template <int MASK, bool GOUT>  // MASK: ReLU mask source (see bn_bwd_fetch)
 __global__ void __launch_bounds__(kRedThreads, 2)
-bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
+bn_bwd_apply_kernel(View dz, View y, View msk, const uint8_t* __restrict__ mask_bits, const float* __restrict__ scale,
                     const float* __restrict__ shift, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ dgamma, const float* __restrict__ dbeta, int relu,
@@ -367,8 +410,8 @@ bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
   const int c = tx << 3;
   // dy = gamma*invstd*(g - dbeta/M - xhat*dgamma/M) = k0*g - ka*y + kb   (xhat = (y-mean)*invstd folded in)
   float sc[8], sh[8], k0[8], ka[8], kb[8];
-  constexpr bool has_mask = MASK;
-  if (relu && !has_mask) { load8f(scale + c, sc); load8f(shift + c, sh); }
+  constexpr int mode = MASK;
+  if (relu && mode == 0) { load8f(scale + c, sc); load8f(shift + c, sh); }
   {
     float ga[8], dg[8], db[8], mu[8], is[8];
     load8f(mean + c, mu);
@@ -391,7 +434,7 @@ bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
 #pragma unroll
     for (int u = 0; u < kBnUnroll; ++u) { m[u] = m0 + u * stride; ok[u] = m[u] < M; }
     BnBwdRaw r;
-    bn_bwd_fetch(dz, y, has_mask ? msk : View{nullptr, 0, 0}, relu, m, ok, c, r);
+    bn_bwd_fetch(dz, y, msk, mask_bits, CV, relu ? mode : 3, m, ok, c, r);
     uint4 old[kBnUnroll];
     if (GOUT && g_accumulate) {
 #pragma unroll
@@ -404,17 +447,7 @@ bn_bwd_apply_kernel(View dz, View y, View msk, const float* __restrict__ scale,
         float g[8], yv[8], o[8];
         unpack8(r.dz[u], g);
         unpack8(r.y[u], yv);
-        if (relu) {
-          if (has_mask) {
-            float mv[8];
-            unpack8(r.mk[u], mv);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
-          } else {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], sc[i], sh[i]) > 0.f ? g[i] : 0.f;
-          }
-        }
+        if (relu) bn_apply_mask(r, u, mode, yv, sc, sh, g);
 #pragma unroll
         for (int i = 0; i < 8; ++i) o[i] = fmaf(k0[i], g[i], fmaf(-ka[i], yv[i], kb[i]));
         vstore(dy, m[u], c, pack8(o));

@@ -919,42 +919,44 @@ static bool view_ok(const void* p, int ld, int coff, int C) {
 
 int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift, const void* r,
                     int32_t r_ld, int32_t r_coff, const float* r_scale, const float* r_shift, void* out, int32_t o_ld,
-                    int32_t o_coff, int64_t M, int32_t C, int32_t relu, void* stream) {
-  if (M <= 0 || C <= 0 || (C & 7) || !scale || !shift) return SFB_ERR_BAD_ARG;
+                    int32_t o_coff, uint8_t* mask_bits, int64_t M, int32_t C, int32_t relu, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !scale || !shift) return SFB_ERR_BAD_ARG;
   if (!view_ok(y, y_ld, y_coff, C) || !view_ok(out, o_ld, o_coff, C)) return SFB_ERR_BAD_ARG;
   if (r && !view_ok(r, r_ld, r_coff, C)) return SFB_ERR_BAD_ARG;
   if (r_scale && (!r || !r_shift)) return SFB_ERR_BAD_ARG;
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   View vr{(const __nv_bfloat16*)r, r_ld, r_coff};
   ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
-  bn_add_relu_kernel<<<grid_for(M * (C >> 3), 256), 256, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale,
-                                                                                    r_shift, vo, M, C, relu);
+  const int RL = kTailThreads / (C >> 3);
+  const int grid = grid_for((M + (long long)RL * kTailUnroll - 1) / ((long long)RL * kTailUnroll), 1, 148 * 8);
+  bn_add_relu_kernel<<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
+                                                                      mask_bits, M, C, relu);
   SFB_CHECK_LAUNCH("bn_add_relu_kernel");
   return SFB_OK;
 }
 
 int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
-                      const void* mask_src, int32_t m_ld, int32_t m_coff, const float* scale, const float* shift,
-                      const float* mean, const float* invstd, int32_t relu, int64_t M, int32_t C, float* dgamma,
-                      float* dbeta, void* stream) {
+                      const void* mask_src, int32_t m_ld, int32_t m_coff, const uint8_t* mask_bits, const float* scale,
+                      const float* shift, const float* mean, const float* invstd, int32_t relu, int64_t M, int32_t C,
+                      float* dgamma, float* dbeta, void* stream) {
   if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !mean || !invstd || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
   if (!view_ok(dz, dz_ld, dz_coff, C) || !view_ok(y, y_ld, y_coff, C)) return SFB_ERR_BAD_ARG;
   if (mask_src && !view_ok(mask_src, m_ld, m_coff, C)) return SFB_ERR_BAD_ARG;
-  if (relu && !mask_src && (!scale || !shift)) return SFB_ERR_BAD_ARG;
+  if (relu && !mask_src && !mask_bits && (!scale || !shift)) return SFB_ERR_BAD_ARG;
   View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
   const int RL = kRedThreads / (C >> 3);
   const int grid = grid_for((M + (long long)RL * kBnUnroll - 1) / ((long long)RL * kBnUnroll), 1, 148 * 8);
-  bn_bwd_reduce_kernel<<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, vy, vm, scale, shift, mean, invstd, relu, M,
-                                                                       C, dgamma, dbeta);
+  bn_bwd_reduce_kernel<<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, vy, vm, mask_bits, scale, shift, mean, invstd,
+                                                                       relu, M, C, dgamma, dbeta);
   SFB_CHECK_LAUNCH("bn_bwd_reduce_kernel");
   return SFB_OK;
 }
 
 int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
-                     const void* mask_src, int32_t m_ld, int32_t m_coff, const float* scale, const float* shift,
-                     const float* mean, const float* invstd, const float* gamma, const float* dgamma,
+                     const void* mask_src, int32_t m_ld, int32_t m_coff, const uint8_t* mask_bits, const float* scale,
+                     const float* shift, const float* mean, const float* invstd, const float* gamma, const float* dgamma,
                      const float* dbeta, int32_t relu, int64_t M, int32_t C, void* dy, int32_t dy_ld, int32_t dy_coff,
                      void* g_out, int32_t g_ld, int32_t g_coff, int32_t g_accumulate, void* stream) {
   if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
@@ -962,7 +964,7 @@ int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void*
     return SFB_ERR_BAD_ARG;
   if (mask_src && !view_ok(mask_src, m_ld, m_coff, C)) return SFB_ERR_BAD_ARG;
   if (g_out && !view_ok(g_out, g_ld, g_coff, C)) return SFB_ERR_BAD_ARG;
-  if (relu && !mask_src && (!scale || !shift)) return SFB_ERR_BAD_ARG;
+  if (relu && !mask_src && !mask_bits && (!scale || !shift)) return SFB_ERR_BAD_ARG;
   View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
@@ -970,12 +972,15 @@ int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void*
   ViewW vg{(__nv_bfloat16*)g_out, g_ld, g_coff};
   const int RLa = kRedThreads / (C >> 3);
   const int grid_a = grid_for((M + (long long)RLa * kBnUnroll - 1) / ((long long)RLa * kBnUnroll), 1, 148 * 8);
-  const bool hm = relu && mask_src != nullptr, hg = g_out != nullptr;
-#define SFB_APPLY(MK, GO) bn_bwd_apply_kernel<MK, GO><<<grid_a, kRedThreads, 0, (cudaStream_t)stream>>>(       vdz, vy, vm, scale, shift, mean, invstd, gamma, dgamma, dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, g_accumulate)
-  if (hm && hg) SFB_APPLY(true, true);
-  else if (hm) SFB_APPLY(true, false);
-  else if (hg) SFB_APPLY(false, true);
-  else SFB_APPLY(false, false);
+  const int mode = !relu ? 0 : (mask_bits ? 2 : (mask_src ? 1 : 0));
+  const bool hg = g_out != nullptr;
+#define SFB_APPLY(MK, GO) bn_bwd_apply_kernel<MK, GO><<<grid_a, kRedThreads, 0, (cudaStream_t)stream>>>(       vdz, vy, vm, mask_bits, scale, shift, mean, invstd, gamma, dgamma, dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, g_accumulate)
+  if (mode == 2 && hg) SFB_APPLY(2, true);
+  else if (mode == 2) SFB_APPLY(2, false);
+  else if (mode == 1 && hg) SFB_APPLY(1, true);
+  else if (mode == 1) SFB_APPLY(1, false);
+  else if (hg) SFB_APPLY(0, true);
+  else SFB_APPLY(0, false);
 #undef SFB_APPLY
   SFB_CHECK_LAUNCH("bn_bwd_apply_kernel");
   return SFB_OK;

@@ -112,6 +112,7 @@ class Plan:
         self.bwd: List[Tuple] = []
         self.keep = []  # ctypes structs / tensors that must outlive the op lists
         self.x_in: List[Act] = []
+        self.mask_bits = []  # (block output Act, packed ReLU mask) pairs of a training plan
         self.logits = None
         self.dlogits = None
         self.act_bytes = 0
@@ -425,10 +426,15 @@ class SlowFastEngine:
             self._emit(lst, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
                        bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
 
-    def _bn_bwd(self, plan, lst, L: ConvL, dz: Act, y: Act, mask: Optional[Act], dy: Act, g_out: Optional[Act] = None,
+    def _bn_bwd(self, plan, lst, L: ConvL, dz: Act, y: Act, mask, dy: Act, g_out: Optional[Act] = None,
                 g_acc=False, do_reduce=True):
+        """mask: None (ReLU mask recomputed from y), an Act (sign of that tensor) or a uint8 tensor (packed bits
+        written by the forward residual tail)"""
         bn = L.bn
-        m = (mask.ptr(), mask.ld, mask.coff) if mask is not None else (0, 0, 0)
+        if isinstance(mask, torch.Tensor):
+            m = (0, 0, 0, mask.data_ptr())
+        else:
+            m = (mask.ptr(), mask.ld, mask.coff, 0) if mask is not None else (0, 0, 0, 0)
         if do_reduce:
             self._emit(lst, self.lib.sfb_bn_bwd_reduce, dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, *m,
                        L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(), L.invstd.data_ptr(), 1, y.M, y.C,
@@ -446,7 +452,7 @@ class SlowFastEngine:
         """out = relu(y * scale_L + shift_L)   (training: BatchNorm needs the batch statistics of the whole tensor
         before it can normalise, so the activated operand of the next conv is materialised by one HBM-bound pass)"""
         self._emit(lst, self.lib.sfb_bn_add_relu, y.ptr(), y.ld, y.coff, L.scale.data_ptr(), L.shift.data_ptr(), 0, 0, 0, 0, 0,
-                   out.ptr(), out.ld, out.coff, y.M, y.C, 1, self.stream, tag=tag)
+                   out.ptr(), out.ld, out.coff, 0, y.M, y.C, 1, self.stream, tag=tag)
 
     # ------------------------------------------------------------------ plan construction
     def build_plan(self, N, Ts, Tf, H, W, training) -> Plan:
@@ -579,16 +585,21 @@ class SlowFastEngine:
                     otag = (d["name"] + ".O", O.act)
                     yc = y1 = None
                     if training:
+                        # packed ReLU mask of O for the backward tail (1 byte per 8 channels instead of re-reading O)
+                        O.bits = torch.empty(O.act.M * (c.Co // 8), dtype=torch.uint8, device=dev)
+                        plan.keep.append(O.bits)
+                        plan.mask_bits.append((O.act, O.bits))
+                        plan.act_bytes += O.bits.numel()
                         yc, _ = conv_bn_act(c, zb, None)
                         if s_ is not None:
                             y1, _ = conv_bn_act(s_, X.act, None)
                             self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
                                        c.shift.data_ptr(), y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
-                                       O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=otag)
+                                       O.act.ptr(), O.act.ld, O.act.coff, O.bits.data_ptr(), yc.M, c.Co, 1, self.stream, tag=otag)
                         else:
                             self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
                                        c.shift.data_ptr(), X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
-                                       O.act.ptr(), O.act.ld, O.act.coff, yc.M, c.Co, 1, self.stream, tag=otag)
+                                       O.act.ptr(), O.act.ld, O.act.coff, O.bits.data_ptr(), yc.M, c.Co, 1, self.stream, tag=otag)
                     else:
                         # eval: shortcut = folded-BN conv (no ReLU) or X itself; conv_c adds it and applies the ReLU
                         if s_ is not None:
@@ -700,13 +711,13 @@ class SlowFastEngine:
             self._emit(bwd, _probe, tag=(d["name"] + ".dO", dO))
             dyc = new_grad(yc)
             if s_ is not None:
-                self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc)
+                self._bn_bwd(plan, bwd, c, dO, yc, O.bits, dyc)
                 dy1 = new_grad(y1)
-                self._bn_bwd(plan, bwd, s_, dO, y1, O.act, dy1)
+                self._bn_bwd(plan, bwd, s_, dO, y1, O.bits, dy1)
             else:
                 # identity shortcut: the masked gradient g also flows straight to the block input
                 ensure_grad(X)
-                self._bn_bwd(plan, bwd, c, dO, yc, O.act, dyc, g_out=X.grad, g_acc=X.ginit)
+                self._bn_bwd(plan, bwd, c, dO, yc, O.bits, dyc, g_out=X.grad, g_acc=X.ginit)
                 X.ginit = True
             self._wgrad(plan, bwd, c, zb, None, dyc)
             dzb = new_grad(yb)
@@ -858,6 +869,11 @@ class SlowFastEngine:
         # outputs: recompute them with the engine's own kernels
         self._run([op for op in plan.fwd if op[0] is self.lib.sfb_maxpool_fwd or
                    (op[0] is self.lib.sfb_bn_add_relu and op[2] is not None and op[2][0].endswith(".z"))])
+        # packed ReLU masks of the block outputs, from the forced O tensors
+        for O_act, bits in plan.mask_bits:
+            o = O_act.torch_view().reshape(-1, O_act.C // 8, 8) > 0
+            w = (2 ** torch.arange(8, device=o.device, dtype=torch.int32)).view(1, 1, 8)
+            bits.copy_((o.to(torch.int32) * w).sum(-1).to(torch.uint8).reshape(-1))
 
     def get_plan(self, xs, xf, training) -> Plan:
         N, Cs, Ts, H, W = xs.shape

@@ -233,25 +233,27 @@ def bn_fold(gamma, beta, rm, rv, eps, scale, shift):
                             scale.data_ptr(), shift.data_ptr(), stream_ptr()), "sfb_bn_fold")
 
 
-def bn_add_relu(y: Act, scale, shift, r: Optional[Act], r_scale, r_shift, out: Act, relu=True):
+def bn_add_relu(y: Act, scale, shift, r: Optional[Act], r_scale, r_shift, out: Act, relu=True, mask_bits=None):
+    """mask_bits: optional uint8 tensor [M, C/8] receiving the packed ReLU mask of `out` (bit i = channel 8*cv+i)"""
     check(lib().sfb_bn_add_relu(y.ptr(), y.ld, y.coff, scale.data_ptr(), shift.data_ptr(),
                                 r.ptr() if r else 0, r.ld if r else 0, r.coff if r else 0, ptr(r_scale), ptr(r_shift),
-                                out.ptr(), out.ld, out.coff, y.M, y.C, int(relu), stream_ptr()), "sfb_bn_add_relu")
+                                out.ptr(), out.ld, out.coff, ptr(mask_bits), y.M, y.C, int(relu), stream_ptr()),
+          "sfb_bn_add_relu")
     return out
 
 
-def bn_bwd_reduce(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, relu, dgamma, dbeta):
+def bn_bwd_reduce(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, relu, dgamma, dbeta, mask_bits=None):
     check(lib().sfb_bn_bwd_reduce(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff,
                                   mask.ptr() if mask else 0, mask.ld if mask else 0, mask.coff if mask else 0,
-                                  ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), int(relu), y.M, y.C,
+                                  ptr(mask_bits), ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), int(relu), y.M, y.C,
                                   dgamma.data_ptr(), dbeta.data_ptr(), stream_ptr()), "sfb_bn_bwd_reduce")
 
 
 def bn_bwd_apply(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, gamma, dgamma, dbeta, relu,
-                 dy: Act, g_out: Optional[Act] = None, g_accumulate=False):
+                 dy: Act, g_out: Optional[Act] = None, g_accumulate=False, mask_bits=None):
     check(lib().sfb_bn_bwd_apply(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff,
                                  mask.ptr() if mask else 0, mask.ld if mask else 0, mask.coff if mask else 0,
-                                 ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                                 ptr(mask_bits), ptr(scale), ptr(shift), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
                                  dgamma.data_ptr(), dbeta.data_ptr(), int(relu), y.M, y.C, dy.ptr(), dy.ld, dy.coff,
                                  g_out.ptr() if g_out else 0, g_out.ld if g_out else 0, g_out.coff if g_out else 0,
                                  int(g_accumulate), stream_ptr()), "sfb_bn_bwd_apply")
