@@ -19,6 +19,7 @@ from video_classification_b200 import _ffi, ops  # noqa: E402
 from video_classification_b200.ops import Act  # noqa: E402
 
 DEV = "cuda"
+NOWARM = False  # --nowarm: no untimed first launch (ncu captures: one launch per layer)
 
 # name, kind, T, H, W, Ci (real), Co, k, s     kind: fprop | fprop_stats | dgrad | dgrad_acc | wgrad
 LAYERS = [
@@ -58,6 +59,8 @@ LAYERS = [
     ("fast_res2_c_8_32", "dgrad", 32, 56, 56, 8, 32, (1, 1, 1), (1, 1, 1)),
     ("fast_res3_b_16_16_s2", "dgrad", 32, 56, 56, 16, 16, (1, 3, 3), (1, 2, 2)),
     ("lateral1_32_64_s4", "dgrad_acc", 32, 56, 56, 32, 64, (3, 1, 1), (4, 1, 1)),
+    ("layout_fast", "layout_s2d", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
+    ("layout_slow", "layout_s2d", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
     ("bn_bwd_256", "bn_bwd", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
     ("bn_apply_256", "bn_apply", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
     ("bn_tail_256", "bn_tail", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
@@ -84,7 +87,13 @@ def run_layer(N, spec, reps):
     flops = 2.0 * M * Co * Ci * taps
     in_b, out_b = N * T * H * W * Ci * 2, M * Co * 2
     xg = Act(x.buf, 0, r16(Ci))
-    if kind in ("s2d_fprop", "s2d_wgrad"):
+    if kind == "layout_s2d":
+        del x, y
+        xf = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
+        fn = lambda: ops.layout_input_s2d(xf)
+        flops = 0.0
+        bytes_ = xf.numel() * 4 + N * T * (H // 2) * (W // 2) * (32 if 4 * Ci <= 32 else 64) * 2
+    elif kind in ("s2d_fprop", "s2d_wgrad"):
         xf = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
         xs = ops.layout_input_s2d(xf)
         del xf
@@ -158,7 +167,8 @@ def run_layer(N, spec, reps):
         flops, bytes_ = 0.0, 2 * out_b
     else:
         raise ValueError(kind)
-    fn()
+    if not NOWARM:
+        fn()
     torch.cuda.synchronize()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
     ts = []
@@ -182,7 +192,10 @@ def main():
     ap.add_argument("--kinds", default="")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--json", default="")
+    ap.add_argument("--nowarm", action="store_true")
     a = ap.parse_args()
+    global NOWARM
+    NOWARM = a.nowarm
     only = set(filter(None, a.only.split(",")))
     kinds = set(filter(None, a.kinds.split(",")))
     rows = []

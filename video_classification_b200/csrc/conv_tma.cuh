@@ -72,6 +72,8 @@ struct ConvTmaParams {
   int epi_relu;
   float* stats;                // [2*Co] or null
   int reduce_add;              // 1: the TMA store is a reduce-add into the output (in-place gradient accumulation)
+  uint32_t stg2_off;           // byte offset of a second staging tile (0: single buffer): the TMA store of chunk k drains
+                               // while chunk k+1 is converted and staged
 };
 
 __device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int32_t c0, int32_t c1, int32_t c2,
@@ -90,6 +92,7 @@ __device__ __forceinline__ void tma_reduce_add_5d(const void* tmap, uint32_t sme
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ uint4 lds_v4(uint32_t saddr) {
   uint4 v;
@@ -101,6 +104,31 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
   return v;
 }
+
+// Walk of a persistent CTA over its pixel patches (patch0, patch0 + step, ...) as (tw, th, tt, n) counters: the
+// mixed-radix decomposition is done once, every further tile is a few adds and compares instead of four divisions.
+struct PatchWalk {
+  int tw, th, tt, n, dw, dh, dt, dn;
+  __device__ __forceinline__ void init(int patch0, int step, const ConvTmaParams& p) {
+    int q = patch0;
+    tw = q % p.tilesW; q /= p.tilesW;
+    th = q % p.tilesH; q /= p.tilesH;
+    tt = q % p.tilesT; n = q / p.tilesT;
+    q = step;
+    dw = q % p.tilesW; q /= p.tilesW;
+    dh = q % p.tilesH; q /= p.tilesH;
+    dt = q % p.tilesT; dn = q / p.tilesT;
+  }
+  __device__ __forceinline__ void next(const ConvTmaParams& p) {
+    tw += dw;
+    if (tw >= p.tilesW) { tw -= p.tilesW; ++th; }
+    th += dh;
+    if (th >= p.tilesH) { th -= p.tilesH; ++tt; }
+    tt += dt;
+    if (tt >= p.tilesT) { tt -= p.tilesT; ++n; }
+    n += dn;
+  }
+};
 
 // BRES: the CTA's whole weight slice [BN][Ktot] stays resident in shared memory (loaded once; a persistent CTA works
 // on one N tile for its whole life), so a pipeline stage carries the activation boxes only.  Small-K layers were bound
@@ -198,12 +226,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const uint32_t smem0 = smem_u32(smem);
     int s = 0;
     uint32_t ph = 1;  // parity to wait on for "stage s is free"
-    for (int patch = patch0; patch < p.total_patches; patch += patch_step) {
-      int q = patch;
-      const int tw = q % p.tilesW; q /= p.tilesW;
-      const int th = q % p.tilesH; q /= p.tilesH;
-      const int tt = q % p.tilesT;
-      const int n = q / p.tilesT;
+    PatchWalk pw;
+    pw.init(patch0, patch_step, p);
+    for (int patch = patch0; patch < p.total_patches; patch += patch_step, pw.next(p)) {
+      const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       const int bw = p.transposed ? tw * p.Wt + p.pW : tw * p.Wt * p.sW - p.pW;
       const int bh = p.transposed ? th * p.Ht + p.pH : th * p.Ht * p.sH - p.pH;
       const int bt = p.transposed ? tt * p.Tt + p.pT : tt * p.Tt * p.sT - p.pT;
@@ -297,7 +323,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int olog = 31 - __clz(ocols);
     const uint32_t rb = (uint32_t)(ocols * 2);
     const uint32_t swz = rb == 128 ? 7u : (rb == 64 ? 3u : (rb == 32 ? 1u : 0u));
-    const uint32_t stg = smem_u32(smem + L::kStagingOff);
+    const uint32_t stg_a = smem_u32(smem + L::kStagingOff);
+    const uint32_t stg_b = p.stg2_off ? smem_u32(smem) + p.stg2_off : stg_a;
+    uint32_t nstaged = 0;
     const uint32_t sub_bytes = 128u * rb;
     const int last_ch = min(NCH, (p.Co - n0 + CH - 1) / CH) - 1;
     float ssum[NCH][8], ssq[NCH][8];
@@ -306,18 +334,31 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
       for (int i = 0; i < 8; ++i) { ssum[c][i] = 0.f; ssq[c][i] = 0.f; }
     }
+    // The epilogue is instruction-bound on the memory-bound layers (ncu r1o, 64->256 pointwise: 15 k warp
+    // instructions per 128x256 tile, 58 % issue utilisation, of which ~6 k were per-group branches, parameter
+    // reloads and address arithmetic): everything that does not change from tile to tile is computed once here.
+    const bool plain = p.epi_scale == nullptr && p.res == nullptr && !p.epi_relu;
+    uint32_t soff[4], toff[4];  // swizzled staging offsets: this thread's four 16-byte stores / four stats loads
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int cl = cslice * 32 + j * 8;
+      uint32_t o = (uint32_t)(cl >> olog) * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl & (ocols - 1)) * 2);
+      soff[j] = o ^ (((o >> 7) & swz) << 4);
+      const int cs = (warp - 2) * 8;
+      o = (uint32_t)(cs >> olog) * sub_bytes + (uint32_t)(lane + 32 * j) * rb + (uint32_t)((cs & (ocols - 1)) * 2);
+      toff[j] = o ^ (((o >> 7) & swz) << 4);
+    }
+    const bool want_stats = p.stats != nullptr;
     bool store_pending = false;
     int it = 0;
-    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
-      int q = patch;
-      const int tw = q % p.tilesW; q /= p.tilesW;
-      const int th = q % p.tilesH; q /= p.tilesH;
-      const int tt = q % p.tilesT;
-      const int n = q / p.tilesT;
+    PatchWalk pw;
+    pw.init(patch0, patch_step, p);
+    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it, pw.next(p)) {
+      const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
       const int wo = w0 + ww, ho = h0 + hh, to = t0 + tq;
       const bool mv = r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
-      const long long m = mv ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
+      const long long m = (p.res && mv) ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
       const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
       const int buf = it & 1;
       mbar_wait(&tfull_bar[buf], (uint32_t)((it >> 1) & 1), 14);
@@ -326,13 +367,28 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       for (int ch = 0; ch < NCH; ++ch) {
         if (ch <= last_ch) {
           const int col0 = n0 + ch * CH;
-          // (A) the previous TMA store must have finished reading the staging tile
-          if (te == 0 && store_pending) tma_store_wait_read();
+          // (A) the TMA store that last used this staging tile must have finished reading it
+          const uint32_t stg = (nstaged & 1) ? stg_b : stg_a;
+          ++nstaged;
+          if (te == 0 && store_pending) {
+            if (p.stg2_off) tma_store_wait_read1(); else tma_store_wait_read();
+          }
           named_bar_sync(1, ET);
           // (B) accumulator -> staging: this warp's 32-column slice
           {
             const int nb = col0 + cslice * 32;
-            if (nb < p.Co) {
+            if (plain && nb + 32 <= p.Co) {
+              // training fprop / dgrad: convert and stage, nothing else
+              float v[32];
+              tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                uint4 pk = pack8(v + j * 8);
+                if (!mv) pk = make_uint4(0, 0, 0, 0);
+                sts_v4(stg + soff[j], pk);
+              }
+            } else if (nb < p.Co) {
               float v[32];
               tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
               tmem_ld_wait();
@@ -386,16 +442,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           }
           // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros): epilogue
           //     warp e owns the 8-column group e of the chunk, its lanes split the 128 rows (16-byte reads)
-          if (p.stats) {
-            const int cl = (warp - 2) * 8;
-            if (col0 + cl < p.Co) {
-              const uint32_t base = stg + (cl >> olog) * sub_bytes + (uint32_t)((cl & (ocols - 1)) * 2);
+          if (want_stats) {
+            if (col0 + (warp - 2) * 8 < p.Co) {
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                uint32_t addr = base + (uint32_t)(lane + 32 * i) * rb;
-                addr ^= ((addr >> 7) & swz) << 4;
                 float x[8];
-                unpack8(lds_v4(addr), x);
+                unpack8(lds_v4(stg + toff[i]), x);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                   ssum[ch][c] += x[c];

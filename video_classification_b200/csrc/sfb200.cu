@@ -317,18 +317,26 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
                          cudaStream_t st) {
   using L = ConvTmaCfg<BN, BRES>;
   const size_t smem = L::smem_bytes(p.nk);
-  static size_t attr_bytes = 0;
-  if (smem > attr_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
-    attr_bytes = smem;
+  // second staging tile behind everything else when it still fits
+  ConvTmaParams pp = p;
+  size_t smem_total = smem;
+  const size_t stg2 = (smem - 1024 + 1023) / 1024 * 1024;  // swizzled tile: 1024-byte aligned
+  if (1024 + stg2 + L::kStagingBytes <= 227 * 1024) {
+    pp.stg2_off = (uint32_t)stg2;
+    smem_total = 1024 + stg2 + L::kStagingBytes;
   }
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
   long long per_nt = num_sms() / p.n_tiles;
   if (per_nt < 1) per_nt = 1;
   if (per_nt > p.total_patches) per_nt = p.total_patches;
   const int grid = (int)per_nt * p.n_tiles;
-  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem, st>>>(ta, tw, to, p);
+  static size_t attr_bytes = 0;
+  if (smem_total > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
+    attr_bytes = smem_total;
+  }
+  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, pp);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
@@ -493,8 +501,16 @@ int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int
   if (!x || !out || N <= 0 || C <= 0 || T <= 0 || H <= 0 || W <= 0 || (H & 1) || (W & 1) || !aligned16(out)) return SFB_ERR_BAD_ARG;
   if ((Cs != 32 && Cs != 64) || 4 * C > Cs) return SFB_ERR_BAD_ARG;
   const long long total = (long long)N * T * (H / 2) * (W / 2);
-  layout_input_s2d_kernel<<<grid_for(total, 128, 148 * 64), 128, 0, (cudaStream_t)stream>>>(
-      x, sn, sc, st, sh, sw, N, C, T, H / 2, W / 2, (__nv_bfloat16*)out, Cs);
+  // W-contiguous clips (what _prepare_slowfast_data hands over) with the reference's channel counts: vector path
+  const bool vec = sw == 1 && ((uintptr_t)x & 7) == 0 && !((sn | sc | st | sh) & 1);
+  const int grid = grid_for(total, 128, 148 * 64);
+  if (vec && C == 5 && Cs == 32)
+    layout_input_s2d_vec_kernel<5, 32><<<grid, 128, 0, (cudaStream_t)stream>>>(x, sn, sc, st, sh, N, T, H / 2, W / 2, (__nv_bfloat16*)out);
+  else if (vec && C == 15 && Cs == 64)
+    layout_input_s2d_vec_kernel<15, 64><<<grid, 128, 0, (cudaStream_t)stream>>>(x, sn, sc, st, sh, N, T, H / 2, W / 2, (__nv_bfloat16*)out);
+  else
+    layout_input_s2d_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
+        x, sn, sc, st, sh, sw, N, C, T, H / 2, W / 2, (__nv_bfloat16*)out, Cs);
   SFB_CHECK_LAUNCH("layout_input_s2d_kernel");
   return SFB_OK;
 }

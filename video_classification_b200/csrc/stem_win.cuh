@@ -480,6 +480,41 @@ __global__ void layout_input_s2d_kernel(const float* __restrict__ x, long long s
   }
 }
 
+// Same layout for W-contiguous input (stride 1 along W, 8-byte aligned rows) and a compile-time channel count: the
+// two sub-pixels of a row come in one 8-byte load, all 2*C loads of a pixel are independent and issued back to back,
+// and the channel shuffle is resolved at compile time (registers only).
+template <int C, int CS>
+__global__ void __launch_bounds__(128)
+layout_input_s2d_vec_kernel(const float* __restrict__ x, long long sn, long long sc, long long st, long long sh,
+                            int N, int T, int H2, int W2, __nv_bfloat16* __restrict__ out) {
+  const long long total = (long long)N * T * H2 * W2;
+  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < total;
+       pix += (long long)gridDim.x * blockDim.x) {
+    const int w = (int)(pix % W2);
+    long long q = pix / W2;
+    const int h = (int)(q % H2);
+    q /= H2;
+    const int t = (int)(q % T);
+    const int n = (int)(q / T);
+    const float* src = x + n * sn + t * st + (long long)(2 * h) * sh + 2 * w;
+    float f[CS];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        const float2 v = __ldg(reinterpret_cast<const float2*>(src + (long long)c * sc + (long long)r * sh));
+        f[(r * 2 + 0) * C + c] = v.x;
+        f[(r * 2 + 1) * C + c] = v.y;
+      }
+    }
+#pragma unroll
+    for (int i = 4 * C; i < CS; ++i) f[i] = 0.f;
+    uint4* dst = reinterpret_cast<uint4*>(out + (size_t)pix * CS);
+#pragma unroll
+    for (int cv = 0; cv < CS / 8; ++cv) dst[cv] = pack8(f + cv * 8);
+  }
+}
+
 // ---- stem weight packing: fp32 (Co, Ci, 1, 7, 7) -> bf16 [rows_pad][16*Cs], k = (dh*4+dw)*Cs + (sh*2+sw)*Ci + c ---
 __global__ void pack_weight_stem_kernel(const float* __restrict__ w, int Co, int Ci, int Cs,
                                         __nv_bfloat16* __restrict__ wp, int rows_pad) {

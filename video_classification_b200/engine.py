@@ -810,7 +810,19 @@ class SlowFastEngine:
                 ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])
                 gf = 2.0 * args[1] * args[2] * args[3] * args[4] * co * ci * 49 / 1e9
                 desc = f"stem s2d in({args[2]},{2 * args[3]},{2 * args[4]})x{ci} out x{co} k(1,7,7) s(1,2,2)"
-            rows.append((name, desc, e0.elapsed_time(e1), gf))
+            ms = e0.elapsed_time(e1)
+            # HBM-bound BatchNorm passes: tensors moved (bf16 [M][C]) and the bandwidth that implies
+            nt = 0
+            if name == "sfb_bn_add_relu":      # y (+ r) -> out
+                M, Cc, nt = args[14], args[15], 2 + (1 if args[5] else 0)
+            elif name == "sfb_bn_bwd_reduce":  # dz, y (+ bf16 mask)
+                M, Cc, nt = args[15], args[16], 2 + (1 if args[6] else 0)
+            elif name == "sfb_bn_bwd_apply":   # dz, y (+ mask) -> dy (+ g_out (+ old g))
+                M, Cc = args[18], args[19]
+                nt = 3 + (1 if args[6] else 0) + (1 if args[23] else 0) + (1 if args[23] and args[26] else 0)
+            if nt:
+                desc = f"M={M} C={Cc} tensors={nt} {nt * M * Cc * 2 / ms / 1e6:7.0f} GB/s"
+            rows.append((name, desc, ms, gf))
         return rows
 
     def profile_summary(self):
