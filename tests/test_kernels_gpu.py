@@ -174,8 +174,9 @@ def test_head_pool(T, H, W, k):
     ops.head_pool_bwd(df, 8, k, 0.0, 0, dx)
     assert kc.relerr(kc.from_act(dx), xq.grad) < 6e-3
     # dropout: forward/backward consistency (d feat / d x == backward weights) and keep-rate
-    feat_d = torch.zeros(N, C_ + 8, device=DEV)
+    feat_d = torch.full((N, C_ + 8), 7.0, device=DEV)  # stale contents: the kernel owns (and must reset) its columns
     ops.head_pool_fwd(xa, k, 0.5, 1234, feat_d, 8)
+    assert bool((feat_d[:, :8] == 7.0).all())
     ones = torch.ones(N, C_ + 8, device=DEV)
     dxd = Act.empty(N, T, H, W, C_)
     ops.head_pool_bwd(ones, 8, k, 0.5, 1234, dxd)

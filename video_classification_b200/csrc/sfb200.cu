@@ -1011,9 +1011,10 @@ int sfb_maxpool_fwd(const void* y, int32_t y_ld, int32_t y_coff, const float* sc
   const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
-  const long long total = (long long)N * T * Ho * Wo * (C >> 3);
-  maxpool_fwd_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(vy, scale, shift, N, T, H, W, C,
-                                                                                       vo, idx);
+  if ((long long)N * T > 65535 || (long long)H * W * (C >> 3) >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+  const long long per_frame = (long long)Ho * Wo * (C >> 3);
+  dim3 grid((unsigned)grid_for(per_frame, 256, 64), (unsigned)(N * T));
+  maxpool_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vy, scale, shift, N, T, H, W, C, vo, idx);
   SFB_CHECK_LAUNCH("maxpool_fwd_kernel");
   return SFB_OK;
 }
@@ -1024,8 +1025,10 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
   if (!view_ok(dout, d_ld, d_coff, C) || !view_ok(dz, dz_ld, dz_coff, C)) return SFB_ERR_BAD_ARG;
   View vd{(const __nv_bfloat16*)dout, d_ld, d_coff};
   ViewW vz{(__nv_bfloat16*)dz, dz_ld, dz_coff};
-  const long long total = (long long)N * T * H * W * (C >> 3);
-  maxpool_bwd_kernel<<<grid_for(total, 256, 148 * 32), 256, 0, (cudaStream_t)stream>>>(vd, idx, N, T, H, W, C, vz);
+  if ((long long)N * T > 65535 || (long long)H * W * (C >> 3) >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+  const long long per_frame = (long long)H * W * (C >> 3);
+  dim3 grid((unsigned)grid_for(per_frame, 256, 64), (unsigned)(N * T));
+  maxpool_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vd, idx, N, T, H, W, C, vz);
   SFB_CHECK_LAUNCH("maxpool_bwd_kernel");
   return SFB_OK;
 }
@@ -1036,9 +1039,19 @@ int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, in
   if (N <= 0 || C <= 0 || (C & 7) || kT <= 0 || kH <= 0 || kW <= 0 || kT > T || kH > H || kW > W || !feat) return SFB_ERR_BAD_ARG;
   if (!view_ok(x, x_ld, x_coff, C) || f_off + C > f_ld || dropout_p < 0.f || dropout_p >= 1.f) return SFB_ERR_BAD_ARG;
   View vx{(const __nv_bfloat16*)x, x_ld, x_coff};
-  const int total = N * (C >> 3);
-  head_pool_fwd_kernel<<<(total + 63) / 64, 64, 0, (cudaStream_t)stream>>>(vx, N, T, H, W, C, kT, kH, kW, dropout_p, seed,
-                                                                           feat, f_ld, f_off);
+  const int CV = C >> 3;
+  int cvb = 1;
+  while (cvb < 32 && cvb < CV) cvb <<= 1;  // channel vectors per block (power of two <= 32); the other threads split positions
+  // dropout acts per pooled position: one block per window, accumulated into feat; without it the windows collapse
+  const long long npos = dropout_p > 0.f ? (long long)(T - kT + 1) * (H - kH + 1) * (W - kW + 1) : 1;
+  if ((long long)N * npos > 0x7fffffffll) return SFB_ERR_UNSUPPORTED;
+  if (npos > 1) {
+    cudaError_t e = cudaMemset2DAsync(feat + f_off, (size_t)f_ld * 4, 0, (size_t)C * 4, (size_t)N, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMemset2DAsync(head_pool_fwd)");
+  }
+  dim3 grid((unsigned)(N * npos), (unsigned)((CV + cvb - 1) / cvb));
+  head_pool_fwd_kernel<<<grid, kHeadThreads, 0, (cudaStream_t)stream>>>(vx, N, T, H, W, C, kT, kH, kW, dropout_p, seed, feat,
+                                                                        f_ld, f_off, cvb, (int)npos);
   SFB_CHECK_LAUNCH("head_pool_fwd_kernel");
   return SFB_OK;
 }
