@@ -165,7 +165,9 @@ def run_gpu_arm(args):
     model.train()
     if world > 1:
         attach_ddp(model, bucket_mb=args.bucket_mb)
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+    # same update rule as the reference's optim.Adam (train.py:182); fused=True runs it as one multi-tensor kernel
+    # instead of ~50 foreach launches (1.0 -> 0.3 ms of a 72 ms step)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, fused=True)
     g = torch.Generator().manual_seed(1000 + rank)
     # synthetic clips, per-rank seed; resident copies for `value`, a pinned host copy for `e2e`
     host = [torch.randn((B, 5, T_SLOW, SIZE, SIZE), generator=g).pin_memory(),
@@ -313,6 +315,7 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": world * B,
                        "step": "fwd + CrossEntropy + bwd + bucketed grad all-reduce + Adam (reference train.py:225-231)",
+                       "optimizer": "torch.optim.Adam(lr=1e-4, fused=True)",
                        "parallelism": f"dp{world}", "l2": "working set (>= 30 GB of activations per step) exceeds the 126 MB L2",
                        "weights": "random init (seed 0)", "loss_after_bench": r["loss"]},
             "e2e": {"value": e2e_clips_s, "unit": "clips/s", "ms_per_step": r["e2e_ms"],

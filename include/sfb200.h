@@ -148,6 +148,22 @@ int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int
                          int32_t N, int32_t C, int32_t T, int32_t H, int32_t W, void* out, int32_t Cs, void* stream);
 /* fp32 (Co, Ci, 1, 7, 7) -> bf16 [rows_pad][16*Cs]; rows_pad = 16 / 32 / 64 (Co rounded up) */
 int sfb_pack_weight_stem(const float* w, int32_t Co, int32_t Ci, int32_t Cs, void* wp, int32_t rows_pad, void* stream);
+
+/* Batched form of the four packing entry points above (nn.Conv3d.weight -> the bf16 operands of every conv of the
+ * network, re-derived after each optimizer step): the caller describes the jobs once, sfb_pack_plan turns them into a
+ * device-resident table (synchronous copy; pointers must stay valid), sfb_pack_run executes the whole table in ONE
+ * launch.  kind: 0 = sfb_pack_weight (kT*kH*kW taps, Cg, transposed), 1 = sfb_pack_weight_dgrad (k, s, Cg),
+ * 2 = sfb_fold_weight (k, f, ldo, ldi), 3 = sfb_pack_weight_stem (Cg = Cs).  Jobs of one table must not depend on
+ * each other (pack folded weights from a second table run after the table holding the fold jobs). */
+typedef struct SfbPackJob {
+  int32_t kind;
+  int32_t Co, Ci, kT, kH, kW, sT, sH, sW, Cg, transposed, f, ldo, ldi, rows_pad, k_pad;
+  const float* src;
+  void* dst;
+} SfbPackJob;
+int64_t sfb_pack_table_bytes(int32_t n_jobs);
+int sfb_pack_plan(const SfbPackJob* jobs, int32_t n_jobs, void* table_dev, int64_t table_bytes, int32_t* total_blocks);
+int sfb_pack_run(const void* table_dev, int32_t n_jobs, int32_t total_blocks, void* stream);
 /* y[N,T,H2,W2,Co] (view o_ld/o_coff) = conv(x) ; stats as in SfbEpilogue.stats (may be NULL) */
 int sfb_stem_conv_fprop(const void* xs2d, int32_t N, int32_t T, int32_t H2, int32_t W2, int32_t Ci, int32_t Cs,
                         const void* wp, int32_t rows_pad, void* out, int32_t o_ld, int32_t o_coff, int32_t Co,

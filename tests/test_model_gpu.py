@@ -211,6 +211,33 @@ def test_noncontiguous_inputs_and_time_mismatch():
             product([torch.randn(1, 5, 8, 64, 64, device=DEV), torch.randn(1, 15, 32, 64, 64, device=DEV)])
 
 
+@pytest.mark.parametrize("variant", ["REF", "HYB"])
+def test_batched_operand_packing_is_bit_identical(variant):
+    """sfb_pack_plan / sfb_pack_run (one launch per level, used from the second training step on) writes exactly the
+    operands the per-layer packing entry points wrote in the first step"""
+    _, product = pu.build_pair(variant, True)
+    xs, xf = _clips(variant, 2, 64 if variant == "REF" else 224, 8, 8 if variant == "REF" else 32)
+    product.train()
+    product([xs, xf]).sum().backward()  # first step: per-layer path allocates and fills every operand
+    eng = product._engine
+    names = ("wp", "wpt", "wf", "wpf", "wptf", "wps")
+    before = {(i, n): getattr(l, n).clone() for i, l in enumerate(eng.layers) for n in names if getattr(l, n, None) is not None}
+    assert any(n == "wptf" for _, n in before) and any(n == "wps" for _, n in before)
+    for l in eng.layers:
+        for n in names:
+            if getattr(l, n, None) is not None:
+                getattr(l, n).fill_(3.0)  # poison: the batched launch must rewrite everything
+    with torch.no_grad():
+        for p_ in product.parameters():
+            p_.add_(0.0)  # same values, new version counter (what an optimizer step does)
+    launches = _ffi.launch_count()
+    eng.refresh_weights(True)
+    assert _ffi.launch_count() - launches <= 2, "batched path not taken"
+    torch.cuda.synchronize()
+    for (i, n), ref in before.items():
+        assert torch.equal(getattr(eng.layers[i], n), ref), (i, n)
+
+
 def test_simt_impl_matches_tc():
     """the CUDA-core cross-check kernels and the tcgen05 kernels implement the same contract end to end"""
     oracle, product = pu.build_pair("REF", True)

@@ -35,6 +35,16 @@ class Epilogue(C.Structure):
 
 _i32, _i64, _u64, _f32, _vp = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_void_p
 
+
+class PackJob(C.Structure):
+    """SfbPackJob (include/sfb200.h): one weight-operand packing job of a batched table"""
+    _fields_ = [(n, C.c_int32) for n in (
+        "kind", "Co", "Ci", "kT", "kH", "kW", "sT", "sH", "sW", "Cg", "transposed", "f", "ldo", "ldi", "rows_pad",
+        "k_pad")] + [("src", C.c_void_p), ("dst", C.c_void_p)]
+
+
+PACK_WEIGHT, PACK_WEIGHT_DGRAD, PACK_FOLD, PACK_STEM = 0, 1, 2, 3
+
 # name -> argtypes; every function returns int (status) unless listed in _SPECIAL
 SIGNATURES = {
     "sfb_packed_weight_dims": [_i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
@@ -63,6 +73,8 @@ SIGNATURES = {
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
+    "sfb_pack_plan": [C.POINTER(PackJob), _i32, _vp, _i64, C.POINTER(_i32)],
+    "sfb_pack_run": [_vp, _i32, _i32, _vp],
 }
 _SPECIAL = {
     "sfb_strerror": ([_i32], C.c_char_p),
@@ -70,6 +82,7 @@ _SPECIAL = {
     "sfb_version": ([], _i32),
     "sfb_launch_count": ([], _i64),
     "sfb_stem_s2d_channels": ([_i32], _i32),
+    "sfb_pack_table_bytes": ([_i32], _i64),
 }
 ALL_SYMBOLS = sorted(list(SIGNATURES) + list(_SPECIAL))
 

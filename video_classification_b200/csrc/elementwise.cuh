@@ -52,11 +52,12 @@ __global__ void layout_input_kernel(const float* __restrict__ x, long long sn, l
 }
 
 // ---- weight packing: fp32 OIDHW -> bf16 [rows_pad][k_pad] ---------------------------------------
-__global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, int taps, int Cg, int transposed,
-                                   __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+// (bodies are __device__ functions over [first, total) with a stride so the batched launch below can run them too)
+__device__ __forceinline__ void pack_weight_body(const float* __restrict__ w, int Co, int Ci, int taps, int Cg,
+                                                 int transposed, __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad,
+                                                 long long first, long long step) {
   const long long total = (long long)rows_pad * k_pad;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = first; idx < total; idx += step) {
     const int k = (int)(idx % k_pad);
     const int row = (int)(idx / k_pad);
     float v = 0.f;
@@ -70,6 +71,11 @@ __global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, 
     }
     wp[idx] = __float2bfloat16_rn(v);
   }
+}
+__global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, int taps, int Cg, int transposed,
+                                   __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+  pack_weight_body(w, Co, Ci, taps, Cg, transposed, wp, rows_pad, k_pad,
+                   (long long)blockIdx.x * blockDim.x + threadIdx.x, (long long)gridDim.x * blockDim.x);
 }
 
 
@@ -89,12 +95,12 @@ struct DgradClassTable {
 };
 
 // fp32 OIDHW (Co, Ci, kT,kH,kW) -> bf16 [rows_pad (>= Ci)][k_pad], column = class k0 + tap_in_class*Cg + co
-__global__ void pack_weight_dgrad_kernel(const float* __restrict__ w, int Co, int Ci, int Cg, DgradClassTable tb,
-                                         __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+__device__ __forceinline__ void pack_weight_dgrad_body(const float* __restrict__ w, int Co, int Ci, int Cg,
+                                                       const DgradClassTable& tb, __nv_bfloat16* __restrict__ wp,
+                                                       int rows_pad, int k_pad, long long first, long long step) {
   const long long total = (long long)rows_pad * k_pad;
   const int taps_all = tb.k[0] * tb.k[1] * tb.k[2];
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = first; idx < total; idx += step) {
     const int col = (int)(idx % k_pad);
     const int row = (int)(idx / k_pad);
     float v = 0.f;
@@ -115,6 +121,11 @@ __global__ void pack_weight_dgrad_kernel(const float* __restrict__ w, int Co, in
     wp[idx] = __float2bfloat16_rn(v);
   }
 }
+__global__ void pack_weight_dgrad_kernel(const float* __restrict__ w, int Co, int Ci, int Cg, DgradClassTable tb,
+                                         __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
+  pack_weight_dgrad_body(w, Co, Ci, Cg, tb, wp, rows_pad, k_pad, (long long)blockIdx.x * blockDim.x + threadIdx.x,
+                         (long long)gridDim.x * blockDim.x);
+}
 
 __global__ void zero_view_kernel(ViewW v, long long M, int C) {
   const int CV = C >> 3;
@@ -132,13 +143,13 @@ __global__ void zero_view_kernel(ViewW v, long long M, int C) {
 //   Wf[(j,co)][(j',c)][kt][kh][kw'] = W[co][c][kt][kh][kw],  kw = f*(kw' - kW'/2) + j' - j + kW/2   (0 outside [0,kW))
 // (kW' = 1 for kW = 1, 3 for kW = 3).  The heavy kernels run unchanged on 128-byte rows; these three small kernels
 // translate weights, BatchNorm statistics and weight gradients between the folded and the reference layout.
-__global__ void fold_weight_kernel(const float* __restrict__ w, int Co, int Ci, int kT, int kH, int kW, int f, int ldo,
-                                   int ldi, float* __restrict__ wf) {
+__device__ __forceinline__ void fold_weight_body(const float* __restrict__ w, int Co, int Ci, int kT, int kH, int kW,
+                                                 int f, int ldo, int ldi, float* __restrict__ wf, long long first,
+                                                 long long step) {
   const int kWf = kW == 1 ? 1 : 3;
   const int Cof = f * ldo, Cif = f * ldi;
   const long long total = (long long)Cof * Cif * kT * kH * kWf;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = first; idx < total; idx += step) {
     long long q = idx;
     const int kwf = (int)(q % kWf); q /= kWf;
     const int kh = (int)(q % kH); q /= kH;
@@ -152,6 +163,11 @@ __global__ void fold_weight_kernel(const float* __restrict__ w, int Co, int Ci, 
     if (co < Co && c < Ci && kw >= 0 && kw < kW) v = w[((((size_t)co * Ci + c) * kT + kt) * kH + kh) * kW + kw];
     wf[idx] = v;
   }
+}
+__global__ void fold_weight_kernel(const float* __restrict__ w, int Co, int Ci, int kT, int kH, int kW, int f, int ldo,
+                                   int ldi, float* __restrict__ wf) {
+  fold_weight_body(w, Co, Ci, kT, kH, kW, f, ldo, ldi, wf, (long long)blockIdx.x * blockDim.x + threadIdx.x,
+                   (long long)gridDim.x * blockDim.x);
 }
 
 // dW[co][c][kt][kh][kw] += sum over (j, j', kw') mapping to kw of dWf[(j,co)][(j',c)][kt][kh][kw']

@@ -6,6 +6,7 @@
 #include "wgrad_tma.cuh"
 #include "stem_win.cuh"
 #include "elementwise.cuh"
+#include "pack_batch.cuh"
 
 #include <algorithm>
 #include <array>
@@ -16,6 +17,7 @@
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
 
 using namespace sfb;
 
@@ -520,6 +522,67 @@ int sfb_pack_weight_stem(const float* w, int32_t Co, int32_t Ci, int32_t Cs, voi
   const long long total = (long long)rows_pad * 16 * Cs;
   pack_weight_stem_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(w, Co, Ci, Cs, (__nv_bfloat16*)wp, rows_pad);
   SFB_CHECK_LAUNCH("pack_weight_stem_kernel");
+  return SFB_OK;
+}
+
+int64_t sfb_pack_table_bytes(int32_t n_jobs) { return n_jobs > 0 ? (int64_t)n_jobs * (int64_t)sizeof(PackJobDev) : 0; }
+
+int sfb_pack_plan(const SfbPackJob* jobs, int32_t n_jobs, void* table_dev, int64_t table_bytes, int32_t* total_blocks) {
+  if (!jobs || n_jobs <= 0 || !table_dev || !total_blocks || table_bytes < sfb_pack_table_bytes(n_jobs)) return SFB_ERR_BAD_ARG;
+  std::vector<PackJobDev> tab((size_t)n_jobs);
+  int block0 = 0;
+  for (int i = 0; i < n_jobs; ++i) {
+    const SfbPackJob& j = jobs[i];
+    PackJobDev& d = tab[(size_t)i];
+    memset(&d, 0, sizeof(d));
+    if (!j.src || !j.dst || j.Co <= 0 || j.Ci <= 0) return SFB_ERR_BAD_ARG;
+    d.kind = j.kind; d.Co = j.Co; d.Ci = j.Ci; d.kT = j.kT; d.kH = j.kH; d.kW = j.kW; d.Cg = j.Cg;
+    d.transposed = j.transposed; d.f = j.f; d.ldo = j.ldo; d.ldi = j.ldi; d.rows_pad = j.rows_pad; d.k_pad = j.k_pad;
+    d.src = j.src; d.dst = j.dst;
+    long long total = 0;
+    switch (j.kind) {
+      case 0:
+        if (j.kT <= 0 || j.kH <= 0 || j.kW <= 0 || j.Cg <= 0 || j.rows_pad <= 0 || j.k_pad <= 0) return SFB_ERR_BAD_ARG;
+        total = (long long)j.rows_pad * j.k_pad;
+        break;
+      case 1: {
+        if ((j.Cg & 7) || j.Cg < j.Co || j.rows_pad < j.Ci) return SFB_ERR_BAD_ARG;
+        const int k[3] = {j.kT, j.kH, j.kW}, s[3] = {j.sT, j.sH, j.sW};
+        int kp = 0;
+        int rc = build_dgrad_classes(k, s, nullptr, nullptr, j.Cg, &d.tb, &kp);
+        if (rc) return rc;
+        if (kp != j.k_pad) return SFB_ERR_BAD_ARG;
+        total = (long long)j.rows_pad * j.k_pad;
+        break;
+      }
+      case 2:
+        if (!fold_args_ok(j.Co, j.Ci, j.kT, j.kH, j.kW, j.f, j.ldo, j.ldi)) return SFB_ERR_BAD_ARG;
+        total = (long long)j.f * j.ldo * j.f * j.ldi * j.kT * j.kH * (j.kW == 1 ? 1 : 3);
+        break;
+      case 3:
+        if ((j.Cg != 32 && j.Cg != 64) || 4 * j.Ci > j.Cg || j.rows_pad < j.Co) return SFB_ERR_BAD_ARG;
+        total = (long long)j.rows_pad * 16 * j.Cg;
+        break;
+      default:
+        return SFB_ERR_BAD_ARG;
+    }
+    long long nb = (total + 256ll * 8 - 1) / (256ll * 8);  // ~8 elements per thread
+    if (nb < 1) nb = 1;
+    if (nb > 512) nb = 512;
+    d.block0 = block0;
+    d.nblocks = (int)nb;
+    block0 += (int)nb;
+  }
+  cudaError_t e = cudaMemcpy(table_dev, tab.data(), (size_t)n_jobs * sizeof(PackJobDev), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(pack table)");
+  *total_blocks = block0;
+  return SFB_OK;
+}
+
+int sfb_pack_run(const void* table_dev, int32_t n_jobs, int32_t total_blocks, void* stream) {
+  if (!table_dev || n_jobs <= 0 || total_blocks <= 0) return SFB_ERR_BAD_ARG;
+  pack_batch_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>((const PackJobDev*)table_dev, n_jobs);
+  SFB_CHECK_LAUNCH("pack_batch_kernel");
   return SFB_OK;
 }
 

@@ -535,12 +535,12 @@ layout_input_s2d_vec_kernel(const float* __restrict__ x, long long sn, long long
 }
 
 // ---- stem weight packing: fp32 (Co, Ci, 1, 7, 7) -> bf16 [rows_pad][16*Cs], k = (dh*4+dw)*Cs + (sh*2+sw)*Ci + c ---
-__global__ void pack_weight_stem_kernel(const float* __restrict__ w, int Co, int Ci, int Cs,
-                                        __nv_bfloat16* __restrict__ wp, int rows_pad) {
+__device__ __forceinline__ void pack_weight_stem_body(const float* __restrict__ w, int Co, int Ci, int Cs,
+                                                      __nv_bfloat16* __restrict__ wp, int rows_pad, long long first,
+                                                      long long step) {
   const int K = 16 * Cs;
   const long long total = (long long)rows_pad * K;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
+  for (long long idx = first; idx < total; idx += step) {
     const int k = (int)(idx % K);
     const int row = (int)(idx / K);
     const int tap = k / Cs, cs = k - tap * Cs;
@@ -551,6 +551,11 @@ __global__ void pack_weight_stem_kernel(const float* __restrict__ w, int Co, int
     if (row < Co && quad < 4 && kh >= 0 && kw >= 0 && kh < 7 && kw < 7) v = w[(((size_t)row * Ci + c) * 7 + kh) * 7 + kw];
     wp[idx] = __float2bfloat16_rn(v);
   }
+}
+__global__ void pack_weight_stem_kernel(const float* __restrict__ w, int Co, int Ci, int Cs,
+                                        __nv_bfloat16* __restrict__ wp, int rows_pad) {
+  pack_weight_stem_body(w, Co, Ci, Cs, wp, rows_pad, (long long)blockIdx.x * blockDim.x + threadIdx.x,
+                        (long long)gridDim.x * blockDim.x);
 }
 
 }  // namespace sfb

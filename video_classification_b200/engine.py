@@ -135,6 +135,7 @@ class SlowFastEngine:
         self.lib = lib()
         self.stream = C.c_void_p(0)
         self.impl = _ffi.IMPL_TC
+        self._pack_cache = {}
         self.plans: Dict[Tuple, Plan] = {}
         self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
         self.step_seed = 0
@@ -256,10 +257,87 @@ class SlowFastEngine:
     def invalidate_weights(self):
         for l in self.layers:
             l.packed_version = -1
+        self._pack_cache = {}
 
     # ------------------------------------------------------------------ weights
+    def _pack_tables(self, training: bool):
+        """Device-resident job tables that re-derive EVERY operand in two launches (level 0: straight from the
+        master weights, incl. the folded fp32 weights; level 1: operands packed from those).  Built once per
+        (mode, kernel impl) -- buffers and master-weight storage are stable; load_state_dict / optimizers write in
+        place -- and dropped by invalidate_weights()."""
+        key = (bool(training), self.impl)
+        tabs = self._pack_cache.get(key)
+        if tabs is not None and tabs["ptrs"] == [l.conv.weight.data_ptr() for l in self.layers]:
+            return tabs
+        P = _ffi.PackJob
+        lv0, lv1 = [], []
+        for l in self.layers:
+            w = l.conv.weight
+            if not w.is_contiguous():
+                return None
+            src = w.data_ptr()
+            kT, kH, kW = l.k
+            rp, kp = l.wp.shape
+            lv0.append(P(_ffi.PACK_WEIGHT, l.Co, l.Ci, kT, kH, kW, 1, 1, 1, l.Cg, 0, 0, 0, 0, rp, kp, src, l.wp.data_ptr()))
+            dg = training and l.needs_dgrad
+            if dg:
+                rpt, kpt = l.wpt.shape
+                if self.impl == _ffi.IMPL_TC:
+                    lv0.append(P(_ffi.PACK_WEIGHT_DGRAD, l.Co, l.Ci, kT, kH, kW, l.s[0], l.s[1], l.s[2], l.Cgt, 0, 0, 0, 0,
+                                 rpt, kpt, src, l.wpt.data_ptr()))
+                else:
+                    lv0.append(P(_ffi.PACK_WEIGHT, l.Co, l.Ci, kT, kH, kW, 1, 1, 1, l.Cgt, 1, 0, 0, 0, rpt, kpt, src,
+                                 l.wpt.data_ptr()))
+            if l.wps is not None:
+                lv0.append(P(_ffi.PACK_STEM, l.Co, l.Ci, 1, 7, 7, 1, 2, 2, l.wps.shape[1] // 16, 0, 0, 0, 0, l.wps.shape[0],
+                             l.wps.shape[1], src, l.wps.data_ptr()))
+            if l.fold_f > 1:
+                f = l.fold_f
+                lv0.append(P(_ffi.PACK_FOLD, l.Co, l.Ci, kT, kH, kW, 1, 1, 1, 0, 0, f, l.ldo, l.ldi, 0, 0, src, l.wf.data_ptr()))
+                fk = l.kf
+                lv1.append(P(_ffi.PACK_WEIGHT, f * l.ldo, f * l.ldi, fk[0], fk[1], fk[2], 1, 1, 1, f * l.ldi, 0, 0, 0, 0,
+                             l.wpf.shape[0], l.wpf.shape[1], l.wf.data_ptr(), l.wpf.data_ptr()))
+                if dg:
+                    if self.impl == _ffi.IMPL_TC:
+                        lv1.append(P(_ffi.PACK_WEIGHT_DGRAD, f * l.ldo, f * l.ldi, fk[0], fk[1], fk[2], 1, 1, 1, f * l.ldo, 0,
+                                     0, 0, 0, l.wptf.shape[0], l.wptf.shape[1], l.wf.data_ptr(), l.wptf.data_ptr()))
+                    else:
+                        lv1.append(P(_ffi.PACK_WEIGHT, f * l.ldo, f * l.ldi, fk[0], fk[1], fk[2], 1, 1, 1, f * l.ldo, 1,
+                                     0, 0, 0, l.wptf.shape[0], l.wptf.shape[1], l.wf.data_ptr(), l.wptf.data_ptr()))
+        levels = []
+        for jobs in (lv0, lv1):
+            if not jobs:
+                continue
+            arr = (P * len(jobs))(*jobs)
+            nbytes = int(self.lib.sfb_pack_table_bytes(len(jobs)))
+            tab = torch.empty(nbytes, dtype=torch.uint8, device=self.dev)
+            nblk = C.c_int32(0)
+            _ffi.check(self.lib.sfb_pack_plan(arr, len(jobs), tab.data_ptr(), nbytes, C.byref(nblk)), "sfb_pack_plan")
+            levels.append((tab, len(jobs), nblk.value))
+        tabs = {"levels": levels, "ptrs": [l.conv.weight.data_ptr() for l in self.layers]}
+        self._pack_cache[key] = tabs
+        return tabs
+
     def refresh_weights(self, training: bool):
         """(Re)pack bf16 GEMM operands of every conv whose fp32 master weight changed (optimizer step / load)."""
+        stale = [l for l in self.layers
+                 if not (l.packed_version == l.conv.weight._version and l.wp is not None and
+                         getattr(l, "packed_impl", None) == self.impl and
+                         (l.wpt is not None or not (training and l.needs_dgrad)))]
+        if not stale:
+            return
+        # every operand buffer exists (a first pass went through the per-layer path) and all weights changed --
+        # the per-step case after an optimizer update: two batched launches instead of ~330 small ones
+        if (len(stale) == len(self.layers) and not self.dry_run and all(l.wp is not None for l in self.layers) and
+                all(l.wpt is not None for l in self.layers if training and l.needs_dgrad) and
+                all(getattr(l, "packed_impl", None) == self.impl for l in self.layers)):
+            tabs = self._pack_tables(training)
+            if tabs is not None:
+                for tab, n, nblk in tabs["levels"]:
+                    _ffi.check(self.lib.sfb_pack_run(tab.data_ptr(), n, nblk, self.stream), "sfb_pack_run")
+                for l in self.layers:
+                    l.packed_version = l.conv.weight._version
+                return
         for l in self.layers:
             w = l.conv.weight
             if l.packed_version == w._version and l.wp is not None and getattr(l, "packed_impl", None) == self.impl and \
