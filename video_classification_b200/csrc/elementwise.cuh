@@ -243,8 +243,8 @@ __global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __r
 // mask_bits (optional, [M][C/8] bytes, bit i = channel 8*cv+i): the ReLU mask of `out`, so that the backward pass
 // reads one byte instead of 16 to know where the gradient passes.
 constexpr int kTailThreads = 256;
-constexpr int kTailUnroll = 4;
-__global__ void __launch_bounds__(kTailThreads)
+template <bool HAS_R>
+__global__ void __launch_bounds__(kTailThreads, 2)
 bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, View r,
                    const float* __restrict__ r_scale, const float* __restrict__ r_shift, ViewW out,
                    uint8_t* __restrict__ mask_bits, long long M, int C, int relu) {
@@ -257,7 +257,9 @@ bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restr
   float s[8], b[8], rs[8], rb[8];
   load8f(scale + c, s);
   load8f(shift + c, b);
-  const bool has_r = r.p != nullptr, r_bn = r_scale != nullptr;
+  constexpr bool has_r = HAS_R;
+  constexpr int kTailUnroll = HAS_R ? 4 : 8;  // rows in flight per thread: 8 x 16 B loads either way
+  const bool r_bn = r_scale != nullptr;
   if (r_bn) { load8f(r_scale + c, rs); load8f(r_shift + c, rb); }
   const long long stride = (long long)gridDim.x * RL;
   for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kTailUnroll) {
@@ -355,11 +357,17 @@ __device__ __forceinline__ void bn_bwd_math(const BnBwdRaw& r, int u, int mode, 
   if (relu) bn_apply_mask(r, u, mode, yv, s, b, g);
 }
 
-// block = (CV channel-vectors) x (RL row lanes); grid.x strides over row groups
-__global__ void __launch_bounds__(kRedThreads)
+// block = (CV channel-vectors) x (RL row lanes); grid.x strides over row groups.
+// MODE = ReLU mask source (bn_bwd_fetch; 3 = no ReLU).  A read-only pass lives on bytes in flight: with 121
+// registers (2 blocks / SM) and 4 rows per tensor it reached 5.3 TB/s (ncu r1g: 24 % warps active, 40 % long
+// scoreboard), so the mask source is a template parameter (dead operands cost no registers), the centred sum
+// sum g*(y - mean) replaces sum g*xhat (invstd is applied once per block) and kRedUnroll rows are in flight.
+constexpr int kRedUnroll = 8;
+template <int MODE>
+__global__ void __launch_bounds__(kRedThreads, 2)
 bn_bwd_reduce_kernel(View dz, View y, View msk, const uint8_t* __restrict__ mask_bits, const float* __restrict__ scale,
                      const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
-                     int relu, long long M, int C, float* dgamma, float* dbeta) {
+                     long long M, int C, float* dgamma, float* dbeta) {
   __shared__ float red[kRedThreads * 16];
   const int CV = C >> 3;
   const int RL = kRedThreads / CV;  // >= 1 (C <= 2048)
@@ -370,29 +378,50 @@ bn_bwd_reduce_kernel(View dz, View y, View msk, const uint8_t* __restrict__ mask
 #pragma unroll
   for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
   if (ty < RL) {
-    float sc[8], sh[8], mu[8], is[8];
-    const int mode = !relu ? 3 : (mask_bits ? 2 : (msk.p ? 1 : 0));
-    if (mode == 0) { load8f(scale + c, sc); load8f(shift + c, sh); }
+    float sc[8], sh[8], mu[8];
+    if (MODE == 0) { load8f(scale + c, sc); load8f(shift + c, sh); }
     load8f(mean + c, mu);
-    load8f(invstd + c, is);
     const long long stride = (long long)gridDim.x * RL;
-    for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kBnUnroll) {
-      long long m[kBnUnroll];
-      bool ok[kBnUnroll];
+    for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kRedUnroll) {
+      uint4 qd[kRedUnroll], qy[kRedUnroll], qm[kRedUnroll];
 #pragma unroll
-      for (int u = 0; u < kBnUnroll; ++u) { m[u] = m0 + u * stride; ok[u] = m[u] < M; }
-      BnBwdRaw r;
-      bn_bwd_fetch(dz, y, msk, mask_bits, CV, mode, m, ok, c, r);
+      for (int u = 0; u < kRedUnroll; ++u) {
+        const long long m = m0 + u * stride;
+        if (m < M) {
+          qd[u] = vload(dz, m, c);
+          qy[u] = vload(y, m, c);
+          if (MODE == 1) qm[u] = vload(msk, m, c);
+          else if (MODE == 2) qm[u].x = mask_bits[m * CV + tx];
+        }
+      }
 #pragma unroll
-      for (int u = 0; u < kBnUnroll; ++u) {
-        if (ok[u]) {
-          float g[8], xh[8];
-          bn_bwd_math(r, u, mode, relu, sc, sh, mu, is, g, xh);
+      for (int u = 0; u < kRedUnroll; ++u) {
+        if (m0 + u * stride < M) {
+          float g[8], yv[8];
+          unpack8(qd[u], g);
+          unpack8(qy[u], yv);
+          if (MODE == 1) {
+            float mv[8];
+            unpack8(qm[u], mv);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], xh[i], s2[i]); }
+            for (int i = 0; i < 8; ++i) g[i] = mv[i] > 0.f ? g[i] : 0.f;
+          } else if (MODE == 2) {
+            const uint32_t bits = qm[u].x;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = (bits >> i) & 1u ? g[i] : 0.f;
+          } else if (MODE == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], sc[i], sh[i]) > 0.f ? g[i] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], yv[i] - mu[i], s2[i]); }
         }
       }
     }
+    float is[8];
+    load8f(invstd + c, is);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s2[i] *= is[i];
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {

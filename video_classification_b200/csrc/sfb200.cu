@@ -1007,9 +1007,14 @@ int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* sc
   View vr{(const __nv_bfloat16*)r, r_ld, r_coff};
   ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
   const int RL = kTailThreads / (C >> 3);
-  const int grid = grid_for((M + (long long)RL * kTailUnroll - 1) / ((long long)RL * kTailUnroll), 1, 148 * 8);
-  bn_add_relu_kernel<<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
-                                                                      mask_bits, M, C, relu);
+  const int unroll = r ? 4 : 8;
+  const int grid = grid_for((M + (long long)RL * unroll - 1) / ((long long)RL * unroll), 1, 148 * 8);
+  if (r)
+    bn_add_relu_kernel<true><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
+                                                                              mask_bits, M, C, relu);
+  else
+    bn_add_relu_kernel<false><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
+                                                                               mask_bits, M, C, relu);
   SFB_CHECK_LAUNCH("bn_add_relu_kernel");
   return SFB_OK;
 }
@@ -1026,9 +1031,14 @@ int sfb_bn_bwd_reduce(const void* dz, int32_t dz_ld, int32_t dz_coff, const void
   View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
   View vm{(const __nv_bfloat16*)mask_src, m_ld, m_coff};
   const int RL = kRedThreads / (C >> 3);
-  const int grid = grid_for((M + (long long)RL * kBnUnroll - 1) / ((long long)RL * kBnUnroll), 1, 148 * 8);
-  bn_bwd_reduce_kernel<<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, vy, vm, mask_bits, scale, shift, mean, invstd,
-                                                                       relu, M, C, dgamma, dbeta);
+  const int grid = grid_for((M + (long long)RL * kRedUnroll - 1) / ((long long)RL * kRedUnroll), 1, 148 * 8);
+  const int mode = !relu ? 3 : (mask_bits ? 2 : (mask_src ? 1 : 0));
+#define SFB_REDUCE(MD) bn_bwd_reduce_kernel<MD><<<grid, kRedThreads, 0, (cudaStream_t)stream>>>(       vdz, vy, vm, mask_bits, scale, shift, mean, invstd, M, C, dgamma, dbeta)
+  if (mode == 0) SFB_REDUCE(0);
+  else if (mode == 1) SFB_REDUCE(1);
+  else if (mode == 2) SFB_REDUCE(2);
+  else SFB_REDUCE(3);
+#undef SFB_REDUCE
   SFB_CHECK_LAUNCH("bn_bwd_reduce_kernel");
   return SFB_OK;
 }
