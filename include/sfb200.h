@@ -191,6 +191,30 @@ int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* sc
                     void* out, int32_t o_ld, int32_t o_coff, uint8_t* mask_bits, int64_t M, int32_t C, int32_t relu,
                     void* stream);
 
+/* Training-mode form of sfb_bn_add_relu that finalises the BatchNorm statistics itself: the coefficients are derived
+ * in-kernel from the raw sums the producing conv accumulated (sfb_conv_gemm's `stats`), and scale / shift /
+ * save_mean / save_invstd are stored and the running statistics updated exactly as sfb_bn_finalize would -- without
+ * the extra launch per BatchNorm.  fold_f > 1: `stats` is the pixel-folded layout [2*fold_f*fold_ld] that
+ * sfb_unfold_stats would otherwise translate.  r_bn == NULL: the shortcut r (if any) is added as is. */
+typedef struct SfbBnRaw {
+  const float* stats;
+  int64_t count;
+  const float* gamma;
+  const float* beta;
+  float eps, momentum;
+  float* running_mean;   /* may be NULL */
+  float* running_var;
+  float* scale;          /* outputs, [C] each */
+  float* shift;
+  float* save_mean;
+  float* save_invstd;
+  int32_t fold_f, fold_ld;
+} SfbBnRaw;
+int sfb_bn_add_relu_raw(const void* y, int32_t y_ld, int32_t y_coff, const SfbBnRaw* y_bn,
+                        const void* r, int32_t r_ld, int32_t r_coff, const SfbBnRaw* r_bn,
+                        void* out, int32_t o_ld, int32_t o_coff, uint8_t* mask_bits, int64_t M, int32_t C, int32_t relu,
+                        void* stream);
+
 /* BatchNorm3d(+ReLU) backward, phase 1: per-channel reductions accumulated (atomically) into
  * dgamma/dbeta:  g = dz * [relu ? (y*scale+shift > 0) : 1] ;  dbeta += sum g ; dgamma += sum g*xhat.
  * mask_src: optional bf16 tensor whose sign gives the ReLU mask instead (block output O).

@@ -92,6 +92,64 @@ def test_bn_add_relu(C_, with_rbn):
     assert torch.equal(bits, (o.to(torch.int32) * w).sum(-1).to(torch.uint8))
 
 
+@pytest.mark.parametrize("C_,fold_f,with_r", [(64, 0, False), (256, 0, True), (16, 4, False), (32, 2, True)])
+def test_bn_add_relu_raw_equals_finalize_then_apply(C_, fold_f, with_r):
+    """the fused-finalize form gives the same coefficients, running statistics and output as
+    sfb_bn_finalize (+ sfb_unfold_stats) followed by sfb_bn_add_relu"""
+    N, T, H, W = 2, 3, 6, 8
+    M = N * T * H * W
+    y = torch.randn(N, C_, T, H, W, device=DEV) * 1.7 + 0.4
+    r = torch.randn(N, C_, T, H, W, device=DEV)
+    ya, ra = kc.to_act(y), kc.to_act(r)
+    yq = kc.from_act(ya).permute(0, 2, 3, 4, 1).reshape(M, C_)
+    sums = torch.cat([yq.sum(0), (yq * yq).sum(0)])
+
+    def bn_state():
+        g = torch.Generator(device=DEV).manual_seed(3)
+        return dict(gamma=torch.rand(C_, device=DEV, generator=g) + 0.5, beta=torch.randn(C_, device=DEV, generator=g),
+                    rm=torch.randn(C_, device=DEV, generator=g), rv=torch.rand(C_, device=DEV, generator=g) + 0.5,
+                    sc=torch.empty(C_, device=DEV), sh=torch.empty(C_, device=DEV), mean=torch.empty(C_, device=DEV),
+                    inv=torch.empty(C_, device=DEV))
+    a, b = bn_state(), bn_state()
+    ra_, rb_ = bn_state(), bn_state()
+    # reference path
+    ops.bn_finalize(sums, M, a["gamma"], a["beta"], 1e-5, 0.1, a["rm"], a["rv"], a["sc"], a["sh"], a["mean"], a["inv"])
+    if with_r:
+        rq = kc.from_act(ra).permute(0, 2, 3, 4, 1).reshape(M, C_)
+        rsums = torch.cat([rq.sum(0), (rq * rq).sum(0)])
+        ops.bn_finalize(rsums, M, ra_["gamma"], ra_["beta"], 1e-5, 0.1, ra_["rm"], ra_["rv"], ra_["sc"], ra_["sh"],
+                        ra_["mean"], ra_["inv"])
+    out_ref = Act.empty(N, T, H, W, C_)
+    ops.bn_add_relu(ya, a["sc"], a["sh"], ra if with_r else None, ra_["sc"] if with_r else None,
+                    ra_["sh"] if with_r else None, out_ref)
+    # fused path; folded layout: the sums spread over fold_f column groups of width ld
+    if fold_f:
+        ld = C_ + 8
+        raw = torch.zeros(2 * fold_f * ld, device=DEV)
+        w = torch.rand(fold_f, 1, device=DEV)
+        w = w / w.sum(0, keepdim=True)
+        raw[:fold_f * ld].view(fold_f, ld)[:, :C_] = w * sums[:C_]
+        raw[fold_f * ld:].view(fold_f, ld)[:, :C_] = w * sums[C_:]
+    else:
+        ld, raw = 0, sums
+    qy = ops.bn_raw(raw, M, b["gamma"], b["beta"], 1e-5, 0.1, b["rm"], b["rv"], b["sc"], b["sh"], b["mean"], b["inv"],
+                    fold_f, ld)
+    qr = ops.bn_raw(rsums, M, rb_["gamma"], rb_["beta"], 1e-5, 0.1, rb_["rm"], rb_["rv"], rb_["sc"], rb_["sh"],
+                    rb_["mean"], rb_["inv"]) if with_r else None
+    out = Act.empty(N, T, H, W, C_)
+    ops.bn_add_relu_raw(ya, qy, ra if with_r else None, qr, out)
+    torch.cuda.synchronize()
+    tol = dict(rtol=2e-5, atol=2e-6) if fold_f else dict(rtol=0, atol=0)  # folded: fp32 partial sums re-associated
+    for k in ("sc", "sh", "mean", "inv", "rm", "rv"):
+        torch.testing.assert_close(b[k], a[k], **tol)
+        if with_r:
+            torch.testing.assert_close(rb_[k], ra_[k], rtol=0, atol=0)
+    if fold_f:
+        assert kc.relerr(kc.from_act(out), kc.from_act(out_ref)) < 1e-2
+    else:
+        assert torch.equal(out.buf, out_ref.buf)
+
+
 @pytest.mark.parametrize("C_,relu,use_mask", [(64, True, False), (256, True, True), (8, False, False), (1280, True, False),
                                               (256, True, "bits"), (32, True, "bits")])
 def test_bn_bwd(C_, relu, use_mask):

@@ -45,6 +45,14 @@ class PackJob(C.Structure):
 
 PACK_WEIGHT, PACK_WEIGHT_DGRAD, PACK_FOLD, PACK_STEM = 0, 1, 2, 3
 
+
+class BnRaw(C.Structure):
+    """SfbBnRaw (include/sfb200.h): raw BatchNorm sums + where the finalised coefficients go"""
+    _fields_ = [("stats", C.c_void_p), ("count", C.c_int64), ("gamma", C.c_void_p), ("beta", C.c_void_p),
+                ("eps", C.c_float), ("momentum", C.c_float), ("running_mean", C.c_void_p), ("running_var", C.c_void_p),
+                ("scale", C.c_void_p), ("shift", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
+                ("fold_f", C.c_int32), ("fold_ld", C.c_int32)]
+
 # name -> argtypes; every function returns int (status) unless listed in _SPECIAL
 SIGNATURES = {
     "sfb_packed_weight_dims": [_i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
@@ -73,6 +81,8 @@ SIGNATURES = {
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
+    "sfb_bn_add_relu_raw": [_vp, _i32, _i32, C.POINTER(BnRaw), _vp, _i32, _i32, C.POINTER(BnRaw), _vp, _i32, _i32, _vp, _i64,
+                            _i32, _i32, _vp],
     "sfb_pack_plan": [C.POINTER(PackJob), _i32, _vp, _i64, C.POINTER(_i32)],
     "sfb_pack_run": [_vp, _i32, _i32, _vp],
 }

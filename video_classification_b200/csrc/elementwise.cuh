@@ -205,6 +205,16 @@ __global__ void unfold_stats_kernel(const float* __restrict__ sf, int f, int ld,
   stats[C + c] += b;
 }
 
+// one channel: (sum, sum of squares) -> mean, biased variance (the cancelling difference in double), invstd
+__device__ __forceinline__ void bn_moments(float sum, float sq, double inv_count, float eps, float* mean, float* var,
+                                           float* invstd) {
+  const double m = (double)sum * inv_count;
+  double v = (double)sq * inv_count - m * m;
+  if (v < 0.0) v = 0.0;
+  *mean = (float)m;
+  *var = (float)v;
+  *invstd = 1.0f / sqrtf((float)v + eps);
+}
 // ---- BatchNorm finalize / fold ---------------------------------------------------------------------
 __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, double inv_count, double unbias,
                                    const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
@@ -212,18 +222,16 @@ __global__ void bn_finalize_kernel(const float* __restrict__ stats, int C, doubl
                                    float* shift, float* save_mean, float* save_invstd) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  const double mean = (double)stats[c] * inv_count;
-  double var = (double)stats[C + c] * inv_count - mean * mean;
-  if (var < 0.0) var = 0.0;
-  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  float mean, var, invstd;
+  bn_moments(stats[c], stats[C + c], inv_count, eps, &mean, &var, &invstd);
   const float sc = gamma[c] * invstd;
   scale[c] = sc;
-  shift[c] = beta[c] - (float)mean * sc;
-  save_mean[c] = (float)mean;
+  shift[c] = beta[c] - mean * sc;
+  save_mean[c] = mean;
   save_invstd[c] = invstd;
   if (running_mean) {
-    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
-    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)(var * unbias);
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (var * (float)unbias);
   }
 }
 
@@ -242,25 +250,88 @@ __global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __r
 // kTailUnroll rows of every operand in flight (one 16-byte load per row and tensor was latency-bound at 75 % of HBM).
 // mask_bits (optional, [M][C/8] bytes, bit i = channel 8*cv+i): the ReLU mask of `out`, so that the backward pass
 // reads one byte instead of 16 to know where the gradient passes.
+// RAW: the BatchNorm coefficients are derived here from the raw sums the producing conv accumulated (what
+// bn_finalize_kernel does in a launch of its own: ~150 launches of ~7 us per training step); every thread needs only
+// its 8 channels, the first block's first row lane also stores scale / shift / mean / invstd for the backward pass
+// and updates the running statistics.  fold_f > 1: the sums are in the pixel-folded layout (f column groups).
+struct BnRawDev {
+  const float* stats;
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  float* scale;
+  float* shift;
+  float* save_mean;
+  float* save_invstd;
+  double inv_count, unbias;
+  float eps, momentum;
+  int fold_f, fold_ld;
+};
+__device__ __forceinline__ void bn_raw_channel(const BnRawDev& q, int C, int ch, bool writer, float* s, float* b) {
+  float sum, sq;
+  if (q.fold_f > 1) {
+    sum = 0.f; sq = 0.f;
+    for (int j = 0; j < q.fold_f; ++j) {
+      sum += q.stats[j * q.fold_ld + ch];
+      sq += q.stats[q.fold_f * q.fold_ld + j * q.fold_ld + ch];
+    }
+  } else {
+    sum = q.stats[ch];
+    sq = q.stats[C + ch];
+  }
+  float mean, var, invstd;
+  bn_moments(sum, sq, q.inv_count, q.eps, &mean, &var, &invstd);
+  const float sc = q.gamma[ch] * invstd;
+  *s = sc;
+  *b = q.beta[ch] - mean * sc;
+  if (writer) {
+    q.scale[ch] = sc;
+    q.shift[ch] = *b;
+    q.save_mean[ch] = mean;
+    q.save_invstd[ch] = invstd;
+    if (q.running_mean) {
+      q.running_mean[ch] = (1.f - q.momentum) * q.running_mean[ch] + q.momentum * mean;
+      q.running_var[ch] = (1.f - q.momentum) * q.running_var[ch] + q.momentum * (var * (float)q.unbias);
+    }
+  }
+}
+
 constexpr int kTailThreads = 256;
-template <bool HAS_R>
+template <bool HAS_R, bool RAW>
 __global__ void __launch_bounds__(kTailThreads, 2)
 bn_add_relu_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, View r,
                    const float* __restrict__ r_scale, const float* __restrict__ r_shift, ViewW out,
-                   uint8_t* __restrict__ mask_bits, long long M, int C, int relu) {
+                   uint8_t* __restrict__ mask_bits, long long M, int C, int relu, BnRawDev yraw, BnRawDev rraw) {
   const int CV = C >> 3;
   const int RL = kTailThreads / CV;
   const int tx = threadIdx.x % CV;
   const int ty = threadIdx.x / CV;
-  if (ty >= RL) return;
   const int c = tx << 3;
   float s[8], b[8], rs[8], rb[8];
-  load8f(scale + c, s);
-  load8f(shift + c, b);
   constexpr bool has_r = HAS_R;
   constexpr int kTailUnroll = HAS_R ? 4 : 8;  // rows in flight per thread: 8 x 16 B loads either way
-  const bool r_bn = r_scale != nullptr;
-  if (r_bn) { load8f(r_scale + c, rs); load8f(r_shift + c, rb); }
+  const bool r_bn = RAW ? rraw.stats != nullptr : r_scale != nullptr;
+  if constexpr (RAW) {
+    // each channel is finalised once per block and shared (the double-precision moments are too slow to repeat in
+    // every row lane), block 0 stores the coefficients / updates the running statistics
+    __shared__ float coef[4][2048];
+    const bool writer = blockIdx.x == 0;
+    for (int ch = threadIdx.x; ch < C; ch += kTailThreads) {
+      bn_raw_channel(yraw, C, ch, writer, &coef[0][ch], &coef[1][ch]);
+      if (has_r && r_bn) bn_raw_channel(rraw, C, ch, writer, &coef[2][ch], &coef[3][ch]);
+    }
+    __syncthreads();
+    if (ty >= RL) return;
+    load8f(&coef[0][c], s);
+    load8f(&coef[1][c], b);
+    if (has_r && r_bn) { load8f(&coef[2][c], rs); load8f(&coef[3][c], rb); }
+  } else {
+    if (ty >= RL) return;
+    load8f(scale + c, s);
+    load8f(shift + c, b);
+    if (r_bn) { load8f(r_scale + c, rs); load8f(r_shift + c, rb); }
+  }
   const long long stride = (long long)gridDim.x * RL;
   for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kTailUnroll) {
     uint4 qy[kTailUnroll], qr[kTailUnroll];

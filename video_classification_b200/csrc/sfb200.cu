@@ -1009,12 +1009,59 @@ int sfb_bn_add_relu(const void* y, int32_t y_ld, int32_t y_coff, const float* sc
   const int RL = kTailThreads / (C >> 3);
   const int unroll = r ? 4 : 8;
   const int grid = grid_for((M + (long long)RL * unroll - 1) / ((long long)RL * unroll), 1, 148 * 8);
+  BnRawDev none;
+  memset(&none, 0, sizeof(none));
   if (r)
-    bn_add_relu_kernel<true><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
-                                                                              mask_bits, M, C, relu);
+    bn_add_relu_kernel<true, false><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift,
+                                                                                     vo, mask_bits, M, C, relu, none, none);
   else
-    bn_add_relu_kernel<false><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift, vo,
-                                                                               mask_bits, M, C, relu);
+    bn_add_relu_kernel<false, false><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, scale, shift, vr, r_scale, r_shift,
+                                                                                      vo, mask_bits, M, C, relu, none, none);
+  SFB_CHECK_LAUNCH("bn_add_relu_kernel");
+  return SFB_OK;
+}
+
+static int bn_raw_dev(const SfbBnRaw* q, int C, BnRawDev* d) {
+  memset(d, 0, sizeof(*d));
+  if (!q) return SFB_OK;
+  if (!q->stats || q->count <= 0 || !q->gamma || !q->beta || !q->scale || !q->shift || !q->save_mean || !q->save_invstd)
+    return SFB_ERR_BAD_ARG;
+  if ((q->running_mean == nullptr) != (q->running_var == nullptr)) return SFB_ERR_BAD_ARG;
+  if (q->fold_f > 1 && (q->fold_f > 8 || q->fold_ld < C)) return SFB_ERR_BAD_ARG;
+  d->stats = q->stats; d->gamma = q->gamma; d->beta = q->beta;
+  d->running_mean = q->running_mean; d->running_var = q->running_var;
+  d->scale = q->scale; d->shift = q->shift; d->save_mean = q->save_mean; d->save_invstd = q->save_invstd;
+  d->inv_count = 1.0 / (double)q->count;
+  d->unbias = q->count > 1 ? (double)q->count / (double)(q->count - 1) : 1.0;
+  d->eps = q->eps; d->momentum = q->momentum;
+  d->fold_f = q->fold_f; d->fold_ld = q->fold_ld;
+  return SFB_OK;
+}
+
+int sfb_bn_add_relu_raw(const void* y, int32_t y_ld, int32_t y_coff, const SfbBnRaw* y_bn, const void* r, int32_t r_ld,
+                        int32_t r_coff, const SfbBnRaw* r_bn, void* out, int32_t o_ld, int32_t o_coff, uint8_t* mask_bits,
+                        int64_t M, int32_t C, int32_t relu, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !y_bn) return SFB_ERR_BAD_ARG;
+  if (!view_ok(y, y_ld, y_coff, C) || !view_ok(out, o_ld, o_coff, C)) return SFB_ERR_BAD_ARG;
+  if (r && !view_ok(r, r_ld, r_coff, C)) return SFB_ERR_BAD_ARG;
+  if (r_bn && !r) return SFB_ERR_BAD_ARG;
+  BnRawDev dy, dr;
+  int rc = bn_raw_dev(y_bn, C, &dy);
+  if (rc) return rc;
+  rc = bn_raw_dev(r_bn, C, &dr);
+  if (rc) return rc;
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  View vr{(const __nv_bfloat16*)r, r_ld, r_coff};
+  ViewW vo{(__nv_bfloat16*)out, o_ld, o_coff};
+  const int RL = kTailThreads / (C >> 3);
+  const int unroll = r ? 4 : 8;
+  const int grid = grid_for((M + (long long)RL * unroll - 1) / ((long long)RL * unroll), 1, 148 * 8);
+  if (r)
+    bn_add_relu_kernel<true, true><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, nullptr, nullptr, vr, nullptr, nullptr,
+                                                                                    vo, mask_bits, M, C, relu, dy, dr);
+  else
+    bn_add_relu_kernel<false, true><<<grid, kTailThreads, 0, (cudaStream_t)stream>>>(vy, nullptr, nullptr, vr, nullptr, nullptr,
+                                                                                     vo, mask_bits, M, C, relu, dy, dr);
   SFB_CHECK_LAUNCH("bn_add_relu_kernel");
   return SFB_OK;
 }

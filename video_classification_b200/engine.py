@@ -113,6 +113,7 @@ class Plan:
         self.keep = []  # ctypes structs / tensors that must outlive the op lists
         self.x_in: List[Act] = []
         self.mask_bits = []  # (block output Act, packed ReLU mask) pairs of a training plan
+        self.stats_folded = {}  # conv name -> its fused BatchNorm sums are in the pixel-folded layout
         self.logits = None
         self.dlogits = None
         self.act_bytes = 0
@@ -451,8 +452,8 @@ class SlowFastEngine:
         self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
                    out.ptr(), C.byref(ep), self.impl, self.stream,
                    tag=tag if tag is not None else (None if transposed else (L.conv_name + ".y", out)))
-        if f > 1 and stats:
-            self._emit(lst, self.lib.sfb_unfold_stats, L.sf.data_ptr(), f, L.ldo, L.Co, L.stats.data_ptr(), self.stream)
+        if stats:
+            plan.stats_folded[L.conv_name] = f > 1  # the consumer reads the folded sums directly (sfb_bn_add_relu_raw)
 
     def _fold_of(self, L: ConvL, x: Act, out: Act, transposed: bool) -> int:
         """fold factor to run this conv pass with (1 = unfolded): needs whole dense buffers on both sides"""
@@ -526,6 +527,23 @@ class SlowFastEngine:
             self.ddp.note_grad_ready(plan, lst, bn.weight)
             self.ddp.note_grad_ready(plan, lst, bn.bias)
 
+    def _bn_raw(self, plan, L: ConvL, count: int):
+        """SfbBnRaw of layer L's training statistics (the conv's fused sums; folded layout when L runs pixel-folded)"""
+        bn = L.bn
+        folded = plan.stats_folded.get(L.conv_name, False)
+        q = _ffi.BnRaw((L.sf if folded else L.stats).data_ptr(), int(count), bn.weight.data_ptr(), bn.bias.data_ptr(),
+                       float(bn.eps), float(bn.momentum if bn.momentum is not None else 0.1),
+                       bn.running_mean.data_ptr(), bn.running_var.data_ptr(), L.scale.data_ptr(), L.shift.data_ptr(),
+                       L.mean.data_ptr(), L.invstd.data_ptr(), L.fold_f if folded else 0, L.ldo if folded else 0)
+        plan.keep.append(q)
+        return q
+
+    def _apply_raw(self, plan, lst, L: ConvL, y: Act, out: Act, tag=None):
+        """training: out = relu(BatchNorm(y)) with the finalize of L's batch statistics fused into the same launch"""
+        q = self._bn_raw(plan, L, y.M)
+        self._emit(lst, self.lib.sfb_bn_add_relu_raw, y.ptr(), y.ld, y.coff, C.byref(q), 0, 0, 0, None,
+                   out.ptr(), out.ld, out.coff, 0, y.M, y.C, 1, self.stream, tag=tag)
+
     def _apply(self, lst, L: ConvL, y: Act, out: Act, tag=None):
         """out = relu(y * scale_L + shift_L)   (training: BatchNorm needs the batch statistics of the whole tensor
         before it can normalise, so the activated operand of the next conv is materialised by one HBM-bound pass)"""
@@ -565,10 +583,9 @@ class SlowFastEngine:
             if training:
                 y = new_act(n_, to, ho, wo, L.Co)
                 self._conv(plan, fwd, L, x, None, y, stats=True)
-                self._bn_stats_ready(plan, fwd, L, y.M, True)
                 if out_z is not None:
-                    self._apply(fwd, L, y, out_z, tag=(L.conv_name + ".z", out_z))
-                return y, out_z
+                    self._apply_raw(plan, fwd, L, y, out_z, tag=(L.conv_name + ".z", out_z))
+                return y, out_z  # out_z is None: the residual tail finalises this layer's statistics
             fold(L)
             assert out_z is not None
             self._conv(plan, fwd, L, x, None, out_z, epi=(L.scale, L.shift, relu), residual=residual,
@@ -671,12 +688,14 @@ class SlowFastEngine:
                         yc, _ = conv_bn_act(c, zb, None)
                         if s_ is not None:
                             y1, _ = conv_bn_act(s_, X.act, None)
-                            self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
-                                       c.shift.data_ptr(), y1.ptr(), y1.ld, y1.coff, s_.scale.data_ptr(), s_.shift.data_ptr(),
+                            qc, qs = self._bn_raw(plan, c, yc.M), self._bn_raw(plan, s_, y1.M)
+                            self._emit(fwd, self.lib.sfb_bn_add_relu_raw, yc.ptr(), yc.ld, yc.coff, C.byref(qc),
+                                       y1.ptr(), y1.ld, y1.coff, C.byref(qs),
                                        O.act.ptr(), O.act.ld, O.act.coff, O.bits.data_ptr(), yc.M, c.Co, 1, self.stream, tag=otag)
                         else:
-                            self._emit(fwd, self.lib.sfb_bn_add_relu, yc.ptr(), yc.ld, yc.coff, c.scale.data_ptr(),
-                                       c.shift.data_ptr(), X.act.ptr(), X.act.ld, X.act.coff, 0, 0,
+                            qc = self._bn_raw(plan, c, yc.M)
+                            self._emit(fwd, self.lib.sfb_bn_add_relu_raw, yc.ptr(), yc.ld, yc.coff, C.byref(qc),
+                                       X.act.ptr(), X.act.ld, X.act.coff, None,
                                        O.act.ptr(), O.act.ld, O.act.coff, O.bits.data_ptr(), yc.M, c.Co, 1, self.stream, tag=otag)
                     else:
                         # eval: shortcut = folded-BN conv (no ReLU) or X itself; conv_c adds it and applies the ReLU
@@ -893,6 +912,8 @@ class SlowFastEngine:
             nt = 0
             if name == "sfb_bn_add_relu":      # y (+ r) -> out
                 M, Cc, nt = args[14], args[15], 2 + (1 if args[5] else 0)
+            elif name == "sfb_bn_add_relu_raw":
+                M, Cc, nt = args[12], args[13], 2 + (1 if args[4] else 0)
             elif name == "sfb_bn_bwd_reduce":  # dz, y (+ bf16 mask)
                 M, Cc, nt = args[15], args[16], 2 + (1 if args[6] else 0)
             elif name == "sfb_bn_bwd_apply":   # dz, y (+ mask) -> dy (+ g_out (+ old g))
@@ -953,12 +974,22 @@ class SlowFastEngine:
                 L.invstd.copy_(invstd)
                 L.scale.copy_(L.bn.weight.detach() * invstd)
                 L.shift.copy_(L.bn.bias.detach() - mean * L.bn.weight.detach() * invstd)
+                # the raw sums the fused-finalize kernels read (re-run below for the activated operands)
+                cnt = float(yf.shape[0])
+                sums = torch.cat([mean * cnt, (var + mean * mean) * cnt])
+                if plan.stats_folded.get(L.conv_name, False):
+                    L.sf.zero_()
+                    L.sf[:L.Co].copy_(sums[:L.Co])
+                    L.sf[L.fold_f * L.ldo:L.fold_f * L.ldo + L.Co].copy_(sums[L.Co:])
+                else:
+                    L.stats.copy_(sums)
         if feat is not None:
             plan.feat.copy_(feat)
         # activated operands (z = relu(bn(y))) and the stem pools (+ arg-max indices) derive from the forced raw
         # outputs: recompute them with the engine's own kernels
         self._run([op for op in plan.fwd if op[0] is self.lib.sfb_maxpool_fwd or
-                   (op[0] is self.lib.sfb_bn_add_relu and op[2] is not None and op[2][0].endswith(".z"))])
+                   (op[0] in (self.lib.sfb_bn_add_relu, self.lib.sfb_bn_add_relu_raw) and op[2] is not None and
+                    op[2][0].endswith(".z"))])
         # packed ReLU masks of the block outputs, from the forced O tensors
         for O_act, bits in plan.mask_bits:
             o = O_act.torch_view().reshape(-1, O_act.C // 8, 8) > 0

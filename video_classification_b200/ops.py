@@ -242,6 +242,22 @@ def bn_add_relu(y: Act, scale, shift, r: Optional[Act], r_scale, r_shift, out: A
     return out
 
 
+def bn_raw(stats, count, gamma, beta, eps, momentum, running_mean, running_var, scale, shift, save_mean, save_invstd,
+           fold_f=0, fold_ld=0):
+    """SfbBnRaw descriptor (keep the returned object alive until the launch has been enqueued)"""
+    return _ffi.BnRaw(stats.data_ptr(), int(count), gamma.data_ptr(), beta.data_ptr(), float(eps), float(momentum),
+                      ptr(running_mean), ptr(running_var), scale.data_ptr(), shift.data_ptr(), save_mean.data_ptr(),
+                      save_invstd.data_ptr(), int(fold_f), int(fold_ld))
+
+
+def bn_add_relu_raw(y: Act, y_bn, r: Optional[Act], r_bn, out: Act, relu=True, mask_bits=None):
+    """sfb_bn_add_relu with the BatchNorm finalize fused in (y_bn / r_bn: bn_raw(...) descriptors, r_bn may be None)"""
+    check(lib().sfb_bn_add_relu_raw(y.ptr(), y.ld, y.coff, C.byref(y_bn), r.ptr() if r else 0, r.ld if r else 0,
+                                    r.coff if r else 0, C.byref(r_bn) if r_bn is not None else None, out.ptr(), out.ld,
+                                    out.coff, ptr(mask_bits), y.M, y.C, int(relu), stream_ptr()), "sfb_bn_add_relu_raw")
+    return out
+
+
 def bn_bwd_reduce(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invstd, relu, dgamma, dbeta, mask_bits=None):
     check(lib().sfb_bn_bwd_reduce(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff,
                                   mask.ptr() if mask else 0, mask.ld if mask else 0, mask.coff if mask else 0,
