@@ -131,6 +131,12 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
  *   sfb_unfold_stats: stats[2*C] += column-group sums of the folded BatchNorm statistics [2*f*ld] */
 int sfb_fold_weight(const float* w, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
                     int32_t ldi, float* wf, void* stream);
+/* Weight gradient of a pixel-folded conv written straight into the reference-layout gradient: `geom` describes the
+ * FOLDED conv (what sfb_conv_wgrad would get, with dy / x viewed as f*ld channels), dw is the fp32 (Co,Ci,kT,kH,kW)
+ * gradient of the real conv; the band map of sfb_fold_weight is applied in the kernel's epilogue (replaces
+ * sfb_conv_wgrad into a folded buffer + sfb_unfold_wgrad). */
+int sfb_conv_wgrad_folded(const SfbConvGeom* geom, const void* x, const void* dy, int32_t dy_ld, int32_t dy_coff, float* dw,
+                          int32_t Co, int32_t Ci, int32_t kW, int32_t f, int32_t ldo, int32_t ldi, void* stream);
 int sfb_unfold_wgrad(const float* dwf, int32_t Co, int32_t Ci, int32_t kT, int32_t kH, int32_t kW, int32_t f, int32_t ldo,
                      int32_t ldi, float* dw, void* stream);
 int sfb_unfold_stats(const float* stats_folded, int32_t f, int32_t ld, int32_t C, float* stats, void* stream);

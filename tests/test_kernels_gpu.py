@@ -427,6 +427,12 @@ def test_folded_conv_matches_reference(N, T, H, W, Ci, Co, k):
     ops.unfold_wgrad(dwf, f, ldo, ldi, dw)
     torch.cuda.synchronize()
     assert kc.relerr(dw, wz.grad) < 2e-2
+    # ---- wgrad with the band map applied in the kernel's epilogue (what the engine uses): same sums, on top of a base
+    dw2 = torch.full_like(w, 0.25)
+    ops.conv_wgrad_folded(ops.folded(xa, f), ops.folded(dya, f), dw2, kf, pf, f, ldo, ldi)
+    torch.cuda.synchronize()
+    assert kc.relerr(dw2 - 0.25, wz.grad) < 2e-2
+    torch.testing.assert_close(dw2 - 0.25, dw, rtol=1e-3, atol=1e-3 * float(dw.abs().max()))
 
 
 def test_bad_args_rejected():

@@ -106,7 +106,8 @@ def test_backward_parity_teacher_forced(variant, fuse, N, S, Ts, Tf):
     bf16-representable) are loaded into the engine's buffers (engine.force_forward_state), then both sides
     back-propagate the same dlogits.
 
-    One structural exception, stated here and in DESIGN.md: a BatchNorm bias gradient is the plain sum of the incoming
+    One structural exception, stated here and in DESIGN.md (it covers a BatchNorm's weight gradient sum g*xhat in the
+    same way, with g*xhat as the summand): a BatchNorm bias gradient is the plain sum of the incoming
     gradient over all positions, and for the two STEM BatchNorms that sum cancels analytically (their output feeds only
     1x1x1 / (3,1,1) convolutions whose own BatchNorm backward makes sum_m dX ~= 0 per channel: measured
     |sum g| / sqrt(sum g^2) = 0.05 (fast stem) and 0.09 (slow stem) on the fp32 twin, against >= 0.39 for every other
@@ -115,11 +116,21 @@ def test_backward_parity_teacher_forced(variant, fuse, N, S, Ts, Tf):
     4x that floor (absolute)."""
     pu.fp32_reference_mode()
     twin, product = pu.build_pair(variant, fuse, twin=True)
-    gsq = {}
+    gsq, bn_out = {}, {}
+
+    def _bwd_hook(m_, gi, go, name):
+        g = go[0].detach().float()
+        gsq[name + ".bias"] = g.pow(2).sum(dim=(0, 2, 3, 4)).sqrt()
+        # the weight gradient is sum g*xhat: same storage floor with g*xhat as the summand
+        bc = lambda t: t.detach().float().view(1, -1, 1, 1, 1)
+        wsafe = torch.where(m_.weight.detach() == 0, torch.ones_like(m_.weight), m_.weight.detach())
+        xhat = (bn_out[name] - bc(m_.bias)) / bc(wsafe)
+        gsq[name + ".weight"] = (g * xhat).pow(2).sum(dim=(0, 2, 3, 4)).sqrt()
+
     for name, mod in twin.named_modules():
         if isinstance(mod, torch.nn.BatchNorm3d) and ".residual." not in name and ".res_unit." not in name:
-            mod.register_full_backward_hook(
-                lambda m_, gi, go, name=name: gsq.__setitem__(name + ".bias", go[0].detach().float().pow(2).sum(dim=(0, 2, 3, 4)).sqrt()))
+            mod.register_forward_hook(lambda m_, i_, o_, name=name: bn_out.__setitem__(name, o_.detach().float()))
+            mod.register_full_backward_hook(lambda m_, gi, go, name=name: _bwd_hook(m_, gi, go, name))
     xs, xf = _clips(variant, N, S, Ts, Tf)
     y = torch.randint(0, 249, (N,), generator=torch.Generator().manual_seed(7)).to(DEV)
     twin.train()

@@ -83,6 +83,7 @@ SIGNATURES = {
     "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_bn_add_relu_raw": [_vp, _i32, _i32, C.POINTER(BnRaw), _vp, _i32, _i32, C.POINTER(BnRaw), _vp, _i32, _i32, _vp, _i64,
                             _i32, _i32, _vp],
+    "sfb_conv_wgrad_folded": [C.POINTER(ConvGeom), _vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp],
     "sfb_pack_plan": [C.POINTER(PackJob), _i32, _vp, _i64, C.POINTER(_i32)],
     "sfb_pack_run": [_vp, _i32, _i32, _vp],
 }

@@ -644,28 +644,35 @@ __global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, 
     float acc[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    // The windows covering input (h, w): ho = (h+1)/2 with tap kh = h+1-2*ho (0 or 1) and, when that tap is 0, also
+    // ho-1 with tap 2 -- same along w.  Written as two candidates per dimension with validity predicates instead of
+    // parity tests inside a 3x3 tap loop: neighbouring lanes have opposite parities, so the tap loop made every warp
+    // run all taps with half its lanes idle.  The arg-max bytes are compared four at a time and turned into
+    // bf16-pair masks (no per-channel extract / compare / select).
+    const int ha = (h + 1) >> 1, kha = h + 1 - 2 * ha;
+    const int wa = (w + 1) >> 1, kwa = w + 1 - 2 * wa;
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int hn = h + 1 - kh;
-      if (hn < 0 || (hn & 1)) continue;
-      const int ho = hn >> 1;
-      if (ho >= Ho) continue;
+    for (int a = 0; a < 2; ++a) {
+      const int ho = ha - a, kh = kha + 2 * a;
+      const bool vh = a == 0 ? ho < Ho : (kha == 0 && ho >= 0);
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int wn = w + 1 - kw;
-        if (wn < 0 || (wn & 1)) continue;
-        const int wo = wn >> 1;
-        if (wo >= Wo) continue;
-        const long long opix = (q * Ho + ho) * Wo + wo;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
-        float d[8];
-        unpack8(vload(dout, opix, c), d);
-        const int tap = kh * 3 + kw;
+      for (int bq = 0; bq < 2; ++bq) {
+        const int wo = wa - bq, kw = kwa + 2 * bq;
+        const bool vw = bq == 0 ? wo < Wo : (kwa == 0 && wo >= 0);
+        if (vh && vw) {
+          const long long opix = (q * Ho + ho) * Wo + wo;
+          const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
+          uint4 d = vload(dout, opix, c);
+          const uint32_t tap4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
+          const uint32_t m0 = __vcmpeq4(pk.x, tap4), m1 = __vcmpeq4(pk.y, tap4);  // 0xFF per matching channel
+          d.x &= __byte_perm(m0, 0, 0x1100);
+          d.y &= __byte_perm(m0, 0, 0x3322);
+          d.z &= __byte_perm(m1, 0, 0x1100);
+          d.w &= __byte_perm(m1, 0, 0x3322);
+          float f[8];
+          unpack8(d, f);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint32_t word = i < 4 ? pk.x : pk.y;
-          const int sel = (word >> ((i & 3) * 8)) & 0xFF;
-          if (sel == tap) acc[i] += d[i];
+          for (int i = 0; i < 8; ++i) acc[i] += f[i];
         }
       }
     }

@@ -842,8 +842,29 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
   }
 }
 
+namespace {
+struct WgradFold { int f, ldo, ldi, kW, Co, Ci; };
+int conv_wgrad_impl(const SfbConvGeom* geom, const void* x, const SfbPrologue* pro, const void* dy, int32_t dy_ld,
+                    int32_t dy_coff, float* dw, int32_t Ci_real, int32_t impl, void* stream, const WgradFold* fold);
+}  // namespace
+
 int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pro, const void* dy, int32_t dy_ld,
                    int32_t dy_coff, float* dw, int32_t Ci_real, int32_t impl, void* stream) {
+  return conv_wgrad_impl(geom, x, pro, dy, dy_ld, dy_coff, dw, Ci_real, impl, stream, nullptr);
+}
+
+int sfb_conv_wgrad_folded(const SfbConvGeom* geom, const void* x, const void* dy, int32_t dy_ld, int32_t dy_coff, float* dw,
+                          int32_t Co, int32_t Ci, int32_t kW, int32_t f, int32_t ldo, int32_t ldi, void* stream) {
+  if (!geom || !fold_args_ok(Co, Ci, geom->kT, geom->kH, kW, f, ldo, ldi)) return SFB_ERR_BAD_ARG;
+  if (geom->Co != f * ldo || geom->Cg != f * ldi || geom->kW != (kW == 1 ? 1 : 3)) return SFB_ERR_BAD_ARG;
+  if (geom->sT != 1 || geom->sH != 1 || geom->sW != 1 || (geom->Cg % 16)) return SFB_ERR_UNSUPPORTED;
+  const WgradFold fold{f, ldo, ldi, kW, Co, Ci};
+  return conv_wgrad_impl(geom, x, nullptr, dy, dy_ld, dy_coff, dw, geom->Cg, SFB_IMPL_TC, stream, &fold);
+}
+
+namespace {
+int conv_wgrad_impl(const SfbConvGeom* geom, const void* x, const SfbPrologue* pro, const void* dy, int32_t dy_ld,
+                    int32_t dy_coff, float* dw, int32_t Ci_real, int32_t impl, void* stream, const WgradFold* fold) {
   int rc = check_geom(geom);
   if (rc) return rc;
   if (geom->transposed) return SFB_ERR_BAD_ARG;
@@ -880,6 +901,7 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
   }
   if (impl != SFB_IMPL_TC && impl != SFB_IMPL_TC_GATHER) return SFB_ERR_BAD_ARG;
   if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
+  if (fold && !(impl == SFB_IMPL_TC && !p.pro_scale && (geom->Cg % 16) == 0)) return SFB_ERR_UNSUPPORTED;
   if (impl == SFB_IMPL_TC && !p.pro_scale && (geom->Cg % 16) == 0) {
     // ---- TMA-fed tcgen05 kernel ----
     WgradTmaParams q;
@@ -908,6 +930,10 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
     if (tp >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
     q.total_patches = (int)tp;
     q.dW = dw;
+    if (fold) {
+      q.fold_f = fold->f; q.fold_ldo = fold->ldo; q.fold_ldi = fold->ldi; q.fold_kW = fold->kW;
+      q.fold_Co = fold->Co; q.fold_Ci = fold->Ci;
+    }
     const int gx = (q.n_units + q.upc - 1) / q.upc;
     // second accumulator only where the X boxes dominate the stage traffic (many tap/channel units) and enough CTAs remain
     q.mh = (geom->Co > 128 && q.n_units >= 2 * q.upc) ? 2 : 1;
@@ -968,6 +994,7 @@ int sfb_conv_wgrad(const SfbConvGeom* geom, const void* x, const SfbPrologue* pr
   SFB_CHECK_LAUNCH("conv_wgrad_tc_kernel");
   return SFB_OK;
 }
+}  // namespace
 
 int sfb_bn_finalize(const float* stats, int32_t C, int64_t count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, float* scale, float* shift,

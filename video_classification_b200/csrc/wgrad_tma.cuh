@@ -28,6 +28,10 @@ struct WgradTmaParams {
   int patches_per_split;
   int mh;                      // 128-channel halves of dY per CTA: 2 when Co > 128 (two TMEM accumulators share the X boxes)
   float* dW;
+  // pixel-folded conv (elementwise.cuh, fold_weight_kernel): the GEMM runs on the folded operands, the epilogue adds
+  // each element straight into the REFERENCE-layout gradient (Co, Ci, kT, kH, kW) through the band map
+  // kw = f*(kw' - kW'/2) + j' - j + kW/2 -- no folded gradient buffer, no unfold launch.  fold_f = 0: plain conv.
+  int fold_f, fold_ldo, fold_ldi, fold_kW, fold_Co, fold_Ci;
 };
 
 constexpr int kWtStages = 4;
@@ -211,7 +215,24 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_consta
         const int co_b = co0 + h * 128 + q4 * 32;
         float* dst = p.dW + (size_t)co_b * co_stride + (size_t)(cv ? c : 0) * p.taps + tap;
         const int nrows = min(32, p.Co - co_b);
-        if (cv) {
+        if (p.fold_f > 1) {
+          // folded column (j', c) at folded tap (kt, kh, kw'); rows are (j, co)
+          const int kWf = p.fold_kW == 1 ? 1 : 3;
+          const int jp = c / p.fold_ldi, cc = c - jp * p.fold_ldi;
+          const int kwf = tap % kWf, tkh = tap / kWf;              // tkh = kt*kH + kh
+          const int kw_base = p.fold_f * (kwf - kWf / 2) + jp + p.fold_kW / 2;
+          const int tkh_n = p.taps / kWf;
+          if (cv && cc < p.fold_Ci) {
+            int j = co_b / p.fold_ldo, co = co_b - j * p.fold_ldo;
+            float* base = p.dW + ((size_t)cc * tkh_n + tkh) * p.fold_kW;
+            const size_t cstride = (size_t)p.fold_Ci * tkh_n * p.fold_kW;
+            for (int rr = 0; rr < nrows; ++rr) {
+              const int kw = kw_base - j;
+              if (co < p.fold_Co && kw >= 0 && kw < p.fold_kW) atomicAdd(base + (size_t)co * cstride + kw, scratch[rr * 33 + lane]);
+              if (++co == p.fold_ldo) { co = 0; ++j; }
+            }
+          }
+        } else if (cv) {
 #pragma unroll 4
           for (int rr = 0; rr < nrows; ++rr) atomicAdd(dst + (size_t)rr * co_stride, scratch[rr * 33 + lane]);
         }

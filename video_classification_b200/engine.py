@@ -477,10 +477,15 @@ class SlowFastEngine:
             g.real_k, g.real_n, g.real_m = L.Ci * L.taps, L.Co, N * To * Ho * Wo
             pr = Prologue(0, 0, 0)
             plan.keep += [g, pr]
-            self._emit(lst, self.lib.sfb_conv_wgrad, C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), f * dy.ld, 0,
-                       L.dwf.data_ptr(), f * x.ld, self.impl, self.stream)
-            self._emit(lst, self.lib.sfb_unfold_wgrad, L.dwf.data_ptr(), L.Co, L.Ci, L.k[0], L.k[1], L.k[2], f, L.ldo, L.ldi,
-                       L.dw.data_ptr(), self.stream)
+            if self.impl == _ffi.IMPL_TC:
+                # the band map back to the reference layout is applied in the kernel's epilogue
+                self._emit(lst, self.lib.sfb_conv_wgrad_folded, C.byref(g), x.ptr(), dy.ptr(), f * dy.ld, 0, L.dw.data_ptr(),
+                           L.Co, L.Ci, L.k[2], f, L.ldo, L.ldi, self.stream)
+            else:
+                self._emit(lst, self.lib.sfb_conv_wgrad, C.byref(g), x.ptr(), C.byref(pr), dy.ptr(), f * dy.ld, 0,
+                           L.dwf.data_ptr(), f * x.ld, self.impl, self.stream)
+                self._emit(lst, self.lib.sfb_unfold_wgrad, L.dwf.data_ptr(), L.Co, L.Ci, L.k[0], L.k[1], L.k[2], f, L.ldo,
+                           L.ldi, L.dw.data_ptr(), self.stream)
             if self.ddp is not None:
                 self.ddp.note_grad_ready(plan, lst, L.conv.weight)
             return
@@ -896,6 +901,7 @@ class SlowFastEngine:
         rows = []
         for name, e0, e1, args in self.prof:
             desc, gf = "", 0.0
+            name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
             if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
                 g = args[0]._obj
                 kind = "wgrad" if name == "sfb_conv_wgrad" else ("dgrad" if g.transposed else "fprop")
@@ -930,6 +936,7 @@ class SlowFastEngine:
         out, flops = {}, {}
         for name, e0, e1, args in self.prof:
             ms = e0.elapsed_time(e1)
+            name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
             key = name
             if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
                 g = args[0]._obj

@@ -222,6 +222,15 @@ def conv_wgrad(x: Act, dy: Act, dw: torch.Tensor, k, s, p, *, pro=None, impl=_ff
     return dw
 
 
+def conv_wgrad_folded(xf: Act, dyf: Act, dw: torch.Tensor, kf, pf, f, ldo, ldi):
+    """dw (fp32 reference layout (Co, Ci, kT, kH, kW)) += wgrad of the pixel-folded conv (xf / dyf = folded views)"""
+    assert dw.dtype == torch.float32 and dw.is_contiguous()
+    g = make_geom(xf, dyf, kf, (1, 1, 1), pf, False)
+    check(lib().sfb_conv_wgrad_folded(C.byref(g), xf.ptr(), dyf.ptr(), dyf.ld, dyf.coff, dw.data_ptr(), dw.shape[0],
+                                      dw.shape[1], dw.shape[4], f, ldo, ldi, stream_ptr()), "sfb_conv_wgrad_folded")
+    return dw
+
+
 def bn_finalize(stats, count, gamma, beta, eps, momentum, running_mean, running_var, scale, shift, mean, invstd):
     check(lib().sfb_bn_finalize(stats.data_ptr(), gamma.numel(), count, gamma.data_ptr(), beta.data_ptr(), eps,
                                 momentum, ptr(running_mean), ptr(running_var), scale.data_ptr(), shift.data_ptr(),
