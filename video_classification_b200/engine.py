@@ -947,6 +947,11 @@ class SlowFastEngine:
                 # algorithmic work: rows of the forward conv's OUTPUT (for dgrad that is the gathered tensor dY)
                 M = getattr(g, "real_m", None) or (g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo)
                 flops[key] = flops.get(key, 0.0) + 2.0 * M * g.real_n * g.real_k
+                # algorithmic bytes: gathered tensor + written tensor (bf16), + the old value when accumulating in place
+                byt = 2.0 * g.N * (g.Ti * g.Hi * g.Wi * g.Cg + g.To * g.Ho * g.Wo * g.Co)
+                if name == "sfb_conv_gemm" and args[7]._obj.residual:
+                    byt += 2.0 * g.N * g.To * g.Ho * g.Wo * g.Co
+                flops[key + "#bytes"] = flops.get(key + "#bytes", 0.0) + byt
             if name in ("sfb_stem_conv_fprop", "sfb_stem_conv_wgrad"):
                 ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])
                 flops[name] = flops.get(name, 0.0) + 2.0 * args[1] * args[2] * args[3] * args[4] * co * ci * 49
