@@ -105,7 +105,9 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     # the two stems run as space-to-depth row-window kernels, everything else as the generic implicit GEMM
     convs = [op for op in plan.fwd if op[0] is lib.sfb_conv_gemm]
     assert len(convs) == n_conv - 2 and len([op for op in plan.fwd if op[0] is lib.sfb_stem_conv_fprop]) == 2
-    wgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_wgrad]
+    # (pixel-folded Fast-pathway layers write their gradient through sfb_conv_wgrad_folded)
+    wgrads = [op for op in plan.bwd if op[0] in (lib.sfb_conv_wgrad, lib.sfb_conv_wgrad_folded)]
+    assert any(op[0] is lib.sfb_conv_wgrad_folded for op in wgrads)
     assert len(wgrads) == n_conv - 2 and len([op for op in plan.bwd if op[0] is lib.sfb_stem_conv_wgrad]) == 2
     dgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_gemm]
     assert len(dgrads) == n_conv - 2  # the stems need no input gradient
