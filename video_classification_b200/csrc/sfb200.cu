@@ -221,8 +221,8 @@ int launch_stem_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const StemPa
 
 template <int BN, int CS>
 int launch_stem_wgrad(const CUtensorMap& tx, const CUtensorMap& tdy, const StemParams& p, int grid, cudaStream_t st) {
-  const size_t smem = 1024 + (size_t)kStemSlots * 128 * p.Cs * 2 + 1024 + (size_t)kStemDySlots * 128 * BN * 2 + 512;
-  if (smem > kMaxSmem || 4 * (p.Cs / 32) * BN > 512) return SFB_ERR_UNSUPPORTED;
+  const size_t smem = 1024 + (size_t)kStemSlots * 128 * p.Cs * 2 + 1024 + (size_t)StemDyRing<BN>::kSlots * 128 * BN * 2 + 512;
+  if (smem > kMaxSmem || 4 * (p.Cs / 32) * BN > 256) return SFB_ERR_UNSUPPORTED;
   static size_t attr_bytes = 0;
   if (smem > attr_bytes) {
     cudaError_t e = cudaFuncSetAttribute(stem_wgrad_kernel<BN, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -287,14 +287,26 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 // ---------------------------------------------------------------------------------------------------------------
 // wgrad
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int kStemDySlots = 4;
+// wgrad.  The loop runs over INPUT rows: s2d row r contributes to the four output rows ho = r-1 .. r+2 (dh = r+2-ho), so
+// its [pixels][(dw,cs)] window is multiplied ONCE against the four dY rows placed side by side in the MMA's N
+// dimension -- N = 4*BN, accumulator column block i <-> dY row r-1+i <-> dh = 3-i -- instead of four N = BN MMAs
+// that each re-read the same 4 KB A window from shared memory (the kernel was bound by exactly that traffic, and half
+// of every N = 16 tile was channel padding).  The dY rows live in a ring whose first three slots are mirrored behind
+// its end, so any four consecutive rows are contiguous for the descriptor (next N block = next slot).  dY rows that
+// belong to another CTA's range (or lie outside the frame) are fetched with an out-of-range row coordinate, i.e. as
+// TMA zero fill.
+template <int BN>
+struct StemDyRing {
+  static constexpr int NB = BN == 64 ? 5 : 8;   // ring slots (+3 mirror slots)
+  static constexpr int kSlots = NB + 3;
+};
 
 template <int BN, int CS>  // BN = padded Co: 16, 32 or 64
 __global__ void __launch_bounds__(192, 1)
 stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_dy,
                   const StemParams p) {
   constexpr int NS = kStemSlots;
-  constexpr int NB = kStemDySlots;
+  constexpr int NB = StemDyRing<BN>::NB;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   constexpr uint32_t span = (uint32_t)CS * 2;
@@ -302,8 +314,9 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
   constexpr uint32_t ring_bytes = NS * slot_bytes;
   constexpr uint32_t span_b = BN * 2;
   constexpr uint32_t bslot_bytes = 128u * span_b;
+  constexpr uint32_t bring_bytes = StemDyRing<BN>::kSlots * bslot_bytes;
   uint8_t* bsm = smem + ring_bytes + 1024;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bsm + NB * bslot_bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bsm + bring_bytes);
   uint64_t* full_bar = bars;                 // [NS]
   uint64_t* empty_bar = bars + NS;           // [NS]
   uint64_t* bfull_bar = bars + 2 * NS;       // [NB]
@@ -319,11 +332,12 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_x); tma_prefetch_desc(&tmap_dy); }
-  constexpr int G = CS / 32;                 // M groups per dh: 4 taps * Cs / 128
+  constexpr int G = CS / 32;                 // M groups: 4 dw taps * Cs / 128
   constexpr int bpg = 4 / G;                 // dw taps (= M blocks of Cs channels) per group
-  constexpr uint32_t kTmemCols = 512;        // 4*G*BN accumulator columns, live for the whole kernel
+  constexpr int NW = 4 * BN;                 // accumulator width: four dY rows
+  constexpr uint32_t kTmemCols = G * NW <= 64 ? 64 : (G * NW <= 128 ? 128 : 256);
   if (warp == 2) { tmem_alloc(tmem_holder, kTmemCols); tmem_relinquish(); }
-  for (uint32_t i = tid; i < (ring_bytes + 1024 + NB * bslot_bytes) / 16; i += blockDim.x)
+  for (uint32_t i = tid; i < (ring_bytes + 1024 + bring_bytes) / 16; i += blockDim.x)
     reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();
   tc_fence_before();
@@ -337,84 +351,86 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 
   if (g0 < g1) {
     if (warp == 0) {
-      // TMA producer: warp-uniform loop, one elected lane issues (see common.cuh)
+      // TMA producer (warp-uniform loop, one elected lane issues).  A frame segment [ha, hb) of this CTA's output
+      // rows needs X rows ha-2+j, j = 0 .. n+2, and dY positions q = 0 .. n+5 (row ha-3+q; only ha <= row < hb is real)
       const bool leader = elect_one();
-      uint32_t L = 0, it = 0;
-      int frame = g0 / p.Ho, ho = g0 - frame * p.Ho;
-      bool fresh = true;
-      for (int g = g0; g < g1; ++g, ++it) {
-        for (int r = fresh ? ho - 2 : ho + 1; r <= ho + 1; ++r, ++L) {
+      uint32_t L = 0, Q = 0;  // running X-row / dY-position counters (ring slot = counter % slots)
+      for (int g = g0; g < g1;) {
+        const int frame = g / p.Ho, ha = g - frame * p.Ho;
+        const int hb = min(p.Ho, ha + (g1 - g));
+        const int n = hb - ha;
+        int q = 0;
+        for (int j = 0; j < n + 3; ++j, ++L) {
+          for (; q <= j + 3; ++q, ++Q) {
+            const int sb = Q % NB;
+            mbar_wait(&bempty_bar[sb], ((Q / NB) & 1) ^ 1, 42);
+            if (leader) {
+              const int row = ha - 3 + q;
+              const int rc = (row >= ha && row < hb) ? row : -8;  // foreign rows arrive as zeros
+              mbar_arrive_expect_tx(&bfull_bar[sb], sb < 3 ? 2 * bslot_bytes : bslot_bytes);
+              tma_load_4d(bring0 + sb * bslot_bytes, &tmap_dy, &bfull_bar[sb], 0, 0, rc, frame);
+              if (sb < 3) tma_load_4d(bring0 + (sb + NB) * bslot_bytes, &tmap_dy, &bfull_bar[sb], 0, 0, rc, frame);
+            }
+            __syncwarp();
+          }
           const int s = L % NS;
           mbar_wait(&empty_bar[s], ((L / NS) & 1) ^ 1, 41);
           if (leader) {
             mbar_arrive_expect_tx(&full_bar[s], slot_bytes);
-            tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, r, frame);
+            tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, ha - 2 + j, frame);
           }
           __syncwarp();
         }
-        const int sb = it % NB;
-        mbar_wait(&bempty_bar[sb], ((it / NB) & 1) ^ 1, 42);
-        if (leader) {
-          mbar_arrive_expect_tx(&bfull_bar[sb], bslot_bytes);
-          tma_load_4d(bring0 + sb * bslot_bytes, &tmap_dy, &bfull_bar[sb], 0, 0, ho, frame);
-        }
-        __syncwarp();
-        fresh = false;
-        if (++ho == p.Ho) { ho = 0; ++frame; fresh = true; }
+        g += n;
       }
     } else if (warp == 1) {
-      // MMA issuer: warp-uniform loop, one elected lane issues
+      // MMA issuer: per X row, G * ksteps MMAs of N = 4*BN
       const bool leader = elect_one();
-      const uint32_t idesc = umma_idesc_bf16(128, BN, 1, 1);
+      const uint32_t idesc = umma_idesc_bf16(128, NW, 1, 1);
       const uint64_t adesc0 = umma_smem_desc_mnmajor(ring0, span, span);       // next M block = next pixel (dw tap)
-      const uint64_t bdesc0 = umma_smem_desc_mnmajor(bring0, span_b, bslot_bytes);
-      uint32_t L = 0, it = 0;
-      int ho = g0 % p.Ho;
-      bool fresh = true;
-      for (int g = g0; g < g1; ++g, ++it) {
-        L += fresh ? 4 : 1;
-        const int sb = it % NB;
-        mbar_wait(&bfull_bar[sb], (it / NB) & 1, 43);
-        const uint64_t bd_slot = bdesc0 + (uint64_t)((sb * bslot_bytes) >> 4);
-#pragma unroll
-        for (int dh = 0; dh < 4; ++dh) {
-          const uint32_t l = L - 4 + dh;
-          const int s = l % NS;
-          mbar_wait(&full_bar[s], (l / NS) & 1, 44);
+      const uint64_t bdesc0 = umma_smem_desc_mnmajor(bring0, span_b, bslot_bytes);  // next N block = next dY row
+      uint32_t L = 0, Q = 0, Qw = 0;  // Qw: dY positions already waited for
+      for (int g = g0; g < g1;) {
+        const int frame = g / p.Ho, ha = g - frame * p.Ho;
+        const int hb = min(p.Ho, ha + (g1 - g));
+        const int n = hb - ha;
+        for (int j = 0; j < n + 3; ++j, ++L) {
+          const uint32_t qj = Q + (uint32_t)j;  // first dY position of this row's window
+          for (; Qw <= qj + 3; ++Qw) mbar_wait(&bfull_bar[Qw % NB], (Qw / NB) & 1, 43);
+          const int s = L % NS;
+          mbar_wait(&full_bar[s], (L / NS) & 1, 44);
           tc_fence_after();
           const uint64_t ad_slot = adesc0 + (uint64_t)((s * slot_bytes) >> 4);
+          const uint64_t bd_slot = bdesc0 + (uint64_t)(((qj % NB) * bslot_bytes) >> 4);
           if (leader) {
 #pragma unroll
             for (int gi = 0; gi < G; ++gi) {
-              const uint32_t d_tmem = tmem_base + (uint32_t)((dh * G + gi) * BN);
+              const uint32_t d_tmem = tmem_base + (uint32_t)(gi * NW);
               uint64_t ad = ad_slot + (uint64_t)((gi * bpg * span) >> 4);
               uint64_t bd = bd_slot;
               for (int k = 0; k < p.ksteps; ++k) {
-                umma_bf16(d_tmem, ad, bd, idesc, (it | (uint32_t)k) != 0 ? 1u : 0u);
+                umma_bf16(d_tmem, ad, bd, idesc, (L | (uint32_t)k) != 0 ? 1u : 0u);
                 ad += (uint64_t)((16 * span) >> 4);
                 bd += (uint64_t)((16 * span_b) >> 4);
               }
             }
+            umma_commit(&empty_bar[s]);
+            umma_commit(&bempty_bar[qj % NB]);  // dY position qj is not used by later rows
           }
           __syncwarp();
         }
-        fresh = false;
-        if (++ho == p.Ho) { ho = 0; fresh = true; }
-        const bool last_of_run = (g + 1 == g1) || fresh;
+        // positions n+3 .. n+5 of this segment were only needed as window tails: free them as well
         if (leader) {
-          if (last_of_run) {
-            for (int dh = 0; dh < 4; ++dh) umma_commit(&empty_bar[(L - 4 + dh) % NS]);
-          } else {
-            umma_commit(&empty_bar[(L - 4) % NS]);
-          }
-          umma_commit(&bempty_bar[sb]);
+          for (uint32_t t = 0; t < 3; ++t) umma_commit(&bempty_bar[(Q + (uint32_t)n + 3 + t) % NB]);
         }
         __syncwarp();
+        Q += (uint32_t)n + 6;
+        g += n;
       }
       if (leader) umma_commit(done_bar);
       __syncwarp();
     } else {
-      // epilogue: TMEM lane m = (dw block j, s2d channel cs); columns = co, per (dh, group)
+      // epilogue: TMEM lane m = (dw block j, s2d channel cs); column block i = dY row r-1+i <-> dh = 3-i
       const int q4 = warp & 3;
       mbar_wait(done_bar, 0, 45);
       tc_fence_after();
@@ -422,10 +438,11 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
       const int j = m / CS, cs = m - j * CS;
       const int quad = cs / p.Ci, ci = cs - quad * p.Ci;   // s2d channel -> (sub-pixel, input channel)
       const int sh = quad >> 1, sw = quad & 1;
-      for (int dh = 0; dh < 4; ++dh) {
+      for (int i = 0; i < 4; ++i) {
+        const int dh = 3 - i;
         for (int gi = 0; gi < G; ++gi) {
           float v[BN];
-          const uint32_t ta = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)((dh * G + gi) * BN);
+          const uint32_t ta = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(gi * NW + i * BN);
           if constexpr (BN == 16) {
             tmem_ld16(ta, v);
           } else {
