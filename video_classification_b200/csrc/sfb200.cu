@@ -219,6 +219,21 @@ int launch_stem_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const StemPa
   return SFB_OK;
 }
 
+template <int BR, int CS>
+int launch_stem_fprop_rows(const CUtensorMap& tx, const CUtensorMap& tw, const StemParams& p, int grid, cudaStream_t st) {
+  const size_t smem = StemFpropRowsCfg<BR>::smem_bytes(p.Cs);
+  if (smem > kMaxSmem) return SFB_ERR_UNSUPPORTED;
+  static size_t attr_bytes = 0;
+  if (smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(stem_fprop_rows_kernel<BR, CS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(stem_fprop_rows)");
+    attr_bytes = smem;
+  }
+  stem_fprop_rows_kernel<BR, CS><<<grid, 192, smem, st>>>(tx, tw, p);
+  SFB_CHECK_LAUNCH("stem_fprop_rows_kernel");
+  return SFB_OK;
+}
+
 template <int BN, int CS>
 int launch_stem_wgrad(const CUtensorMap& tx, const CUtensorMap& tdy, const StemParams& p, int grid, cudaStream_t st) {
   const size_t smem = 1024 + (size_t)kStemSlots * 128 * p.Cs * 2 + 1024 + (size_t)StemDyRing<BN>::kSlots * 128 * BN * 2 + 512;
@@ -602,15 +617,17 @@ int sfb_stem_conv_fprop(const void* xs2d, int32_t N, int32_t T, int32_t H2, int3
   const int xb[4] = {Cs, 128, 1, 1};
   rc = get_tmap_generic(xs2d, 4, xd, xs, xb, Cs * 2, &tx);
   if (rc) return rc;
+  // narrow outputs: four output rows per tile (stem_fprop_rows_kernel), row blocks of br channels
+  const int br = Co <= 8 ? 8 : (Co <= 16 && Cs == 32 ? 16 : 0);
   const long long wd[2] = {16ll * Cs, bn};
   const long long ws[1] = {16ll * Cs * 2};
-  const int wb[2] = {64, bn};
+  const int wb[2] = {64, br ? br : bn};
   rc = get_tmap_generic(wp, 2, wd, ws, wb, 128, &tw);
   if (rc) return rc;
   StemParams p;
   memset(&p, 0, sizeof(p));
   p.F = (int)F; p.Ho = H2; p.Wo = W2; p.Cs = Cs; p.Co = Co; p.o_ld = o_ld; p.o_coff = o_coff; p.Ci = Ci;
-  p.total_tiles = (int)(F * H2);
+  p.total_tiles = br ? (int)(F * ((H2 + kStemRowsF - 1) / kStemRowsF)) : (int)(F * H2);
   int grid = num_sms();
   if (grid > p.total_tiles) grid = p.total_tiles;
   p.tiles_per_cta = (p.total_tiles + grid - 1) / grid;
@@ -618,6 +635,8 @@ int sfb_stem_conv_fprop(const void* xs2d, int32_t N, int32_t T, int32_t H2, int3
   p.base_off_mode = stem_base_off_mode();
   p.out = (__nv_bfloat16*)out; p.stats = stats;
   cudaStream_t st = (cudaStream_t)stream;
+  if (br == 8) return Cs == 64 ? launch_stem_fprop_rows<8, 64>(tx, tw, p, grid, st) : launch_stem_fprop_rows<8, 32>(tx, tw, p, grid, st);
+  if (br == 16) return launch_stem_fprop_rows<16, 32>(tx, tw, p, grid, st);
   if (Cs == 64) return bn == 16 ? launch_stem_fprop<16, 64>(tx, tw, p, grid, st) : launch_stem_fprop<32, 64>(tx, tw, p, grid, st);
   switch (bn) {
     case 16: return launch_stem_fprop<16, 32>(tx, tw, p, grid, st);

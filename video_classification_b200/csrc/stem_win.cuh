@@ -285,6 +285,218 @@ stem_fprop_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_const
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// fprop, four output rows per tile (narrow Co)
+// ---------------------------------------------------------------------------------------------------------------
+// With Co = 8 the one-row kernel issues N = 16 MMAs (half channel padding) that each re-read a 4 KB A window: it is
+// bound by that shared-memory operand traffic.  Here a tile is FOUR output rows h0..h0+3 whose channels sit side by
+// side in N (N = 4*BR, no padding for Co = 8): s2d input row h0-2+j, j = 0..6, is multiplied once per (dw, k-step)
+// against the weights of all output rows it feeds.  Output row h0+p takes W[dh = j-p] from input row j; with the
+// column blocks in reverse row order (block p' <-> row h0+3-p') that is the window of blocks j .. j+3 of the sequence
+// [0,0,0,W[dh=0],W[1],W[2],W[3],0,0,0] -- one resident operand, the descriptor start moves by j blocks (whole 8-row
+// swizzle atoms).  28 MMAs per output row instead of 64.
+constexpr int kStemRowsF = 4;
+constexpr int kStemRowsSlots = 11;  // 7 rows of the current tile + the 4 new rows of the next
+
+template <int BR>  // channels per row block: 8 or 16
+struct StemFpropRowsCfg {
+  static size_t smem_bytes(int Cs) {
+    return 1024 + (size_t)kStemRowsSlots * 128 * Cs * 2 + 1024 + (size_t)(4 * Cs / 64) * 10 * BR * 128 + 256;
+  }
+};
+
+template <int BR, int CS>
+__global__ void __launch_bounds__(192, 1)
+stem_fprop_rows_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                       const StemParams p) {
+  constexpr int NS = kStemRowsSlots;
+  constexpr int F = kStemRowsF;
+  constexpr int NW = F * BR;                       // accumulator width
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr uint32_t span = (uint32_t)CS * 2;
+  constexpr uint32_t slot_bytes = 128u * span;
+  constexpr uint32_t ring_bytes = NS * slot_bytes;
+  constexpr int NKC = 4 * CS / 64;                 // 64-wide K chunks of one input row (K = 4 dw * CS)
+  constexpr uint32_t chunk_bytes = 10u * BR * 128u;  // [10 blocks * BR rows][128 B]
+  uint8_t* bsm = smem + ring_bytes + 1024;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bsm + NKC * chunk_bytes);
+  uint64_t* full_bar = bars;            // [NS]
+  uint64_t* empty_bar = bars + NS;      // [NS]
+  uint64_t* tfull_bar = bars + 2 * NS;  // [2]
+  uint64_t* tempty_bar = tfull_bar + 2; // [2]
+  uint64_t* b_bar = tempty_bar + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(b_bar + 1);
+
+  const int tid = threadIdx.x, warp = uniform_warp_idx(), lane = tid & 31;
+  if (tid == 0) {
+    for (int s = 0; s < NS; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 4); }
+    mbar_init(b_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmap_x); tma_prefetch_desc(&tmap_w); }
+  constexpr uint32_t kTmemCols = 2 * NW < 32 ? 32 : (2 * NW <= 64 ? 64 : 128);
+  if (warp == 2) { tmem_alloc(tmem_holder, kTmemCols); tmem_relinquish(); }
+  // zero the ring, its tail pad and the weight sequence (its first and last three blocks stay zero)
+  for (uint32_t i = tid; i < (ring_bytes + 1024 + NKC * chunk_bytes) / 16; i += blockDim.x)
+    reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = uniform_u32(*tmem_holder);
+  const int tpf = (p.Ho + F - 1) / F;              // tiles per frame
+  const int g0 = blockIdx.x * p.tiles_per_cta;
+  const int g1 = min(p.total_tiles, g0 + p.tiles_per_cta);
+  const uint32_t ring0 = smem_u32(smem);
+
+  if (warp == 0) {
+    if (g0 < g1) {
+      const bool leader = elect_one();
+      if (leader) {
+        // W[dh] of the packed operand [rows][(dh,dw,cs)] -> block dh+3 of every K chunk
+        mbar_arrive_expect_tx(b_bar, (uint32_t)(4 * NKC * BR * 128));
+        for (int dh = 0; dh < 4; ++dh)
+          for (int kc = 0; kc < NKC; ++kc)
+            tma_load_2d_u32(smem_u32(bsm) + kc * chunk_bytes + (dh + 3) * (BR * 128), &tmap_w, b_bar,
+                            dh * 4 * CS + kc * 64, 0);
+      }
+      uint32_t L = 0;
+      int frame = g0 / tpf, t = g0 - frame * tpf;
+      bool fresh = true;
+      for (int g = g0; g < g1; ++g) {
+        const int h0 = t * F;
+        for (int r = fresh ? h0 - 2 : h0 + 1; r <= h0 + F; ++r, ++L) {
+          const int s = L % NS;
+          mbar_wait(&empty_bar[s], ((L / NS) & 1) ^ 1, 31);
+          if (leader) {
+            mbar_arrive_expect_tx(&full_bar[s], slot_bytes);
+            tma_load_4d(ring0 + s * slot_bytes, &tmap_x, &full_bar[s], 0, -2, r, frame);
+          }
+          __syncwarp();
+        }
+        fresh = false;
+        if (++t == tpf) { t = 0; ++frame; fresh = true; }
+      }
+    }
+  } else if (warp == 1) {
+    if (g0 < g1) {
+      const bool leader = elect_one();
+      const uint32_t idesc = umma_idesc_bf16(128, NW, 0, 0);
+      constexpr int KS = CS / 16;
+      const uint64_t adesc0 = umma_smem_desc_kmajor(ring0, span);
+      const uint64_t bdesc0 = umma_smem_desc_kmajor(smem_u32(bsm), 128);
+      mbar_wait(b_bar, 0, 32);
+      uint32_t L = 0;
+      int t = g0 % tpf, it = 0;
+      bool fresh = true;
+      for (int g = g0; g < g1; ++g, ++it) {
+        L += fresh ? F + 3 : F;
+        const int buf = it & 1;
+        mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 33);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(buf * NW);
+#pragma unroll
+        for (int j = 0; j < F + 3; ++j) {
+          const uint32_t l = L - (F + 3) + j;
+          const int s = l % NS;
+          mbar_wait(&full_bar[s], (l / NS) & 1, 34);
+          tc_fence_after();
+          const uint64_t ad_slot = adesc0 + (uint64_t)((s * slot_bytes) >> 4);
+          if (leader) {
+#pragma unroll
+            for (int dw = 0; dw < 4; ++dw) {
+#pragma unroll
+              for (int ks = 0; ks < KS; ++ks) {
+                const int kidx = dw * CS + ks * 16;
+                const uint32_t b_off = (uint32_t)((kidx >> 6) * chunk_bytes + j * (BR * 128) + (kidx & 63) * 2);
+                const uint64_t ad = ad_slot + (uint64_t)((dw * span + ks * 32) >> 4);
+                const uint64_t bd = bdesc0 + (uint64_t)(b_off >> 4);
+                umma_bf16(d_tmem, ad, bd, idesc, (j | dw | ks) != 0 ? 1u : 0u);
+              }
+            }
+          }
+          __syncwarp();
+        }
+        fresh = false;
+        if (++t == tpf) { t = 0; fresh = true; }
+        const bool last_of_run = (g + 1 == g1) || fresh;
+        if (leader) {
+          const int nfree = last_of_run ? F + 3 : F;  // the last three rows also serve the next tile of the frame
+          for (int j = 0; j < nfree; ++j) umma_commit(&empty_bar[(L - (F + 3) + j) % NS]);
+          umma_commit(&tfull_bar[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int q4 = warp & 3;
+    const int r = q4 * 32 + lane;        // pixel of the row
+    const bool pv = r < p.Wo;
+    float acc_s = 0.f, acc_q = 0.f;
+    int col_base = 0, it = 0;
+    int frame = g0 / tpf, t = g0 - frame * tpf;
+    for (int g = g0; g < g1; ++g, ++it) {
+      const int h0 = t * F;
+      const int buf = it & 1;
+      mbar_wait(&tfull_bar[buf], (uint32_t)((it >> 1) & 1), 35);
+      tc_fence_after();
+      float v[NW];
+      const uint32_t ta = tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * NW);
+      if constexpr (NW == 32) {
+        tmem_ld32(ta, v);
+      } else {
+        tmem_ld32(ta, v);
+        tmem_ld32(ta + 32, v + 32);
+      }
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+      float sv[BR], sq[BR];
+#pragma unroll
+      for (int i = 0; i < BR; ++i) { sv[i] = 0.f; sq[i] = 0.f; }
+#pragma unroll
+      for (int pb = 0; pb < F; ++pb) {           // column block pb <-> output row h0 + 3 - pb
+        const int row = h0 + (F - 1) - pb;
+        const bool valid = pv && row < p.Ho;
+        __nv_bfloat16* orow = p.out + (((size_t)frame * p.Ho + (valid ? row : 0)) * p.Wo + (valid ? r : 0)) * p.o_ld + p.o_coff;
+#pragma unroll
+        for (int jv = 0; jv < BR / 8; ++jv) {
+          uint4 pk = pack8(v + pb * BR + jv * 8);
+          if (valid && jv * 8 < p.Co) *reinterpret_cast<uint4*>(orow + jv * 8) = pk;
+          float f[8];
+          unpack8(pk, f);  // statistics from the bf16-rounded values the consumer will read
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float x = valid ? f[i] : 0.f;
+            sv[jv * 8 + i] += x;
+            sq[jv * 8 + i] = fmaf(x, x, sq[jv * 8 + i]);
+          }
+        }
+      }
+      if (p.stats) {
+        col_base = warp_reduce_columns<BR>(sv, lane);
+        warp_reduce_columns<BR>(sq, lane);
+        acc_s += sv[0];
+        acc_q += sq[0];
+      }
+      if (++t == tpf) { t = 0; ++frame; }
+    }
+    if (p.stats && g0 < g1) {
+      constexpr int REP = 32 / BR;
+      if ((lane & (REP - 1)) == 0 && col_base < p.Co) {
+        atomicAdd(p.stats + col_base, acc_s);
+        atomicAdd(p.stats + p.Co + col_base, acc_q);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // wgrad
 // ---------------------------------------------------------------------------------------------------------------
 // wgrad.  The loop runs over INPUT rows: s2d row r contributes to the four output rows ho = r-1 .. r+2 (dh = r+2-ho), so
