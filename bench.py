@@ -220,41 +220,66 @@ def run_gpu_arm(args):
 
     if args.skip_e2e:  # profiling runs only (ncu launch lists); the JSON line then carries no e2e number
         return dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
-                    e2e_ms=None, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B)
+                    e2e_ms=None, e2e_u8=None, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B)
     # ---- e2e: pinned host -> device every step (double-buffered prefetch on a copy stream) + loss read-back ----
     copy_stream = torch.cuda.Stream(dev)
+
+    def run_e2e(host_tensors, dbuf, run_step):
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        state = {"i": 0}
+
+        def prefetch(slot):
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[slot])
+                for d, h in zip(dbuf[slot], host_tensors):
+                    d.copy_(h, non_blocking=True)
+                ready[slot].record(copy_stream)
+
+        for s_ in range(2):
+            consumed[s_].record()
+
+        def e2e_step():
+            i = state["i"]
+            slot = i & 1
+            if i == 0:
+                prefetch(0)
+            prefetch(slot ^ 1)  # next step's clips travel while this step computes
+            torch.cuda.current_stream().wait_event(ready[slot])
+            loss = run_step(dbuf[slot])
+            consumed[slot].record()
+            float(loss.detach())  # device -> host read of the step's result
+            state["i"] = i + 1
+
+        for _ in range(2):
+            e2e_step()
+        ms, _ = timed(e2e_step, args.steps)
+        torch.cuda.synchronize(dev)
+        return ms
+
     dbuf = [[torch.empty_like(r) for r in resident] for _ in range(2)]
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    consumed = [torch.cuda.Event(), torch.cuda.Event()]
-    state = {"i": 0}
+    e2e_ms = run_e2e(host, dbuf, lambda bufs: step(*bufs))
+    del dbuf
 
-    def prefetch(slot):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(consumed[slot])
-            for d, h in zip(dbuf[slot], host):
-                d.copy_(h, non_blocking=True)
-            ready[slot].record(copy_stream)
+    # ---- e2e_u8: the same step fed uint8 frames as the dataset holds them before ToTensor/Normalize:
+    # (B, 32, 224, 224, 21) uint8 from pinned host memory, normalised + split + laid out by sfb_stage_clips_u8 ----
+    from video_classification_b200.staging import RawClips
+    host_u8 = [torch.randint(0, 256, (B, T_FAST, SIZE, SIZE, 21), generator=g, dtype=torch.uint8).pin_memory()]
+    dbuf_u8 = [[torch.empty_like(h, device=dev) for h in host_u8] for _ in range(2)]
 
-    for s_ in range(2):
-        consumed[s_].record()
+    def step_u8(bufs):
+        out = model(RawClips(bufs[0], slow_t_stride=T_FAST // T_SLOW))
+        loss = F.cross_entropy(out, y)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        return loss
 
-    def e2e_step():
-        i = state["i"]
-        slot = i & 1
-        if i == 0:
-            prefetch(0)
-        prefetch(slot ^ 1)  # next step's clips travel while this step computes
-        torch.cuda.current_stream().wait_event(ready[slot])
-        loss = step(*dbuf[slot])
-        consumed[slot].record()
-        float(loss.detach())  # device -> host read of the step's result
-        state["i"] = i + 1
-
-    for _ in range(2):
-        e2e_step()
-    e2e_ms, _ = timed(e2e_step, args.steps)
+    e2e_u8_ms = run_e2e(host_u8, dbuf_u8, step_u8)
+    u8 = dict(ms=e2e_u8_ms, h2d_bytes=host_u8[0].numel())
+    del dbuf_u8, host_u8
     return dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
-                e2e_ms=e2e_ms, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B)
+                e2e_ms=e2e_ms, e2e_u8=u8, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B)
 
 
 def profile_kernels(r, peaks, steps=2):
@@ -347,6 +372,13 @@ def main():
                     "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": 4,
                     "note": "fp32 NCTHW clips from pinned host memory each step (as train.py:136 .cuda()), "
                             "prefetched on a copy stream; loss.item() each step"},
+            "e2e_u8": None if not r["e2e_u8"] else {
+                "value": world * B / (r["e2e_u8"]["ms"] * 1e-3), "unit": "clips/s", "ms_per_step": r["e2e_u8"]["ms"],
+                "h2d_bytes_per_step": r["e2e_u8"]["h2d_bytes"], "d2h_bytes_per_step": 4,
+                "note": "SURVEY 8(f) row f1: the same training step fed uint8 (N,32,224,224,21) frames from pinned host "
+                        "memory, as the dataset holds them before ToTensor/Normalize (chalearn_dataset.py:41-46); "
+                        "model(staging.RawClips) normalises, splits 0:5/5:20, subsamples the Slow pathway and writes the "
+                        "stem operands in one kernel (sfb_stage_clips_u8), bit-identical to the fp32 path"},
             "gpu_launches": r["launches"], "clocks": r["clocks"],
             "step_tensor_roofline": {"algorithmic_tflop_per_clip": F_TRAIN_GF / 1e3, "achieved_tflops_per_gpu": tf_gpu,
                                      "peak_sustained": peaks["sustained"], "frac_sustained": tf_gpu / peaks["sustained"],

@@ -152,6 +152,25 @@ int sfb_stem_s2d_channels(int32_t C);
 /* replaces: train.py:136-140 (_prepare_slowfast_data) feeding the stem: fp32 strided NCTHW -> s2d bf16 */
 int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t sh, int64_t sw,
                          int32_t N, int32_t C, int32_t T, int32_t H, int32_t W, void* out, int32_t Cs, void* stream);
+/* ---- raw clip staging ---------------------------------------------------------------------
+ * replaces, in one device pass over the uint8 frames: dataset/chalearn_dataset.py:41-46,113-118 (ToTensor: HWC uint8
+ * -> fp32 / 255, Normalize: (x - mean) / std), dataset/chalearn_dataset.py:79-88 (RandomCrop(size, padding) of the
+ * whole clip, zero padding in the normalised domain), train.py:136-140 (permute + channel split 0:5 / 5:20) and
+ * sfb_layout_input_s2d.  frames: uint8 [N][T][H][W][Ct] (cv2 HWC frames stacked).  crop_yx: int32 device [N][2] or
+ * NULL; output pixel (y, x) of clip n takes source pixel (y + crop_yx[2n], x + crop_yx[2n+1]), zero outside the
+ * frame (RandomCrop's (i, j) window of the padded clip = offsets (i - padding, j - padding)).  Every pathway takes
+ * channels [c0, c0+C) of frames 0, t_stride, 2*t_stride ... and receives bf16 s2d [N][T/t_stride][H/2][W/2][Cs].
+ * Values are bf16_rn(((float)v / 255 - mean) / std) in the reference's fp32 operation order: bit-identical to
+ * sfb_layout_input_s2d of the reference's fp32 clip. */
+typedef struct {
+  int32_t c0, C;     /* channel range of the raw frames */
+  int32_t t_stride;  /* temporal subsampling of this pathway (T % t_stride == 0) */
+  int32_t Cs;        /* s2d channels of the destination (>= 4*C) */
+  void* out;
+} SfbStagePathway;
+int sfb_stage_clips_u8(const uint8_t* frames, int32_t N, int32_t T, int32_t H, int32_t W, int32_t Ct,
+                       const int32_t* crop_yx, float mean, float std, const SfbStagePathway* pw, int32_t n_pw,
+                       void* stream);
 /* fp32 (Co, Ci, 1, 7, 7) -> bf16 [rows_pad][16*Cs]; rows_pad = 16 / 32 / 64 (Co rounded up) */
 int sfb_pack_weight_stem(const float* w, int32_t Co, int32_t Ci, int32_t Cs, void* wp, int32_t rows_pad, void* stream);
 

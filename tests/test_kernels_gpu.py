@@ -441,3 +441,63 @@ def test_bad_args_rejected():
     out = Act.empty(1, 2, 4, 4, 64)
     with pytest.raises(_ffi.SfbError):
         ops.conv_gemm(x, w, out, (1, 1, 1), (1, 1, 1), (0, 0, 0))
+
+
+# ---- raw clip staging (sfb_stage_clips_u8) ---------------------------------------------------------
+def _stage_expected(frames, crop, pathways, pad):
+    from oracle import staging_oracle as st
+    windows = None if crop is None else [(int(dy) + pad, int(dx) + pad) for dy, dx in crop.tolist()]
+    x = st.stage_clips(frames.cpu(), windows, pad)
+    exp = []
+    for c0, Cc, ts in pathways:
+        xp = torch.permute(x, [0, 2, 1, 3, 4])[:, c0:c0 + Cc, ::ts].contiguous()
+        exp.append(st.space_to_depth_bf16(xp, ops.stem_s2d_channels(Cc)))
+    return exp
+
+
+@pytest.mark.parametrize("N,T,H,W,Ct,pathways,crop", [
+    (2, 4, 16, 16, 21, ((0, 5, 1), (5, 15, 1)), False),      # reference graph: equal clip lengths
+    (2, 8, 20, 36, 21, ((0, 5, 4), (5, 15, 1)), False),      # 8x8 SlowFast: Slow takes every 4th frame
+    (3, 2, 20, 20, 21, ((0, 5, 1), (5, 15, 1)), True),       # RandomCrop windows, rows 420 B (not 16-B multiples)
+    (2, 2, 18, 22, 20, ((0, 5, 2), (5, 15, 1)), True),
+    (1, 2, 64, 250, 21, ((0, 5, 1), (5, 15, 1)), True),      # widest s2d row (W/2 = 125)
+    (2, 3, 12, 14, 7, ((0, 3, 1), (3, 4, 3)), True),         # other channel splits
+])
+def test_stage_clips_u8_bit_identical_to_oracle(N, T, H, W, Ct, pathways, crop):
+    g = torch.Generator().manual_seed(N * 1000 + W)
+    frames = torch.randint(0, 256, (N, T, H, W, Ct), generator=g, dtype=torch.uint8)
+    pad = max(H, W) // 10 + 3
+    cyx = None
+    if crop:
+        cyx = torch.randint(-pad, pad + 1, (N, 2), generator=g, dtype=torch.int32)
+        cyx[0, 0], cyx[0, 1] = -pad, pad  # extremes
+    exp = _stage_expected(frames, cyx, pathways, pad)
+    got = ops.stage_clips_u8(frames.cuda(), pathways, None if cyx is None else cyx.cuda())
+    torch.cuda.synchronize()
+    for e, o in zip(exp, got):
+        assert o.shape == e.shape
+        assert torch.equal(o.cpu().view(torch.int16), e.view(torch.int16))
+
+
+def test_stage_clips_u8_against_torchvision_golden_and_fp32_layout():
+    import os
+    g = torch.load(os.path.join(os.path.dirname(__file__), "golden", "staging_small.pt"))
+    pad = g["padding"]
+    cyx = torch.tensor([(i - pad, j - pad) for i, j in g["windows"]], dtype=torch.int32)
+    pathways = ((0, 5, 1), (5, 15, 1))
+    got = ops.stage_clips_u8(g["frames"].cuda(), pathways, cyx.cuda())
+    # the fp32 batch torchvision produced, through the fp32 entry point the strict drop-in path uses
+    x = torch.permute(g["aug"].cuda(), [0, 2, 1, 3, 4])
+    for (c0, Cc, _), o in zip(pathways, got):
+        ref = ops.layout_input_s2d(x[:, c0:c0 + Cc])
+        assert torch.equal(o.view(torch.int16), ref.view(torch.int16))
+
+
+def test_stage_clips_u8_rejects_bad_arguments():
+    f = torch.zeros((1, 2, 8, 8, 21), dtype=torch.uint8, device="cuda")
+    with pytest.raises(_ffi.SfbError):
+        ops.stage_clips_u8(f, ((0, 5, 3), (5, 15, 1)))            # T % t_stride
+    with pytest.raises(_ffi.SfbError):
+        ops.stage_clips_u8(f, ((0, 5, 1), (10, 15, 1)))           # channel range beyond the frame
+    with pytest.raises(_ffi.SfbError):
+        ops.stage_clips_u8(torch.zeros((1, 2, 7, 8, 21), dtype=torch.uint8, device="cuda"), ((0, 5, 1),))  # odd H

@@ -351,3 +351,74 @@ def test_against_golden_fixture(name):
         if e_norm > (0.40 if g.numel() <= 64 else 0.25) or cos < 0.8:
             bad.append((n, e_norm, cos))
     assert not bad, bad[:8]
+
+
+# ---- uint8 clips through the model (staging.RawClips) ----------------------------------------------
+@pytest.mark.parametrize("variant,N,S,T,stride,augment", [
+    ("REF", 2, 64, 8, 1, False),
+    ("REF", 2, 64, 8, 1, True),
+    ("HYB", 2, 224, 32, 4, True),
+])
+def test_raw_uint8_clips_match_the_reference_loader_path(variant, N, S, T, stride, augment):
+    """model(RawClips(uint8)) against (a) the fp32 oracle fed what the reference loader would yield (ToTensor,
+    Normalize, RandomCrop, permute, split -- oracle/staging_oracle.py) and (b) the product's own fp32 entry."""
+    from oracle import staging_oracle as st
+    from video_classification_b200.staging import RawClips, random_crop_offsets
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair(variant, True)
+    g = torch.Generator().manual_seed(3)
+    # smooth-ish frames: a random low-resolution field upsampled, so the clip is not white noise
+    low = torch.rand((N, T, S // 8, S // 8, 21), generator=g)
+    frames = (F.interpolate(low.permute(0, 1, 4, 2, 3).reshape(N * T, 21, S // 8, S // 8), scale_factor=8, mode="bilinear")
+              .reshape(N, T, 21, S, S).permute(0, 1, 3, 4, 2) * 255).round().clamp(0, 255).to(torch.uint8).contiguous()
+    crop, windows, pad = None, None, S // 10
+    if augment:
+        crop = random_crop_offsets(N, S, g)
+        windows = [(int(dy) + pad, int(dx) + pad) for dy, dx in crop.tolist()]
+    x = st.stage_clips(frames, windows, pad)
+    xs, xf = [t.to(DEV) for t in st.prepare_slowfast_data(x, slow_t_stride=stride)]
+    raw = RawClips(frames.to(DEV), None if crop is None else crop.to(DEV), slow_t_stride=stride)
+    oracle.eval()
+    product.eval()
+    with torch.no_grad():
+        ref = oracle([xs, xf])
+        got_fp32 = product([xs, xf])
+        got_raw = product(raw)
+    assert pu.rel_max(got_raw, ref) <= pu.LOGIT_TOL
+    pu.assert_same_top1(got_raw, ref)
+    # identical stem operands: eval mode has no batch statistics, so only summation order can differ
+    assert pu.rel_max(got_raw, got_fp32) <= 1e-4
+    # training step: loss and gradients flow through the raw path
+    product.train()
+    labels = torch.randint(0, 249, (N,), generator=g).to(DEV)
+    def step(inp):
+        product.zero_grad(set_to_none=True)
+        loss = F.cross_entropy(product(inp), labels)
+        loss.backward()
+        return float(loss.detach()), {k: p.grad.clone() for k, p in product.named_parameters() if p.grad is not None}
+
+    def dist(a, b):
+        num = sum(float((a[k] - b[k]).double().pow(2).sum()) for k in a)
+        den = sum(float(b[k].double().pow(2).sum()) for k in a)
+        return (num / den) ** 0.5
+
+    loss_raw, g_raw = step(raw)
+    loss_a, g_a = step([xs, xf])
+    loss_b, g_b = step([xs, xf])
+    assert abs(loss_raw - loss_a) <= 2e-3 * abs(loss_a)
+    # the stem operands are bit-identical (test_kernels_gpu.py), so the raw path may differ from the fp32 path only by
+    # what two runs of the SAME path differ by: fp32 atomics order -> bf16 rounding -> ReLU mask flips (DESIGN.md 3.6)
+    noise = dist(g_b, g_a)
+    assert dist(g_raw, g_a) <= max(3e-2, 3.0 * noise), (dist(g_raw, g_a), noise)
+
+
+def test_raw_uint8_clips_error_paths():
+    from video_classification_b200.staging import RawClips
+    _, product = pu.build_pair("REF", True)
+    product.eval()
+    with pytest.raises(ValueError):
+        product(RawClips(torch.zeros((1, 8, 64, 64, 12), dtype=torch.uint8, device=DEV)))   # 5:20 needs 20 channels
+    with pytest.raises(TypeError):
+        product(RawClips(torch.zeros((1, 8, 64, 64, 21), device=DEV)))
+    with pytest.raises(_ffi.SfbError):
+        product(RawClips(torch.zeros((1, 8, 64, 64, 21), dtype=torch.uint8)))                # host tensor

@@ -124,3 +124,44 @@ def test_no_fuse_variant_and_fuse_flag():
     m.eval()
     with torch.no_grad():
         assert m([xs, xf]).shape == (1, 249)
+
+
+# ---- input staging oracle against torchvision's own transforms ------------------------------------
+def _staging_golden():
+    return torch.load(os.path.join(os.path.dirname(__file__), "golden", "staging_small.pt"))
+
+
+def test_staging_oracle_reproduces_torchvision_golden():
+    from oracle import staging_oracle as st
+    g = _staging_golden()
+    assert torch.equal(st.stage_clips(g["frames"]), g["plain"])
+    assert torch.equal(st.stage_clips(g["frames"], g["windows"], g["padding"]), g["aug"])
+    ramp = torch.arange(256, dtype=torch.uint8).reshape(1, 256, 1)
+    assert torch.equal(st.to_tensor_normalize(ramp)[0, 0], g["lut"])
+
+
+def test_staging_oracle_split_and_s2d_layout():
+    from oracle import staging_oracle as st
+    g = _staging_golden()
+    x = st.stage_clips(g["frames"])
+    xs, xf = st.prepare_slowfast_data(x, slow_t_stride=2)
+    assert xs.shape == (3, 5, 1, 20, 20) and xf.shape == (3, 15, 2, 20, 20)
+    assert torch.equal(xs[:, :, 0], x[:, 0, 0:5]) and torch.equal(xf[:, :, 1], x[:, 1, 5:20])
+    s2d = st.space_to_depth_bf16(xf.contiguous(), 64)
+    assert s2d.shape == (3, 2, 10, 10, 64) and float(s2d[..., 60:].abs().max()) == 0.0
+    # channel (sh*2+sw)*C + c of s2d pixel (h, w) is input channel c of pixel (2h+sh, 2w+sw)
+    assert torch.equal(s2d[1, 1, 3, 4, 2 * 15 + 7], xf[1, 7, 1, 7, 8].to(torch.bfloat16))
+    assert torch.equal(s2d[2, 0, 9, 0, 1 * 15 + 14], xf[2, 14, 0, 18, 1].to(torch.bfloat16))
+
+
+def test_raw_clips_host_checks():
+    from video_classification_b200.staging import RawClips, random_crop_offsets
+    off = random_crop_offsets(500, 64, torch.Generator().manual_seed(0))
+    assert off.dtype == torch.int32 and off.shape == (500, 2) and int(off.min()) == -6 and int(off.max()) == 6
+    rc = RawClips(torch.zeros((2, 8, 4, 4, 21), dtype=torch.uint8), slow_t_stride=4)
+    rc.validate()
+    assert rc.pathways() == ((0, 5, 4), (5, 15, 1))
+    with pytest.raises(ValueError):
+        RawClips(torch.zeros((2, 6, 4, 4, 21), dtype=torch.uint8), slow_t_stride=4).validate()
+    with pytest.raises(TypeError):
+        RawClips(torch.zeros((2, 8, 4, 4, 21))).validate()

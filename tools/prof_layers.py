@@ -60,6 +60,7 @@ LAYERS = [
     ("fast_res3_b_16_16_s2", "dgrad", 32, 56, 56, 16, 16, (1, 3, 3), (1, 2, 2)),
     ("lateral1_32_64_s4", "dgrad_acc", 32, 56, 56, 32, 64, (3, 1, 1), (4, 1, 1)),
     ("layout_fast", "layout_s2d", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
+    ("stage_u8_hyb", "stage_u8", 32, 224, 224, 15, 8, (1, 7, 7), (1, 2, 2)),
     ("layout_slow", "layout_s2d", 8, 224, 224, 5, 64, (1, 7, 7), (1, 2, 2)),
     ("bn_bwd_256", "bn_bwd", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
     ("bn_apply_256", "bn_apply", 8, 56, 56, 256, 256, (1, 1, 1), (1, 1, 1)),
@@ -93,6 +94,14 @@ def run_layer(N, spec, reps):
         fn = lambda: ops.layout_input_s2d(xf)
         flops = 0.0
         bytes_ = xf.numel() * 4 + N * T * (H // 2) * (W // 2) * (32 if 4 * Ci <= 32 else 64) * 2
+    elif kind == "stage_u8":
+        del x, y
+        fr = torch.randint(0, 256, (N, T, H, W, 21), device=DEV, dtype=torch.uint8)
+        pws = ((0, 5, 4), (5, 15, 1))
+        outs = ops.stage_clips_u8(fr, pws)
+        fn = lambda: ops.stage_clips_u8(fr, pws, outs=outs)
+        flops = 0.0
+        bytes_ = fr.numel() + sum(o.numel() * 2 for o in outs)
     elif kind in ("s2d_fprop", "s2d_wgrad"):
         xf = torch.randn((N, Ci, T, H, W), device=DEV, generator=g)
         xs = ops.layout_input_s2d(xf)

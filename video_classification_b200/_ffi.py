@@ -53,6 +53,11 @@ class BnRaw(C.Structure):
                 ("scale", C.c_void_p), ("shift", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
                 ("fold_f", C.c_int32), ("fold_ld", C.c_int32)]
 
+class StagePathway(C.Structure):
+    """SfbStagePathway (include/sfb200.h): one destination of sfb_stage_clips_u8"""
+    _fields_ = [("c0", C.c_int32), ("C", C.c_int32), ("t_stride", C.c_int32), ("Cs", C.c_int32), ("out", C.c_void_p)]
+
+
 # name -> argtypes; every function returns int (status) unless listed in _SPECIAL
 SIGNATURES = {
     "sfb_packed_weight_dims": [_i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],
@@ -78,6 +83,7 @@ SIGNATURES = {
     "sfb_unfold_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp],
     "sfb_unfold_stats": [_vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_layout_input_s2d": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
+    "sfb_stage_clips_u8": [_vp, _i32, _i32, _i32, _i32, _i32, _vp, C.c_float, C.c_float, C.POINTER(StagePathway), _i32, _vp],
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],

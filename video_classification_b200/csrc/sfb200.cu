@@ -7,6 +7,7 @@
 #include "stem_win.cuh"
 #include "elementwise.cuh"
 #include "pack_batch.cuh"
+#include "stage_u8.cuh"
 
 #include <algorithm>
 #include <array>
@@ -529,6 +530,48 @@ int sfb_layout_input_s2d(const float* x, int64_t sn, int64_t sc, int64_t st, int
     layout_input_s2d_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(
         x, sn, sc, st, sh, sw, N, C, T, H / 2, W / 2, (__nv_bfloat16*)out, Cs);
   SFB_CHECK_LAUNCH("layout_input_s2d_kernel");
+  return SFB_OK;
+}
+
+int sfb_stage_clips_u8(const uint8_t* frames, int32_t N, int32_t T, int32_t H, int32_t W, int32_t Ct,
+                       const int32_t* crop_yx, float mean, float std, const SfbStagePathway* pw, int32_t n_pw,
+                       void* stream) {
+  if (!frames || !pw || N <= 0 || T <= 0 || H <= 0 || W <= 0 || Ct <= 0 || n_pw <= 0) return SFB_ERR_BAD_ARG;
+  if (n_pw > kStageMaxPw || Ct > 64 || !(std > 0.f) || !aligned16(frames)) return SFB_ERR_BAD_ARG;
+  if ((H & 1) || (W & 1)) return SFB_ERR_UNSUPPORTED;  // the s2d stems need even frames (as sfb_layout_input_s2d)
+  StageParams p;
+  memset(&p, 0, sizeof(p));
+  for (int q = 0; q < n_pw; ++q) {
+    const SfbStagePathway& s = pw[q];
+    if (!s.out || !aligned16(s.out) || s.C <= 0 || s.c0 < 0 || s.c0 + s.C > Ct || s.t_stride <= 0 || (T % s.t_stride))
+      return SFB_ERR_BAD_ARG;
+    if ((s.Cs != 8 && s.Cs != 16 && s.Cs != 32 && s.Cs != 64) || 4 * s.C > s.Cs) return SFB_ERR_BAD_ARG;
+    p.pw[q].c0 = s.c0; p.pw[q].C = s.C; p.pw[q].t_stride = s.t_stride; p.pw[q].Cs = s.Cs;
+    p.pw[q].out = (__nv_bfloat16*)s.out;
+  }
+  p.frames = frames;
+  p.total_bytes = (long long)N * T * H * W * Ct;
+  p.N = N; p.T = T; p.H = H; p.W = W; p.Ct = Ct;
+  p.crop_yx = crop_yx; p.mean = mean; p.std = std; p.n_pw = n_pw;
+  p.row_bytes = (W * Ct + 32 + 15) & ~15;
+  const size_t smem = 256 * 32 * 4 + kStageMaxPw * 8 * 16 + 2 * (size_t)p.row_bytes;
+  if (smem > kMaxSmem) return SFB_ERR_UNSUPPORTED;
+  static size_t attr_bytes = 48 * 1024;
+  if (smem > attr_bytes) {
+    cudaError_t e = cudaFuncSetAttribute(stage_clips_u8_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(stage_clips_u8_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(stage_clips_u8)");
+    attr_bytes = smem;
+  }
+  const long long n_rows = (long long)N * T * (H / 2);
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 1024)));
+  const int grid = (int)std::min<long long>(n_rows, (long long)num_sms() * per_sm);
+  if (crop_yx)
+    stage_clips_u8_kernel<true><<<grid, kStageThreads, smem, (cudaStream_t)stream>>>(p);
+  else
+    stage_clips_u8_kernel<false><<<grid, kStageThreads, smem, (cudaStream_t)stream>>>(p);
+  SFB_CHECK_LAUNCH("stage_clips_u8_kernel");
   return SFB_OK;
 }
 

@@ -1029,12 +1029,44 @@ class SlowFastEngine:
             self.plans[key] = plan
         return plan
 
-    def forward(self, xs: torch.Tensor, xf: torch.Tensor, training: bool) -> Tuple[torch.Tensor, Plan]:
+    def _stage_raw(self, raw, training: bool) -> Plan:
+        """uint8 clips -> the stems' s2d operands (sfb_stage_clips_u8; reference dataset/chalearn_dataset.py:41-46,
+        79-88,113-118 + train.py:136-140 in one device pass)"""
+        raw.validate()
+        if raw.frames.device != self.dev or (raw.crop_yx is not None and raw.crop_yx.device != self.dev):
+            raise _ffi.SfbError("inputs must live on the model's CUDA device")
+        N, T, H, W, Ct = raw.frames.shape
+        pws = raw.pathways()
+        Cs_, Cf_ = self.cfg["input_channels"]
+        if (pws[0][1], pws[1][1]) != (Cs_, Cf_):
+            raise ValueError(f"expected input channels {(Cs_, Cf_)}, got {(pws[0][1], pws[1][1])}")
+        if max(pws[0][0] + pws[0][1], pws[1][0] + pws[1][1]) > Ct:
+            raise ValueError("channel ranges exceed the channels of the raw frames")
+        # shape-only stand-ins: get_plan reads .shape
+        xs = torch.empty((N, Cs_, T // raw.slow_t_stride, H, W), device="meta")
+        xf = torch.empty((N, Cf_, T, H, W), device="meta")
+        plan = self.get_plan(xs, xf, training)
+        if any(isinstance(a, Act) for a in plan.x_in):
+            raise _ffi.SfbError("uint8 staging needs both stems in space-to-depth form ((1,7,7)/s(1,2,2) stems, even H, W)")
+        arr = (_ffi.StagePathway * 2)()
+        for i, ((c0, Cc, ts), a) in enumerate(zip(pws, plan.x_in)):
+            arr[i].c0, arr[i].C, arr[i].t_stride, arr[i].Cs, arr[i].out = c0, Cc, ts, a.shape[4], a.data_ptr()
+        _ffi.check(self.lib.sfb_stage_clips_u8(raw.frames.data_ptr(), N, T, H, W, Ct,
+                                               None if raw.crop_yx is None else raw.crop_yx.data_ptr(),
+                                               float(raw.mean), float(raw.std), arr, 2, self.stream), "sfb_stage_clips_u8")
+        return plan
+
+    def forward(self, xs, xf, training: bool) -> Tuple[torch.Tensor, Plan]:
+        """xs, xf: fp32 NCTHW clips (any strides), or xs = staging.RawClips and xf = None"""
+        self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
+        if xf is None:
+            self.refresh_weights(training)
+            plan = self._stage_raw(xs, training)
+            return self._forward_staged(plan, training)
         if xs.dtype != torch.float32 or xf.dtype != torch.float32:
             raise TypeError("inputs must be float32 (as produced by the reference loader)")
         if xs.device != self.dev or xf.device != self.dev:
             raise _ffi.SfbError("inputs must live on the model's CUDA device")
-        self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
         plan = self.get_plan(xs, xf, training)
         self.refresh_weights(training)
         for x, a in zip((xs, xf), plan.x_in):
@@ -1046,6 +1078,9 @@ class SlowFastEngine:
             else:
                 _ffi.check(self.lib.sfb_layout_input_s2d(x.data_ptr(), sn, sc, st, sh, sw, N, Cc, T, H, W, a.data_ptr(),
                                                          a.shape[4], self.stream), "sfb_layout_input_s2d")
+        return self._forward_staged(plan, training)
+
+    def _forward_staged(self, plan: Plan, training: bool) -> Tuple[torch.Tensor, Plan]:
         if training:
             plan.gen += 1
             self.stats_flat.zero_()

@@ -225,11 +225,14 @@ class SlowFastB200(_ParamTree):
 
     # -- nn.Module API ---------------------------------------------------------------------------
     def forward(self, x: List[torch.Tensor]) -> torch.Tensor:
-        assert isinstance(x, (list, tuple)) and len(x) == 2, "expects [slow, fast] NCTHW tensors"
         from .engine import SlowFastEngine, run_model
+        from .staging import RawClips
+        raw = isinstance(x, RawClips)
+        assert raw or (isinstance(x, (list, tuple)) and len(x) == 2), \
+            "expects [slow, fast] NCTHW tensors (or staging.RawClips: uint8 frames, normalised on the device)"
         if self._engine is None:
             self._engine = SlowFastEngine(self)
-        return run_model(self._engine, x[0], x[1])
+        return run_model(self._engine, x, None) if raw else run_model(self._engine, x[0], x[1])
 
     def _apply(self, fn, *a, **k):
         self._engine = None  # device / dtype moves invalidate packed weights and buffers

@@ -165,6 +165,33 @@ def layout_input_s2d(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def stage_clips_u8(frames: torch.Tensor, pathways, crop_yx: Optional[torch.Tensor] = None, mean: float = 0.45,
+                   std: float = 0.225, outs=None):
+    """uint8 (N,T,H,W,Ct) raw frames -> one s2d bf16 (N,T/t_stride,H/2,W/2,Cs) operand per pathway.
+    pathways: sequence of (c0, C, t_stride).  Replaces the host-side ToTensor/Normalize/RandomCrop/permute/split of
+    reference dataset/chalearn_dataset.py:41-46,79-88,113-118 and train.py:136-140."""
+    assert frames.dtype == torch.uint8 and frames.dim() == 5 and frames.is_cuda and frames.is_contiguous()
+    N, T, H, W, Ct = frames.shape
+    pws = (_ffi.StagePathway * len(pathways))()
+    res = []
+    for i, (c0, Cc, ts) in enumerate(pathways):
+        cs = stem_s2d_channels(Cc)
+        if outs is not None:
+            o = outs[i]
+            assert o.dtype == torch.bfloat16 and o.is_contiguous() and tuple(o.shape) == (N, T // ts, H // 2, W // 2, cs)
+        else:
+            o = torch.empty((N, T // max(ts, 1), H // 2, W // 2, cs), dtype=torch.bfloat16, device=frames.device)
+        res.append(o)
+        pws[i].c0, pws[i].C, pws[i].t_stride, pws[i].Cs, pws[i].out = c0, Cc, ts, cs, o.data_ptr()
+    cptr = None
+    if crop_yx is not None:
+        assert crop_yx.dtype == torch.int32 and crop_yx.is_cuda and crop_yx.is_contiguous() and tuple(crop_yx.shape) == (N, 2)
+        cptr = crop_yx.data_ptr()
+    check(lib().sfb_stage_clips_u8(frames.data_ptr(), N, T, H, W, Ct, cptr, mean, std, pws, len(pathways), stream_ptr()),
+          "sfb_stage_clips_u8")
+    return res
+
+
 def pack_weight_stem(w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     assert w.dtype == torch.float32 and w.is_cuda and w.is_contiguous() and tuple(w.shape[2:]) == (1, 7, 7)
     Co, Ci = w.shape[0], w.shape[1]
