@@ -553,8 +553,10 @@ int sfb_stage_clips_u8(const uint8_t* frames, int32_t N, int32_t T, int32_t H, i
   p.total_bytes = (long long)N * T * H * W * Ct;
   p.N = N; p.T = T; p.H = H; p.W = W; p.Ct = Ct;
   p.crop_yx = crop_yx; p.mean = mean; p.std = std; p.n_pw = n_pw;
-  p.row_bytes = (W * Ct + 32 + 15) & ~15;
-  const size_t smem = 256 * 32 * 4 + kStageMaxPw * 8 * 16 + 2 * (size_t)p.row_bytes;
+  // rows of a pair 16 bytes off a multiple of 128: the byte gathers of the two rows then fall on interleaved banks
+  // (measured 1.83 -> 1.76 ms on the 64 x 32 x 224^2 x 21 batch)
+  p.row_bytes = ((W * Ct + 32 + 127) & ~127) + 16;
+  const size_t smem = 256 * 32 * 4 + kStageMaxPw * 8 * 16 + 4 * (size_t)p.row_bytes;  // two buffers of a row pair
   if (smem > kMaxSmem) return SFB_ERR_UNSUPPORTED;
   static size_t attr_bytes = 48 * 1024;
   if (smem > attr_bytes) {
@@ -565,6 +567,7 @@ int sfb_stage_clips_u8(const uint8_t* frames, int32_t N, int32_t T, int32_t H, i
     attr_bytes = smem;
   }
   const long long n_rows = (long long)N * T * (H / 2);
+  if (n_rows + 148 * 8 >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(4, (220 * 1024) / (smem + 1024)));
   const int grid = (int)std::min<long long>(n_rows, (long long)num_sms() * per_sm);
   if (crop_yx)
