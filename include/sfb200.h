@@ -289,6 +289,23 @@ int sfb_fc_fwd(const float* feat, const float* w, const float* b, int32_t N, int
 int sfb_fc_bwd(const float* dlogits, const float* feat, const float* w, int32_t N, int32_t K, int32_t C,
                float* dfeat, float* dw, float* db, void* stream);
 
+/* ---- after the network: evaluation drivers ------------------------------------------
+ * replaces: Trainer.run_eval's host tail, reference train.py:337-360 (softmax = np.exp(x)/np.sum(np.exp(x)) per clip,
+ * np.mean over the clips of a video, np.argmax) and SparseFusionTrainer.test, train_sparse.py:214-232 (softmax = 0).
+ * scores: fp32 [n_clips][C]; seg: int32 device [n_videos + 1], clips seg[v] .. seg[v+1]-1 belong to video v
+ * (the running sum of samples_per_video).  Outputs (each may be NULL): clip_probs [n_clips][C], video_mean
+ * [n_videos][C], top1 [n_videos] (lowest index on ties, -1 for a video without clips). */
+int sfb_video_scores(const float* scores, int32_t n_clips, int32_t C, const int32_t* seg, int32_t n_videos,
+                     int32_t softmax, float* clip_probs, float* video_mean, int32_t* top1, void* stream);
+/* replaces: SparseModel.forward, reference train_sparse.py:89-105 (num_class nn.Linear(num_part, 1) in a Python loop +
+ * concat): y[n][c] = sum_p w[c][p] * x[n][p][c] + b[c].  x: [N][P][C] part scores, w: [C][P] (fcs[c].weight), b: [C]. */
+int sfb_sparse_fuse(const float* x, const float* w, const float* b, int32_t N, int32_t P, int32_t C, float* y,
+                    void* stream);
+/* its backward (the reference trains SparseModel through autograd, train_sparse.py:160-190): dw [C][P], db [C] are
+ * overwritten; dx [N][P][C] may be NULL. */
+int sfb_sparse_fuse_bwd(const float* dy, const float* x, const float* w, int32_t N, int32_t P, int32_t C, float* dw,
+                        float* db, float* dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -501,3 +501,87 @@ def test_stage_clips_u8_rejects_bad_arguments():
         ops.stage_clips_u8(f, ((0, 5, 1), (10, 15, 1)))           # channel range beyond the frame
     with pytest.raises(_ffi.SfbError):
         ops.stage_clips_u8(torch.zeros((1, 2, 7, 8, 21), dtype=torch.uint8, device="cuda"), ((0, 5, 1),))  # odd H
+
+
+# ---- evaluation drivers on the device (sfb_video_scores / sfb_sparse_fuse, SURVEY.md 8(f) f4 + f2) ---------------------
+@pytest.mark.parametrize("C,sv", [(249, [7, 5, 10, 1, 3]), (10, [1] * 17), (1000, [4, 4]), (249, [64])])
+def test_video_scores_match_run_eval_tail(C, sv):
+    from oracle import eval_oracle as eo
+    from video_classification_b200 import evaluation as ev
+    g = torch.Generator().manual_seed(C + len(sv))
+    n = sum(sv)
+    logits = torch.randn((n, C), generator=g) * 3.0
+    labels = torch.cat([torch.full((k,), int(torch.randint(0, C, (1,), generator=g))) for k in sv])
+    # make some videos correct on purpose
+    for v, (a, k) in enumerate(zip([0] + list(torch.tensor(sv).cumsum(0)[:-1]), sv)):
+        if v % 2 == 0:
+            logits[a:a + k, labels[a]] += 6.0
+    ref = eo.run_eval_tail(logits.numpy(), labels.numpy(), sv)
+    acc = ev.EvalAccumulator()
+    half = n // 2
+    acc.add(logits[:half].cuda(), labels[:half].cuda(), sv[:1])        # batches and videos arrive in pieces
+    acc.add(logits[half:].cuda(), labels[half:].cuda(), sv[1:])
+    got = acc.result()
+    assert got["sv"] == ref["sv"] and (got["t"] == ref["t"]).all()
+    assert abs(got["ps"] - ref["ps"]).max() <= 1e-6
+    assert abs(got["video_mean"] - ref["video_mean"]).max() <= 1e-6
+    assert (got["video_top1"] == ref["video_top1"]).all()
+    assert got["acc"] == pytest.approx(float(ref["acc"]))
+
+
+def test_video_scores_ties_and_errors():
+    from video_classification_b200 import evaluation as ev
+    s = torch.zeros((3, 300), device="cuda")
+    s[:, 17] = 2.0
+    s[:, 290] = 2.0   # equal maxima: np.argmax takes the first
+    r = ev.video_scores(s, [2, 1])
+    assert r["top1"].tolist() == [17, 17]
+    with pytest.raises(ValueError):
+        ev.video_scores(s, [2, 2])
+    with pytest.raises(_ffi.SfbError):
+        ev.video_scores(s.cpu(), [2, 1])
+
+
+@pytest.mark.parametrize("N,P,C", [(33, 5, 249), (4, 6, 10), (300, 1, 7)])
+def test_sparse_model_matches_reference_forward_and_gradients(N, P, C):
+    from oracle import eval_oracle as eo
+    from video_classification_b200 import evaluation as ev
+    torch.manual_seed(N + P)
+    ref = eo.SparseModelRef(C, P)
+    mine = ev.SparseModel(C, P)
+    assert list(mine.state_dict().keys()) == list(ref.state_dict().keys())
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    mine.cuda()
+    x = torch.softmax(torch.randn(N, P, C), -1)
+    t = torch.randint(0, C, (N,))
+    xr = x.clone().requires_grad_(True)
+    yr = ref(xr)
+    F.cross_entropy(yr, t).backward()
+    xm = x.clone().cuda().requires_grad_(True)
+    ym = mine(xm)
+    F.cross_entropy(ym, t.cuda()).backward()
+    assert torch.allclose(ym.detach().cpu(), yr.detach(), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(xm.grad.cpu(), xr.grad, rtol=1e-5, atol=1e-7)
+    for (k, pm), (_, pr) in zip(mine.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(pm.grad.cpu(), pr.grad, rtol=1e-4, atol=1e-7), k
+
+
+def test_fuse_ensemble_matches_sparse_test_tail():
+    from oracle import eval_oracle as eo
+    from video_classification_b200 import evaluation as ev
+    torch.manual_seed(5)
+    P, C, sv = 5, 249, [6, 9, 4, 11]
+    n = sum(sv)
+    ref_m = eo.SparseModelRef(C, P)
+    mine = ev.SparseModel(C, P)
+    mine.load_state_dict(ref_m.state_dict())
+    mine.cuda()
+    ps = torch.softmax(torch.randn(n, P, C) * 2, -1)
+    labels = torch.cat([torch.full((k,), i * 7) for i, k in enumerate(sv)])
+    with torch.no_grad():
+        fused_ref = ref_m(ps).numpy()
+    ref = eo.sparse_test_tail(fused_ref, labels.numpy(), sv)
+    got = ev.fuse_ensemble(mine, ps.cuda(), labels.cuda(), sv)
+    assert abs(got["video_mean"] - ref["video_mean"]).max() <= 1e-5
+    assert (got["video_top1"] == ref["video_top1"]).all()
+    assert got["acc"] == pytest.approx(float(ref["acc"]))

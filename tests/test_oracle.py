@@ -165,3 +165,23 @@ def test_raw_clips_host_checks():
         RawClips(torch.zeros((2, 6, 4, 4, 21), dtype=torch.uint8), slow_t_stride=4).validate()
     with pytest.raises(TypeError):
         RawClips(torch.zeros((2, 8, 4, 4, 21))).validate()
+
+
+# ---- evaluation-tail oracle ------------------------------------------------------------------
+def test_eval_oracle_hand_example_and_sparse_model_keys():
+    import numpy as np
+    from oracle import eval_oracle as eo
+    from video_classification_b200 import evaluation as ev
+    logits = np.log(np.array([[0.7, 0.2, 0.1], [0.1, 0.8, 0.1], [0.6, 0.3, 0.1], [0.2, 0.2, 0.6]], dtype=np.float32))
+    r = eo.run_eval_tail(logits, np.array([0, 0, 0, 2]), [3, 1])
+    assert np.allclose(r["ps"].sum(1), 1.0, atol=1e-6)
+    assert np.allclose(r["video_mean"][0], [1.4 / 3, 1.3 / 3, 0.1], atol=1e-6)
+    assert r["video_top1"].tolist() == [0, 2] and r["acc"] == 1.0
+    # product SparseModel: same constructor, parameters and state_dict keys as the reference module; CUDA only
+    ref, mine = eo.SparseModelRef(7, 3), ev.SparseModel(7, 3)
+    assert list(ref.state_dict().keys()) == list(mine.state_dict().keys()) == \
+        [f"fcs.{c}.{n}" for c in range(7) for n in ("weight", "bias")]
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    from video_classification_b200 import _ffi
+    with pytest.raises(_ffi.SfbError):
+        mine(torch.rand(2, 3, 7))

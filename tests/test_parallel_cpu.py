@@ -98,3 +98,35 @@ def test_engine_plan_inserts_one_launch_per_bucket():
     covered = sum(n for _, n in eng.ddp.bucketer.spans)
     dead = sum(p.numel() for n, p in m.named_parameters() if ".residual." in n or ".res_unit." in n)
     assert covered == sum(p.numel() for p in eng.live_params) == 38077321 - dead
+
+
+def _gather_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from video_classification_b200.parallel import gather_part_scores
+        n, C = 6, 11
+        mine = torch.full((n, C), float(rank)) + torch.arange(n).view(n, 1) * 0.01
+        got = gather_part_scores(mine)
+        ok = tuple(got.shape) == (n, world, C)
+        for r in range(world):
+            ok = ok and torch.equal(got[:, r], torch.full((n, C), float(r)) + torch.arange(n).view(n, 1) * 0.01)
+        ret[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ensemble_part_scores_gather_gloo_world2():
+    """one part model per rank -> (n_clips, P, C) in rank order on every rank (BASELINE config 4 placement)"""
+    world = 2
+    port = _free_port()
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_gather_worker, args=(world, port, ret), nprocs=world, join=True)
+    assert all(ret.get(r) for r in range(world)), dict(ret)
+
+
+def test_ensemble_gather_single_process_is_a_view_with_one_part():
+    from video_classification_b200.parallel import gather_part_scores
+    x = torch.rand(4, 9)
+    assert torch.equal(gather_part_scores(x), x.unsqueeze(1))

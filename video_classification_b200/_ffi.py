@@ -84,6 +84,9 @@ SIGNATURES = {
     "sfb_unfold_stats": [_vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_layout_input_s2d": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stage_clips_u8": [_vp, _i32, _i32, _i32, _i32, _i32, _vp, C.c_float, C.c_float, C.POINTER(StagePathway), _i32, _vp],
+    "sfb_video_scores": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp],
+    "sfb_sparse_fuse": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],
+    "sfb_sparse_fuse_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
     "sfb_pack_weight_stem": [_vp, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_stem_conv_fprop": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_stem_conv_wgrad": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _i32, _vp, _vp],

@@ -8,6 +8,7 @@
 #include "elementwise.cuh"
 #include "pack_batch.cuh"
 #include "stage_u8.cuh"
+#include "scores.cuh"
 
 #include <algorithm>
 #include <array>
@@ -1298,6 +1299,38 @@ int sfb_fc_bwd(const float* dlogits, const float* feat, const float* w, int32_t 
   SFB_CHECK_LAUNCH("fc_bwd_dfeat_kernel");
   fc_bwd_dw_kernel<<<(C * K + 255) / 256, 256, 0, st>>>(dlogits, feat, N, K, C, dw, db);
   SFB_CHECK_LAUNCH("fc_bwd_dw_kernel");
+  return SFB_OK;
+}
+
+int sfb_video_scores(const float* scores, int32_t n_clips, int32_t C, const int32_t* seg, int32_t n_videos,
+                     int32_t softmax, float* clip_probs, float* video_mean, int32_t* top1, void* stream) {
+  if (!scores || !seg || n_clips <= 0 || C <= 0 || n_videos <= 0 || (!video_mean && !top1 && !clip_probs))
+    return SFB_ERR_BAD_ARG;
+  if (C > kScoreThreads * kScoreMaxPer) return SFB_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (softmax)
+    video_scores_kernel<true><<<n_videos, kScoreThreads, 0, st>>>(scores, C, seg, clip_probs, video_mean, top1);
+  else
+    video_scores_kernel<false><<<n_videos, kScoreThreads, 0, st>>>(scores, C, seg, clip_probs, video_mean, top1);
+  SFB_CHECK_LAUNCH("video_scores_kernel");
+  return SFB_OK;
+}
+
+int sfb_sparse_fuse(const float* x, const float* w, const float* b, int32_t N, int32_t P, int32_t C, float* y,
+                    void* stream) {
+  if (!x || !w || !b || !y || N <= 0 || P <= 0 || C <= 0) return SFB_ERR_BAD_ARG;
+  const long long total = (long long)N * C;
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)num_sms() * 8);
+  sparse_fuse_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, w, b, N, P, C, y);
+  SFB_CHECK_LAUNCH("sparse_fuse_kernel");
+  return SFB_OK;
+}
+
+int sfb_sparse_fuse_bwd(const float* dy, const float* x, const float* w, int32_t N, int32_t P, int32_t C, float* dw,
+                        float* db, float* dx, void* stream) {
+  if (!dy || !x || !w || !dw || !db || N <= 0 || P <= 0 || C <= 0) return SFB_ERR_BAD_ARG;
+  sparse_fuse_bwd_kernel<<<(C + 7) / 8, 256, 0, (cudaStream_t)stream>>>(dy, x, w, N, P, C, dw, db, dx);
+  SFB_CHECK_LAUNCH("sparse_fuse_bwd_kernel");
   return SFB_OK;
 }
 

@@ -159,3 +159,17 @@ def attach_ddp(model, bucket_mb: float = 25.0, group=None, broadcast: bool = Tru
     if broadcast:
         eng.invalidate_weights()
     return eng.ddp
+
+
+def gather_part_scores(clip_probs: torch.Tensor, group=None) -> torch.Tensor:
+    """Ensemble placement of BASELINE config 4 (one body-part model per GPU; reference train_sparse.py:36-86 runs the
+    parts one after another and pickles each part's scores): every rank holds the softmax scores (n_clips, C) of ITS
+    part for the same clips; one all-gather returns (n_clips, P, C) with parts in rank order -- the layout
+    SparseFusionDataset stacks from the pickles (train_sparse.py:109-131) and SparseModel.forward expects."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return clip_probs.unsqueeze(1).contiguous()
+    world = dist.get_world_size(group)
+    clip_probs = clip_probs.contiguous()
+    out = torch.empty((world,) + tuple(clip_probs.shape), dtype=clip_probs.dtype, device=clip_probs.device)
+    dist.all_gather([out[r] for r in range(world)], clip_probs, group=group)  # views of one buffer; gloo and nccl
+    return out.permute(1, 0, 2).contiguous()
