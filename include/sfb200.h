@@ -306,6 +306,27 @@ int sfb_sparse_fuse(const float* x, const float* w, const float* b, int32_t N, i
 int sfb_sparse_fuse_bwd(const float* dy, const float* x, const float* w, int32_t N, int32_t P, int32_t C, float* dw,
                         float* db, float* dx, void* stream);
 
+/* replaces: optim.Adam(model.parameters(), lr=cfg.MODEL.LR).step(), reference train.py:182 (construction) and
+ * train.py:231 (the call), i.e. torch.optim.Adam with amsgrad=False, maximize=False: per parameter tensor
+ *   g = grad * grad_scale (+ weight_decay * param);  m = lerp(m, g, 1-beta1);  v = beta2*v + (1-beta2)*g*g;
+ *   param -= lr/(1-beta1^t) * m / (sqrt(v)/sqrt(1-beta2^t) + eps)
+ * in torch's operation order and roundings (oracle/adam_oracle.py).  The caller describes every live parameter once
+ * (fp32 device pointers, element counts; they must stay valid), sfb_adam_plan turns the list into a device-resident
+ * table (synchronous copy) and sfb_adam_step updates ALL of them in ONE launch.  step = 1-based count of this update
+ * (the bias corrections are computed on the host in double, as torch does); grad_scale = 1 for an averaged gradient,
+ * 1/world_size for a summed all-reduce. */
+typedef struct SfbAdamJob {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t n;
+} SfbAdamJob;
+int64_t sfb_adam_table_bytes(int32_t n_jobs);
+int sfb_adam_plan(const SfbAdamJob* jobs, int32_t n_jobs, void* table_dev, int64_t table_bytes, int32_t* total_blocks);
+int sfb_adam_step(const void* table_dev, int32_t n_jobs, int32_t total_blocks, int64_t step, double lr, double beta1,
+                  double beta2, double eps, double weight_decay, double grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

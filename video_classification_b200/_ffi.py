@@ -43,6 +43,12 @@ class PackJob(C.Structure):
         "k_pad")] + [("src", C.c_void_p), ("dst", C.c_void_p)]
 
 
+class AdamJob(C.Structure):
+    """SfbAdamJob (include/sfb200.h): one parameter tensor of the batched optimizer step"""
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_int64)]
+
+
 PACK_WEIGHT, PACK_WEIGHT_DGRAD, PACK_FOLD, PACK_STEM = 0, 1, 2, 3
 
 
@@ -95,6 +101,8 @@ SIGNATURES = {
     "sfb_conv_wgrad_folded": [C.POINTER(ConvGeom), _vp, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp],
     "sfb_pack_plan": [C.POINTER(PackJob), _i32, _vp, _i64, C.POINTER(_i32)],
     "sfb_pack_run": [_vp, _i32, _i32, _vp],
+    "sfb_adam_plan": [C.POINTER(AdamJob), _i32, _vp, _i64, C.POINTER(_i32)],
+    "sfb_adam_step": [_vp, _i32, _i32, _i64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _vp],
 }
 _SPECIAL = {
     "sfb_strerror": ([_i32], C.c_char_p),
@@ -103,6 +111,7 @@ _SPECIAL = {
     "sfb_launch_count": ([], _i64),
     "sfb_stem_s2d_channels": ([_i32], _i32),
     "sfb_pack_table_bytes": ([_i32], _i64),
+    "sfb_adam_table_bytes": ([_i32], _i64),
 }
 ALL_SYMBOLS = sorted(list(SIGNATURES) + list(_SPECIAL))
 

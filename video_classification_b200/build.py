@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libsfb200.so")
 SOURCES = ["sfb200.cu"]
-HEADERS = ["common.cuh", "conv_tc.cuh", "conv_tma.cuh", "wgrad_tma.cuh", "stem_win.cuh", "pack_batch.cuh", "stage_u8.cuh", "scores.cuh", "conv_simt.cuh", "elementwise.cuh", os.path.join("..", "..", "include", "sfb200.h")]
+HEADERS = ["common.cuh", "conv_tc.cuh", "conv_tma.cuh", "wgrad_tma.cuh", "stem_win.cuh", "pack_batch.cuh", "stage_u8.cuh", "scores.cuh", "adam.cuh", "conv_simt.cuh", "elementwise.cuh", os.path.join("..", "..", "include", "sfb200.h")]
 
 
 def _stale() -> bool:

@@ -9,8 +9,10 @@
 #include "pack_batch.cuh"
 #include "stage_u8.cuh"
 #include "scores.cuh"
+#include "adam.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <array>
 #include <atomic>
 #include <cstdio>
@@ -645,6 +647,50 @@ int sfb_pack_run(const void* table_dev, int32_t n_jobs, int32_t total_blocks, vo
   if (!table_dev || n_jobs <= 0 || total_blocks <= 0) return SFB_ERR_BAD_ARG;
   pack_batch_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>((const PackJobDev*)table_dev, n_jobs);
   SFB_CHECK_LAUNCH("pack_batch_kernel");
+  return SFB_OK;
+}
+
+int64_t sfb_adam_table_bytes(int32_t n_jobs) { return n_jobs > 0 ? (int64_t)n_jobs * (int64_t)sizeof(AdamJobDev) : 0; }
+
+int sfb_adam_plan(const SfbAdamJob* jobs, int32_t n_jobs, void* table_dev, int64_t table_bytes, int32_t* total_blocks) {
+  if (!jobs || n_jobs <= 0 || !table_dev || !total_blocks || table_bytes < sfb_adam_table_bytes(n_jobs)) return SFB_ERR_BAD_ARG;
+  std::vector<AdamJobDev> tab((size_t)n_jobs);
+  long long block0 = 0;
+  for (int i = 0; i < n_jobs; ++i) {
+    const SfbAdamJob& j = jobs[i];
+    if (!j.param || !j.grad || !j.exp_avg || !j.exp_avg_sq || j.n <= 0) return SFB_ERR_BAD_ARG;
+    if (((uintptr_t)j.param | (uintptr_t)j.grad | (uintptr_t)j.exp_avg | (uintptr_t)j.exp_avg_sq) & 3) return SFB_ERR_BAD_ARG;
+    AdamJobDev& d = tab[(size_t)i];
+    d.p = j.param; d.g = j.grad; d.m = j.exp_avg; d.v = j.exp_avg_sq; d.n = j.n;
+    d.vec = aligned16(j.param) && aligned16(j.grad) && aligned16(j.exp_avg) && aligned16(j.exp_avg_sq);
+    d.block0 = (int)block0;
+    block0 += (j.n + kAdamChunk - 1) / kAdamChunk;
+    if (block0 > 0x7fffffffll) return SFB_ERR_BAD_ARG;
+  }
+  cudaError_t e = cudaMemcpy(table_dev, tab.data(), (size_t)n_jobs * sizeof(AdamJobDev), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMemcpy(adam table)");
+  *total_blocks = (int)block0;
+  return SFB_OK;
+}
+
+int sfb_adam_step(const void* table_dev, int32_t n_jobs, int32_t total_blocks, int64_t step, double lr, double beta1,
+                  double beta2, double eps, double weight_decay, double grad_scale, void* stream) {
+  if (!table_dev || n_jobs <= 0 || total_blocks <= 0 || step < 1) return SFB_ERR_BAD_ARG;
+  if (!(lr >= 0.0) || !(eps >= 0.0) || !(beta1 >= 0.0 && beta1 < 1.0) || !(beta2 >= 0.0 && beta2 < 1.0) || !(weight_decay >= 0.0))
+    return SFB_ERR_BAD_ARG;
+  // scalars in double, rounded to fp32 once (torch passes Python doubles to its fp32 kernels the same way)
+  const double bc1 = 1.0 - std::pow(beta1, (double)step), bc2 = 1.0 - std::pow(beta2, (double)step);
+  AdamHyper h;
+  h.one_minus_beta1 = (float)(1.0 - beta1);
+  h.beta2 = (float)beta2;
+  h.one_minus_beta2 = (float)(1.0 - beta2);
+  h.eps = (float)eps;
+  h.weight_decay = (float)weight_decay;
+  h.neg_step_size = (float)(-(lr / bc1));
+  h.bc2_sqrt = (float)std::sqrt(bc2);
+  h.grad_scale = (float)grad_scale;
+  adam_step_kernel<<<total_blocks, kAdamThreads, 0, (cudaStream_t)stream>>>((const AdamJobDev*)table_dev, n_jobs, h);
+  SFB_CHECK_LAUNCH("adam_step_kernel");
   return SFB_OK;
 }
 
