@@ -37,8 +37,17 @@ class Adam(torch.optim.Optimizer):
                         decoupled_weight_decay=False)
         super().__init__(params, defaults)
         self.grad_scale = float(grad_scale)
-        self._tables: Dict[Tuple[int, int], Tuple[tuple, torch.Tensor, int, int]] = {}
+        self._plans: Dict[int, dict] = {}
+        self._epoch = 0  # bumped whenever state tensors may have been replaced (load_state_dict, add_param_group)
         self.launches = 0
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._epoch += 1
+
+    def add_param_group(self, param_group):
+        super().add_param_group(param_group)
+        self._epoch = getattr(self, "_epoch", 0) + 1
 
     def _init_state(self, p):
         st = self.state[p]
@@ -49,7 +58,7 @@ class Adam(torch.optim.Optimizer):
         return st
 
     @staticmethod
-    def _check(p, g):
+    def _check(p, g, st):
         if not p.is_cuda:
             raise RuntimeError("video_classification_b200.optim.Adam runs on the GPU only (no CPU fallback): "
                                "move the model to a CUDA device before building the optimizer state")
@@ -61,24 +70,48 @@ class Adam(torch.optim.Optimizer):
             raise RuntimeError("gradient does not match its parameter (device / element count)")
         if not p.is_contiguous() or not g.is_contiguous():
             raise RuntimeError("contiguous parameters and gradients expected")
+        for k in ("exp_avg", "exp_avg_sq"):
+            m = st[k]
+            if m.device != p.device or m.dtype != torch.float32 or m.numel() != p.numel() or not m.is_contiguous():
+                raise RuntimeError(f"optimizer state {k} does not match its parameter")
 
-    def _table(self, key, rows: List[tuple], dev):
-        sig = tuple(rows)
-        hit = self._tables.get(key)
-        if hit is not None and hit[0] == sig:
-            return hit
+    def _plan_group(self, live: List[torch.nn.Parameter], sig: tuple) -> dict:
+        """One table per (device, step count) class: a model trained from scratch has exactly one."""
         lib = _ffi.lib()
-        arr = (_ffi.AdamJob * len(rows))()
-        for a, (pp, gp, mp, vp, n) in zip(arr, rows):
-            a.param, a.grad, a.exp_avg, a.exp_avg_sq, a.n = pp, gp, mp, vp, n
-        nbytes = int(lib.sfb_adam_table_bytes(len(rows)))
-        tab = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-        nblk = C.c_int32(0)
-        with torch.cuda.device(dev):
-            _ffi.check(lib.sfb_adam_plan(arr, len(rows), tab.data_ptr(), nbytes, C.byref(nblk)), "sfb_adam_plan")
-        hit = (sig, tab, len(rows), int(nblk.value))
-        self._tables[key] = hit
-        return hit
+        classes: Dict[Tuple[torch.device, int], dict] = {}
+        for p in live:
+            if not p.is_cuda:
+                self._check(p, p.grad, None)
+            st = self._init_state(p)
+            self._check(p, p.grad, st)
+            if st["step"].is_cuda:  # a checkpoint of a capturable / fused torch optimizer: keep torch's CPU layout
+                st["step"] = st["step"].detach().to("cpu", torch.float32)
+            c = classes.setdefault((p.device, int(st["step"])), dict(rows=[], steps=[]))
+            c["rows"].append((p.data_ptr(), p.grad.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
+                              p.numel()))
+            c["steps"].append(st["step"])
+        out = []
+        for (dev, t), c in classes.items():
+            rows = c["rows"]
+            arr = (_ffi.AdamJob * len(rows))()
+            for a, (pp, gp, mp, vp, n) in zip(arr, rows):
+                a.param, a.grad, a.exp_avg, a.exp_avg_sq, a.n = pp, gp, mp, vp, n
+            nbytes = int(lib.sfb_adam_table_bytes(len(rows)))
+            tab = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            nblk = C.c_int32(0)
+            with torch.cuda.device(dev):
+                _ffi.check(lib.sfb_adam_plan(arr, len(rows), tab.data_ptr(), nbytes, C.byref(nblk)), "sfb_adam_plan")
+            out.append(dict(dev=dev, t=t, tab=tab, n=len(rows), nblk=int(nblk.value), steps=c["steps"]))
+        return dict(sig=sig, epoch=self._epoch, classes=out)
+
+    def _launch(self, group, cl):
+        beta1, beta2 = group["betas"]
+        with torch.cuda.device(cl["dev"]):
+            _ffi.check(_ffi.lib().sfb_adam_step(cl["tab"].data_ptr(), cl["n"], cl["nblk"], cl["t"], float(group["lr"]),
+                                                float(beta1), float(beta2), float(group["eps"]),
+                                                float(group["weight_decay"]), self.grad_scale,
+                                                torch.cuda.current_stream(cl["dev"]).cuda_stream), "sfb_adam_step")
+        self.launches += 1
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -86,29 +119,32 @@ class Adam(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        lib = _ffi.lib()
         for gi, group in enumerate(self.param_groups):
             if group.get("amsgrad") or group.get("maximize"):
                 raise NotImplementedError("amsgrad / maximize are not part of the reference's configuration")
-            beta1, beta2 = group["betas"]
-            # one launch per (device, step count); a model trained from scratch has exactly one such class
-            classes: Dict[Tuple[torch.device, int], List[tuple]] = {}
+            live, ptrs = [], []
             for p in group["params"]:
                 g = p.grad
                 if g is None:  # the reference model's 48 unused parameters: skipped like torch does
                     continue
-                self._check(p, g)
-                st = self._init_state(p)
-                st["step"] += 1
-                t = int(st["step"])
-                classes.setdefault((p.device, t), []).append(
-                    (p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(), p.numel()))
-            for ci, ((dev, t), rows) in enumerate(classes.items()):
-                _, tab, n, nblk = self._table((gi, ci), rows, dev)
-                with torch.cuda.device(dev):
-                    _ffi.check(lib.sfb_adam_step(tab.data_ptr(), n, nblk, t, float(group["lr"]), float(beta1),
-                                                 float(beta2), float(group["eps"]), float(group["weight_decay"]),
-                                                 self.grad_scale, torch.cuda.current_stream(dev).cuda_stream),
-                               "sfb_adam_step")
-                self.launches += 1
+                live.append(p)
+                ptrs.append(p.data_ptr())
+                ptrs.append(g.data_ptr())
+            if not live:
+                continue
+            sig = tuple(ptrs)
+            plan = self._plans.get(gi)
+            if plan is None or plan["epoch"] != self._epoch or plan["sig"] != sig:
+                plan = self._plans[gi] = self._plan_group(live, sig)
+            for cl in plan["classes"]:
+                cl["t"] += 1
+                torch._foreach_add_(cl["steps"], 1)
+                self._launch(group, cl)
         return loss
+
+    def replay_last(self):
+        """Launch the tables of the last step() again with the same step count (measurement only: bench.py times the
+        kernel alone with it; the parameters move as in a real step)."""
+        for gi, group in enumerate(self.param_groups):
+            for cl in self._plans.get(gi, {"classes": []})["classes"]:
+                self._launch(group, cl)
