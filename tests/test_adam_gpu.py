@@ -115,3 +115,84 @@ def test_adam_full_model_size_properties():
         # |g| >> eps: m/(sqrt(v)) = sign(g) after bias correction
         big = p.grad.abs() > 1e-3
         assert torch.allclose(d[big], -1e-4 * torch.sign(p.grad[big]), rtol=1e-3, atol=2.5e-7 * float(p0.abs().max()))
+
+
+def test_training_loop_with_own_adam_tracks_torch_adam_on_the_oracle():
+    """The reference loop (train.py:225-231) on both sides: oracle + torch.optim.Adam against product + our Adam, same
+    weights, same clips, 3 steps.  After every step the engine must have re-packed its bf16 conv operands from the
+    updated fp32 weights (the kernel writes through raw pointers and bumps the version counters itself)."""
+    import torch.nn.functional as F
+    import parity_utils as pu
+    from oracle import slowfast_oracle as so
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair("REF", True, device="cuda")
+    oracle.train()
+    product.train()
+    xs, xf = so.synthetic_clips(2, 8, 8, 64)
+    xs, xf = xs.cuda(), xf.cuda()
+    y = torch.tensor([3, 200], device="cuda")
+    o_ref, o_own = torch.optim.Adam(oracle.parameters(), lr=1e-3, foreach=False), Adam(product.parameters(), lr=1e-3)
+    with torch.no_grad():
+        product([xs, xf])  # the engine is built by the first forward
+    eng = product._engine
+    w = eng.layers[0].conv.weight
+    losses = []
+    for t in range(3):
+        v0, w0 = w._version, w.detach().clone()
+        for model, opt in ((oracle, o_ref), (product, o_own)):
+            out = model([xs, xf])
+            loss = F.cross_entropy(out, y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.detach()))
+        assert w._version > v0 and not torch.equal(w, w0), "the optimizer step must be visible to autograd"
+        assert abs(losses[-1] - losses[-2]) <= 2e-2 * abs(losses[-2]), (t, losses)
+    # next forward re-packs: every layer's operand version follows its weight, and a pointwise layer's packed rows are
+    # the bf16 rounding of the CURRENT fp32 weight
+    with torch.no_grad():
+        product([xs, xf])
+    assert all(l.packed_version == l.conv.weight._version for l in eng.layers)
+    pw = next(l for l in eng.layers if l.taps == 1 and l.fold_f == 1 and l.wp is not None)
+    Co, Ci = pw.conv.weight.shape[:2]
+    assert torch.equal(pw.wp[:Co, :Ci].float(), pw.conv.weight.detach().view(Co, Ci).bfloat16().float())
+    # parameters stay on the oracle's trajectory: Adam's first steps move every element by ~lr, so compare in units of lr
+    n_bad = 0
+    for (k, p), q in zip(product.named_parameters(), oracle.parameters()):
+        if p.grad is None:
+            continue
+        d = (p - q).abs().max().item()
+        n_bad += d > 3 * 1e-3 * 3  # never further apart than the 3 steps' total travel
+    assert n_bad == 0
+    assert losses[-1] < losses[1], "three steps on one batch must reduce its loss"
+
+
+@pytest.mark.parametrize("kind", ["fused", "foreach", "raw"])
+def test_engine_repacks_operands_after_any_optimizer(kind):
+    """Whatever updates the fp32 weights between two training steps -- torch's fused or foreach Adam, or a write that
+    never touches a version counter -- the next forward runs on operands packed from the CURRENT weights."""
+    import torch.nn.functional as F
+    import parity_utils as pu
+    from oracle import slowfast_oracle as so
+    _, product = pu.build_pair("REF", True, device="cuda")
+    product.train()
+    xs, xf = so.synthetic_clips(2, 8, 8, 64)
+    xs, xf = xs.cuda(), xf.cuda()
+    y = torch.tensor([3, 200], device="cuda")
+    opt = None if kind == "raw" else torch.optim.Adam(product.parameters(), lr=1e-3, fused=kind == "fused",
+                                                      foreach=kind == "foreach")
+    F.cross_entropy(product([xs, xf]), y).backward()
+    eng = product._engine
+    pw = next(l for l in eng.layers if l.taps == 1 and l.fold_f == 1 and l.wp is not None)
+    Co, Ci = pw.conv.weight.shape[:2]
+    old = pw.wp[:Co, :Ci].clone()
+    if opt is not None:
+        opt.step()
+    else:  # through a detached alias and an out= kernel on its storage view: the parameter's own counter may not move
+        alias = torch.as_strided(pw.conv.weight.detach().view(-1).view(torch.int32).view(torch.float32), (Co * Ci,), (1,))
+        torch.mul(alias.clone(), 1.5, out=alias)
+    n0 = _ffi.launch_count()
+    product([xs, xf])
+    assert not torch.equal(pw.wp[:Co, :Ci], old)
+    assert torch.equal(pw.wp[:Co, :Ci].float(), pw.conv.weight.detach().view(Co, Ci).bfloat16().float())
+    assert _ffi.launch_count() - n0 > 0

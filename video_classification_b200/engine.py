@@ -320,7 +320,15 @@ class SlowFastEngine:
         return tabs
 
     def refresh_weights(self, training: bool):
-        """(Re)pack bf16 GEMM operands of every conv whose fp32 master weight changed (optimizer step / load)."""
+        """(Re)pack bf16 GEMM operands of every conv whose fp32 master weight changed (optimizer step / load).
+        Version counters catch ordinary in-place updates; optimizers that write through raw pointers or fused
+        multi-tensor kernels do not always move them (torch.optim.Adam(fused=True) left them unchanged in this build:
+        the ncu launch lists r1z/r2e show no re-pack), so the first forward after ANY backward re-packs everything --
+        one redundant batched launch pair if no optimizer ran in between, never a stale operand."""
+        if getattr(self, "_bwd_since_pack", False):
+            self._bwd_since_pack = False
+            for l in self.layers:
+                l.packed_version = -1
         stale = [l for l in self.layers
                  if not (l.packed_version == l.conv.weight._version and l.wp is not None and
                          getattr(l, "packed_impl", None) == self.impl and
@@ -1094,6 +1102,7 @@ class SlowFastEngine:
     def backward(self, plan: Plan, dlogits: torch.Tensor):
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
         plan.dlogits.copy_(dlogits)
+        self._bwd_since_pack = True  # an optimizer step may follow: see refresh_weights
         self.grad_flat.zero_()
         if self.ddp is not None:
             self.ddp.begin_backward(self)

@@ -86,10 +86,11 @@ class Adam(torch.optim.Optimizer):
             self._check(p, p.grad, st)
             if st["step"].is_cuda:  # a checkpoint of a capturable / fused torch optimizer: keep torch's CPU layout
                 st["step"] = st["step"].detach().to("cpu", torch.float32)
-            c = classes.setdefault((p.device, int(st["step"])), dict(rows=[], steps=[]))
+            c = classes.setdefault((p.device, int(st["step"])), dict(rows=[], steps=[], touched=[]))
             c["rows"].append((p.data_ptr(), p.grad.data_ptr(), st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr(),
                               p.numel()))
             c["steps"].append(st["step"])
+            c["touched"] += [p, st["exp_avg"], st["exp_avg_sq"]]
         out = []
         for (dev, t), c in classes.items():
             rows = c["rows"]
@@ -101,7 +102,8 @@ class Adam(torch.optim.Optimizer):
             nblk = C.c_int32(0)
             with torch.cuda.device(dev):
                 _ffi.check(lib.sfb_adam_plan(arr, len(rows), tab.data_ptr(), nbytes, C.byref(nblk)), "sfb_adam_plan")
-            out.append(dict(dev=dev, t=t, tab=tab, n=len(rows), nblk=int(nblk.value), steps=c["steps"]))
+            out.append(dict(dev=dev, t=t, tab=tab, n=len(rows), nblk=int(nblk.value), steps=c["steps"],
+                            touched=c["touched"]))
         return dict(sig=sig, epoch=self._epoch, classes=out)
 
     def _launch(self, group, cl):
@@ -111,6 +113,9 @@ class Adam(torch.optim.Optimizer):
                                                 float(beta1), float(beta2), float(group["eps"]),
                                                 float(group["weight_decay"]), self.grad_scale,
                                                 torch.cuda.current_stream(cl["dev"]).cuda_stream), "sfb_adam_step")
+        # the kernel wrote through raw pointers: tell autograd these tensors changed in place, as torch's own in-place
+        # update does (the engine re-packs its bf16 conv operands when a weight's version counter moves)
+        torch.autograd.graph.increment_version(cl["touched"])
         self.launches += 1
 
     @torch.no_grad()
