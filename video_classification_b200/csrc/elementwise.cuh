@@ -53,15 +53,17 @@ __global__ void layout_input_kernel(const float* __restrict__ x, long long sn, l
 
 // ---- weight packing: fp32 OIDHW -> bf16 [rows_pad][k_pad] ---------------------------------------
 // (bodies are __device__ functions over [first, total) with a stride so the batched launch below can run them too)
-__device__ __forceinline__ void pack_weight_body(const float* __restrict__ w, int Co, int Ci, int taps, int Cg,
-                                                 int transposed, __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad,
-                                                 long long first, long long step) {
-  const long long total = (long long)rows_pad * k_pad;
-  for (long long idx = first; idx < total; idx += step) {
-    const int k = (int)(idx % k_pad);
+// IdxT = unsigned for operands below 2^31 elements (every layer of this network): the 64-bit div/mod pair per element
+// was most of the kernel's instruction count.
+template <typename IdxT>
+__device__ __forceinline__ void pack_weight_loop(const float* __restrict__ w, int Co, int Ci, int taps, int Cg,
+                                                 int transposed, __nv_bfloat16* __restrict__ wp, IdxT total, IdxT k_pad,
+                                                 IdxT first, IdxT step) {
+  for (IdxT idx = first; idx < total; idx += step) {
     const int row = (int)(idx / k_pad);
+    const int k = (int)(idx - (IdxT)row * k_pad);
     float v = 0.f;
-    const int tap = k / Cg, c = k % Cg;
+    const int tap = k / Cg, c = k - tap * Cg;
     if (tap < taps) {
       if (!transposed) {
         if (row < Co && c < Ci) v = w[((size_t)row * Ci + c) * taps + tap];
@@ -71,6 +73,16 @@ __device__ __forceinline__ void pack_weight_body(const float* __restrict__ w, in
     }
     wp[idx] = __float2bfloat16_rn(v);
   }
+}
+__device__ __forceinline__ void pack_weight_body(const float* __restrict__ w, int Co, int Ci, int taps, int Cg,
+                                                 int transposed, __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad,
+                                                 long long first, long long step) {
+  const long long total = (long long)rows_pad * k_pad;
+  if (total + step < 0x7fffffffll)
+    pack_weight_loop<unsigned>(w, Co, Ci, taps, Cg, transposed, wp, (unsigned)total, (unsigned)k_pad, (unsigned)first,
+                               (unsigned)step);
+  else
+    pack_weight_loop<long long>(w, Co, Ci, taps, Cg, transposed, wp, total, (long long)k_pad, first, step);
 }
 __global__ void pack_weight_kernel(const float* __restrict__ w, int Co, int Ci, int taps, int Cg, int transposed,
                                    __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
@@ -95,14 +107,14 @@ struct DgradClassTable {
 };
 
 // fp32 OIDHW (Co, Ci, kT,kH,kW) -> bf16 [rows_pad (>= Ci)][k_pad], column = class k0 + tap_in_class*Cg + co
-__device__ __forceinline__ void pack_weight_dgrad_body(const float* __restrict__ w, int Co, int Ci, int Cg,
+template <typename IdxT>
+__device__ __forceinline__ void pack_weight_dgrad_loop(const float* __restrict__ w, int Co, int Ci, int Cg,
                                                        const DgradClassTable& tb, __nv_bfloat16* __restrict__ wp,
-                                                       int rows_pad, int k_pad, long long first, long long step) {
-  const long long total = (long long)rows_pad * k_pad;
+                                                       IdxT total, IdxT k_pad, IdxT first, IdxT step) {
   const int taps_all = tb.k[0] * tb.k[1] * tb.k[2];
-  for (long long idx = first; idx < total; idx += step) {
-    const int col = (int)(idx % k_pad);
+  for (IdxT idx = first; idx < total; idx += step) {
     const int row = (int)(idx / k_pad);
+    const int col = (int)(idx - (IdxT)row * k_pad);
     float v = 0.f;
     for (int ci = 0; ci < tb.n; ++ci) {
       const DgradClass& c = tb.c[ci];
@@ -120,6 +132,16 @@ __device__ __forceinline__ void pack_weight_dgrad_body(const float* __restrict__
     }
     wp[idx] = __float2bfloat16_rn(v);
   }
+}
+__device__ __forceinline__ void pack_weight_dgrad_body(const float* __restrict__ w, int Co, int Ci, int Cg,
+                                                       const DgradClassTable& tb, __nv_bfloat16* __restrict__ wp,
+                                                       int rows_pad, int k_pad, long long first, long long step) {
+  const long long total = (long long)rows_pad * k_pad;
+  if (total + step < 0x7fffffffll)
+    pack_weight_dgrad_loop<unsigned>(w, Co, Ci, Cg, tb, wp, (unsigned)total, (unsigned)k_pad, (unsigned)first,
+                                     (unsigned)step);
+  else
+    pack_weight_dgrad_loop<long long>(w, Co, Ci, Cg, tb, wp, total, (long long)k_pad, first, step);
 }
 __global__ void pack_weight_dgrad_kernel(const float* __restrict__ w, int Co, int Ci, int Cg, DgradClassTable tb,
                                          __nv_bfloat16* __restrict__ wp, int rows_pad, int k_pad) {
