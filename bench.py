@@ -4,10 +4,13 @@ beta=1/8, 224^2, 5+15 input channels, 249 classes), bf16 storage / fp32 accumula
 
     python bench.py --gpus N --steps K --warmup W          our arm (libsfb200 kernels through the drop-in model)
     python bench.py --impl reference ...                    the reference's own CPU path (oracle restatement) on host cores
+    python bench.py --mode infer [--batch 1|8|64]           BASELINE configs[1]: single-part inference (eval forward)
+    python bench.py --workload ref_lhand                    the reference's own shapes (slowfast-LHand.yaml: 300 x 20 x 64^2)
 
-A step is what reference train.py:225-231 does per batch: forward, CrossEntropy, zero_grad, backward (+ bucketed
-gradient all-reduce when N > 1), Adam step.  `value` keeps the clips resident in HBM; `e2e` copies every step's fp32
-clips from pinned host memory (double-buffered on a copy stream) and reads the loss back.  One JSON line on stdout.
+A training step is what reference train.py:225-231 does per batch: forward, CrossEntropy, zero_grad, backward (+ bucketed
+gradient all-reduce when N > 1), Adam step; an inference step is train.py:304-306 (eval forward under no_grad).
+`value` keeps the clips resident in HBM; `e2e` copies every step's fp32 clips from pinned host memory (double-buffered
+on a copy stream) and reads the result back.  One JSON line on stdout.
 """
 import argparse
 import json
@@ -20,12 +23,34 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-# workload constants (SURVEY.md 8d / BASELINE.md 2): algorithmic conv+FC FLOPs per clip, 1 MAC = 2 FLOP
-F_FWD_GF = 100.616
-F_TRAIN_GF = 293.98
+NUM_CLASS = 249
 HYB_KW = dict(fusion_conv_stride=(4, 1, 1), head_pool_kernel_sizes=((8, 7, 7), (32, 7, 7)))
-T_SLOW, T_FAST, SIZE, NUM_CLASS = 8, 32, 224, 249
-WORKLOAD = "configs[2]: slowfast-LHand SlowFast-R50 training, slow 5x8x224^2 + fast 15x32x224^2 (alpha=4 lateral), 249 classes"
+# workload constants (SURVEY.md 8d / BASELINE.md 2): algorithmic conv+FC GFLOP per clip, 1 MAC = 2 FLOP
+WORKLOADS = {
+    "hyb": dict(graph_kw=HYB_KW, oracle="HYB", ts=8, tf=32, size=224, batch=64, f_fwd=100.616, f_train=293.98,
+                label="slowfast-LHand SlowFast-R50, slow 5x8x224^2 + fast 15x32x224^2 (alpha=4 lateral), 249 classes"),
+    # the reference exactly as written: both pathways see the same 20 frames (train.py:136-140), config/slowfast-*.yaml
+    "ref_lhand": dict(graph_kw={}, oracle="REF", ts=20, tf=20, size=64, batch=300, f_fwd=18.936, f_train=55.93,
+                      label="reference graph as written, slowfast-LHand.yaml: slow 5x20x64^2 + fast 15x20x64^2, batch 300"),
+    "ref_htah": dict(graph_kw={}, oracle="REF", ts=20, tf=20, size=192, batch=55, f_fwd=170.737, f_train=504.3,
+                     label="reference graph as written, slowfast-HTAH.yaml: slow 5x20x192^2 + fast 15x20x192^2, batch 55"),
+}
+# kept for tools/ that import them
+T_SLOW, T_FAST, SIZE = 8, 32, 224
+F_FWD_GF, F_TRAIN_GF = 100.616, 293.98
+
+
+def metric_name(mode, wl):
+    shape = "8x8 224^2" if wl == "hyb" else f"{WORKLOADS[wl]['ts']}x{WORKLOADS[wl]['size']}^2 (reference shapes)"
+    return f"{'train' if mode == 'train' else 'inference'} clips/sec SlowFast-R50 {shape}"
+
+
+def workload_name(mode, wl):
+    w = WORKLOADS[wl]
+    if wl == "hyb":
+        return ("configs[2]: " + w["label"].replace("SlowFast-R50,", "SlowFast-R50 training,")) if mode == "train" else \
+            ("configs[1]: " + w["label"].replace("SlowFast-R50,", "SlowFast-R50 single-part inference,"))
+    return ("SURVEY 8(d) config 3 (REF shapes), training: " if mode == "train" else "SURVEY 8(d) config 2 (REF row), inference: ") + w["label"]
 
 
 def load_peaks():
@@ -34,6 +59,17 @@ def load_peaks():
         d = json.load(open(p))
         return dict(hbm=d["hbm_gbs"], burst=d["bf16_tflops"], sustained=d["bf16_tflops_sustained"], src="measured")
     return dict(hbm=6650.0, burst=1590.0, sustained=1400.0, src="fallback")
+
+
+def cpu_model_string():
+    try:
+        with open("/proc/cpuinfo") as f:
+            for ln in f:
+                if ln.lower().startswith("model name"):
+                    return ln.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
 
 
 class ClockSampler(threading.Thread):
@@ -87,32 +123,44 @@ class ClockSampler(threading.Thread):
 # travel to the GPU box; what is timed is the oracle restatement (oracle/slowfast_oracle.py), which
 # tests/test_oracle.py pins bit-identical to the verbatim import of the reference's model/my_slowfast.py.
 # ------------------------------------------------------------------------------------------------------------------
-def cpu_train_steps(n_clips, steps, warmup, threads=None):
-    """-> (seconds per step, threads used).  One step = train.py:225-231 on a batch of n_clips HYB clips."""
+def cpu_steps(mode, wl, n_clips, steps, warmup, threads=None):
+    """-> (seconds per step, threads used).  One step = train.py:225-231 (train) or :304-306 (infer) on n_clips clips."""
     import torch
     import torch.nn.functional as F
     from oracle import slowfast_oracle as so
-    if threads:
-        torch.set_num_threads(threads)
+    # explicit: under torch.distributed.run the launcher exports OMP_NUM_THREADS=1, which would time ONE thread
+    threads = int(threads or len(os.sched_getaffinity(0)) or os.cpu_count() or 1)
+    torch.set_num_threads(threads)
     threads = torch.get_num_threads()
+    w = WORKLOADS[wl]
     torch.manual_seed(0)
-    model = so.build_oracle(num_class=NUM_CLASS, fuse=True, **so.VARIANTS["HYB"])
+    model = so.build_oracle(num_class=NUM_CLASS, fuse=True, **so.VARIANTS[w["oracle"]])
     so.randomize_bn_(model, 123, 0.1)
-    model.train()
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4)
-    xs, xf = so.synthetic_clips(n_clips, T_SLOW, T_FAST, SIZE, seed=1)
+    xs, xf = so.synthetic_clips(n_clips, w["ts"], w["tf"], w["size"], seed=1)
     y = torch.randint(0, NUM_CLASS, (n_clips,), generator=torch.Generator().manual_seed(7))
     times = []
-    for it in range(warmup + steps):
-        t0 = time.perf_counter()
-        out = model([xs, xf])
-        loss = F.cross_entropy(out, y)
-        opt.zero_grad()
-        loss.backward()
-        opt.step()
-        float(loss.detach())
-        if it >= warmup:
-            times.append(time.perf_counter() - t0)
+    if mode == "train":
+        model.train()
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            out = model([xs, xf])
+            loss = F.cross_entropy(out, y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            float(loss.detach())
+            if it >= warmup:
+                times.append(time.perf_counter() - t0)
+    else:
+        model.eval()
+        with torch.no_grad():
+            for it in range(warmup + steps):
+                t0 = time.perf_counter()
+                out = model([xs, xf])
+                int(out.argmax(1)[0])
+                if it >= warmup:
+                    times.append(time.perf_counter() - t0)
     return sum(times) / len(times), threads
 
 
@@ -121,16 +169,19 @@ def run_reference_arm(args):
     if rank != 0:
         return  # one CPU measurement per box; other ranks exit 0 without work
     n = args.cpu_clips
-    sec, threads = cpu_train_steps(n, args.steps, max(1, min(args.warmup, 2)))
+    sec, threads = cpu_steps(args.mode, args.workload, n, args.steps, args.warmup)
     v = n / sec
-    line = {"impl": "reference", "metric": "train clips/sec SlowFast-R50 8x8 224^2", "value": v, "unit": "clips/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": max(1, min(args.warmup, 2)), "ms_per_step": sec * 1e3,
+    what = "fwd+CE+bwd+Adam" if args.mode == "train" else "eval forward"
+    line = {"impl": "reference", "metric": metric_name(args.mode, args.workload), "value": v, "unit": "clips/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_step": n, "note": "bounded sample: each step trains on "
-                       f"{n} clips instead of 64 (CPU throughput is batch-insensitive); fwd+CE+bwd+Adam"},
-            "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port",
-                             "sample": f"{args.steps} train steps of {n} HYB clips, fp32 eager PyTorch CPU, oracle "
-                                       "restatement pinned bit-identical to the reference's verbatim my_slowfast.py"},
+            "config": {"workload": workload_name(args.mode, args.workload), "batch_per_step": n,
+                       "note": f"bounded sample: each step runs {n} clips instead of the GPU arm's batch (CPU throughput is "
+                               f"batch-insensitive); {what}; {threads} threads on '{cpu_model_string()}'"},
+            "cpu_baseline": {"value": v, "unit": "clips/s", "cores": threads, "kind": "port", "cpu": cpu_model_string(),
+                             "sample": f"{args.steps} steps ({what}) of {n} clips after {args.warmup} warm-up, fp32 eager "
+                                       "PyTorch CPU, oracle restatement pinned bit-identical to the reference's verbatim "
+                                       "my_slowfast.py"},
             "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -139,12 +190,44 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------------------
+_ORIG_AFFINITY = None
+
+
+def bind_to_gpu_numa_node(local):
+    """Pin this rank's threads (and, through first-touch, its pinned host buffers) to the CPUs of the NUMA node its
+    GPU hangs off, BEFORE anything is allocated: with 8 ranks copying 6.7 GB per step each, buffers on the far socket
+    halve the aggregate host->device rate.  Best effort; returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        path = f"/sys/bus/pci/devices/{bus.lower()[-12:]}/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return {"numa_node": None, "note": "no NUMA affinity reported for the GPU"}
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus += list(range(int(a), int(b or a) + 1))
+        global _ORIG_AFFINITY
+        allowed = os.sched_getaffinity(0)
+        _ORIG_AFFINITY = set(allowed)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus)}
+    except Exception as e:  # noqa: BLE001
+        return {"numa_node": None, "note": f"not bound ({type(e).__name__})"}
+
+
 def run_gpu_arm(args):
     import torch
     import torch.distributed as dist
     import torch.nn.functional as F
-    from oracle import slowfast_oracle as so  # only make_cfg (a SimpleNamespace stand-in for the yacs CfgNode)
     from video_classification_b200 import _ffi
+    from video_classification_b200.config import make_cfg
     from video_classification_b200.my_slowfast import init_my_slowfast
     from video_classification_b200.parallel import attach_ddp
     from video_classification_b200.optim import Adam
@@ -155,35 +238,50 @@ def run_gpu_arm(args):
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+    numa = bind_to_gpu_numa_node(local) if not args.no_numa_bind else {"numa_node": None, "note": "disabled"}
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
-    B = args.batch
+    w = WORKLOADS[args.workload]
+    train = args.mode == "train"
+    B = args.batch or w["batch"]
+    TS, TF, S = w["ts"], w["tf"], w["size"]
     torch.manual_seed(0)
-    model = init_my_slowfast(so.make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **HYB_KW).to(dev)
-    model.train()
-    if world > 1:
+    model = init_my_slowfast(make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **w["graph_kw"]).to(dev)
+    model.train(train)
+    if world > 1 and train:
         attach_ddp(model, bucket_mb=args.bucket_mb)
     # same update rule as the reference's optim.Adam (train.py:182), same constructor: sfb_adam_step updates all 332
     # live parameters in ONE launch (csrc/adam.cuh) instead of torch's 10 + 5 fused multi-tensor launches
-    opt = Adam(model.parameters(), lr=1e-4)
+    opt = Adam(model.parameters(), lr=1e-4) if train else None
     g = torch.Generator().manual_seed(1000 + rank)
     # synthetic clips, per-rank seed; resident copies for `value`, a pinned host copy for `e2e`
-    host = [torch.randn((B, 5, T_SLOW, SIZE, SIZE), generator=g).pin_memory(),
-            torch.randn((B, 15, T_FAST, SIZE, SIZE), generator=g).pin_memory()]
+    host = [torch.randn((B, 5, TS, S, S), generator=g).pin_memory(),
+            torch.randn((B, 15, TF, S, S), generator=g).pin_memory()]
     y = torch.randint(0, NUM_CLASS, (B,), generator=g).to(dev)
     resident = [h.to(dev) for h in host]
     h2d_bytes = sum(h.numel() * 4 for h in host)
 
-    def step(xs, xf):
-        out = model([xs, xf])
-        loss = F.cross_entropy(out, y)
-        opt.zero_grad()
-        loss.backward()
-        opt.step()
-        return loss
+    if train:
+        def step(xs, xf):
+            out = model([xs, xf])
+            loss = F.cross_entropy(out, y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            return loss
+        d2h_bytes = 4
+    else:
+        def step(xs, xf):
+            with torch.no_grad():
+                return model([xs, xf])
+        d2h_bytes = B * NUM_CLASS * 4
+
+    def read_back(res):
+        """device -> host read of the step's result: the loss (train.py:232) or the logits (train.py:306)"""
+        return float(res.detach()) if train else res.cpu()
 
     def barrier():
         if world > 1:
@@ -217,12 +315,29 @@ def run_gpu_arm(args):
     sampler.start()
     ms_step, launches = timed(lambda: step(*resident), args.steps)
     clocks = sampler.stop()
-    loss_val = float(step(*resident).detach())
+    last = step(*resident)
+    loss_val = float(last.detach()) if train else None
+    r = dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
+             e2e_ms=None, e2e_u8=None, h2d_bytes=h2d_bytes, d2h_bytes=d2h_bytes, loss=loss_val, step=step,
+             resident=resident, B=B, opt=opt, numa=numa, replica_check=None, train=train)
+
+    # ---- replicas must still hold identical parameters after the timed steps (N > 1) ----
+    if world > 1 and train:
+        with torch.no_grad():
+            flat = torch.cat([p.detach().flatten() for p in model.parameters()])
+            chk = torch.stack([flat.view(torch.int32).to(torch.int64).sum(), flat.double().sum().view(torch.int64)])
+        allc = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(allc, chk)
+        same = all(bool((c == allc[0]).all()) for c in allc)
+        r["replica_check"] = {"ranks": world, "param_checksum_equal": same,
+                              "what": "int64 sum of the fp32 bit patterns + bit pattern of the double sum of all parameters, "
+                                      "all-gathered after the timed steps"}
+        if not same:
+            raise SystemExit(f"rank {rank}: data-parallel replicas diverged (parameter checksums differ across ranks)")
 
     if args.skip_e2e:  # profiling runs only (ncu launch lists); the JSON line then carries no e2e number
-        return dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
-                    e2e_ms=None, e2e_u8=None, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B, opt=opt)
-    # ---- e2e: pinned host -> device every step (double-buffered prefetch on a copy stream) + loss read-back ----
+        return r
+    # ---- e2e: pinned host -> device every step (double-buffered prefetch on a copy stream) + result read-back ----
     copy_stream = torch.cuda.Stream(dev)
 
     def run_e2e(host_tensors, dbuf, run_step):
@@ -247,9 +362,9 @@ def run_gpu_arm(args):
                 prefetch(0)
             prefetch(slot ^ 1)  # next step's clips travel while this step computes
             torch.cuda.current_stream().wait_event(ready[slot])
-            loss = run_step(dbuf[slot])
+            res = run_step(dbuf[slot])
             consumed[slot].record()
-            float(loss.detach())  # device -> host read of the step's result
+            read_back(res)
             state["i"] = i + 1
 
         for _ in range(2):
@@ -258,29 +373,31 @@ def run_gpu_arm(args):
         torch.cuda.synchronize(dev)
         return ms
 
-    dbuf = [[torch.empty_like(r) for r in resident] for _ in range(2)]
-    e2e_ms = run_e2e(host, dbuf, lambda bufs: step(*bufs))
+    dbuf = [[torch.empty_like(t) for t in resident] for _ in range(2)]
+    r["e2e_ms"] = run_e2e(host, dbuf, lambda bufs: step(*bufs))
     del dbuf
 
     # ---- e2e_u8: the same step fed uint8 frames as the dataset holds them before ToTensor/Normalize:
-    # (B, 32, 224, 224, 21) uint8 from pinned host memory, normalised + split + laid out by sfb_stage_clips_u8 ----
+    # (B, T, S, S, 21) uint8 from pinned host memory, normalised + split + laid out by sfb_stage_clips_u8 ----
     from video_classification_b200.staging import RawClips
-    host_u8 = [torch.randint(0, 256, (B, T_FAST, SIZE, SIZE, 21), generator=g, dtype=torch.uint8).pin_memory()]
+    host_u8 = [torch.randint(0, 256, (B, TF, S, S, 21), generator=g, dtype=torch.uint8).pin_memory()]
     dbuf_u8 = [[torch.empty_like(h, device=dev) for h in host_u8] for _ in range(2)]
 
     def step_u8(bufs):
-        out = model(RawClips(bufs[0], slow_t_stride=T_FAST // T_SLOW))
+        raw = RawClips(bufs[0], slow_t_stride=TF // TS)
+        if not train:
+            with torch.no_grad():
+                return model(raw)
+        out = model(raw)
         loss = F.cross_entropy(out, y)
         opt.zero_grad()
         loss.backward()
         opt.step()
         return loss
 
-    e2e_u8_ms = run_e2e(host_u8, dbuf_u8, step_u8)
-    u8 = dict(ms=e2e_u8_ms, h2d_bytes=host_u8[0].numel())
+    r["e2e_u8"] = dict(ms=run_e2e(host_u8, dbuf_u8, step_u8), h2d_bytes=host_u8[0].numel())
     del dbuf_u8, host_u8
-    return dict(rank=rank, world=world, dev=dev, model=model, ms_step=ms_step, launches=launches, clocks=clocks,
-                e2e_ms=e2e_ms, e2e_u8=u8, h2d_bytes=h2d_bytes, loss=loss_val, step=step, resident=resident, B=B, opt=opt)
+    return r
 
 
 def profile_adam(r, peaks, reps=5):
@@ -308,7 +425,7 @@ def profile_adam(r, peaks, reps=5):
 
 
 def profile_kernels(r, peaks, steps=2):
-    """per-plan-entry CUDA-event timing over `steps` extra training steps (events on the launching stream)."""
+    """per-plan-entry CUDA-event timing over `steps` extra steps (events on the launching stream)."""
     import torch
     eng = r["model"]._engine
     eng.prof = []
@@ -326,17 +443,20 @@ def profile_kernels(r, peaks, steps=2):
         if k.endswith("#bytes"):
             per_step[k[:-6]]["algorithmic_bytes"] = f / steps
             continue
+        if k.endswith("#kernels"):
+            per_step[k[:-8]]["kernel_launches"] = f / steps
+            continue
         per_step[k]["algorithmic_tflop"] = f / steps / 1e12
         per_step[k]["tflops"] = f / steps / 1e9 / per_step[k]["ms"]
     return per_step
 
 
-def conv_traffic_from_ncu(launches_per_step):
-    """`traffic` of the roofline object: DRAM bytes (read + write) per conv_tma_kernel launch, averaged over the
-    launches of one step, from the committed ncu pass `profiles/r*_traffic.json` (tools/summarize_traffic.py;
-    measured under ncu, so a static input of this line, never a timing)"""
+def conv_traffic_from_ncu():
+    """DRAM bytes (read + write) per conv_tma_kernel LAUNCH, averaged over the launches of one training step, from the
+    newest committed ncu pass `profiles/r*_traffic.json` (tools/summarize_traffic.py; measured under ncu with cold
+    caches, so a static input of this line, never a timing)"""
     import glob
-    files = sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_traffic.json")))
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
     if not files:
         return {}
     try:
@@ -349,8 +469,25 @@ def conv_traffic_from_ncu(launches_per_step):
     if not n:
         return {}
     byt = sum(v["dram_read_bytes"] + v["dram_write_bytes"] for v in rows)
-    return {"traffic": byt / n, "traffic_unit": "DRAM bytes per launch (mean over the step's launches)",
+    return {"traffic": byt / n, "traffic_unit": "DRAM bytes per kernel launch (mean over the training step's launches)",
             "traffic_launches": n, "traffic_source": os.path.basename(files[-1])}
+
+
+def library_baseline_from_profiles():
+    """PyTorch eager on the same B200 (the 'library kernel to beat'): numbers of the newest committed
+    run of tools/bench_torch_eager.py (profiles/r*_torch_eager.json); a static input of this line, measured on another
+    box of the same pool -- re-measure with `python tools/bench_torch_eager.py`."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_torch_eager.json")))
+    if not files:
+        return None
+    try:
+        with open(files[-1]) as f:
+            d = json.load(f)
+    except (OSError, ValueError):
+        return None
+    d["source"] = os.path.basename(files[-1])
+    return d
 
 
 def main():
@@ -359,11 +496,14 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="clips per GPU (BASELINE config: 64)")
+    ap.add_argument("--mode", default="train", choices=["train", "infer"])
+    ap.add_argument("--workload", default="hyb", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="clips per GPU (default: the workload's, 64 for the headline)")
     ap.add_argument("--bucket-mb", type=float, default=25.0)
     ap.add_argument("--cpu-clips", type=int, default=2, help="clips per CPU step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-numa-bind", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -371,12 +511,14 @@ def main():
     args.warmup = max(args.warmup, 3)
     peaks = load_peaks()
     r = run_gpu_arm(args)
-    world, B = r["world"], r["B"]
+    world, B, train = r["world"], r["B"], r["train"]
+    w = WORKLOADS[args.workload]
+    flops_clip = w["f_train"] if train else w["f_fwd"]
     kernels = None
     adam = None
     if not args.no_profile:
         kernels = profile_kernels(r, peaks)
-        adam = profile_adam(r, peaks)
+        adam = profile_adam(r, peaks) if train else None
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
@@ -386,31 +528,37 @@ def main():
         return
     clips_s = world * B / (r["ms_step"] * 1e-3)
     e2e_clips_s = world * B / (r["e2e_ms"] * 1e-3) if r["e2e_ms"] else None
-    tf_gpu = clips_s / world * F_TRAIN_GF / 1e3
-    line = {"metric": "train clips/sec SlowFast-R50 8x8 224^2", "value": clips_s, "unit": "clips/s", "n_gpus": world,
+    tf_gpu = clips_s / world * flops_clip / 1e3
+    step_desc = "fwd + CrossEntropy + bwd + bucketed grad all-reduce + Adam (reference train.py:225-231)" if train else \
+        "eval forward under no_grad (reference train.py:304-306), BatchNorm folded, no dropout"
+    line = {"metric": metric_name(args.mode, args.workload), "value": clips_s, "unit": "clips/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": world * B,
-                       "step": "fwd + CrossEntropy + bwd + bucketed grad all-reduce + Adam (reference train.py:225-231)",
-                       "optimizer": "video_classification_b200.optim.Adam(lr=1e-4): sfb_adam_step, one launch per step",
-                       "parallelism": f"dp{world}", "l2": "working set (>= 30 GB of activations per step) exceeds the 126 MB L2",
-                       "weights": "random init (seed 0)", "loss_after_bench": r["loss"]},
+            "config": {"workload": workload_name(args.mode, args.workload), "batch_per_gpu": B, "global_batch": world * B,
+                       "step": step_desc,
+                       "parallelism": f"dp{world}", "l2": "working set (GBs of activations per step) exceeds the 126 MB L2"
+                       if B * w["size"] ** 2 * w["tf"] > 5e7 else "small batch: activations may stay L2-resident between kernels",
+                       "weights": "random init (seed 0)", "loss_after_bench": r["loss"], "host_affinity": r["numa"]},
             "e2e": {"value": e2e_clips_s, "unit": "clips/s", "ms_per_step": r["e2e_ms"],
-                    "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": 4,
+                    "h2d_bytes_per_step": r["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"],
                     "note": "fp32 NCTHW clips from pinned host memory each step (as train.py:136 .cuda()), "
-                            "prefetched on a copy stream; loss.item() each step"},
+                            "prefetched on a copy stream; " + ("loss.item() each step" if train else "logits .cpu() each step")},
             "e2e_u8": None if not r["e2e_u8"] else {
                 "value": world * B / (r["e2e_u8"]["ms"] * 1e-3), "unit": "clips/s", "ms_per_step": r["e2e_u8"]["ms"],
-                "h2d_bytes_per_step": r["e2e_u8"]["h2d_bytes"], "d2h_bytes_per_step": 4,
-                "note": "SURVEY 8(f) row f1: the same training step fed uint8 (N,32,224,224,21) frames from pinned host "
+                "h2d_bytes_per_step": r["e2e_u8"]["h2d_bytes"], "d2h_bytes_per_step": r["d2h_bytes"],
+                "note": "SURVEY 8(f) row f1: the same step fed uint8 (N,T,S,S,21) frames from pinned host "
                         "memory, as the dataset holds them before ToTensor/Normalize (chalearn_dataset.py:41-46); "
                         "model(staging.RawClips) normalises, splits 0:5/5:20, subsamples the Slow pathway and writes the "
                         "stem operands in one kernel (sfb_stage_clips_u8), bit-identical to the fp32 path"},
             "gpu_launches": r["launches"], "clocks": r["clocks"],
-            "step_tensor_roofline": {"algorithmic_tflop_per_clip": F_TRAIN_GF / 1e3, "achieved_tflops_per_gpu": tf_gpu,
+            "step_tensor_roofline": {"algorithmic_tflop_per_clip": flops_clip / 1e3, "achieved_tflops_per_gpu": tf_gpu,
                                      "peak_sustained": peaks["sustained"], "frac_sustained": tf_gpu / peaks["sustained"],
                                      "peak_burst": peaks["burst"], "frac_burst": tf_gpu / peaks["burst"],
                                      "peaks": peaks["src"]}}
+    if train:
+        line["config"]["optimizer"] = "video_classification_b200.optim.Adam(lr=1e-4): sfb_adam_step, one launch per step"
+    if r["replica_check"] is not None:
+        line["replica_check"] = r["replica_check"]
     if kernels:
         # dominant kernel = conv_tma_kernel<BN,BRES>: sfb_conv_gemm forward and input-gradient launches are the same
         # CUDA kernel (csrc/conv_tma.cuh); the weight gradient is a different kernel and listed in the breakdown
@@ -418,26 +566,36 @@ def main():
         if fam:
             ms = sum(v["ms"] for v in fam)
             tfl = sum(v["algorithmic_tflop"] for v in fam)
-            nl = sum(v["launches"] for v in fam)
+            calls = sum(v["launches"] for v in fam)
+            # kernel launches, not API calls: a strided dgrad is one conv_tma_kernel launch per parity class
+            nk = sum(v.get("kernel_launches", v["launches"]) for v in fam)
             ach = tfl * 1e3 / ms
             line["roofline"] = {"kernel": "conv_tma_kernel (sfb_conv_gemm fprop + dgrad)", "bound": "tensor", "achieved": ach,
                                 "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach / peaks["sustained"],
-                                "traffic": None, "launches_per_step": nl, "ms_per_step": ms,
+                                "traffic": None, "launches_per_step": nk, "api_calls_per_step": calls, "ms_per_step": ms,
                                 "algorithmic_tflop_per_step": tfl,
                                 "peak_source": f"{peaks['src']} bf16_tflops_sustained (kernel timed inside a long step)",
                                 "share_of_step": ms / sum(v["ms"] for v in kernels.values())}
-            line["roofline"]["algorithmic_bytes_per_launch"] = sum(v.get("algorithmic_bytes", 0.0) for v in fam) / nl
-            line["roofline"].update(conv_traffic_from_ncu(nl))
+            line["roofline"]["algorithmic_bytes_per_launch"] = sum(v.get("algorithmic_bytes", 0.0) for v in fam) / nk
+            if train and args.workload == "hyb":
+                line["roofline"].update(conv_traffic_from_ncu())
         line["kernel_breakdown_ms_per_step"] = {k: round(v["ms"], 3) for k, v in sorted(kernels.items(), key=lambda t: -t[1]["ms"])}
         line["kernel_tflops"] = {k: round(v["tflops"], 1) for k, v in kernels.items() if "tflops" in v}
     if adam is not None:
         line["optimizer_step"] = adam
+    lib = library_baseline_from_profiles()
+    if lib is not None and args.workload == "hyb":
+        line["library_baseline"] = lib
     if world == 1 and not args.no_cpu_baseline:
+        if _ORIG_AFFINITY:
+            os.sched_setaffinity(0, _ORIG_AFFINITY)  # the CPU baseline uses every host core, not the GPU's NUMA node only
         n = args.cpu_clips
-        sec, threads = cpu_train_steps(n, 2, 1)
+        sec, threads = cpu_steps(args.mode, args.workload, n, 2, 1)
+        what = "train steps" if train else "eval forwards"
         line["cpu_baseline"] = {"value": n / sec, "unit": "clips/s", "cores": threads, "kind": "port",
-                                "sample": f"2 train steps (after 1 warm-up) of {n} HYB clips, fp32 eager PyTorch on the "
-                                          "host cores; oracle restatement of the reference path"}
+                                "cpu": cpu_model_string(),
+                                "sample": f"2 {what} (after 1 warm-up) of {n} clips of this workload, fp32 eager PyTorch on "
+                                          "the host cores; oracle restatement of the reference path"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

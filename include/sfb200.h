@@ -274,12 +274,15 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
 
 /* replaces: PoolConcatPathway AvgPool3d(k, stride 1) + ResNetBasicHead Dropout + AdaptiveAvgPool3d(1)
  * (the Linear commutes with the mean).  feat[n, f_off + c] = mean_p drop(avgpool_k(x))[n, p, c].
- * dropout_p = 0 disables dropout; otherwise a counter-based mask from `seed` (recomputed in backward). */
+ * dropout_p = 0 disables dropout; otherwise a counter-based mask from `seed` (recomputed in backward).
+ * seed_dev (may be NULL): device address of the 64-bit seed; when given it replaces `seed`, so that a launch captured
+ * in a CUDA graph draws a fresh mask every replay (the caller rewrites the word between replays; nn.Dropout in the
+ * reference, ResNetBasicHead, draws from the process's CUDA generator at every call). */
 int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
-                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed,
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
                       float* feat, int32_t f_ld, int32_t f_off, void* stream);
 int sfb_head_pool_bwd(const float* dfeat, int32_t f_ld, int32_t f_off, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
-                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed,
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
                       void* dx, int32_t dx_ld, int32_t dx_coff, void* stream);
 
 /* replaces: ResNetBasicHead.proj (nn.Linear 2304 -> NUM_CLASS), fp32. */

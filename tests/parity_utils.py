@@ -21,19 +21,21 @@ PRODUCT_KW = {
 }
 
 
-def build_pair(variant="REF", fuse=True, num_class=249, seed=0, bn_seed=123, device="cuda", final_gamma=None, twin=False):
+def build_pair(variant="REF", fuse=True, num_class=249, seed=0, bn_seed=123, device="cuda", final_gamma=None, twin=False,
+               input_channels=(5, 15)):
     """(oracle, product) on identical seeded weights.  twin=True: the oracle becomes the bf16-storage twin
     (oracle.slowfast_oracle.add_bf16_storage_hooks_; conv weights pre-rounded to bf16 in BOTH models) -- the
     comparison partner for gradients; twin=False: the pure fp32 reference path -- the partner for logits/top-1."""
     torch.manual_seed(seed)
-    oracle = so.build_oracle(num_class=num_class, fuse=fuse, **so.VARIANTS[variant])
+    oracle = so.build_oracle(num_class=num_class, fuse=fuse, input_channels=tuple(input_channels), **so.VARIANTS[variant])
     if final_gamma is None:
         final_gamma = float(os.environ.get("SFB_FINAL_GAMMA", FINAL_GAMMA))
     so.randomize_bn_(oracle, bn_seed, final_gamma)
     so.disable_dropout_(oracle)
     if twin:
         so.round_conv_weights_to_bf16_(oracle)
-    product = init_my_slowfast(so.make_cfg(num_class=num_class, fuse=fuse), (5, 15), (64, 8), **PRODUCT_KW[variant])
+    product = init_my_slowfast(so.make_cfg(num_class=num_class, fuse=fuse), tuple(input_channels), (64, 8),
+                               **PRODUCT_KW[variant])
     product.load_state_dict(oracle.state_dict(), strict=True)
     product.blocks[6].dropout.p = 0.0
     if twin:

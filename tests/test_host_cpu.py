@@ -119,3 +119,42 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     assert lat.buf is slow.buf and slow.coff == 0 and lat.coff == slow.C == 256 and lat.buf.shape[-1] == 320
     with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
         eng.get_plan(torch.empty(1, 5, 8, 64, 64, device="meta"), torch.empty(1, 15, 32 if variant == "REF" else 8, 64, 64, device="meta"), False)
+
+
+def test_dropout_seed_follows_torch_generator_and_rank(monkeypatch):
+    """engine._draw_dropout_seed: reproducible under torch.manual_seed, different from step to step and from rank to
+    rank (the reference's nn.Dropout draws from the process generator at every call)"""
+    import torch.distributed as dist
+    from oracle import slowfast_oracle as so
+    from video_classification_b200.engine import SlowFastEngine
+    from video_classification_b200.my_slowfast import init_my_slowfast
+    eng = SlowFastEngine(init_my_slowfast(so.make_cfg(), (5, 15), (64, 8)), dry_run=True)
+    torch.manual_seed(3)
+    a1, a2 = eng._draw_dropout_seed(), eng._draw_dropout_seed()
+    torch.manual_seed(3)
+    b1 = eng._draw_dropout_seed()
+    torch.manual_seed(4)
+    c1 = eng._draw_dropout_seed()
+    assert a1 == b1 and a1 != a2 and a1 != c1
+    assert all(-(1 << 63) <= v < (1 << 63) for v in (a1, a2, c1))
+    monkeypatch.setattr(dist, "is_initialized", lambda: True)
+    monkeypatch.setattr(dist, "get_rank", lambda: 1)
+    torch.manual_seed(3)
+    r1 = eng._draw_dropout_seed()
+    assert r1 != a1
+
+
+def test_every_plan_owns_its_batchnorm_scratch():
+    """the coefficients a backward pass reads are per plan: building / running another shape or an eval plan cannot
+    overwrite them (dry-run planning on the meta device: the pointers baked into the op lists are disjoint)"""
+    from oracle import slowfast_oracle as so
+    from video_classification_b200.engine import SlowFastEngine
+    from video_classification_b200.my_slowfast import init_my_slowfast
+    eng = SlowFastEngine(init_my_slowfast(so.make_cfg(), (5, 15), (64, 8)), dry_run=True)
+    eng.refresh_weights(True)
+    p1 = eng.build_plan(2, 8, 8, 64, 64, True)
+    p2 = eng.build_plan(2, 8, 8, 64, 64, False)
+    p3 = eng.build_plan(1, 8, 8, 64, 64, True)
+    assert p1.bn_flat is not p2.bn_flat and p1.bn_flat is not p3.bn_flat
+    assert p1.bn_flat.numel() == p2.bn_flat.numel() == p3.bn_flat.numel() > 0
+    assert p1.stats_flat.numel() < p1.bn_flat.numel()

@@ -240,6 +240,17 @@ def test_head_pool(T, H, W, k):
     ops.head_pool_bwd(ones, 8, k, 0.5, 1234, dxd)
     recon = (kc.from_act(dxd) * xq.detach()).sum(dim=(2, 3, 4))
     assert kc.relerr(recon, feat_d[:, 8:]) < 2e-2
+    # the seed read from device memory (the form a CUDA-graph replay needs) draws the same mask as the by-value seed
+    sd = torch.tensor([1234], dtype=torch.int64, device=DEV)
+    feat_e = torch.zeros(N, C_ + 8, device=DEV)
+    ops.head_pool_fwd(xa, k, 0.5, 0, feat_e, 8, seed_dev=sd)
+    torch.testing.assert_close(feat_e[:, 8:], feat_d[:, 8:], rtol=1e-5, atol=1e-6)  # atomics order only
+    dxe = Act.empty(N, T, H, W, C_)
+    ops.head_pool_bwd(ones, 8, k, 0.5, 0, dxe, seed_dev=sd)
+    assert torch.equal(kc.from_act(dxe), kc.from_act(dxd))
+    sd.fill_(99)
+    ops.head_pool_fwd(xa, k, 0.5, 0, feat_e, 8, seed_dev=sd)
+    assert float((feat_e[:, 8:] - feat_d[:, 8:]).abs().max()) > 1e-2 * float(feat_d[:, 8:].abs().max())
 
 
 def test_fc():

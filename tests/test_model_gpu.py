@@ -28,6 +28,9 @@ CASES = [
     ("REF", False, 2, 64, 8, 8),
     ("REF", True, 2, 128, 20, 20),
     ("HYB", True, 2, 224, 8, 32),
+    # the reference's largest crop: CropHTAH at 192^2, 20 frames on both pathways (config/crop_cfg.py:18-24,
+    # config/defaults.py CLIP_LEN)
+    ("REF", True, 2, 192, 20, 20),
 ]
 
 
@@ -422,3 +425,88 @@ def test_raw_uint8_clips_error_paths():
         product(RawClips(torch.zeros((1, 8, 64, 64, 21), device=DEV)))
     with pytest.raises(_ffi.SfbError):
         product(RawClips(torch.zeros((1, 8, 64, 64, 21), dtype=torch.uint8)))                # host tensor
+
+
+# ---- call-site variants of the reference -------------------------------------------------------------------------
+def test_two_channel_fast_pathway_new_feature_test():
+    """init_my_slowfast(cfg, (5, 2), (64, 8)) as reference new_feature_test.py:715 builds it (bgr+uv Slow, 2-channel
+    flow Fast): eval / train logits against the fp32 oracle and gradients of every live parameter"""
+    pu.fp32_reference_mode()
+    oracle, product = pu.build_pair("REF", True, input_channels=(5, 2))
+    xs, xf = so.synthetic_clips(2, 8, 8, 64, input_channels=(5, 2))
+    xs, xf = xs.to(DEV), xf.to(DEV)
+    assert xf.shape[1] == 2
+    oracle.eval()
+    product.eval()
+    with torch.no_grad():
+        ref, got = oracle([xs, xf]), product([xs, xf])
+    assert pu.rel_max(got, ref) <= pu.LOGIT_TOL
+    pu.assert_same_top1(got, ref)
+    oracle.train()
+    product.train()
+    y = torch.tensor([5, 100], device=DEV)
+    out_o, out_p = oracle([xs, xf]), product([xs, xf])
+    assert pu.rel_max(out_p.detach(), out_o.detach()) <= pu.LOGIT_TOL
+    F.cross_entropy(out_p, y).backward()
+    assert sum(p.grad is not None for p in product.parameters()) == 332
+    g = product.blocks[0].multipathway_blocks[1].conv.weight.grad
+    assert tuple(g.shape) == (8, 2, 1, 7, 7) and bool(torch.isfinite(g).all()) and float(g.abs().sum()) > 0
+
+
+def test_dropout_follows_torch_generator():
+    """the head's Dropout(0.5) (reference ResNetBasicHead, trained with p = 0.5) draws its mask seed from torch's
+    generator: torch.manual_seed reproduces a step, another seed gives another mask, successive steps differ, and
+    the expectation of the pooled features is preserved.  (Forward and backward read the same device-resident seed
+    word of the plan; their mask consistency is checked at kernel level, test_kernels_gpu.py::test_head_pool.)"""
+    _, product = pu.build_pair("REF", True)
+    product.blocks[6].dropout.p = 0.5
+    xs, xf = _clips("REF", 2, 64, 8, 8)
+    product.train()
+
+    def feat(seed):
+        if seed is not None:
+            torch.manual_seed(seed)
+        with torch.no_grad():
+            product([xs, xf])
+        eng = product._engine
+        return eng.get_plan(xs, xf, True).feat.clone()
+
+    a, b, c = feat(11), feat(11), feat(12)
+    d = feat(None)  # the generator moved on: a new mask without re-seeding
+    base = float(a.abs().mean())
+    assert float((a - b).abs().max()) <= 2e-2 * float(a.abs().max())      # same mask (BatchNorm atomics noise only)
+    assert float((a - c).abs().mean()) > 0.2 * base                         # different mask: half the units differ
+    assert float((c - d).abs().mean()) > 0.2 * base
+    # keep rate: (4,2,2) pooling windows x 2304 channels x 2 clips, each kept with probability 0.5 and scaled by 2 --
+    # the mean of the pooled features is preserved in expectation
+    product.blocks[6].dropout.p = 0.0
+    product._engine = None
+    with torch.no_grad():
+        product([xs, xf])
+    nodrop = product._engine.get_plan(xs, xf, True).feat.clone()
+    assert abs(float(a.mean()) - float(nodrop.mean())) <= 0.1 * float(nodrop.abs().mean())
+
+
+def test_free_running_gradients_vs_bf16_twin():
+    """NOT teacher-forced: the product's own forward state (saved raw outputs, BatchNorm statistics, packed ReLU
+    masks, max-pool arg-max indices) feeds its backward, and the result is compared with the bf16-storage twin's
+    free-running gradients.  The two forwards differ by accumulation order, hence by a few bf16 rounding and ReLU-mask
+    flips (the same effect two runs of the product differ by), so the bound is statistical:
+    whole-gradient relative L2 and the median / 90th percentile of the per-parameter errors."""
+    pu.fp32_reference_mode()
+    twin, product = pu.build_pair("REF", True, twin=True)
+    xs, xf = _clips("REF", 4, 64, 8, 8)
+    y = torch.randint(0, 249, (4,), generator=torch.Generator().manual_seed(7)).to(DEV)
+    twin.train()
+    product.train()
+    F.cross_entropy(twin([xs, xf]), y).backward()
+    F.cross_entropy(product([xs, xf]), y).backward()
+    tg = {n: p.grad for n, p in twin.named_parameters()}
+    rep = pu.grad_report(product, tg)
+    errs = sorted(e for _, e in rep)
+    num = sum(float((p.grad.float() - tg[n].float()).pow(2).sum()) for n, p in product.named_parameters() if p.grad is not None)
+    den = sum(float(tg[n].float().pow(2).sum()) for n, p in product.named_parameters() if p.grad is not None)
+    whole = (num / den) ** 0.5
+    med, p90 = errs[len(errs) // 2], errs[int(0.9 * len(errs))]
+    print(f"free-running product vs twin: whole {whole:.3e} median {med:.3e} p90 {p90:.3e} max {errs[-1]:.3e}")
+    assert whole <= 5e-2 and med <= pu.GRAD_TOL and p90 <= 0.1, (whole, med, p90, errs[-1])

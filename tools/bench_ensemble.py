@@ -18,13 +18,15 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
-from oracle import slowfast_oracle as so  # noqa: E402  (only make_cfg, the yacs stand-in)
 from video_classification_b200 import _ffi  # noqa: E402
+from video_classification_b200.config import CLIP_LEN, PART_WORKLOADS, make_cfg  # noqa: E402
 from video_classification_b200.evaluation import SparseModel, fuse_ensemble, video_scores  # noqa: E402
 from video_classification_b200.my_slowfast import init_my_slowfast  # noqa: E402
 from video_classification_b200.parallel import broadcast_parameters, gather_part_scores  # noqa: E402
 
-PARTS = ["LHand", "RHand", "LHandArm", "RHandArm", "Torso", "HTAH", "part6", "part7"]
+# the ensemble's parts in the order reference train_sparse.py:36 loads them (+ the optional Torso), each at its own crop
+# size (config/crop_cfg.py:18-32); ranks beyond the sixth repeat the list
+PARTS = ["HTAH", "LHandArm", "LHand", "RHandArm", "RHand", "Torso", "HTAH", "LHandArm"]
 
 
 def main():
@@ -33,6 +35,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--clips-per-video", type=int, default=4)
+    ap.add_argument("--shapes", default="ref", choices=["ref", "hyb"],
+                    help="ref: the reference's per-part crops (64/128/192^2, 20 frames on both pathways, reference graph); "
+                         "hyb: every part at the headline 8/32 x 224^2 shape")
     a = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -43,14 +48,19 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     B, C = a.batch, bench.NUM_CLASS
     torch.manual_seed(100 + rank)  # every part has its own weights
-    model = init_my_slowfast(so.make_cfg(C, True), (5, 15), (64, 8), **bench.HYB_KW).to(dev).eval()
+    part = PARTS[rank % len(PARTS)]
+    if a.shapes == "ref":
+        size, ts, tf, kw = PART_WORKLOADS[part]["size"], CLIP_LEN, CLIP_LEN, {}
+    else:
+        size, ts, tf, kw = bench.SIZE, bench.T_SLOW, bench.T_FAST, bench.HYB_KW
+    model = init_my_slowfast(make_cfg(C, True), (5, 15), (64, 8), **kw).to(dev).eval()
     torch.manual_seed(7)
     fuser = SparseModel(C, world).to(dev).eval()
     if world > 1:
         broadcast_parameters(fuser, 0)
     g = torch.Generator().manual_seed(1000 + rank)  # each part sees its own crop of the same clips
-    xs = torch.randn((B, 5, bench.T_SLOW, bench.SIZE, bench.SIZE), generator=g).to(dev)
-    xf = torch.randn((B, 15, bench.T_FAST, bench.SIZE, bench.SIZE), generator=g).to(dev)
+    xs = torch.randn((B, 5, ts, size, size), generator=g).to(dev)
+    xf = torch.randn((B, 15, tf, size, size), generator=g).to(dev)
     labels = torch.randint(0, C, (B // a.clips_per_video,), generator=torch.Generator().manual_seed(5))
     labels = labels.repeat_interleave(a.clips_per_video).to(dev)
     sv = [a.clips_per_video] * (B // a.clips_per_video)
@@ -90,7 +100,9 @@ def main():
     if rank == 0:
         ms = float(ms)
         print(json.dumps({
-            "metric": "ensemble clips/sec, one body-part SlowFast-R50 (8/32 x 224^2) per GPU, fused logits",
+            "metric": "ensemble clips/sec, one body-part SlowFast-R50 per GPU, fused logits",
+            "shapes": a.shapes, "part_sizes": {p_: (PART_WORKLOADS[p_]["size"] if a.shapes == "ref" else bench.SIZE)
+                                               for p_ in PARTS[:world]},
             "value": B / (ms * 1e-3), "unit": "clips/s", "n_gpus": world, "parts": PARTS[:world], "steps": a.steps,
             "warmup": max(a.warmup, 3), "ms_per_step": ms, "part_forwards_per_s": world * B / (ms * 1e-3),
             "config": {"workload": "configs[3]: slowfast-HTAH ensemble, eval forward per part + softmax + all-gather "

@@ -79,8 +79,8 @@ SIGNATURES = {
                          _i32, _i64, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp],
     "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
     "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
-    "sfb_head_pool_fwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
-    "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _i32, _i32, _vp],
+    "sfb_head_pool_fwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
+    "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
     "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],
     "sfb_fc_bwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp, _vp, _vp],
     "sfb_packed_weight_dims_dgrad": [_i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)],

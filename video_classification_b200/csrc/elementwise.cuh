@@ -721,8 +721,10 @@ __device__ __forceinline__ float dropout_keep_scale(uint64_t seed, int n, int c,
 constexpr int kHeadThreads = 256;
 __global__ void __launch_bounds__(kHeadThreads)
 head_pool_fwd_kernel(View x, int N, int T, int H, int W, int C, int kT, int kH, int kW, float p_drop,
-                     uint64_t seed, float* __restrict__ feat, int f_ld, int f_off, int cvb, int npos) {
+                     uint64_t seed, const uint64_t* __restrict__ seed_dev, float* __restrict__ feat, int f_ld, int f_off,
+                     int cvb, int npos) {
   __shared__ float red[kHeadThreads * 8];
+  if (seed_dev) seed = *seed_dev;
   const int CV = C >> 3;
   const int RL = kHeadThreads / cvb;
   const int tx = threadIdx.x % cvb, ty = threadIdx.x / cvb;
@@ -775,7 +777,9 @@ head_pool_fwd_kernel(View x, int N, int T, int H, int W, int C, int kT, int kH, 
 }
 
 __global__ void head_pool_bwd_kernel(const float* __restrict__ dfeat, int f_ld, int f_off, int N, int T, int H, int W,
-                                     int C, int kT, int kH, int kW, float p_drop, uint64_t seed, ViewW dx) {
+                                     int C, int kT, int kH, int kW, float p_drop, uint64_t seed,
+                                     const uint64_t* __restrict__ seed_dev, ViewW dx) {
+  if (seed_dev) seed = *seed_dev;
   const int CV = C >> 3;
   const long long total = (long long)N * T * H * W * CV;
   const int Pt = T - kT + 1, Ph = H - kH + 1, Pw = W - kW + 1;

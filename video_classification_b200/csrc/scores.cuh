@@ -97,6 +97,9 @@ video_scores_kernel(const float* __restrict__ scores, int C, const int* __restri
     const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
     if (ob > best || (ob == best && oi < besti)) { best = ob; besti = oi; }
   }
+  // the last block_reduce_sum ends with every warp READING red[]: a fast warp must not overwrite it with its arg-max
+  // candidate before the slow ones are through
+  __syncthreads();
   if ((tid & 31) == 0) { red[tid >> 5] = best; redi[tid >> 5] = besti; }
   __syncthreads();
   if (tid == 0 && top1) {

@@ -1293,8 +1293,8 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
 }
 
 int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
-                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, float* feat, int32_t f_ld,
-                      int32_t f_off, void* stream) {
+                      int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
+                      float* feat, int32_t f_ld, int32_t f_off, void* stream) {
   if (N <= 0 || C <= 0 || (C & 7) || kT <= 0 || kH <= 0 || kW <= 0 || kT > T || kH > H || kW > W || !feat) return SFB_ERR_BAD_ARG;
   if (!view_ok(x, x_ld, x_coff, C) || f_off + C > f_ld || dropout_p < 0.f || dropout_p >= 1.f) return SFB_ERR_BAD_ARG;
   View vx{(const __nv_bfloat16*)x, x_ld, x_coff};
@@ -1309,21 +1309,21 @@ int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, in
     if (e != cudaSuccess) return cuda_fail(e, "cudaMemset2DAsync(head_pool_fwd)");
   }
   dim3 grid((unsigned)(N * npos), (unsigned)((CV + cvb - 1) / cvb));
-  head_pool_fwd_kernel<<<grid, kHeadThreads, 0, (cudaStream_t)stream>>>(vx, N, T, H, W, C, kT, kH, kW, dropout_p, seed, feat,
-                                                                        f_ld, f_off, cvb, (int)npos);
+  head_pool_fwd_kernel<<<grid, kHeadThreads, 0, (cudaStream_t)stream>>>(vx, N, T, H, W, C, kT, kH, kW, dropout_p, seed,
+                                                                        seed_dev, feat, f_ld, f_off, cvb, (int)npos);
   SFB_CHECK_LAUNCH("head_pool_fwd_kernel");
   return SFB_OK;
 }
 
 int sfb_head_pool_bwd(const float* dfeat, int32_t f_ld, int32_t f_off, int32_t N, int32_t T, int32_t H, int32_t W,
-                      int32_t C, int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, void* dx,
-                      int32_t dx_ld, int32_t dx_coff, void* stream) {
+                      int32_t C, int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed,
+                      const uint64_t* seed_dev, void* dx, int32_t dx_ld, int32_t dx_coff, void* stream) {
   if (N <= 0 || C <= 0 || (C & 7) || kT <= 0 || kH <= 0 || kW <= 0 || kT > T || kH > H || kW > W || !dfeat) return SFB_ERR_BAD_ARG;
   if (!view_ok(dx, dx_ld, dx_coff, C) || f_off + C > f_ld || dropout_p < 0.f || dropout_p >= 1.f) return SFB_ERR_BAD_ARG;
   ViewW vx{(__nv_bfloat16*)dx, dx_ld, dx_coff};
   const long long total = (long long)N * T * H * W * (C >> 3);
   head_pool_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(dfeat, f_ld, f_off, N, T, H, W, C, kT, kH,
-                                                                               kW, dropout_p, seed, vx);
+                                                                               kW, dropout_p, seed, seed_dev, vx);
   SFB_CHECK_LAUNCH("head_pool_bwd_kernel");
   return SFB_OK;
 }

@@ -17,6 +17,7 @@ import ctypes as C
 from typing import Dict, List, Optional, Tuple
 
 import torch
+import torch.distributed
 import torch.nn as nn
 
 from . import _ffi
@@ -117,7 +118,9 @@ class Plan:
         self.logits = None
         self.dlogits = None
         self.act_bytes = 0
-        self.seed_slot = None
+        self.seed_dev = None  # int64[1] on the device: the head dropout's seed of the current step
+        self.bn_flat = None   # this plan's BatchNorm scratch (SlowFastEngine._bind_bn_arena)
+        self.stats_flat = None
         self.gen = 0  # bumped by every training forward; backward checks it saw the latest one
 
 
@@ -205,24 +208,32 @@ class SlowFastEngine:
         self.proj = m.blocks[6].proj
         self.bn_modules = [l.bn for l in self.layers]
 
-    def _alloc_arenas(self):
-        dev = self.dev
-        # ---- BN scratch: [all stats | per layer scale, shift, mean, invstd] ----
-        n_stats = sum(2 * l.Co + (2 * l.fold_f * l.ldo if l.fold_f > 1 else 0) for l in self.layers)
-        n_rest = sum(4 * l.Co for l in self.layers)
-        self.bn_flat = _f32(n_stats + n_rest, dev, zero=True)
-        self.stats_flat = self.bn_flat[:n_stats]
-        o_s, o_r = 0, n_stats
+    def _bind_bn_arena(self, plan: "Plan"):
+        """BatchNorm scratch of ONE plan: [all raw sums | per layer scale, shift, mean, invstd].  Every plan owns its
+        arena (≈ 0.2 MB), so a forward of another shape, or an eval forward (whose sfb_bn_fold rewrites scale / shift
+        from the running statistics), between a training forward and its backward cannot touch the coefficients that
+        backward reads -- the reference's autograd graph allows any such interleaving.  The layer attributes
+        l.stats / l.scale / ... are (re)bound to the plan being built or inspected."""
+        if plan.bn_flat is None:
+            n_stats = sum(2 * l.Co + (2 * l.fold_f * l.ldo if l.fold_f > 1 else 0) for l in self.layers)
+            n_rest = sum(4 * l.Co for l in self.layers)
+            plan.bn_flat = _f32(n_stats + n_rest, self.dev, zero=True)
+            plan.stats_flat = plan.bn_flat[:n_stats]
+        flat = plan.bn_flat
+        o_s, o_r = 0, plan.stats_flat.numel()
         for l in self.layers:
             c = l.Co
-            l.stats = self.bn_flat[o_s:o_s + 2 * c]
+            l.stats = flat[o_s:o_s + 2 * c]
             o_s += 2 * c
             if l.fold_f > 1:
-                l.sf = self.bn_flat[o_s:o_s + 2 * l.fold_f * l.ldo]
+                l.sf = flat[o_s:o_s + 2 * l.fold_f * l.ldo]
                 o_s += 2 * l.fold_f * l.ldo
-            l.scale, l.shift = self.bn_flat[o_r:o_r + c], self.bn_flat[o_r + c:o_r + 2 * c]
-            l.mean, l.invstd = self.bn_flat[o_r + 2 * c:o_r + 3 * c], self.bn_flat[o_r + 3 * c:o_r + 4 * c]
+            l.scale, l.shift = flat[o_r:o_r + c], flat[o_r + c:o_r + 2 * c]
+            l.mean, l.invstd = flat[o_r + 2 * c:o_r + 3 * c], flat[o_r + 3 * c:o_r + 4 * c]
             o_r += 4 * c
+
+    def _alloc_arenas(self):
+        dev = self.dev
         # ---- flat gradient arena, reverse forward order (head first) ----
         live: List[torch.nn.Parameter] = []
         for l in self.layers:
@@ -568,6 +579,7 @@ class SlowFastEngine:
         cfg = self.cfg
         dev = self.dev
         plan = Plan()
+        self._bind_bn_arena(plan)
         pool = BufferPool(dev)
         fwd = plan.fwd
 
@@ -738,7 +750,8 @@ class SlowFastEngine:
         plan.logits = logits
         hk = cfg["head_pool_kernel_sizes"]
         drop = float(self.dropout_p) if training else 0.0
-        plan.seed_slot = C.c_uint64(0)
+        plan.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        seed_ptr = plan.seed_dev.data_ptr() if drop > 0.0 else None
         f_off = 0
         for p in range(2):
             a = cur[p].act
@@ -747,7 +760,7 @@ class SlowFastEngine:
                 raise _ffi.SfbError(f"head pool kernel {hk[p]} larger than the final feature map {(t_, h_, w_)} "
                                     f"(same failure as nn.AvgPool3d in the reference)")
             self._emit(fwd, self.lib.sfb_head_pool_fwd, a.ptr(), a.ld, a.coff, n_, t_, h_, w_, a.C, hk[p][0], hk[p][1], hk[p][2],
-                       drop, plan.seed_slot, feat.data_ptr(), feat_dim, f_off, self.stream)
+                       drop, 0, seed_ptr, feat.data_ptr(), feat_dim, f_off, self.stream)
             f_off += a.C
         self._emit(fwd, self.lib.sfb_fc_fwd, feat.data_ptr(), self.proj.weight.data_ptr(), self.proj.bias.data_ptr(), N,
                    feat_dim, ncls, logits.data_ptr(), self.stream, tag=("logits", logits))
@@ -805,7 +818,7 @@ class SlowFastEngine:
             a, ga = fa.act, fa.grad
             n_, t_, h_, w_ = a.dims
             self._emit(bwd, self.lib.sfb_head_pool_bwd, dfeat.data_ptr(), feat_dim, f_off, n_, t_, h_, w_, a.C,
-                       hk[p][0], hk[p][1], hk[p][2], drop, plan.seed_slot, ga.ptr(), ga.ld, ga.coff, self.stream)
+                       hk[p][0], hk[p][1], hk[p][2], drop, 0, seed_ptr, ga.ptr(), ga.ld, ga.coff, self.stream)
             fa.ginit = True
             f_off += a.C
 
@@ -896,18 +909,20 @@ class SlowFastEngine:
         st = torch.cuda.current_stream(self.dev)
         for fn, args, tag in ops:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            k0 = _ffi.launch_count()
             e0.record(st)
             rc = fn(*args)
             e1.record(st)
             if rc:
                 _ffi.check(rc, getattr(fn, "__name__", "libsfb200 call"))
-            self.prof.append((getattr(fn, "__name__", "op"), e0, e1, args))
+            # kernel launches of this entry (a strided dgrad is one launch per parity class)
+            self.prof.append((getattr(fn, "__name__", "op"), e0, e1, args, _ffi.launch_count() - k0))
 
     def profile_ops(self):
         """-> list of (entry name, layer description, ms, algorithmic GFLOP) per recorded plan entry"""
         torch.cuda.synchronize(self.dev)
         rows = []
-        for name, e0, e1, args in self.prof:
+        for name, e0, e1, args, _nk in self.prof:
             desc, gf = "", 0.0
             name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
             if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
@@ -942,7 +957,7 @@ class SlowFastEngine:
         """-> {entry name: (launches, total ms)}, plus conv FLOPs per class, from the events in self.prof"""
         torch.cuda.synchronize(self.dev)
         out, flops = {}, {}
-        for name, e0, e1, args in self.prof:
+        for name, e0, e1, args, nk in self.prof:
             ms = e0.elapsed_time(e1)
             name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
             key = name
@@ -960,6 +975,7 @@ class SlowFastEngine:
                 if name == "sfb_conv_gemm" and args[7]._obj.residual:
                     byt += 2.0 * g.N * g.To * g.Ho * g.Wo * g.Co
                 flops[key + "#bytes"] = flops.get(key + "#bytes", 0.0) + byt
+                flops[key + "#kernels"] = flops.get(key + "#kernels", 0.0) + nk
             if name in ("sfb_stem_conv_fprop", "sfb_stem_conv_wgrad"):
                 ci, co = args[5], (args[12] if name == "sfb_stem_conv_fprop" else args[10])
                 flops[name] = flops.get(name, 0.0) + 2.0 * args[1] * args[2] * args[3] * args[4] * co * ci * 49
@@ -979,6 +995,7 @@ class SlowFastEngine:
         from the forced raw conv outputs -- so that a following backward() can be compared with a reference
         backward evaluated on the very same forward state (no ReLU-mask divergence)."""
         bufs = self.tagged_buffers(plan)
+        self._bind_bn_arena(plan)  # l.mean / l.scale / ... below are this plan's
         by_conv = {l.conv_name: l for l in self.layers}
         for name, t in tensors.items():
             dst = bufs[name]
@@ -1091,13 +1108,29 @@ class SlowFastEngine:
     def _forward_staged(self, plan: Plan, training: bool) -> Tuple[torch.Tensor, Plan]:
         if training:
             plan.gen += 1
-            self.stats_flat.zero_()
-            self.step_seed += 1
-            plan.seed_slot.value = (self.step_seed * 0x9E3779B97F4A7C15 + 12345) & 0xFFFFFFFFFFFFFFFF
+            plan.stats_flat.zero_()
+            if self.dropout_p > 0.0:
+                plan.seed_dev.fill_(self._draw_dropout_seed())
         self._run(plan.fwd)
         if training:
             torch._foreach_add_([bn.num_batches_tracked for bn in self.bn_modules], 1)
         return plan.logits, plan
+
+    def _draw_dropout_seed(self) -> int:
+        """64-bit seed of this step's head dropout mask, drawn from torch's default generator -- so torch.manual_seed
+        reproduces a run, successive steps / runs / resumed runs differ, as with the reference's nn.Dropout
+        (ResNetBasicHead; it draws from the process's generator at every call) -- and mixed with the data-parallel
+        rank so that replicas seeded alike do not drop the same units of their local sample n."""
+        v = int(torch.randint(-(1 << 62), 1 << 62, (1,), dtype=torch.int64))
+        self.step_seed += 1
+        rank = 0
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            rank = torch.distributed.get_rank()
+        z = (v ^ ((rank + 1) * 0x9E3779B97F4A7C15)) & 0xFFFFFFFFFFFFFFFF
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+        z ^= z >> 31
+        return z - (1 << 64) if z >= (1 << 63) else z  # as a signed int64 for Tensor.fill_
 
     def backward(self, plan: Plan, dlogits: torch.Tensor):
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream

@@ -22,8 +22,10 @@ from ._ffi import check, lib, stream_ptr
 
 def _segments(samples_per_video: Sequence[int], device) -> torch.Tensor:
     sv = torch.as_tensor(list(samples_per_video), dtype=torch.int64)
-    if sv.numel() == 0 or int(sv.min()) < 0:
-        raise ValueError("samples_per_video must be a non-empty list of non-negative counts")
+    if sv.numel() == 0 or int(sv.min()) < 1:
+        # a video without clips has no mean / arg-max (the reference's run_eval never produces one: every video
+        # yields at least one sliding window, train.py:337-349)
+        raise ValueError("samples_per_video must be a non-empty list of positive counts")
     seg = torch.zeros(sv.numel() + 1, dtype=torch.int64)
     seg[1:] = torch.cumsum(sv, 0)
     return seg.to(torch.int32).to(device)

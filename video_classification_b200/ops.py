@@ -325,16 +325,18 @@ def maxpool_bwd(dout: Act, idx: torch.Tensor, dz: Act):
     return dz
 
 
-def head_pool_fwd(x: Act, k, dropout_p, seed, feat: torch.Tensor, f_off: int):
+def head_pool_fwd(x: Act, k, dropout_p, seed, feat: torch.Tensor, f_off: int, seed_dev: torch.Tensor = None):
     N, T, H, W = x.dims
     check(lib().sfb_head_pool_fwd(x.ptr(), x.ld, x.coff, N, T, H, W, x.C, k[0], k[1], k[2], float(dropout_p), seed,
+                                  seed_dev.data_ptr() if seed_dev is not None else None,
                                   feat.data_ptr(), feat.shape[1], f_off, stream_ptr()), "sfb_head_pool_fwd")
 
 
-def head_pool_bwd(dfeat: torch.Tensor, f_off: int, k, dropout_p, seed, dx: Act):
+def head_pool_bwd(dfeat: torch.Tensor, f_off: int, k, dropout_p, seed, dx: Act, seed_dev: torch.Tensor = None):
     N, T, H, W = dx.dims
     check(lib().sfb_head_pool_bwd(dfeat.data_ptr(), dfeat.shape[1], f_off, N, T, H, W, dx.C, k[0], k[1], k[2],
-                                  float(dropout_p), seed, dx.ptr(), dx.ld, dx.coff, stream_ptr()), "sfb_head_pool_bwd")
+                                  float(dropout_p), seed, seed_dev.data_ptr() if seed_dev is not None else None,
+                                  dx.ptr(), dx.ld, dx.coff, stream_ptr()), "sfb_head_pool_bwd")
 
 
 def fc_fwd(feat, w, b, logits):

@@ -25,6 +25,11 @@ class Adam(torch.optim.Optimizer):
             raise ValueError(f"Invalid epsilon value: {eps}")
         if not 0.0 <= betas[0] < 1.0:
             raise ValueError(f"Invalid beta parameter at index 0: {betas[0]}")
+        if betas[0] < 0.5:
+            # torch's lerp switches formula at weight >= 0.5 (weight = 1 - beta1); the kernel reproduces the
+            # weight < 0.5 branch only, which every usual beta1 (the reference keeps the default 0.9) takes
+            raise NotImplementedError("beta1 < 0.5 is not implemented by sfb_adam_step (bit-exactness with torch's "
+                                      "lerp is only established for beta1 >= 0.5)")
         if not 0.0 <= betas[1] < 1.0:
             raise ValueError(f"Invalid beta parameter at index 1: {betas[1]}")
         if not 0.0 <= weight_decay:
@@ -135,12 +140,22 @@ class Adam(torch.optim.Optimizer):
                 live.append(p)
                 ptrs.append(p.data_ptr())
                 ptrs.append(g.data_ptr())
+                st = self.state.get(p)
+                if st:  # replaced / cleared state tensors must rebuild the table, not update orphans
+                    ptrs.append(st["exp_avg"].data_ptr())
+                    ptrs.append(st["exp_avg_sq"].data_ptr())
+                else:
+                    ptrs += [0, 0]
             if not live:
                 continue
             sig = tuple(ptrs)
             plan = self._plans.get(gi)
             if plan is None or plan["epoch"] != self._epoch or plan["sig"] != sig:
                 plan = self._plans[gi] = self._plan_group(live, sig)
+                # state tensors created by the planning pass are part of the signature from now on
+                plan["sig"] = tuple(v for p in live for v in (p.data_ptr(), p.grad.data_ptr(),
+                                                              self.state[p]["exp_avg"].data_ptr(),
+                                                              self.state[p]["exp_avg_sq"].data_ptr()))
             for cl in plan["classes"]:
                 cl["t"] += 1
                 torch._foreach_add_(cl["steps"], 1)
