@@ -79,6 +79,10 @@ const char* sfb_last_cuda_error(void);
 int sfb_version(void);
 /* number of kernel launches issued by this library since load (bench.py's gpu_launches) */
 int64_t sfb_launch_count(void);
+/* A CUDA graph captured from these entry points launches the same kernels again at every replay without passing
+ * through the library: the host reports the captured graph's kernel count here per replay so the counter keeps
+ * meaning "kernels of this library that ran".  Returns the new total. */
+int64_t sfb_launch_count_add(int64_t n);
 
 /* sizes of the packed bf16 weight matrix for a conv with `taps`=kT*kH*kW over Cg gathered
  * channels producing Co channels: rows are padded to the N tile, K to 64. */
@@ -112,6 +116,33 @@ int sfb_layout_input(const float* x, int64_t sn, int64_t sc, int64_t st, int64_t
 int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro,
                   const void* wp, int32_t rows_pad, int32_t k_pad,
                   void* out, const SfbEpilogue* epi, int32_t impl, void* stream);
+
+/* Input-gradient GEMM whose result is the gradient dz reaching a conv -> BatchNorm3d -> ReLU layer's activation
+ * (pytorchvideo BottleneckBlock norm_a/act_a, norm_b/act_b; reference model/my_slowfast.py:116-122), with the FIRST
+ * pass of that layer's BatchNorm backward fused into the epilogue.  Replaces cuDNN bwd-data followed by autograd's
+ * threshold_backward and the reduction half of native_batch_norm_backward:
+ *     dz        = conv_transpose(g, W)                         (as sfb_conv_gemm with geom->transposed = 1)
+ *     out[m,c]  = dz[m,c] * [ y[m,c]*scale[c] + shift[c] > 0 ]  -- the MASKED gradient (bf16)
+ *     dbeta[c] += sum_m out[m,c]
+ *     dgamma[c]+= invstd[c] * sum_m out[m,c] * (y[m,c] - mean[c])
+ * y is the raw output of the layer's convolution (same pixels and view layout as `out`); the y tile of every output
+ * tile is fetched by TMA while the accumulator is converted.  sfb_bn_bwd_apply (relu = 0) then turns `out` into the
+ * gradient of y.  Runs on the persistent TMA kernel only (SFB_IMPL_TC geometry rules); anything else is
+ * SFB_ERR_UNSUPPORTED -- there is no fallback inside this entry point. */
+typedef struct SfbBnBwdFuse {
+  const void* y;            /* bf16 (ptr, ld, coff) view, dims of `out` */
+  int32_t y_ld, y_coff;
+  const float* scale;       /* [C] forward coefficients gamma*invstd, beta - mean*gamma*invstd (ReLU mask recompute) */
+  const float* shift;
+  const float* mean;        /* [C] batch mean, 1/sqrt(var + eps) */
+  const float* invstd;
+  float* dgamma;            /* [C] fp32, accumulated */
+  float* dbeta;
+  int32_t C;                /* real channels (multiple of 8, <= geom->Co: zeroed pad lanes / pixel folding) */
+  int32_t fold_ld;          /* 0, or the per-pixel channel stride of a pixel-folded launch: channel = column % fold_ld */
+} SfbBnBwdFuse;
+int sfb_conv_dgrad_bn(const SfbConvGeom* geom, const void* g, const void* wp, int32_t rows_pad, int32_t k_pad,
+                      void* out, const SfbBnBwdFuse* bn, void* stream);
 
 /* replaces: nn.Conv3d weight gradient (cuDNN bwd-filter).
  * dw[co][ci][tap] += sum_m dy[m, co] * pro(x)[in(m,tap), ci]   (fp32, OIDHW, accumulated) */

@@ -96,10 +96,10 @@ def _worker(rank, world, port, backend, ret):
         reduced = eng.grad_flat.clone()
         assert sorted(snaps) == list(range(len(bk.buckets))), "a bucket was never launched"
         product.zero_grad(set_to_none=True)           # .grad aliases the arena: a second backward must not accumulate
+        bk.launch = orig_launch                       # (the snapshots stay those of the data-parallel run)
         w_saved, bk.world = bk.world, 1               # purely local backward of the SAME forward state
         out.backward(dl)
         bk.world = w_saved
-        bk.launch = orig_launch
         torch.cuda.synchronize(dev)
         local = eng.grad_flat.clone()
         lo, hi = bk.buckets[0][0], bk.buckets[-1][1]

@@ -109,8 +109,14 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     wgrads = [op for op in plan.bwd if op[0] in (lib.sfb_conv_wgrad, lib.sfb_conv_wgrad_folded)]
     assert any(op[0] is lib.sfb_conv_wgrad_folded for op in wgrads)
     assert len(wgrads) == n_conv - 2 and len([op for op in plan.bwd if op[0] is lib.sfb_stem_conv_wgrad]) == 2
-    dgrads = [op for op in plan.bwd if op[0] is lib.sfb_conv_gemm]
+    dgrads = [op for op in plan.bwd if op[0] in (lib.sfb_conv_gemm, lib.sfb_conv_dgrad_bn)]
     assert len(dgrads) == n_conv - 2  # the stems need no input gradient
+    # conv_c's and conv_b's input gradients reduce the BatchNorm backward of conv_b / conv_a in their epilogue:
+    # two per bottleneck; only block tails, shortcuts, laterals and stems keep a separate reduction pass
+    fused = [op for op in dgrads if op[0] is lib.sfb_conv_dgrad_bn]
+    assert len(fused) == 2 * 16 * 2
+    reduces = [op for op in plan.bwd if op[0] is lib.sfb_bn_bwd_reduce]
+    assert len(reduces) == n_conv - len(fused)
     assert tuple(plan.logits.shape) == (shape[0], 249)
     # the lateral output lands behind the Slow stage output in ONE buffer (torch.cat never happens)
     bufs = eng.tagged_buffers(plan)

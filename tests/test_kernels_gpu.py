@@ -596,3 +596,124 @@ def test_fuse_ensemble_matches_sparse_test_tail():
     assert abs(got["video_mean"] - ref["video_mean"]).max() <= 1e-5
     assert (got["video_top1"] == ref["video_top1"]).all()
     assert got["acc"] == pytest.approx(float(ref["acc"]))
+
+
+# ---- input gradient with the BatchNorm(+ReLU) backward reduction fused into its epilogue (sfb_conv_dgrad_bn) ----------
+DGRAD_BN_CASES = [
+    # name, N, T, H, W, Ci (= channels of dz / y), Co (= gathered dy channels), k, s
+    ("c_1x1x1_64_256", 2, 4, 12, 12, 64, 256, (1, 1, 1), (1, 1, 1)),          # dgrad of conv_c -> dz of conv_b (BN tile 64)
+    ("b_1x3x3_64_64", 2, 3, 14, 14, 64, 64, (1, 3, 3), (1, 1, 1)),            # dgrad of conv_b -> dz of conv_a
+    ("b_1x3x3_128_128_s2", 1, 4, 14, 14, 128, 128, (1, 3, 3), (1, 2, 2)),     # strided conv_b: one launch per parity class
+    ("c_1x1x1_256_1024", 1, 8, 7, 7, 256, 1024, (1, 1, 1), (1, 1, 1)),        # 256-wide tile, weights streamed (3 stages)
+    ("b_1x3x3_512_512", 1, 4, 7, 7, 512, 512, (1, 3, 3), (1, 1, 1)),          # two N tiles
+    ("big_c_1x1x1_128_512", 2, 8, 28, 28, 128, 512, (1, 1, 1), (1, 1, 1)),    # several persistent waves
+    ("odd_b_1x3x3_32_32", 2, 5, 13, 11, 32, 32, (1, 3, 3), (1, 1, 1)),        # partial patches, 32-channel boxes
+    ("fast_c_1x1x1_8_32", 2, 8, 12, 12, 8, 32, (1, 1, 1), (1, 1, 1)),         # 8 real channels in a 16-channel buffer
+    ("fast_b_1x3x3_16_16_s2", 2, 8, 14, 14, 16, 16, (1, 3, 3), (1, 2, 2)),
+]
+
+
+@pytest.mark.parametrize("case", DGRAD_BN_CASES, ids=[c[0] for c in DGRAD_BN_CASES])
+def test_conv_dgrad_bn_fused_reduction(case):
+    """out = dgrad * relu-mask(y), dbeta = sum out, dgamma = invstd * sum out*(y - mean), against PyTorch fp32 on the
+    same bf16 operands; pad lanes of the output stay zero and the accumulators of neighbouring layers (the arrays sit
+    in one arena) are not touched"""
+    name, N, T, H, W, Ci, Co, k, s = case
+    g = torch.Generator(device=DEV).manual_seed(11)
+    p = tuple(kk // 2 for kk in k)
+    To, Ho, Wo = ops.conv_out_dims((T, H, W), k, s, p)
+    ld = kc.ops.round_up(Ci, 16)
+    dy = torch.randn((N, Co, To, Ho, Wo), device=DEV, generator=g)
+    w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Co * k[0] * k[1] * k[2]) ** 0.5
+    y = torch.randn((N, Ci, T, H, W), device=DEV, generator=g) * 1.3 + 0.2
+    dya = kc.to_act(dy)
+    ya = Act.empty(N, T, H, W, ld, C=Ci, zero=True)
+    ya.torch_view().copy_(y.permute(0, 2, 3, 4, 1))
+    yq, wq = kc.from_act(ya), w.bfloat16().float()
+    x = torch.zeros((N, Ci, T, H, W), device=DEV, requires_grad=True)
+    F.conv3d(x, wq, stride=s, padding=p).backward(kc.from_act(dya))
+    dz = x.grad.bfloat16().float()                       # the epilogue masks the bf16-rounded gradient
+    gamma = torch.rand(Ci, device=DEV, generator=g) + 0.5
+    beta = torch.randn(Ci, device=DEV, generator=g) * 0.3
+    M = N * T * H * W
+    yf = yq.permute(0, 2, 3, 4, 1).reshape(M, Ci)
+    mean, var = yf.mean(0), yf.var(0, unbiased=False)
+    invstd = (var + 1e-5).rsqrt()
+    scale, shift = gamma * invstd, beta - mean * gamma * invstd
+    bc = lambda t: t.view(1, -1, 1, 1, 1)
+    mask = (yq * bc(scale) + bc(shift)) > 0
+    ref = torch.where(mask, dz, torch.zeros_like(dz))
+    ref_dbeta = ref.sum(dim=(0, 2, 3, 4))
+    ref_dgamma = (ref * (yq - bc(mean))).sum(dim=(0, 2, 3, 4)) * invstd
+    # accumulators in the middle of an arena with sentinels around them
+    arena = torch.full((Ci + 32,) , 7.0, device=DEV)
+    arena2 = torch.full((Ci + 32,), 7.0, device=DEV)
+    dgamma, dbeta = arena[16:16 + Ci], arena2[16:16 + Ci]
+    dgamma.zero_(); dbeta.zero_()
+    wpt = ops.pack_weight_dgrad(w.contiguous(), Co, s)
+    out = Act.empty(N, T, H, W, ld, C=Ci, zero=True)
+    outp = Act(out.buf, 0, ld)  # a dgrad writes the padded width
+    ops.conv_dgrad_bn(dya, wpt, outp, k, s, p, Act(ya.buf, 0, ld), scale, shift, mean, invstd, dgamma, dbeta, C_real=Ci)
+    torch.cuda.synchronize()
+    got = kc.from_act(out)
+    # the kernel evaluates the mask with one fma, PyTorch with two roundings: where y*scale+shift is within rounding of
+    # zero either sign is right, those (measure-zero) elements are left out of the elementwise comparison
+    amb = (yq * bc(scale) + bc(shift)).abs() < 1e-5
+    assert kc.relerr(got.masked_fill(amb, 0.0), ref.masked_fill(amb, 0.0)) < 1e-2, name
+    if ld > Ci:
+        assert float(out.buf[..., Ci:].abs().max()) == 0.0
+    assert kc.relerr(dbeta, ref_dbeta) < 2e-3 + 1e-2 * float(ref.abs().max()) / max(float(ref_dbeta.abs().max()), 1e-6), name
+    assert kc.relerr(dgamma, ref_dgamma) < 1e-2, name
+    assert bool((arena[:16] == 7.0).all() and (arena[16 + Ci:] == 7.0).all())
+    assert bool((arena2[:16] == 7.0).all() and (arena2[16 + Ci:] == 7.0).all())
+    # the same result as the two-kernel path: plain dgrad, then sfb_bn_bwd_reduce with the recomputed mask
+    out2 = Act.empty(N, T, H, W, ld, C=Ci, zero=True)
+    ops.conv_gemm(dya, wpt, Act(out2.buf, 0, ld), k, s, p, transposed=True)
+    dg2, db2 = torch.zeros(Ci, device=DEV), torch.zeros(Ci, device=DEV)
+    ops.bn_bwd_reduce(out2, ya, None, scale, shift, mean, invstd, True, dg2, db2)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(dbeta, db2, rtol=2e-3, atol=2e-3 * float(db2.abs().max()))
+    torch.testing.assert_close(dgamma, dg2, rtol=2e-3, atol=2e-3 * float(dg2.abs().max()))
+
+
+@pytest.mark.parametrize("N,T,H,W,Ci,Co,k", [FOLD_CASES[0], FOLD_CASES[2], FOLD_CASES[3]])
+def test_conv_dgrad_bn_fused_reduction_pixel_folded(N, T, H, W, Ci, Co, k):
+    """the fused reduction on a pixel-folded launch: column j of the folded output is channel j % ld"""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    ldi, ldo = kc.ops.round_up(Ci, 16), kc.ops.round_up(Co, 16)
+    s1, p = (1, 1, 1), tuple(kk // 2 for kk in k)
+    f = ops.fold_factor(ldi, ldo, k, s1, W)
+    assert f >= 2
+    w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Co * k[0] * k[1] * k[2]) ** 0.5
+    kf = (k[0], k[1], 1 if k[2] == 1 else 3)
+    pf = tuple(kk // 2 for kk in kf)
+    wf = ops.fold_weight(w.contiguous(), f, ldo, ldi)
+    dy = torch.randn((N, Co, T, H, W), device=DEV, generator=g)
+    dya = Act.empty(N, T, H, W, ldo, C=Co, zero=True)
+    dya.torch_view().copy_(dy.permute(0, 2, 3, 4, 1))
+    y = torch.randn((N, Ci, T, H, W), device=DEV, generator=g) * 1.3 + 0.2
+    ya = Act.empty(N, T, H, W, ldi, C=Ci, zero=True)
+    ya.torch_view().copy_(y.permute(0, 2, 3, 4, 1))
+    yq, wq = kc.from_act(ya), w.bfloat16().float()
+    x = torch.zeros((N, Ci, T, H, W), device=DEV, requires_grad=True)
+    F.conv3d(x, wq, padding=p).backward(kc.from_act(dya))
+    dz = x.grad.bfloat16().float()
+    gamma = torch.rand(Ci, device=DEV, generator=g) + 0.5
+    beta = torch.randn(Ci, device=DEV, generator=g) * 0.3
+    yf = yq.permute(0, 2, 3, 4, 1).reshape(-1, Ci)
+    mean, var = yf.mean(0), yf.var(0, unbiased=False)
+    invstd = (var + 1e-5).rsqrt()
+    scale, shift = gamma * invstd, beta - mean * gamma * invstd
+    bc = lambda t: t.view(1, -1, 1, 1, 1)
+    ref = torch.where((yq * bc(scale) + bc(shift)) > 0, dz, torch.zeros_like(dz))
+    dgamma, dbeta = torch.zeros(Ci, device=DEV), torch.zeros(Ci, device=DEV)
+    out = Act.empty(N, T, H, W, ldi, C=Ci, zero=True)
+    ops.conv_dgrad_bn(ops.folded(dya, f), ops.pack_weight_dgrad(wf, f * ldo, s1), ops.folded(out, f), kf, s1, pf,
+                      ops.folded(ya, f), scale, shift, mean, invstd, dgamma, dbeta, C_real=Ci, fold_ld=ldi)
+    torch.cuda.synchronize()
+    amb = (yq * bc(scale) + bc(shift)).abs() < 1e-5
+    assert kc.relerr(kc.from_act(out).masked_fill(amb, 0.0), ref.masked_fill(amb, 0.0)) < 1.5e-2
+    if ldi > Ci:
+        assert float(out.buf[..., Ci:].abs().max()) == 0.0
+    assert kc.relerr(dbeta, ref.sum(dim=(0, 2, 3, 4))) < 2e-2
+    assert kc.relerr(dgamma, (ref * (yq - bc(mean))).sum(dim=(0, 2, 3, 4)) * invstd) < 1e-2

@@ -33,6 +33,13 @@ class Epilogue(C.Structure):
                 ("res_ld", C.c_int32), ("res_coff", C.c_int32), ("relu", C.c_int32), ("stats", C.c_void_p)]
 
 
+class BnBwdFuse(C.Structure):
+    """SfbBnBwdFuse (include/sfb200.h): BatchNorm(+ReLU) backward reduction fused into the dgrad epilogue"""
+    _fields_ = [("y", C.c_void_p), ("y_ld", C.c_int32), ("y_coff", C.c_int32), ("scale", C.c_void_p),
+                ("shift", C.c_void_p), ("mean", C.c_void_p), ("invstd", C.c_void_p), ("dgamma", C.c_void_p),
+                ("dbeta", C.c_void_p), ("C", C.c_int32), ("fold_ld", C.c_int32)]
+
+
 _i32, _i64, _u64, _f32, _vp = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_void_p
 
 
@@ -70,6 +77,7 @@ SIGNATURES = {
     "sfb_pack_weight": [_vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_layout_input": [_vp, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _vp],
     "sfb_conv_gemm": [C.POINTER(ConvGeom), _vp, C.POINTER(Prologue), _vp, _i32, _i32, _vp, C.POINTER(Epilogue), _i32, _vp],
+    "sfb_conv_dgrad_bn": [C.POINTER(ConvGeom), _vp, _vp, _i32, _i32, _vp, C.POINTER(BnBwdFuse), _vp],
     "sfb_conv_wgrad": [C.POINTER(ConvGeom), _vp, C.POINTER(Prologue), _vp, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_bn_finalize": [_vp, _i32, _i64, _vp, _vp, _f32, _f32, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "sfb_bn_fold": [_vp, _vp, _vp, _vp, _f32, _i32, _vp, _vp, _vp],
@@ -109,6 +117,7 @@ _SPECIAL = {
     "sfb_last_cuda_error": ([], C.c_char_p),
     "sfb_version": ([], _i32),
     "sfb_launch_count": ([], _i64),
+    "sfb_launch_count_add": ([_i64], _i64),
     "sfb_stem_s2d_channels": ([_i32], _i32),
     "sfb_pack_table_bytes": ([_i32], _i64),
     "sfb_adam_table_bytes": ([_i32], _i64),

@@ -189,6 +189,11 @@ __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
   f[4] = bf16lo_to_f32(q.z); f[5] = bf16hi_to_f32(q.z);
   f[6] = bf16lo_to_f32(q.w); f[7] = bf16hi_to_f32(q.w);
 }
+__device__ __forceinline__ void load8f(const float* p, float* f) {
+  const float4 a = *reinterpret_cast<const float4*>(p);
+  const float4 b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+}
 __device__ __forceinline__ uint4 pack8(const float* f) {
   uint4 q;
   q.x = pack_bf16x2(f[0], f[1]); q.y = pack_bf16x2(f[2], f[3]);

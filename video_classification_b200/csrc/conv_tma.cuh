@@ -74,6 +74,22 @@ struct ConvTmaParams {
   int reduce_add;              // 1: the TMA store is a reduce-add into the output (in-place gradient accumulation)
   uint32_t stg2_off;           // byte offset of a second staging tile (0: single buffer): the TMA store of chunk k drains
                                // while chunk k+1 is converted and staged
+  int nstages;                 // pipeline stages in use (<= ConvTmaCfg::kStages; one fewer when the y tile of the
+                               // BatchNorm-backward epilogue takes the last stage's shared memory)
+  // ---- fused BatchNorm(+ReLU) backward reduction (sfb_conv_dgrad_bn): this launch produces dz of a conv -> BN -> ReLU
+  //      layer; the epilogue fetches the matching tile of the layer's raw output y by TMA (tmap_y, same boxes as the
+  //      output store), masks the gradient where the forward ReLU was off, stores the MASKED gradient g and
+  //      accumulates dbeta += sum g, dgamma += invstd * sum g*(y - mean) -- the separate bn_bwd_reduce pass (two
+  //      tensor reads) disappears.
+  int bn_mode;                 // 0: off, 1: mask recomputed from y*scale+shift > 0
+  uint32_t ybuf_off;           // byte offset of the y tile (one staging tile)
+  const float* bn_scale;
+  const float* bn_shift;
+  const float* bn_mean;
+  const float* bn_invstd;
+  float* bn_dgamma;
+  float* bn_dbeta;
+  int bn_C, bn_ld;             // real channels; channel of output column j = j % bn_ld (pixel-folded launches)
 };
 
 __device__ __forceinline__ void tma_store_5d(const void* tmap, uint32_t smem_src, int32_t c0, int32_t c1, int32_t c2,
@@ -144,7 +160,7 @@ struct ConvTmaCfg {
   static constexpr int kStagingOff = kStages * kStage;
   static constexpr int kStagingBytes = 128 * kChunk * 2;
   static constexpr int kBarOff = kStagingOff + kStagingBytes;          // full[S], empty[S], tfull[2], tempty[2]
-  static constexpr int kHolderOff = kBarOff + (2 * kStages + 5) * 8;   // + bres
+  static constexpr int kHolderOff = kBarOff + (2 * kStages + 6) * 8;   // + bres, ybar
   static constexpr int kEnd = kHolderOff + 16;
   static constexpr int kBResOff = (kEnd + 1023) / 1024 * 1024;        // resident weights: nk blocks of [BN][128 B]
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
@@ -159,16 +175,19 @@ struct ConvTmaCfg {
 template <int BN, bool BRES = false>
 __global__ void __launch_bounds__(ConvTmaCfg<BN, BRES>::kThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-                const __grid_constant__ CUtensorMap tmap_o, const ConvTmaParams p) {
+                const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_y,
+                const ConvTmaParams p) {
   using L = ConvTmaCfg<BN, BRES>;
-  constexpr int S = L::kStages;
+  constexpr int SMAX = L::kStages;
+  const int S = p.nstages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
-  uint64_t* empty_bar = full_bar + S;
-  uint64_t* tfull_bar = empty_bar + S;
+  uint64_t* empty_bar = full_bar + SMAX;
+  uint64_t* tfull_bar = empty_bar + SMAX;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* bres_bar = tempty_bar + 2;
+  uint64_t* y_bar = bres_bar + 1;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(smem + L::kHolderOff);
 
   const int tid = threadIdx.x;
@@ -176,7 +195,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const int lane = tid & 31;
 
   if (tid == 0) {
-    for (int s = 0; s < S; ++s) {
+    for (int s = 0; s < SMAX; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
@@ -185,12 +204,20 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       mbar_init(&tempty_bar[b], L::kEpiWarps);
     }
     mbar_init(bres_bar, 1);
+    mbar_init(y_bar, 1);
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_w);
     tma_prefetch_desc(&tmap_o);
+    if (p.bn_mode) tma_prefetch_desc(&tmap_y);
+  }
+  if (p.bn_mode) {
+    // rows of the y tile a box never writes (patches of fewer than 128 pixels) must read as finite numbers
+    for (int i = tid; i < L::kStagingBytes / 16; i += L::kThreads)
+      reinterpret_cast<uint4*>(smem + p.ybuf_off)[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async_smem();
   }
   if (warp == 2) {
     tmem_alloc(tmem_holder, L::kTmemCols);
@@ -349,6 +376,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       toff[j] = o ^ (((o >> 7) & swz) << 4);
     }
     const bool want_stats = p.stats != nullptr;
+    const bool bnred = p.bn_mode != 0;
+    const uint32_t ybuf = smem_u32(smem) + p.ybuf_off;
+    uint32_t yphase = 0;
     bool store_pending = false;
     int it = 0;
     PatchWalk pw;
@@ -368,12 +398,20 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         if (ch <= last_ch) {
           const int col0 = n0 + ch * CH;
           // (A) the TMA store that last used this staging tile must have finished reading it
-          const uint32_t stg = (nstaged & 1) ? stg_b : stg_a;
+          const uint32_t stg = (!bnred && (nstaged & 1)) ? stg_b : stg_a;
           ++nstaged;
           if (te == 0 && store_pending) {
-            if (p.stg2_off) tma_store_wait_read1(); else tma_store_wait_read();
+            if (p.stg2_off && !bnred) tma_store_wait_read1(); else tma_store_wait_read();
           }
           named_bar_sync(1, ET);
+          if (bnred && te == 0) {
+            // the y tile of this chunk travels while the accumulator is converted and staged (every epilogue thread
+            // is past its reads of the previous y tile: they all arrived at the barrier above)
+            const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
+            mbar_arrive_expect_tx(y_bar, (uint32_t)nsub * (uint32_t)rows * rb);
+            for (int gsub = 0; gsub < nsub; ++gsub)
+              tma_load_5d(ybuf + gsub * sub_bytes, &tmap_y, y_bar, col0 + gsub * ocols, w0, h0, t0, n);
+          }
           // (B) accumulator -> staging: this warp's 32-column slice
           {
             const int nb = col0 + cslice * 32;
@@ -428,6 +466,39 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[buf]);
           }
+          // (C') fused BatchNorm(+ReLU) backward reduction: epilogue warp e owns the 8-column group e of the chunk, its
+          //      lanes split the 128 rows (as in (E)); the staged gradient is masked IN PLACE before it is stored
+          if (bnred) {
+            named_bar_sync(1, ET);                       // the whole gradient tile is staged
+            mbar_wait(y_bar, yphase, 16);
+            yphase ^= 1;
+            const int cg = col0 + (warp - 2) * 8;
+            if (cg < p.Co) {
+              const int cb = cg % p.bn_ld;               // channel of this thread's first column
+              float sc[8], sh[8], mu[8];
+              if (cb < p.bn_C) {                         // C is a multiple of 8: the group is real or pad as a whole
+                load8f(p.bn_scale + cb, sc);
+                load8f(p.bn_shift + cb, sh);
+                load8f(p.bn_mean + cb, mu);
+              } else {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) { sc[c] = 0.f; sh[c] = 0.f; mu[c] = 0.f; }
+              }
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                float g[8], yv[8];
+                unpack8(lds_v4(stg + toff[i]), g);
+                unpack8(lds_v4(ybuf + toff[i]), yv);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                  g[c] = fmaf(yv[c], sc[c], sh[c]) > 0.f ? g[c] : 0.f;
+                  ssum[ch][c] += g[c];
+                  ssq[ch][c] = fmaf(g[c], yv[c] - mu[c], ssq[ch][c]);
+                }
+                sts_v4(stg + toff[i], pack8(g));
+              }
+            }
+          }
           // (D) staged tile -> global memory (TMA clips rows/columns outside the tensor)
           fence_proxy_async_smem();
           named_bar_sync(1, ET);
@@ -460,6 +531,26 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       }
     }
     if (te == 0 && store_pending) tma_store_wait_all();
+    if (bnred) {
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        const int col = n0 + ch * CH + (warp - 2) * 8;
+        const int cb = col % p.bn_ld;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float a = ssum[ch][c], b = ssq[ch][c];
+#pragma unroll
+          for (int off = 16; off >= 1; off >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, off);
+            b += __shfl_xor_sync(0xffffffffu, b, off);
+          }
+          if (lane == c && ch <= last_ch && col < p.Co && cb < p.bn_C) {
+            atomicAdd(p.bn_dbeta + cb + c, a);
+            atomicAdd(p.bn_dgamma + cb + c, b * __ldg(p.bn_invstd + cb + c));
+          }
+        }
+      }
+    }
     if (p.stats) {
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {

@@ -21,11 +21,6 @@ __device__ __forceinline__ uint4 vload(const View& v, long long m, int c) {
 __device__ __forceinline__ void vstore(const ViewW& v, long long m, int c, const uint4& q) {
   *reinterpret_cast<uint4*>(v.p + (size_t)m * v.ld + v.coff + c) = q;
 }
-__device__ __forceinline__ void load8f(const float* p, float* f) {
-  const float4 a = *reinterpret_cast<const float4*>(p);
-  const float4 b = *reinterpret_cast<const float4*>(p + 4);
-  f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
-}
 
 // ---- input layout: fp32 strided NCTHW -> bf16 NDHWC (channels zero padded to ld) ----------------
 __global__ void layout_input_kernel(const float* __restrict__ x, long long sn, long long sc, long long st,

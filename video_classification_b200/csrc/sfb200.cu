@@ -334,17 +334,25 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
 }
 
 template <int BN, bool BRES>
-int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
-                         cudaStream_t st) {
+int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
+                         const ConvTmaParams& p, cudaStream_t st) {
   using L = ConvTmaCfg<BN, BRES>;
   const size_t smem = L::smem_bytes(p.nk);
   // second staging tile behind everything else when it still fits
   ConvTmaParams pp = p;
   size_t smem_total = smem;
   const size_t stg2 = (smem - 1024 + 1023) / 1024 * 1024;  // swizzled tile: 1024-byte aligned
+  pp.nstages = L::kStages;
   if (1024 + stg2 + L::kStagingBytes <= 227 * 1024) {
     pp.stg2_off = (uint32_t)stg2;
     smem_total = 1024 + stg2 + L::kStagingBytes;
+    pp.ybuf_off = pp.stg2_off;   // fused BatchNorm backward: the second tile holds y (stores are single-buffered)
+  } else if (p.bn_mode) {
+    // no room for another tile: the y tile takes the shared memory of the last pipeline stage(s)
+    const int drop = (L::kStagingBytes + L::kStage - 1) / L::kStage;
+    if (L::kStages - drop < 2) return SFB_ERR_UNSUPPORTED;
+    pp.nstages = L::kStages - drop;
+    pp.ybuf_off = (uint32_t)(pp.nstages * L::kStage);
   }
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
   long long per_nt = num_sms() / p.n_tiles;
@@ -357,17 +365,27 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
     attr_bytes = smem_total;
   }
-  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, pp);
+  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, ty, pp);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
 
 template <int BN>
-int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const ConvTmaParams& p,
-                    cudaStream_t st) {
+int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
+                    const ConvTmaParams& p, cudaStream_t st) {
   // weights resident in shared memory when the CTA's [BN][Ktot] slice fits next to the pipeline (see ConvTmaCfg)
-  if (ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024) return launch_conv_tma_impl<BN, true>(ta, tw, to, p, st);
-  return launch_conv_tma_impl<BN, false>(ta, tw, to, p, st);
+  if (ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024) return launch_conv_tma_impl<BN, true>(ta, tw, to, ty, p, st);
+  return launch_conv_tma_impl<BN, false>(ta, tw, to, ty, p, st);
+}
+
+// ConvTmaParams fields of the fused BatchNorm-backward epilogue (sfb_conv_dgrad_bn)
+void set_bn_fuse(ConvTmaParams& q, const SfbBnBwdFuse* bn, int Co) {
+  if (!bn) return;
+  q.bn_mode = 1;
+  q.bn_scale = bn->scale; q.bn_shift = bn->shift; q.bn_mean = bn->mean; q.bn_invstd = bn->invstd;
+  q.bn_dgamma = bn->dgamma; q.bn_dbeta = bn->dbeta;
+  q.bn_C = bn->C;
+  q.bn_ld = bn->fold_ld > 0 ? bn->fold_ld : Co;
 }
 
 // Can the TMA kernel take this conv?  (everything else stays on the register-gather kernel)
@@ -416,6 +434,7 @@ const char* sfb_strerror(int status) {
 const char* sfb_last_cuda_error(void) { return g_cuda_err; }
 int sfb_version(void) { return 100; }
 int64_t sfb_launch_count(void) { return (int64_t)g_launches.load(); }
+int64_t sfb_launch_count_add(int64_t n) { return (int64_t)(g_launches.fetch_add(n > 0 ? n : 0) + (n > 0 ? n : 0)); }
 
 int sfb_packed_weight_dims(int32_t Co, int32_t Cg, int32_t taps, int32_t* rows_pad, int32_t* k_pad) {
   if (Co <= 0 || Cg <= 0 || (Cg & 7) || taps <= 0 || !rows_pad || !k_pad) return SFB_ERR_BAD_ARG;
@@ -777,8 +796,33 @@ int sfb_stem_conv_wgrad(const void* xs2d, int32_t N, int32_t T, int32_t H2, int3
   }
 }
 
+}  // extern "C"
+namespace {
+int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro, const void* wp, int32_t rows_pad,
+                   int32_t k_pad, void* out, const SfbEpilogue* epi, int32_t impl, void* stream, const SfbBnBwdFuse* bn);
+}
+extern "C" {
 int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro, const void* wp, int32_t rows_pad,
                   int32_t k_pad, void* out, const SfbEpilogue* epi, int32_t impl, void* stream) {
+  return conv_gemm_impl(geom, g, pro, wp, rows_pad, k_pad, out, epi, impl, stream, nullptr);
+}
+
+int sfb_conv_dgrad_bn(const SfbConvGeom* geom, const void* g, const void* wp, int32_t rows_pad, int32_t k_pad, void* out,
+                      const SfbBnBwdFuse* bn, void* stream) {
+  if (!geom || !bn || !geom->transposed) return SFB_ERR_BAD_ARG;
+  if (!bn->y || !aligned16(bn->y) || !bn->scale || !bn->shift || !bn->mean || !bn->invstd || !bn->dgamma || !bn->dbeta)
+    return SFB_ERR_BAD_ARG;
+  if (bn->C <= 0 || (bn->C & 7) || (bn->y_ld & 7) || (bn->y_coff & 7) || bn->y_coff + geom->Co > bn->y_ld) return SFB_ERR_BAD_ARG;
+  if (bn->fold_ld < 0 || (bn->fold_ld & 7) || (bn->fold_ld > 0 && (geom->Co % bn->fold_ld || bn->C > bn->fold_ld)))
+    return SFB_ERR_BAD_ARG;
+  if (bn->fold_ld == 0 && bn->C > geom->Co) return SFB_ERR_BAD_ARG;
+  return conv_gemm_impl(geom, g, nullptr, wp, rows_pad, k_pad, out, nullptr, SFB_IMPL_TC, stream, bn);
+}
+}  // extern "C"
+
+namespace {
+int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro, const void* wp, int32_t rows_pad,
+                   int32_t k_pad, void* out, const SfbEpilogue* epi, int32_t impl, void* stream, const SfbBnBwdFuse* bn) {
   int rc = check_geom(geom);
   if (rc) return rc;
   if (!g || !wp || !out || !aligned16(g) || !aligned16(wp) || !aligned16(out)) return SFB_ERR_BAD_ARG;
@@ -805,6 +849,7 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
   p.Ktot = taps * geom->Cg;
   p.nk = k_pad / 64;
   cudaStream_t st = (cudaStream_t)stream;
+  if (bn && impl != SFB_IMPL_TC) return SFB_ERR_UNSUPPORTED;
   if (impl == SFB_IMPL_SIMT) {
     ConvSimtParams q;
     q.c = p; q.wp = (const __nv_bfloat16*)wp; q.k_pad = k_pad;
@@ -817,10 +862,10 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
   }
   if (impl != SFB_IMPL_TC && impl != SFB_IMPL_TC_GATHER) return SFB_ERR_BAD_ARG;
   if (geom->Cg > 2048) return SFB_ERR_UNSUPPORTED;
-  const int bn = pick_bn(geom->Co);
-  if (rows_pad % bn) return SFB_ERR_BAD_ARG;
+  const int bnt = pick_bn(geom->Co);
+  if (rows_pad % bnt) return SFB_ERR_BAD_ARG;
   CUtensorMap tm;
-  rc = get_weight_tmap(wp, rows_pad, k_pad, bn, &tm);
+  rc = get_weight_tmap(wp, rows_pad, k_pad, bnt, &tm);
   if (rc) return rc;
   const bool strided_dgrad = geom->transposed && (geom->sT != 1 || geom->sH != 1 || geom->sW != 1);
   if (impl == SFB_IMPL_TC && strided_dgrad) {
@@ -864,7 +909,7 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
       q.taps = c.taps; q.Ktot = c.taps * geom->Cg; q.nk = (q.Ktot + 63) / 64; q.wk0 = c.k0;
       pick_patch(q.Wo, q.Ho, q.To, 1, 1, 1, &q.Wt, &q.Ht, &q.Tt);
       q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
-      q.n_tiles = (geom->Co + bn - 1) / bn;
+      q.n_tiles = (geom->Co + bnt - 1) / bnt;
       q.total_patches = q.N * q.tilesT * q.tilesH * q.tilesW;
       q.ocols = geom->Co >= 64 ? 64 : (geom->Co >= 32 ? 32 : (geom->Co >= 16 ? 16 : 8));
       q.out = p.out;
@@ -884,11 +929,24 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
       CUtensorMap to;
       rc = get_tmap_generic(obase, 5, od, os, ob, q.ocols * 2 >= 128 ? 128 : q.ocols * 2, &to);
       if (rc) return rc;
-      switch (bn) {
-        case 32: rc = launch_conv_tma<32>(ta, tm, to, q, st); break;
-        case 64: rc = launch_conv_tma<64>(ta, tm, to, q, st); break;
-        case 128: rc = launch_conv_tma<128>(ta, tm, to, q, st); break;
-        default: rc = launch_conv_tma<256>(ta, tm, to, q, st); break;
+      CUtensorMap ty = to;
+      if (bn) {
+        // the class's sub-lattice of y: the same strided 5-D tensor on the y view
+        if (accumulate) return SFB_ERR_UNSUPPORTED;
+        const long long yld2 = (long long)bn->y_ld * 2;
+        const __nv_bfloat16* ybase = (const __nv_bfloat16*)bn->y + bn->y_coff +
+                                     (((long long)o0[0] * geom->Ho + o0[1]) * geom->Wo + o0[2]) * bn->y_ld;
+        const long long ys[4] = {s[2] * yld2, (long long)s[1] * geom->Wo * yld2, (long long)s[0] * geom->Ho * geom->Wo * yld2,
+                                 (long long)geom->To * geom->Ho * geom->Wo * yld2};
+        rc = get_tmap_generic(ybase, 5, od, ys, ob, q.ocols * 2 >= 128 ? 128 : q.ocols * 2, &ty);
+        if (rc) return rc;
+        set_bn_fuse(q, bn, geom->Co);
+      }
+      switch (bnt) {
+        case 32: rc = launch_conv_tma<32>(ta, tm, to, ty, q, st); break;
+        case 64: rc = launch_conv_tma<64>(ta, tm, to, ty, q, st); break;
+        case 128: rc = launch_conv_tma<128>(ta, tm, to, ty, q, st); break;
+        default: rc = launch_conv_tma<256>(ta, tm, to, ty, q, st); break;
       }
       if (rc) return rc;
     }
@@ -918,7 +976,7 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     if (geom->Cg >= 64 && q.cchunks * taps != q.nk) return SFB_ERR_BAD_ARG;
     pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt);
     q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
-    q.n_tiles = (geom->Co + bn - 1) / bn;
+    q.n_tiles = (geom->Co + bnt - 1) / bnt;
     const long long tt = (long long)q.N * q.tilesT * q.tilesH * q.tilesW;
     if (tt >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
     q.total_patches = (int)tt;
@@ -939,20 +997,31 @@ int sfb_conv_gemm(const SfbConvGeom* geom, const void* g, const SfbPrologue* pro
     rc = get_act_tmap((const __nv_bfloat16*)out + geom->o_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, geom->o_ld, q.ocols, q.Wt,
                       q.Ht, q.Tt, 1, 1, 1, &to);
     if (rc) return rc;
-    switch (bn) {
-      case 32: return launch_conv_tma<32>(ta, tm, to, q, st);
-      case 64: return launch_conv_tma<64>(ta, tm, to, q, st);
-      case 128: return launch_conv_tma<128>(ta, tm, to, q, st);
-      default: return launch_conv_tma<256>(ta, tm, to, q, st);
+    CUtensorMap ty = to;
+    if (bn) {
+      if (q.reduce_add || q.res || q.epi_scale || q.epi_relu || q.stats) return SFB_ERR_UNSUPPORTED;
+      rc = get_act_tmap((const __nv_bfloat16*)bn->y + bn->y_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, bn->y_ld, q.ocols, q.Wt,
+                        q.Ht, q.Tt, 1, 1, 1, &ty);
+      if (rc) return rc;
+      set_bn_fuse(q, bn, geom->Co);
+    }
+    switch (bnt) {
+      case 32: return launch_conv_tma<32>(ta, tm, to, ty, q, st);
+      case 64: return launch_conv_tma<64>(ta, tm, to, ty, q, st);
+      case 128: return launch_conv_tma<128>(ta, tm, to, ty, q, st);
+      default: return launch_conv_tma<256>(ta, tm, to, ty, q, st);
     }
   }
-  switch (bn) {
+  if (bn) return SFB_ERR_UNSUPPORTED;
+  switch (bnt) {
     case 32: return launch_conv_tc<32, 4>(tm, p, st);
     case 64: return launch_conv_tc<64, 4>(tm, p, st);
     case 128: return launch_conv_tc<128, 3>(tm, p, st);
     default: return launch_conv_tc<256, 4>(tm, p, st);
   }
 }
+}  // namespace
+extern "C" {
 
 namespace {
 struct WgradFold { int f, ldo, ldi, kW, Co, Ci; };

@@ -122,6 +122,11 @@ class Plan:
         self.bn_flat = None   # this plan's BatchNorm scratch (SlowFastEngine._bind_bn_arena)
         self.stats_flat = None
         self.gen = 0  # bumped by every training forward; backward checks it saw the latest one
+        # CUDA graphs of the two op lists (SlowFastEngine._graphed): {"fwd"|"bwd": (CUDAGraph, kernels per replay)},
+        # eager runs so far, and whether a capture failed (then the list keeps running eagerly)
+        self.graphs = {}
+        self.graph_runs = {"fwd": 0, "bwd": 0}
+        self.graph_failed = {}
 
 
 class SlowFastEngine:
@@ -144,6 +149,14 @@ class SlowFastEngine:
         self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
         self.step_seed = 0
         self.ddp = None  # set by parallel.attach_ddp
+        # BatchNorm backward reduction fused into the producing dgrad's epilogue (SFB_NO_BN_FUSE=1: separate passes)
+        import os as _os
+        self.fuse_bn_reduce = not _os.environ.get("SFB_NO_BN_FUSE")
+        self.graph_failed_all = False
+        self.graph_errors = []
+        # static op lists replayed as CUDA graphs from the third run of a plan on (SFB_GRAPHS=0: always eager launches)
+        self.use_graphs = _os.environ.get("SFB_GRAPHS", "1") != "0"
+        self.graph_after = 2
         self.prof = None     # list: bench.py sets it to time every plan entry with CUDA events
         self.capture = None  # dict: tools/layer_diag.py sets it to snapshot tagged intermediates (debug only)
         self._collect_layers()
@@ -436,10 +449,12 @@ class SlowFastEngine:
         lst.append((fn, args, tag))
 
     def _conv(self, plan, lst, L: ConvL, x: Act, pro, out: Act, *, stats=False, transposed=False, residual: Act = None,
-              wp=None, tag=None, epi=None):
+              wp=None, tag=None, epi=None, bnred=None):
         """x is gathered with its channel count rounded up to 16 (the pad lanes of every buffer are zero); a dgrad
         (transposed) writes the full padded width of its output so those lanes stay zero in recycled buffers.
-        epi = (scale, shift, relu): folded-BatchNorm epilogue (eval mode)."""
+        epi = (scale, shift, relu): folded-BatchNorm epilogue (eval mode).
+        bnred = (Lb, y): this dgrad produces the gradient reaching layer Lb's ReLU(BatchNorm(y)); the epilogue masks it
+        with the forward ReLU and accumulates Lb's dgamma / dbeta (sfb_conv_dgrad_bn) -- no bn_bwd_reduce pass."""
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = out.dims
@@ -468,6 +483,16 @@ class SlowFastEngine:
         g.real_n = L.Ci if transposed else L.Co
         g.real_m = N * Ti * Hi * Wi if transposed else N * To * Ho * Wo  # rows of the forward conv's output
         plan.keep += [g, pr, ep]
+        if bnred is not None:
+            Lb, y = bnred
+            assert transposed and residual is None and y.dims == out.dims and y.ld == out.ld and y.coff == out.coff
+            fz = _ffi.BnBwdFuse(y.ptr(), f * y.ld if f > 1 else y.ld, y.coff, Lb.scale.data_ptr(), Lb.shift.data_ptr(),
+                                Lb.mean.data_ptr(), Lb.invstd.data_ptr(), Lb.dgamma.data_ptr(), Lb.dbeta.data_ptr(),
+                                Lb.Co, y.ld if f > 1 else 0)
+            plan.keep.append(fz)
+            self._emit(lst, self.lib.sfb_conv_dgrad_bn, C.byref(g), x.ptr(), wp.data_ptr(), wp.shape[0], wp.shape[1],
+                       out.ptr(), C.byref(fz), self.stream, tag=tag)
+            return
         self._emit(lst, self.lib.sfb_conv_gemm, C.byref(g), x.ptr(), C.byref(pr), wp.data_ptr(), wp.shape[0], wp.shape[1],
                    out.ptr(), C.byref(ep), self.impl, self.stream,
                    tag=tag if tag is not None else (None if transposed else (L.conv_name + ".y", out)))
@@ -530,9 +555,12 @@ class SlowFastEngine:
                        bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
 
     def _bn_bwd(self, plan, lst, L: ConvL, dz: Act, y: Act, mask, dy: Act, g_out: Optional[Act] = None,
-                g_acc=False, do_reduce=True):
+                g_acc=False, do_reduce=True, premasked=False):
         """mask: None (ReLU mask recomputed from y), an Act (sign of that tensor) or a uint8 tensor (packed bits
-        written by the forward residual tail)"""
+        written by the forward residual tail).  premasked: dz already is the masked gradient and dgamma / dbeta are
+        complete (the producing dgrad ran with the fused reduction, _conv(bnred=...)): only the apply pass remains."""
+        if premasked:
+            do_reduce = False
         bn = L.bn
         if isinstance(mask, torch.Tensor):
             m = (0, 0, 0, mask.data_ptr())
@@ -545,8 +573,8 @@ class SlowFastEngine:
         go = (g_out.ptr(), g_out.ld, g_out.coff) if g_out is not None else (0, 0, 0)
         self._emit(lst, self.lib.sfb_bn_bwd_apply, dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, *m,
                    L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(), L.invstd.data_ptr(), bn.weight.data_ptr(),
-                   L.dgamma.data_ptr(), L.dbeta.data_ptr(), 1, y.M, y.C, dy.ptr(), dy.ld, dy.coff, *go, int(g_acc),
-                   self.stream, tag=(L.conv_name + ".dy", dy))
+                   L.dgamma.data_ptr(), L.dbeta.data_ptr(), 0 if premasked else 1, y.M, y.C, dy.ptr(), dy.ld, dy.coff, *go,
+                   int(g_acc), self.stream, tag=(L.conv_name + ".dy", dy))
         if self.ddp is not None:
             self.ddp.note_grad_ready(plan, lst, bn.weight)
             self.ddp.note_grad_ready(plan, lst, bn.bias)
@@ -844,14 +872,17 @@ class SlowFastEngine:
                 X.ginit = True
             self._wgrad(plan, bwd, c, zb, None, dyc)
             dzb = new_grad(yb)
-            self._conv(plan, bwd, c, dyc, None, dzb, transposed=True)
+            # the dgrad that produces dz of conv_b / conv_a also masks it with the layer's forward ReLU and reduces its
+            # BatchNorm's dgamma / dbeta in the epilogue (the y tile arrives by TMA): bn_bwd_reduce is gone here
+            fuse = self.fuse_bn_reduce and self.impl == _ffi.IMPL_TC
+            self._conv(plan, bwd, c, dyc, None, dzb, transposed=True, bnred=(b, yb) if fuse else None)
             pool.release(dyc.buf)
-            self._bn_bwd(plan, bwd, b, dzb, yb, None, dzb)  # mask = (y*scale+shift > 0), recomputed: one tensor read less
+            self._bn_bwd(plan, bwd, b, dzb, yb, None, dzb, premasked=fuse)  # in place: masked dz -> dy
             self._wgrad(plan, bwd, b, za, None, dzb)
             dza = new_grad(ya)
-            self._conv(plan, bwd, b, dzb, None, dza, transposed=True)
+            self._conv(plan, bwd, b, dzb, None, dza, transposed=True, bnred=(a, ya) if fuse else None)
             pool.release(dzb.buf)
-            self._bn_bwd(plan, bwd, a, dza, ya, None, dza)
+            self._bn_bwd(plan, bwd, a, dza, ya, None, dza, premasked=fuse)
             self._wgrad(plan, bwd, a, X.act, None, dza)
             # conv_a (stride 1) writes every pixel of dX first; the strided shortcut then only touches its own
             # sub-lattice with a reduce-add (no zero fill of the pixels a stride-2 conv never reads)
@@ -891,6 +922,49 @@ class SlowFastEngine:
         return plan
 
     # ------------------------------------------------------------------ execution
+    def _graphed(self, plan: Plan, which: str, body) -> bool:
+        """Run one op list (`body()` enqueues it on the current stream: the ~350 C-ABI launches of a forward or
+        backward pass plus the arena zero fills and, under data parallelism, the bucket all-reduces on the side stream)
+        as a CUDA graph.  Every buffer, tensor map and kernel argument of a plan is static, so the list is captured once
+        -- at the third run of the plan, after the kernels' one-time attribute calls -- and replayed afterwards: one
+        graph launch instead of several hundred stream launches, no per-kernel launch gap on the device.  What changes
+        from step to step stays outside: input layout (caller's pointers), the dropout seed word, dlogits.
+        Returns False when the list must run eagerly (profiling / debug capture, gloo, a failed capture)."""
+        if not self.use_graphs or self.dry_run or self.prof is not None or self.capture is not None:
+            return False
+        if self.graph_failed_all or plan.graph_failed.get(which):
+            return False
+        if self.ddp is not None and not self.ddp.bucketer.use_avg:  # host-driven collectives (gloo) cannot be captured
+            return False
+        hit = plan.graphs.get(which)
+        if hit is None:
+            plan.graph_runs[which] += 1
+            if plan.graph_runs[which] <= self.graph_after:
+                return False
+            cur = torch.cuda.current_stream(self.dev)
+            side = torch.cuda.Stream(self.dev)
+            side.wait_stream(cur)
+            g = torch.cuda.CUDAGraph()
+            k0 = _ffi.launch_count()
+            saved = self.stream.value
+            try:
+                with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                    self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
+                    body()
+            except Exception as e:  # noqa: BLE001 -- capture is an optimisation: fall back to stream launches
+                plan.graph_failed[which] = True
+                self.graph_errors.append(f"{which}: {type(e).__name__}: {e}")
+                self.stream.value = saved
+                torch.cuda.synchronize(self.dev)
+                return False
+            self.stream.value = saved
+            cur.wait_stream(side)
+            hit = plan.graphs[which] = (g, _ffi.launch_count() - k0)
+        g, nk = hit
+        g.replay()
+        self.lib.sfb_launch_count_add(nk)
+        return True
+
     def _run(self, ops):
         cap = self.capture
         if self.prof is not None:
@@ -1108,10 +1182,16 @@ class SlowFastEngine:
     def _forward_staged(self, plan: Plan, training: bool) -> Tuple[torch.Tensor, Plan]:
         if training:
             plan.gen += 1
-            plan.stats_flat.zero_()
             if self.dropout_p > 0.0:
                 plan.seed_dev.fill_(self._draw_dropout_seed())
-        self._run(plan.fwd)
+
+        def body():
+            if training:
+                plan.stats_flat.zero_()
+            self._run(plan.fwd)
+
+        if not self._graphed(plan, "fwd", body):
+            body()
         if training:
             torch._foreach_add_([bn.num_batches_tracked for bn in self.bn_modules], 1)
         return plan.logits, plan
@@ -1136,12 +1216,17 @@ class SlowFastEngine:
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
         plan.dlogits.copy_(dlogits)
         self._bwd_since_pack = True  # an optimizer step may follow: see refresh_weights
-        self.grad_flat.zero_()
-        if self.ddp is not None:
-            self.ddp.begin_backward(self)
-        self._run(plan.bwd)
-        if self.ddp is not None:
-            self.ddp.finish_backward(self)
+
+        def body():
+            self.grad_flat.zero_()
+            if self.ddp is not None:
+                self.ddp.begin_backward(self)
+            self._run(plan.bwd)
+            if self.ddp is not None:
+                self.ddp.finish_backward(self)
+
+        if not self._graphed(plan, "bwd", body):
+            body()
         return [self.grad_views[id(p)] for p in self.live_params]
 
 

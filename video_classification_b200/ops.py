@@ -239,6 +239,19 @@ def conv_gemm(x: Act, wp: torch.Tensor, out: Act, k, s, p, *, transposed=False,
     return out
 
 
+def conv_dgrad_bn(dy: Act, wpt: torch.Tensor, out: Act, k, s, p, y: Act, scale, shift, mean, invstd, dgamma, dbeta,
+                  C_real: Optional[int] = None, fold_ld: int = 0):
+    """out = masked input gradient of a conv whose INPUT was relu(BatchNorm(y)); dgamma / dbeta (fp32 [C]) accumulate the
+    BatchNorm backward sums (sfb_conv_dgrad_bn).  y has the dims and view layout of `out`."""
+    g = make_geom(dy, out, k, s, p, True)
+    assert y.dims == out.dims
+    fz = _ffi.BnBwdFuse(y.ptr(), y.ld, y.coff, ptr(scale), ptr(shift), ptr(mean), ptr(invstd), ptr(dgamma), ptr(dbeta),
+                        int(C_real if C_real is not None else out.C), int(fold_ld))
+    check(lib().sfb_conv_dgrad_bn(C.byref(g), dy.ptr(), wpt.data_ptr(), wpt.shape[0], wpt.shape[1], out.ptr(), C.byref(fz),
+                                  stream_ptr()), "sfb_conv_dgrad_bn")
+    return out
+
+
 def conv_wgrad(x: Act, dy: Act, dw: torch.Tensor, k, s, p, *, pro=None, impl=_ffi.IMPL_TC):
     """dw (fp32, (Co, Ci, kT, kH, kW), contiguous) += wgrad."""
     assert dw.dtype == torch.float32 and dw.is_contiguous()
