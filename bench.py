@@ -34,6 +34,10 @@ WORKLOADS = {
                       label="reference graph as written, slowfast-LHand.yaml: slow 5x20x64^2 + fast 15x20x64^2, batch 300"),
     "ref_htah": dict(graph_kw={}, oracle="REF", ts=20, tf=20, size=192, batch=55, f_fwd=170.737, f_train=504.3,
                      label="reference graph as written, slowfast-HTAH.yaml: slow 5x20x192^2 + fast 15x20x192^2, batch 55"),
+    # BASELINE configs[0] (config/res3d.yaml): Slow-only 3D-ResNet-50 (pytorchvideo slow_r50 with the reference's 5-channel
+    # stem, train.py:79-83) on 16 x 112^2 clips, batch 2 -- the reference's own CPU-runnable case; head pool (4,4,4)
+    "res3d": dict(graph_kw={}, oracle="RES3D", ts=16, tf=0, size=112, batch=2, f_fwd=44.6045, f_train=132.240,
+                  label="config/res3d.yaml Slow-only 3D-ResNet-50 (slow_r50, 5-channel stem), 5x16x112^2, batch 2, 400 classes"),
 }
 # kept for tools/ that import them
 T_SLOW, T_FAST, SIZE = 8, 32, 224
@@ -41,6 +45,8 @@ F_FWD_GF, F_TRAIN_GF = 100.616, 293.98
 
 
 def metric_name(mode, wl):
+    if wl == "res3d":
+        return f"{'train' if mode == 'train' else 'inference'} clips/sec 3D-ResNet-50 (slow_r50) 16x112^2"
     shape = "8x8 224^2" if wl == "hyb" else f"{WORKLOADS[wl]['ts']}x{WORKLOADS[wl]['size']}^2 (reference shapes)"
     return f"{'train' if mode == 'train' else 'inference'} clips/sec SlowFast-R50 {shape}"
 
@@ -50,6 +56,8 @@ def workload_name(mode, wl):
     if wl == "hyb":
         return ("configs[2]: " + w["label"].replace("SlowFast-R50,", "SlowFast-R50 training,")) if mode == "train" else \
             ("configs[1]: " + w["label"].replace("SlowFast-R50,", "SlowFast-R50 single-part inference,"))
+    if wl == "res3d":
+        return "configs[0]: " + w["label"] + (", fwd+bwd+Adam" if mode == "train" else ", eval forward")
     return ("SURVEY 8(d) config 3 (REF shapes), training: " if mode == "train" else "SURVEY 8(d) config 2 (REF row), inference: ") + w["label"]
 
 
@@ -134,17 +142,26 @@ def cpu_steps(mode, wl, n_clips, steps, warmup, threads=None):
     threads = torch.get_num_threads()
     w = WORKLOADS[wl]
     torch.manual_seed(0)
-    model = so.build_oracle(num_class=NUM_CLASS, fuse=True, **so.VARIANTS[w["oracle"]])
-    so.randomize_bn_(model, 123, 0.1)
-    xs, xf = so.synthetic_clips(n_clips, w["ts"], w["tf"], w["size"], seed=1)
-    y = torch.randint(0, NUM_CLASS, (n_clips,), generator=torch.Generator().manual_seed(7))
+    if w["oracle"] == "RES3D":
+        model = so.build_res3d_oracle(num_class=400, input_channel=5, head_pool_kernel_size=(4, 4, 4))
+        so.randomize_bn_(model, 123, 0.1)
+        x1 = torch.randn((n_clips, 5, w["ts"], w["size"], w["size"]), generator=torch.Generator().manual_seed(1))
+        inp = x1
+        ncls = 400
+    else:
+        model = so.build_oracle(num_class=NUM_CLASS, fuse=True, **so.VARIANTS[w["oracle"]])
+        so.randomize_bn_(model, 123, 0.1)
+        xs, xf = so.synthetic_clips(n_clips, w["ts"], w["tf"], w["size"], seed=1)
+        inp = None
+        ncls = NUM_CLASS
+    y = torch.randint(0, ncls, (n_clips,), generator=torch.Generator().manual_seed(7))
     times = []
     if mode == "train":
         model.train()
         opt = torch.optim.Adam(model.parameters(), lr=1e-4)
         for it in range(warmup + steps):
             t0 = time.perf_counter()
-            out = model([xs, xf])
+            out = model(inp if inp is not None else [xs, xf])
             loss = F.cross_entropy(out, y)
             opt.zero_grad()
             loss.backward()
@@ -157,7 +174,7 @@ def cpu_steps(mode, wl, n_clips, steps, warmup, threads=None):
         with torch.no_grad():
             for it in range(warmup + steps):
                 t0 = time.perf_counter()
-                out = model([xs, xf])
+                out = model(inp if inp is not None else [xs, xf])
                 int(out.argmax(1)[0])
                 if it >= warmup:
                     times.append(time.perf_counter() - t0)
@@ -249,7 +266,13 @@ def run_gpu_arm(args):
     B = args.batch or w["batch"]
     TS, TF, S = w["ts"], w["tf"], w["size"]
     torch.manual_seed(0)
-    model = init_my_slowfast(make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **w["graph_kw"]).to(dev)
+    single = args.workload == "res3d"
+    ncls = 400 if single else NUM_CLASS
+    if single:
+        from video_classification_b200.res3d import slow_r50
+        model = slow_r50(5, ncls, (4, 4, 4)).to(dev)
+    else:
+        model = init_my_slowfast(make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **w["graph_kw"]).to(dev)
     model.train(train)
     if world > 1 and train:
         attach_ddp(model, bucket_mb=args.bucket_mb)
@@ -258,15 +281,16 @@ def run_gpu_arm(args):
     opt = Adam(model.parameters(), lr=1e-4) if train else None
     g = torch.Generator().manual_seed(1000 + rank)
     # synthetic clips, per-rank seed; resident copies for `value`, a pinned host copy for `e2e`
-    host = [torch.randn((B, 5, TS, S, S), generator=g).pin_memory(),
-            torch.randn((B, 15, TF, S, S), generator=g).pin_memory()]
-    y = torch.randint(0, NUM_CLASS, (B,), generator=g).to(dev)
+    host = [torch.randn((B, 5, TS, S, S), generator=g).pin_memory()]
+    if not single:
+        host.append(torch.randn((B, 15, TF, S, S), generator=g).pin_memory())
+    y = torch.randint(0, ncls, (B,), generator=g).to(dev)
     resident = [h.to(dev) for h in host]
     h2d_bytes = sum(h.numel() * 4 for h in host)
 
     if train:
-        def step(xs, xf):
-            out = model([xs, xf])
+        def step(*xs):
+            out = model(xs[0] if single else list(xs))
             loss = F.cross_entropy(out, y)
             opt.zero_grad()
             loss.backward()
@@ -274,10 +298,10 @@ def run_gpu_arm(args):
             return loss
         d2h_bytes = 4
     else:
-        def step(xs, xf):
+        def step(*xs):
             with torch.no_grad():
-                return model([xs, xf])
-        d2h_bytes = B * NUM_CLASS * 4
+                return model(xs[0] if single else list(xs))
+        d2h_bytes = B * ncls * 4
 
     def read_back(res):
         """device -> host read of the step's result: the loss (train.py:232) or the logits (train.py:306)"""
@@ -379,6 +403,8 @@ def run_gpu_arm(args):
 
     # ---- e2e_u8: the same step fed uint8 frames as the dataset holds them before ToTensor/Normalize:
     # (B, T, S, S, 21) uint8 from pinned host memory, normalised + split + laid out by sfb_stage_clips_u8 ----
+    if single:  # the uint8 staging kernel feeds the two SlowFast stems; the res3d loader path has no such split
+        return r
     from video_classification_b200.staging import RawClips
     host_u8 = [torch.randint(0, 256, (B, TF, S, S, 21), generator=g, dtype=torch.uint8).pin_memory()]
     dbuf_u8 = [[torch.empty_like(h, device=dev) for h in host_u8] for _ in range(2)]
@@ -584,7 +610,7 @@ def main():
     if adam is not None:
         line["optimizer_step"] = adam
     lib = library_baseline_from_profiles()
-    if lib is not None and args.workload == "hyb":
+    if lib is not None and args.workload == "hyb" and train:
         line["library_baseline"] = lib
     if world == 1 and not args.no_cpu_baseline:
         if _ORIG_AFFINITY:

@@ -473,3 +473,51 @@ def create_slowfast(
                            output_size=head_output_size, dropout_rate=dropout_rate, activation=head_activation,
                            output_with_global_average=head_output_with_global_average))
     return Net(blocks=nn.ModuleList(stages))
+
+
+# ----------------------------------------------------------------------------- models/resnet.py::create_resnet
+def create_resnet(
+    *,
+    input_channel: int = 3, model_depth: int = 50, model_num_class: int = 400, dropout_rate: float = 0.5,
+    norm: Callable = nn.BatchNorm3d, activation: Callable = nn.ReLU,
+    stem_dim_out: int = 64, stem_conv_kernel_size=(1, 7, 7), stem_conv_stride=(1, 2, 2), stem_pool: Callable = nn.MaxPool3d,
+    stem_pool_kernel_size=(1, 3, 3), stem_pool_stride=(1, 2, 2), stem: Callable = create_res_basic_stem,
+    stage1_pool: Callable = None, stage1_pool_kernel_size=(2, 1, 1),
+    stage_conv_a_kernel_size=((1, 1, 1), (1, 1, 1), (3, 1, 1), (3, 1, 1)),
+    stage_conv_b_kernel_size=((1, 3, 3), (1, 3, 3), (1, 3, 3), (1, 3, 3)),
+    stage_conv_b_num_groups=(1, 1, 1, 1), stage_conv_b_dilation=((1, 1, 1), (1, 1, 1), (1, 1, 1), (1, 1, 1)),
+    stage_spatial_h_stride=(1, 2, 2, 2), stage_spatial_w_stride=(1, 2, 2, 2), stage_temporal_stride=(1, 1, 1, 1),
+    bottleneck=(create_bottleneck_block,) * 4,
+    head: Callable = create_res_basic_head, head_pool: Callable = nn.AvgPool3d, head_pool_kernel_size=(4, 7, 7),
+    head_output_size=(1, 1, 1), head_activation: Callable = None, head_output_with_global_average: bool = True,
+) -> nn.Module:
+    """pytorchvideo 0.1.5 `create_resnet` (the builder behind the hub entry `slow_r50` that the reference's
+    commented-out res3d path loads, reference train.py:79-83, (deprecated)/train_3dresnet.py:47-49): stem, four
+    ResStages (dims 64 -> 256 -> 512 -> 1024 -> 2048, inner = out / 4), head with its own AvgPool3d."""
+    assert model_depth in _MODEL_STAGE_DEPTH
+    stage_depths = _MODEL_STAGE_DEPTH[model_depth]
+    blocks = [stem(in_channels=input_channel, out_channels=stem_dim_out, conv_kernel_size=stem_conv_kernel_size,
+                   conv_stride=stem_conv_stride, conv_padding=[s // 2 for s in stem_conv_kernel_size], pool=stem_pool,
+                   pool_kernel_size=stem_pool_kernel_size, pool_stride=stem_pool_stride,
+                   pool_padding=[s // 2 for s in stem_pool_kernel_size], norm=norm, activation=activation)]
+    stage_dim_in = stem_dim_out
+    stage_dim_out = stage_dim_in * 4
+    for idx in range(len(stage_depths)):
+        stage_dim_inner = stage_dim_out // 4
+        ka, kb, dil = stage_conv_a_kernel_size[idx], stage_conv_b_kernel_size[idx], stage_conv_b_dilation[idx]
+        blocks.append(create_res_stage(
+            depth=stage_depths[idx], dim_in=stage_dim_in, dim_inner=stage_dim_inner, dim_out=stage_dim_out,
+            bottleneck=bottleneck[idx], conv_a_kernel_size=ka, conv_a_stride=(stage_temporal_stride[idx], 1, 1),
+            conv_a_padding=[s // 2 for s in ka], conv_b_kernel_size=kb,
+            conv_b_stride=(1, stage_spatial_h_stride[idx], stage_spatial_w_stride[idx]),
+            conv_b_padding=(kb[0] // 2, dil[1] if dil[1] > 1 else kb[1] // 2, dil[2] if dil[2] > 1 else kb[2] // 2),
+            conv_b_num_groups=stage_conv_b_num_groups[idx], conv_b_dilation=dil, norm=norm, activation=activation))
+        stage_dim_in = stage_dim_out
+        stage_dim_out = stage_dim_out * 2
+        if idx == 0 and stage1_pool is not None:
+            blocks.append(stage1_pool(kernel_size=stage1_pool_kernel_size, stride=stage1_pool_kernel_size, padding=(0, 0, 0)))
+    if head is not None:
+        blocks.append(head(in_features=stage_dim_in, out_features=model_num_class, pool=head_pool,
+                           output_size=head_output_size, pool_kernel_size=head_pool_kernel_size, dropout_rate=dropout_rate,
+                           activation=head_activation, output_with_global_average=head_output_with_global_average))
+    return Net(blocks=nn.ModuleList(blocks))

@@ -104,6 +104,18 @@ def build_oracle(num_class: int = 249, fuse: bool = True, input_channels: Sequen
         head_pool_kernel_sizes=tuple(head_pool_kernel_sizes))
 
 
+def build_res3d_oracle(num_class: int = 400, input_channel: int = 5, head_pool_kernel_size=(4, 7, 7)) -> nn.Module:
+    """BASELINE config 1 (config/res3d.yaml): the model the reference's res3d path intends -- pytorchvideo `slow_r50`
+    (create_resnet defaults, 400 classes) with its stem convolution replaced by
+    Conv3d(5, 64, (1,7,7), stride (1,2,2), padding (0,3,3), bias=False) (reference train.py:79-83, commented out;
+    (deprecated)/train_3dresnet.py:47-49).  Building create_resnet with input_channel = 5 gives that module tree
+    directly (same state_dict keys as the hub model after the replacement: `blocks.0.conv.weight` is (64,5,1,7,7)).
+    The head's own AvgPool3d is (4,7,7) by default, which needs a >= 7x7 final map (224^2 input); for the 112^2 clips of
+    the config the survey clips it to (4,4,4) -- pass head_pool_kernel_size."""
+    return pv.create_resnet(input_channel=input_channel, model_num_class=num_class,
+                            head_pool_kernel_size=tuple(head_pool_kernel_size))
+
+
 VARIANTS = {
     "REF": dict(),
     "HYB": dict(lateral_stride=(4, 1, 1), head_pool_kernel_sizes=((8, 7, 7), (32, 7, 7))),

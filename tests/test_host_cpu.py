@@ -164,3 +164,34 @@ def test_every_plan_owns_its_batchnorm_scratch():
     assert p1.bn_flat is not p2.bn_flat and p1.bn_flat is not p3.bn_flat
     assert p1.bn_flat.numel() == p2.bn_flat.numel() == p3.bn_flat.numel() > 0
     assert p1.stats_flat.numel() < p1.bn_flat.numel()
+
+
+# ---- BASELINE configs[0]: Slow-only 3D-ResNet (config/res3d.yaml; reference train.py:79-83) --------------------------
+def test_slow_r50_tree_matches_the_create_resnet_restatement():
+    from video_classification_b200.res3d import slow_r50
+    oracle = so.build_res3d_oracle(head_pool_kernel_size=(4, 4, 4))
+    product = slow_r50(5, 400, (4, 4, 4))
+    sd_o, sd_p = oracle.state_dict(), product.state_dict()
+    assert list(sd_o.keys()) == list(sd_p.keys()) and len(sd_o) == 320
+    assert all(sd_o[k].shape == sd_p[k].shape and sd_o[k].dtype == sd_p[k].dtype for k in sd_o)
+    assert sum(p.numel() for p in product.parameters()) == 32460368  # slow_r50 (32 454 096) + 2 extra stem channels
+    assert tuple(product.blocks[0].conv.weight.shape) == (64, 5, 1, 7, 7)  # train.py:81
+    product.load_state_dict(sd_o, strict=True)
+
+
+def test_slow_r50_plans_on_meta_and_rejects_oversized_head_pool(lib):
+    from video_classification_b200.engine import SlowFastEngine
+    from video_classification_b200.res3d import slow_r50
+    eng = SlowFastEngine(slow_r50(5, 400, (4, 4, 4)), dry_run=True)
+    assert eng.P == 1 and len(eng.layers) == 1 + 16 * 3 + 4 and all(l is None for l in eng.laterals)
+    eng.refresh_weights(True)
+    plan = eng.build_plan(2, 16, 0, 112, 112, True)  # configs[0]: batch 2, 16 x 112^2
+    assert len([op for op in plan.fwd if op[0] is lib.sfb_stem_conv_fprop]) == 1
+    assert len([op for op in plan.bwd if op[0] in (lib.sfb_conv_wgrad, lib.sfb_conv_wgrad_folded)]) == 16 * 3 + 4
+    assert tuple(plan.logits.shape) == (2, 400)
+    # the hub model's (4,7,7) head pool does not fit the 4x4 map of a 112^2 clip: same failure as nn.AvgPool3d
+    eng7 = SlowFastEngine(slow_r50(5, 400, (4, 7, 7)), dry_run=True)
+    eng7.refresh_weights(False)
+    with pytest.raises(_ffi.SfbError, match="head pool kernel"):
+        eng7.build_plan(2, 16, 0, 112, 112, False)
+    eng7.build_plan(1, 8, 0, 224, 224, False)

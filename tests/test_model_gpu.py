@@ -513,3 +513,60 @@ def test_free_running_gradients_vs_bf16_twin():
     med, p90 = errs[len(errs) // 2], errs[int(0.9 * len(errs))]
     print(f"free-running product vs twin: whole {whole:.3e} median {med:.3e} p90 {p90:.3e} max {errs[-1]:.3e}")
     assert whole <= 8e-2 and med <= 0.25 and p90 <= 0.35, (whole, med, p90, errs[-1])
+
+
+# ---- BASELINE configs[0]: config/res3d.yaml, Slow-only 3D-ResNet-50 on 16 x 112^2 clips, batch 2 --------------------------
+def _res3d_pair(final_gamma=pu.FINAL_GAMMA):
+    from video_classification_b200.res3d import slow_r50
+    torch.manual_seed(0)
+    oracle = so.build_res3d_oracle(num_class=400, input_channel=5, head_pool_kernel_size=(4, 4, 4))
+    so.randomize_bn_(oracle, 123, final_gamma)
+    so.disable_dropout_(oracle)
+    product = slow_r50(5, 400, (4, 4, 4))
+    product.load_state_dict(oracle.state_dict(), strict=True)
+    product.blocks[5].dropout.p = 0.0
+    return oracle.to(DEV), product.to(DEV)
+
+
+def test_res3d_slow_only_parity():
+    """the reference's res3d model (pytorchvideo slow_r50 with the 5-channel stem of train.py:81) on the config's clip
+    shape: eval and train logits 2e-2 against the fp32 oracle with identical top-1, running statistics, every parameter
+    receives a gradient, and one Adam step moves the loss"""
+    pu.fp32_reference_mode()
+    oracle, product = _res3d_pair()
+    x = torch.randn((2, 5, 16, 112, 112), generator=torch.Generator().manual_seed(1)).to(DEV)
+    y = torch.tensor([7, 311], device=DEV)
+    oracle.eval()
+    product.eval()
+    with torch.no_grad():
+        ref, got = oracle(x), product(x)
+    assert got.shape == ref.shape == (2, 400)
+    assert pu.rel_max(got, ref) <= pu.LOGIT_TOL
+    pu.assert_same_top1(got, ref)
+    oracle.train()
+    product.train()
+    out_o, out_p = oracle(x), product(x)
+    assert pu.rel_max(out_p.detach(), out_o.detach()) <= pu.LOGIT_TOL
+    pu.assert_same_top1(out_p.detach(), out_o.detach())
+    sd_o, sd_p = oracle.state_dict(), product.state_dict()
+    for k in sd_o:
+        if k.endswith("running_mean") or k.endswith("running_var"):
+            assert pu.rel_max(sd_p[k].float(), sd_o[k].float()) < 2e-2, k
+    loss_o, loss_p = F.cross_entropy(out_o, y), F.cross_entropy(out_p, y)
+    assert abs(float(loss_p) - float(loss_o)) <= 2e-2 * abs(float(loss_o))
+    loss_o.backward()
+    loss_p.backward()
+    grads = {n: p.grad for n, p in product.named_parameters()}
+    assert all(g is not None and bool(torch.isfinite(g).all()) for g in grads.values()) and len(grads) == 161
+    # the FC head sees the same pooled features up to bf16 storage: its gradient is a tight check of the whole forward
+    ref_g = dict(oracle.named_parameters())
+    assert pu.rel_l2(grads["blocks.5.proj.weight"], ref_g["blocks.5.proj.weight"].grad) < pu.GRAD_TOL
+    assert pu.rel_l2(grads["blocks.5.proj.bias"], ref_g["blocks.5.proj.bias"].grad) < 1e-3
+    # whole gradient against the pure fp32 oracle: ReLU-mask flips bound it (see test_free_running_gradients_vs_bf16_twin)
+    num = sum(float((grads[n].float() - ref_g[n].grad.float()).pow(2).sum()) for n in grads)
+    den = sum(float(ref_g[n].grad.float().pow(2).sum()) for n in grads)
+    assert (num / den) ** 0.5 < 0.15, (num / den) ** 0.5
+    opt = torch.optim.Adam(product.parameters(), lr=1e-3)
+    opt.step()
+    with torch.no_grad():
+        assert float(F.cross_entropy(product(x), y)) < float(loss_p)

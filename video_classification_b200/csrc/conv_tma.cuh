@@ -379,6 +379,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const bool bnred = p.bn_mode != 0;
     const uint32_t ybuf = smem_u32(smem) + p.ybuf_off;
     uint32_t yphase = 0;
+    bool y_issued = false;
     bool store_pending = false;
     int it = 0;
     PatchWalk pw;
@@ -404,9 +405,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             if (p.stg2_off && !bnred) tma_store_wait_read1(); else tma_store_wait_read();
           }
           named_bar_sync(1, ET);
-          if (bnred && te == 0) {
-            // the y tile of this chunk travels while the accumulator is converted and staged (every epilogue thread
-            // is past its reads of the previous y tile: they all arrived at the barrier above)
+          if (bnred && te == 0 && !y_issued) {
+            // first chunk of the CTA: its y tile travels while the accumulator is converted and staged (every later
+            // tile is requested one chunk ahead, below)
             const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
             mbar_arrive_expect_tx(y_bar, (uint32_t)nsub * (uint32_t)rows * rb);
             for (int gsub = 0; gsub < nsub; ++gsub)
@@ -510,6 +511,26 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
             tma_store_commit();
             store_pending = true;
+            if (bnred) {
+              // every epilogue thread is past its reads of the y tile (barrier above): request the NEXT chunk's tile
+              // now, so that it travels during that chunk's store wait, barrier and accumulator conversion
+              y_issued = false;
+              int ncol = col0 + CH, nw = w0, nh = h0, nt = t0, nn_ = n;
+              bool have = ch < last_ch;
+              if (!have && patch + patch_step < p.total_patches) {
+                PatchWalk pn = pw;
+                pn.next(p);
+                ncol = n0; nw = pn.tw * p.Wt; nh = pn.th * p.Ht; nt = pn.tt * p.Tt; nn_ = pn.n;
+                have = true;
+              }
+              if (have) {
+                const int nsub2 = (min(CH, p.Co - ncol) + ocols - 1) >> olog;
+                mbar_arrive_expect_tx(y_bar, (uint32_t)nsub2 * (uint32_t)rows * rb);
+                for (int gsub = 0; gsub < nsub2; ++gsub)
+                  tma_load_5d(ybuf + gsub * sub_bytes, &tmap_y, y_bar, ncol + gsub * ocols, nw, nh, nt, nn_);
+                y_issued = true;
+              }
+            }
           }
           // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros): epilogue
           //     warp e owns the 8-column group e of the chunk, its lanes split the 128 rows (16-byte reads)

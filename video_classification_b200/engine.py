@@ -146,7 +146,8 @@ class SlowFastEngine:
         self.impl = _ffi.IMPL_TC
         self._pack_cache = {}
         self.plans: Dict[Tuple, Plan] = {}
-        self.dropout_p = model.blocks[6].dropout.p if model.blocks[6].dropout is not None else 0.0
+        self.head_mod = model.blocks[6] if int(cfg.get("npath", 2)) == 2 else model.blocks[5]
+        self.dropout_p = self.head_mod.dropout.p if self.head_mod.dropout is not None else 0.0
         self.step_seed = 0
         self.ddp = None  # set by parallel.attach_ddp
         # BatchNorm backward reduction fused into the producing dgrad's epilogue (SFB_NO_BN_FUSE=1: separate passes)
@@ -168,18 +169,22 @@ class SlowFastEngine:
         cfg = self.cfg
         self.fuse = cfg["fuse"]
         L: List[ConvL] = []
+        # number of pathways: 2 = the SlowFast tree (blocks.N.multipathway_blocks.P...), 1 = the Slow-only 3D-ResNet tree
+        # of pytorchvideo's create_resnet (blocks.0 stem, blocks.1-4 stages, blocks.5 head; res3d.py)
+        P = self.P = int(cfg.get("npath", 2))
+        stem_path = (lambda p: "blocks.0") if P == 1 else (lambda p: f"blocks.0.multipathway_blocks.{p}")
+        stage_path = (lambda si, p: f"blocks.{si}") if P == 1 else (lambda si, p: f"blocks.{si}.multipathway_blocks.{p}")
         self.stems = []
-        for p in range(2):
-            st = m.blocks[0].multipathway_blocks[p]
-            self.stems.append(ConvL(f"blocks.0.multipathway_blocks.{p}", st.conv, st.norm, needs_dgrad=False,
-                                    conv_name=f"blocks.0.multipathway_blocks.{p}.conv"))
+        for p in range(P):
+            st = m.get_submodule(stem_path(p))
+            self.stems.append(ConvL(stem_path(p), st.conv, st.norm, needs_dgrad=False, conv_name=stem_path(p) + ".conv"))
         for st_ in self.stems:
             st_.is_stem = True
         L += self.stems
         self.laterals: List[Optional[ConvL]] = []
         for si in range(5):
-            fu = m.blocks[si].multipathway_fusion
-            if self.fuse and not isinstance(fu, nn.Identity):
+            fu = m.blocks[si].multipathway_fusion if P == 2 else None
+            if self.fuse and fu is not None and not isinstance(fu, nn.Identity):
                 self.laterals.append(ConvL(f"blocks.{si}.multipathway_fusion", fu.conv_fast_to_slow[0], fu.norm[0],
                                            conv_name=f"blocks.{si}.multipathway_fusion.conv_fast_to_slow.0"))
             else:
@@ -187,10 +192,10 @@ class SlowFastEngine:
         self.stages = []  # [stage][pathway] -> list of block dicts
         for si in range(1, 5):
             per_path = []
-            for p in range(2):
+            for p in range(P):
                 blks = []
-                for bi, rb in enumerate(m.blocks[si].multipathway_blocks[p].res_blocks):
-                    nm = f"blocks.{si}.multipathway_blocks.{p}.res_blocks.{bi}"
+                for bi, rb in enumerate(m.get_submodule(stage_path(si, p)).res_blocks):
+                    nm = f"{stage_path(si, p)}.res_blocks.{bi}"
                     b2 = rb.branch2
                     d = dict(a=ConvL(nm + ".a", b2.conv_a, b2.norm_a, conv_name=nm + ".branch2.conv_a"),
                              b=ConvL(nm + ".b", b2.conv_b, b2.norm_b, conv_name=nm + ".branch2.conv_b"),
@@ -205,7 +210,7 @@ class SlowFastEngine:
         if self.laterals[0] is not None:
             order.append(self.laterals[0])
         for si in range(4):
-            for p in (1, 0):  # execution order: Fast first (its output feeds the lateral of the Slow concat buffer)
+            for p in reversed(range(P)):  # execution order: Fast first (its output feeds the lateral of the Slow concat buffer)
                 for d in self.stages[si][p]:
                     if d["s"] is not None:
                         order.append(d["s"])
@@ -218,7 +223,7 @@ class SlowFastEngine:
             for l in order:
                 if not l.is_stem:
                     l.fold_f = _ops.fold_factor(l.ldi, l.ldo, l.k, l.s, 8)
-        self.proj = m.blocks[6].proj
+        self.proj = self.head_mod.proj
         self.bn_modules = [l.bn for l in self.layers]
 
     def _bind_bn_arena(self, plan: "Plan"):
@@ -646,11 +651,12 @@ class SlowFastEngine:
             return None, out_z
 
         T_in = (Ts, Tf)
+        P = self.P
         # ---------------- stems ----------------
         stem_rec = []
         pooled: List[FinalAct] = []
         cat_bufs = {}
-        for p in range(2):
+        for p in range(P):
             L = self.stems[p]
             To, Ho, Wo = conv_out_dims((T_in[p], H, W), L.k, L.s, L.p)
             y0 = new_act(N, To, Ho, Wo, L.Co, pad=False)  # biggest tensors of the net: consumed by the pool only
@@ -707,8 +713,8 @@ class SlowFastEngine:
         if self.laterals[0] is not None:
             cur = [do_lateral(0, cur[0], cur[1]), cur[1]]
         for si in range(4):
-            nxt: List[FinalAct] = [None, None]
-            for p in (1, 0):  # Fast first: its output feeds the lateral that completes the Slow concat buffer
+            nxt: List[FinalAct] = [None] * P
+            for p in reversed(range(P)):  # Fast first: its output feeds the lateral that completes the Slow concat buffer
                 X = cur[p]
                 blks = self.stages[si][p]
                 for bi, d in enumerate(blks):
@@ -770,7 +776,7 @@ class SlowFastEngine:
                 cur = [Xs, cur[1]]
 
         # ---------------- head ----------------
-        feat_dim = cur[0].act.C + cur[1].act.C
+        feat_dim = sum(fa.act.C for fa in cur)
         ncls = self.proj.out_features
         assert feat_dim == self.proj.in_features
         feat = _f32(N * feat_dim, dev).view(N, feat_dim)
@@ -781,7 +787,7 @@ class SlowFastEngine:
         plan.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         seed_ptr = plan.seed_dev.data_ptr() if drop > 0.0 else None
         f_off = 0
-        for p in range(2):
+        for p in range(P):
             a = cur[p].act
             n_, t_, h_, w_ = a.dims
             if hk[p][0] > t_ or hk[p][1] > h_ or hk[p][2] > w_:
@@ -840,7 +846,7 @@ class SlowFastEngine:
             dgrad_into(lat, dz, lr["x"])
 
         f_off = 0
-        for p in range(2):
+        for p in range(P):
             fa = cur[p]
             ensure_grad(fa)
             a, ga = fa.act, fa.grad
@@ -896,7 +902,7 @@ class SlowFastEngine:
 
         if self.laterals[0] is not None:
             lateral_backward(0)
-        for p in range(2):
+        for p in range(P):
             sr = stem_rec[p]
             L, y0, out = sr["L"], sr["y0"], sr["out"]
             assert out.ginit
@@ -1109,6 +1115,16 @@ class SlowFastEngine:
 
     def get_plan(self, xs, xf, training) -> Plan:
         N, Cs, Ts, H, W = xs.shape
+        if self.P == 1:
+            if Cs != self.cfg["input_channels"][0]:
+                raise ValueError(f"expected {self.cfg['input_channels'][0]} input channels, got {Cs}")
+            key = (N, Ts, 0, H, W, bool(training), self.impl)
+            plan = self.plans.get(key)
+            if plan is None:
+                self.refresh_weights(training)
+                plan = self.build_plan(N, Ts, 0, H, W, training)
+                self.plans[key] = plan
+            return plan
         N2, Cf, Tf, H2, W2 = xf.shape
         if (N2, H2, W2) != (N, H, W):
             raise ValueError("slow and fast clips must share batch and spatial size")
@@ -1158,17 +1174,18 @@ class SlowFastEngine:
     def forward(self, xs, xf, training: bool) -> Tuple[torch.Tensor, Plan]:
         """xs, xf: fp32 NCTHW clips (any strides), or xs = staging.RawClips and xf = None"""
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
-        if xf is None:
+        if xf is None and not torch.is_tensor(xs):
             self.refresh_weights(training)
             plan = self._stage_raw(xs, training)
             return self._forward_staged(plan, training)
-        if xs.dtype != torch.float32 or xf.dtype != torch.float32:
+        ins = (xs,) if self.P == 1 else (xs, xf)
+        if any(x.dtype != torch.float32 for x in ins):
             raise TypeError("inputs must be float32 (as produced by the reference loader)")
-        if xs.device != self.dev or xf.device != self.dev:
+        if any(x.device != self.dev for x in ins):
             raise _ffi.SfbError("inputs must live on the model's CUDA device")
         plan = self.get_plan(xs, xf, training)
         self.refresh_weights(training)
-        for x, a in zip((xs, xf), plan.x_in):
+        for x, a in zip(ins, plan.x_in):
             N, Cc, T, H, W = x.shape
             sn, sc, st, sh, sw = x.stride()
             if isinstance(a, Act):
