@@ -275,7 +275,7 @@ def run_gpu_arm(args):
         model = init_my_slowfast(make_cfg(NUM_CLASS, True), (5, 15), (64, 8), **w["graph_kw"]).to(dev)
     model.train(train)
     if world > 1 and train:
-        attach_ddp(model, bucket_mb=args.bucket_mb)
+        attach_ddp(model, bucket_mb=args.bucket_mb, tail_mb=args.tail_mb)
     # same update rule as the reference's optim.Adam (train.py:182), same constructor: sfb_adam_step updates all 332
     # live parameters in ONE launch (csrc/adam.cuh) instead of torch's 10 + 5 fused multi-tensor launches
     opt = Adam(model.parameters(), lr=1e-4) if train else None
@@ -358,6 +358,34 @@ def run_gpu_arm(args):
                                       "all-gathered after the timed steps"}
         if not same:
             raise SystemExit(f"rank {rank}: data-parallel replicas diverged (parameter checksums differ across ranks)")
+
+    # ---- optional: where the collectives sit inside one backward pass (per-bucket CUDA events, eager launches) ----
+    if world > 1 and train and args.ddp_timeline:
+        eng = model._engine
+        bk = eng.ddp.bucketer
+        saved = eng.use_graphs
+        eng.use_graphs = False
+        step(*resident)
+        bk.timeline = []
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        out = model(list(resident))
+        loss = F.cross_entropy(out, y)
+        opt.zero_grad()
+        t0.record()
+        loss.backward()
+        t1.record()
+        torch.cuda.synchronize(dev)
+        rows = [{"bucket": b, "bytes": nbytes, "ready_ms": t0.elapsed_time(ev), "allreduce_start_ms": t0.elapsed_time(e0),
+                 "allreduce_end_ms": t0.elapsed_time(e1)} for b, nbytes, ev, e0, e1 in bk.timeline]
+        bk.timeline = None
+        eng.use_graphs = saved
+        r["ddp_timeline"] = {"backward_ms": t0.elapsed_time(t1), "buckets": rows,
+                             "note": "rank 0, one eager backward pass: ready = the bucket's last gradient is final (compute "
+                                     "stream), all-reduce start / end on the communication stream; backward_ms ends when the "
+                                     "compute stream has waited for the last collective"}
+        opt.step()
 
     if args.skip_e2e:  # profiling runs only (ncu launch lists); the JSON line then carries no e2e number
         return r
@@ -531,6 +559,8 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--no-numa-bind", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg")
+    ap.add_argument("--ddp-timeline", action="store_true", help="N > 1: add per-bucket all-reduce timing of one backward pass")
+    ap.add_argument("--tail-mb", type=float, default=1.0, help="N > 1: size of the split-off last gradient bucket")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -585,6 +615,11 @@ def main():
         line["config"]["optimizer"] = "video_classification_b200.optim.Adam(lr=1e-4): sfb_adam_step, one launch per step"
     if r["replica_check"] is not None:
         line["replica_check"] = r["replica_check"]
+    if r.get("ddp_timeline"):
+        line["ddp_timeline"] = r["ddp_timeline"]
+    eng_ = r["model"]._engine
+    line["config"]["cuda_graphs"] = {"enabled": bool(eng_.use_graphs), "captured": sum(len(p_.graphs) for p_ in eng_.plans.values()),
+                                     "errors": eng_.graph_errors[:2]}
     if kernels:
         # dominant kernel = conv_tma_kernel<BN,BRES>: sfb_conv_gemm forward and input-gradient launches are the same
         # CUDA kernel (csrc/conv_tma.cuh); the weight gradient is a different kernel and listed in the breakdown

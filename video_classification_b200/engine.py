@@ -124,6 +124,10 @@ class Plan:
         self.gen = 0  # bumped by every training forward; backward checks it saw the latest one
         # CUDA graphs of the two op lists (SlowFastEngine._graphed): {"fwd"|"bwd": (CUDAGraph, kernels per replay)},
         # eager runs so far, and whether a capture failed (then the list keeps running eagerly)
+        # eval plans: the BatchNorm folds (running statistics -> scale / shift, ~110 tiny launches) are kept apart from the
+        # forward list and re-run only when a BatchNorm parameter or buffer may have changed (SlowFastEngine._fold_key)
+        self.folds: List[Tuple] = []
+        self.fold_key = None
         self.graphs = {}
         self.graph_runs = {"fwd": 0, "bwd": 0}
         self.graph_failed = {}
@@ -225,6 +229,8 @@ class SlowFastEngine:
                     l.fold_f = _ops.fold_factor(l.ldi, l.ldo, l.k, l.s, 8)
         self.proj = self.head_mod.proj
         self.bn_modules = [l.bn for l in self.layers]
+        self.bn_epoch = 0
+        self._bn_ptrs = [bn.running_mean.data_ptr() for bn in self.bn_modules]
 
     def _bind_bn_arena(self, plan: "Plan"):
         """BatchNorm scratch of ONE plan: [all raw sums | per layer scale, shift, mean, invstd].  Every plan owns its
@@ -279,15 +285,28 @@ class SlowFastEngine:
             st = offs[id(prm)]
             self.grad_views[id(prm)] = self.grad_flat[st:st + prm.numel()].view(prm.shape)
         self.grad_offsets = offs
+        self._grad_view_specs = [(tuple(prm.shape), tuple(self.grad_views[id(prm)].stride()), offs[id(prm)]) for prm in live]
         for l in self.layers:
             l.dw = self.grad_views[id(l.conv.weight)]
             l.dgamma = self.grad_views[id(l.bn.weight)]
             l.dbeta = self.grad_views[id(l.bn.bias)]
 
     def invalidate_weights(self):
+        """public hook: call after writing parameters or BatchNorm buffers through anything that does not move their
+        version counters (raw pointers, p.data = ...); load_state_dict and the model's own training steps call it / are
+        tracked already"""
         for l in self.layers:
             l.packed_version = -1
         self._pack_cache = {}
+        self.bn_epoch += 1
+
+    def _fold_key(self):
+        """changes whenever a folded BatchNorm coefficient may be stale: any training forward of this engine (running
+        statistics), invalidate_weights(), or an in-place update of gamma / beta / the buffers that autograd can see"""
+        v = 0
+        for bn in self.bn_modules:
+            v += bn.weight._version + bn.bias._version + bn.running_mean._version + bn.running_var._version
+        return (self.bn_epoch, v, tuple(self._bn_ptrs) == tuple(bn.running_mean.data_ptr() for bn in self.bn_modules))
 
     # ------------------------------------------------------------------ weights
     def _pack_tables(self, training: bool):
@@ -556,7 +575,7 @@ class SlowFastEngine:
                        bn.running_var.data_ptr(), L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(),
                        L.invstd.data_ptr(), self.stream)
         else:
-            self._emit(lst, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+            self._emit(plan.folds, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
                        bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
 
     def _bn_bwd(self, plan, lst, L: ConvL, dz: Act, y: Act, mask, dy: Act, g_out: Optional[Act] = None,
@@ -629,7 +648,7 @@ class SlowFastEngine:
 
         def fold(L):
             bn = L.bn
-            self._emit(fwd, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+            self._emit(plan.folds, self.lib.sfb_bn_fold, bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
                        bn.running_var.data_ptr(), float(bn.eps), L.Co, L.scale.data_ptr(), L.shift.data_ptr(), self.stream)
 
         def conv_bn_act(L, x: Act, out_z: Optional[Act], *, relu=True, residual=None, keep_raw=True):
@@ -1202,6 +1221,12 @@ class SlowFastEngine:
             if self.dropout_p > 0.0:
                 plan.seed_dev.fill_(self._draw_dropout_seed())
 
+        else:
+            key = self._fold_key()
+            if plan.fold_key != key:
+                self._run(plan.folds)
+                plan.fold_key = key
+
         def body():
             if training:
                 plan.stats_flat.zero_()
@@ -1209,6 +1234,8 @@ class SlowFastEngine:
 
         if not self._graphed(plan, "fwd", body):
             body()
+        if training:
+            self.bn_epoch += 1  # running statistics moved (written through raw pointers: no version counter sees it)
         if training:
             torch._foreach_add_([bn.num_batches_tracked for bn in self.bn_modules], 1)
         return plan.logits, plan
@@ -1233,6 +1260,13 @@ class SlowFastEngine:
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
         plan.dlogits.copy_(dlogits)
         self._bwd_since_pack = True  # an optimizer step may follow: see refresh_weights
+        # A parameter whose .grad still aliases the arena (autograd adopted last step's view and the caller did not
+        # zero_grad) would be wiped by the arena zero fill below and then added to itself: give it storage of its own,
+        # so that gradient accumulation over several backward passes behaves as with the reference's modules.
+        for prm in self.live_params:
+            g = prm.grad
+            if g is not None and g.data_ptr() == self.grad_views[id(prm)].data_ptr():
+                prm.grad = g.clone()
 
         def body():
             self.grad_flat.zero_()
@@ -1244,7 +1278,10 @@ class SlowFastEngine:
 
         if not self._graphed(plan, "bwd", body):
             body()
-        return [self.grad_views[id(p)] for p in self.live_params]
+        # FRESH view objects, referenced by nobody else once returned: autograd then adopts them as .grad (no copy) instead
+        # of cloning every gradient -- 332 device-to-device copies per step with views that the engine also holds
+        flat = self.grad_flat
+        return [torch.as_strided(flat, shp, std, off) for shp, std, off in self._grad_view_specs]
 
 
 class _SlowFastFn(torch.autograd.Function):

@@ -29,7 +29,7 @@ class GradBucketer:
     tensors with gloo (tests) and on CUDA tensors with NCCL (product)."""
 
     def __init__(self, flat: torch.Tensor, spans: Sequence[Tuple[int, int]], bucket_bytes: int = 25 << 20,
-                 group=None):
+                 group=None, tail_bytes: int = 0):
         """spans: (offset, numel) of each parameter's gradient inside `flat`, any order; they are bucketed in
         arena order (ascending offset = order in which backward completes them)."""
         self.flat = flat
@@ -51,6 +51,23 @@ class GradBucketer:
             self.span_bucket[off] = len(self.buckets)
         if members:
             self.buckets.append((start, end))
+        # The gradients at the END of the arena (stems, first residual stage) become final last, so the collective of
+        # the bucket that holds them cannot start before backward is over and its whole duration is exposed.  Split a
+        # small tail off the last bucket: what remains exposed is a latency-sized all-reduce.
+        if tail_bytes > 0 and self.buckets:
+            s0, e0 = self.buckets[-1]
+            cut = None
+            for off, n in self.spans:
+                if off > s0 and (e0 - off) * flat.element_size() <= tail_bytes:
+                    cut = off
+                    break
+            if cut is not None:
+                self.buckets[-1] = (s0, cut)
+                self.buckets.append((cut, e0))
+                nb = len(self.buckets) - 1
+                for off, n in self.spans:
+                    if off >= cut:
+                        self.span_bucket[off] = nb
         self.is_cuda = flat.is_cuda
         self.comm_stream = torch.cuda.Stream(device=flat.device) if self.is_cuda else None
         backend = dist.get_backend(group) if dist.is_initialized() else "none"
@@ -58,6 +75,9 @@ class GradBucketer:
         self._pending = None
         self._works = []
         self.launch_order: List[int] = []  # for tests / introspection
+        # optional per-bucket timeline (bench.py --ddp-timeline): CUDA events at "gradients of the bucket final" on the
+        # compute stream and around the collective on the communication stream
+        self.timeline = None
         self.reset_counts()
 
     def reset_counts(self):
@@ -83,11 +103,18 @@ class GradBucketer:
         view = self.flat[s:e]
         op = dist.ReduceOp.AVG if self.use_avg else dist.ReduceOp.SUM
         if self.is_cuda:
-            ev = torch.cuda.Event()
+            tl = self.timeline
+            ev = torch.cuda.Event(enable_timing=tl is not None)
             ev.record(torch.cuda.current_stream(self.flat.device))
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
+                if tl is not None:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(self.comm_stream)
                 dist.all_reduce(view, op=op, group=self.group)
+                if tl is not None:
+                    e1.record(self.comm_stream)
+                    tl.append((b, (e - s) * self.flat.element_size(), ev, e0, e1))
         else:
             self._works.append(dist.all_reduce(view, op=op, group=self.group, async_op=True))
         return 0
@@ -113,9 +140,10 @@ class GradBucketer:
 class EngineDDP:
     """Glue between SlowFastEngine's static backward plan and a GradBucketer (engine.ddp protocol)."""
 
-    def __init__(self, engine, bucket_mb: float = 25.0, group=None):
+    def __init__(self, engine, bucket_mb: float = 25.0, group=None, tail_mb: float = 1.0):
         spans = [(engine.grad_offsets[id(p)], p.numel()) for p in engine.live_params]
-        self.bucketer = GradBucketer(engine.grad_flat, spans, int(bucket_mb * (1 << 20)), group)
+        self.bucketer = GradBucketer(engine.grad_flat, spans, int(bucket_mb * (1 << 20)), group,
+                                     tail_bytes=int(tail_mb * (1 << 20)))
         self.engine = engine
 
     # called while the backward op list is being built ------------------------------------------
@@ -145,7 +173,7 @@ def broadcast_parameters(model: torch.nn.Module, src: int = 0, group=None):
             dist.broadcast(t.data, src=src, group=group)
 
 
-def attach_ddp(model, bucket_mb: float = 25.0, group=None, broadcast: bool = True) -> EngineDDP:
+def attach_ddp(model, bucket_mb: float = 25.0, group=None, broadcast: bool = True, tail_mb: float = 1.0) -> EngineDDP:
     """model: my_slowfast.SlowFastB200 already on its CUDA device.  After this, loss.backward() leaves the MEAN
     gradient over all ranks in every live parameter's .grad; the training loop (train.py:225-231) is unchanged."""
     from .engine import SlowFastEngine
@@ -155,7 +183,7 @@ def attach_ddp(model, bucket_mb: float = 25.0, group=None, broadcast: bool = Tru
         model._engine = SlowFastEngine(model)
     eng = model._engine
     eng.plans.clear()  # backward plans must be rebuilt with the bucket launch entries in place
-    eng.ddp = EngineDDP(eng, bucket_mb, group)
+    eng.ddp = EngineDDP(eng, bucket_mb, group, tail_mb=tail_mb)
     if broadcast:
         eng.invalidate_weights()
     return eng.ddp
