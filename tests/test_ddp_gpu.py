@@ -44,14 +44,26 @@ def _worker(rank, world, port, backend, ret):
     from video_classification_b200.optim import Adam
     from video_classification_b200.parallel import attach_ddp
 
+    import datetime
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dev = torch.device("cuda", rank if backend == "nccl" else 0)
     torch.cuda.set_device(dev)
+    # a rank that fails must not leave its peer waiting in a collective for NCCL's default 10 minutes
+    tmo = datetime.timedelta(seconds=90)
     if backend == "nccl":
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=tmo)
     else:
-        dist.init_process_group("gloo", rank=rank, world_size=world)
+        dist.init_process_group("gloo", rank=rank, world_size=world, timeout=tmo)
+    log_dir = os.path.join(os.path.dirname(here), "gpurun_out")
+    log = open(os.path.join(log_dir, f"ddp_{backend}_rank{rank}.log"), "w") if os.path.isdir(log_dir) else None
+
+    def mark(msg):
+        if log is not None:
+            log.write(msg + "\n")
+            log.flush()
+
     try:
+        mark("process group up")
         # rank 1 starts from DIFFERENT weights: attach_ddp's broadcast must make the replicas equal
         _, product = pu.build_pair("REF", True, seed=rank, device=dev)
         product.blocks[6].dropout.p = 0.5  # as the reference trains; per-rank masks (engine._draw_dropout_seed)
@@ -64,6 +76,7 @@ def _worker(rank, world, port, backend, ret):
         both = [torch.empty_like(flat0) for _ in range(world)]
         dist.all_gather(both, flat0)
         assert torch.equal(both[0], both[1]), "broadcast_parameters did not equalise the replicas"
+        mark("broadcast ok")
 
         # (c) bucket boundaries inside a (weight, gamma, beta) triple
         offs = eng.grad_offsets
@@ -93,6 +106,7 @@ def _worker(rank, world, port, backend, ret):
         dl, = torch.autograd.grad(loss, out, retain_graph=True)
         out.backward(dl, retain_graph=True)       # data-parallel backward: arena = mean over ranks
         torch.cuda.synchronize(dev)
+        mark("data-parallel backward done")
         reduced = eng.grad_flat.clone()
         assert sorted(snaps) == list(range(len(bk.buckets))), "a bucket was never launched"
         product.zero_grad(set_to_none=True)           # .grad aliases the arena: a second backward must not accumulate
@@ -125,6 +139,7 @@ def _worker(rank, world, port, backend, ret):
         scale = float(mean[lo:hi].abs().max())
         assert err <= 1e-5 * scale, f"all-reduce result is not the mean of the ranks' gradients: {err:.3e} vs {scale:.3e}"
 
+        mark("(a) checks passed")
         # ---- (b) three optimizer steps, replicas stay bit-identical ----
         opt = Adam(product.parameters(), lr=1e-3)
         for it in range(3):
@@ -133,6 +148,8 @@ def _worker(rank, world, port, backend, ret):
             opt.zero_grad()
             loss.backward()
             opt.step()
+            torch.cuda.synchronize(dev)
+            mark(f"step {it} done, graphs: {sorted(k for pl in eng.plans.values() for k in pl.graphs)} errors: {eng.graph_errors[:1]}")
         torch.cuda.synchronize(dev)
         # in the plain training loop .grad of every live parameter aliases the arena the all-reduce ran on (autograd
         # adopts the returned views; with retain_graph above it clones them, which is why (a) reads the arena itself)
@@ -145,14 +162,19 @@ def _worker(rank, world, port, backend, ret):
         assert not torch.equal(flat1, flat0), "parameters did not move"
         assert bool(torch.isfinite(flat1).all())
         ret[rank] = "ok"
+        mark("ok")
     except BaseException as e:  # noqa: BLE001 -- reported to the parent, which fails the test
         import traceback
         ret[rank] = "".join(traceback.format_exception(type(e), e, e.__traceback__))[-3000:]
+        mark("FAILED: " + ret[rank])
+        os._exit(1)  # do not join a process group whose peer may be stuck in a collective
     finally:
-        try:
-            dist.destroy_process_group()
-        except Exception:  # pragma: no cover
-            pass
+        if log is not None:
+            log.close()
+    try:
+        dist.destroy_process_group()
+    except Exception:  # pragma: no cover
+        pass
 
 
 def _run(backend):
@@ -161,17 +183,21 @@ def _run(backend):
     port = _free_port()
     mgr = mp.Manager()
     ret = mgr.dict()
-    mp.spawn(_worker, args=(world, port, backend, ret), nprocs=world, join=True)
+    try:
+        mp.spawn(_worker, args=(world, port, backend, ret), nprocs=world, join=True)
+    except Exception as e:  # a worker exited non-zero: its message is in `ret`
+        if not any(ret.get(r) not in (None, "ok") for r in range(world)):
+            raise e
     bad = {r: ret.get(r) for r in range(world) if ret.get(r) != "ok"}
     assert not bad, "\n".join(f"rank {r}: {m}" for r, m in bad.items())
 
 
-@pytest.mark.timeout(600)
+@pytest.mark.timeout(240)
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
 def test_ddp_nccl_two_gpus():
     _run("nccl")
 
 
-@pytest.mark.timeout(600)
+@pytest.mark.timeout(240)
 def test_ddp_gloo_two_ranks_one_gpu():
     _run("gloo")

@@ -172,7 +172,13 @@ struct ConvTmaCfg {
   static size_t smem_bytes(int nk = 0) { return 1024 + (BRES ? (size_t)kBResOff + (size_t)nk * BN * 128 : (size_t)kEnd); }
 };
 
-template <int BN, bool BRES = false>
+// MODE selects the epilogue, as a template parameter so that no variant pays registers for another one's state (the
+// kernel sits at the 96-register cap of its 576-thread block):
+//   kEpiPlain  training fprop / dgrad: convert + stage (+ BatchNorm statistics of the forward, + reduce-add stores)
+//   kEpiAffine inference: folded-BatchNorm affine, residual, ReLU
+//   kEpiBnBwd  dgrad with the fused BatchNorm-backward reduction (ConvTmaParams::bn_*)
+enum { kEpiPlain = 0, kEpiAffine = 1, kEpiBnBwd = 2 };
+template <int BN, bool BRES = false, int MODE = kEpiPlain>
 __global__ void __launch_bounds__(ConvTmaCfg<BN, BRES>::kThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                 const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_y,
@@ -364,7 +370,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     // The epilogue is instruction-bound on the memory-bound layers (ncu r1o, 64->256 pointwise: 15 k warp
     // instructions per 128x256 tile, 58 % issue utilisation, of which ~6 k were per-group branches, parameter
     // reloads and address arithmetic): everything that does not change from tile to tile is computed once here.
-    const bool plain = p.epi_scale == nullptr && p.res == nullptr && !p.epi_relu;
+    constexpr bool plain = MODE != kEpiAffine;
     uint32_t soff[4], toff[4];  // swizzled staging offsets: this thread's four 16-byte stores / four stats loads
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -375,8 +381,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       o = (uint32_t)(cs >> olog) * sub_bytes + (uint32_t)(lane + 32 * j) * rb + (uint32_t)((cs & (ocols - 1)) * 2);
       toff[j] = o ^ (((o >> 7) & swz) << 4);
     }
-    const bool want_stats = p.stats != nullptr;
-    const bool bnred = p.bn_mode != 0;
+    const bool want_stats = MODE == kEpiPlain && p.stats != nullptr;
+    constexpr bool bnred = MODE == kEpiBnBwd;
     const uint32_t ybuf = smem_u32(smem) + p.ybuf_off;
     uint32_t yphase = 0;
     bool y_issued = false;
@@ -416,18 +422,33 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           // (B) accumulator -> staging: this warp's 32-column slice
           {
             const int nb = col0 + cslice * 32;
-            if (plain && nb + 32 <= p.Co) {
-              // training fprop / dgrad: convert and stage, nothing else
-              float v[32];
-              tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
-              tmem_ld_wait();
+            if constexpr (plain) {
+              // training fprop / dgrad: convert and stage, nothing else (ragged last slice: only the live 8-column groups)
+              if (nb < p.Co) {
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
+                tmem_ld_wait();
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                uint4 pk = pack8(v + j * 8);
-                if (!mv) pk = make_uint4(0, 0, 0, 0);
-                sts_v4(stg + soff[j], pk);
+                for (int j = 0; j < 4; ++j) {
+                  if (nb + j * 8 < p.Co) {
+                    uint4 pk = pack8(v + j * 8);
+                    if (!mv) pk = make_uint4(0, 0, 0, 0);
+                    sts_v4(stg + soff[j], pk);
+                  }
+                }
               }
             } else if (nb < p.Co) {
+              // inference epilogue (folded BatchNorm, residual, ReLU).  The eval forward is epilogue-bound on the
+              // memory-bound layers, so: the residual's 64 bytes are requested before the accumulator is read, the affine
+              // coefficients come as two 16-byte loads per 8 columns (they were 16 scalar loads), the staging offsets are
+              // the precomputed ones.
+              uint4 rq[4];
+              const bool has_res = rrow != nullptr && mv;
+              if (has_res) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  rq[j] = nb + j * 8 < p.Co ? *reinterpret_cast<const uint4*>(rrow + nb + j * 8) : make_uint4(0, 0, 0, 0);
+              }
               float v[32];
               tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
               tmem_ld_wait();
@@ -437,12 +458,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 if (nn < p.Co) {
                   float* f = v + j * 8;
                   if (p.epi_scale) {
+                    float es[8], eb[8];
+                    load8f(p.epi_scale + nn, es);
+                    load8f(p.epi_shift + nn, eb);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], __ldg(p.epi_scale + nn + i), __ldg(p.epi_shift + nn + i));
+                    for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], es[i], eb[i]);
                   }
-                  if (rrow && mv) {
+                  if (has_res) {
                     float rf[8];
-                    unpack8(*reinterpret_cast<const uint4*>(rrow + nn), rf);
+                    unpack8(rq[j], rf);
 #pragma unroll
                     for (int i = 0; i < 8; ++i) f[i] += rf[i];
                   }
@@ -452,11 +476,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                   }
                   uint4 pk = pack8(f);
                   if (!mv) pk = make_uint4(0, 0, 0, 0);
-                  const int cl = cslice * 32 + j * 8;        // column inside the chunk
-                  const int gsub = cl >> olog;
-                  uint32_t addr = stg + gsub * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl & (ocols - 1)) * 2);
-                  addr ^= ((addr >> 7) & swz) << 4;
-                  sts_v4(addr, pk);
+                  sts_v4(stg + soff[j], pk);
                 }
               }
             }

@@ -333,7 +333,7 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
   *Wt = bw; *Ht = bh; *Tt = bt;
 }
 
-template <int BN, bool BRES>
+template <int BN, bool BRES, int MODE>
 int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
                          const ConvTmaParams& p, cudaStream_t st) {
   using L = ConvTmaCfg<BN, BRES>;
@@ -361,11 +361,11 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
   const int grid = (int)per_nt * p.n_tiles;
   static size_t attr_bytes = 0;
   if (smem_total > attr_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total);
+    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
     attr_bytes = smem_total;
   }
-  conv_tma_kernel<BN, BRES><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, ty, pp);
+  conv_tma_kernel<BN, BRES, MODE><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, ty, pp);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
@@ -374,8 +374,19 @@ template <int BN>
 int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
                     const ConvTmaParams& p, cudaStream_t st) {
   // weights resident in shared memory when the CTA's [BN][Ktot] slice fits next to the pipeline (see ConvTmaCfg)
-  if (ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024) return launch_conv_tma_impl<BN, true>(ta, tw, to, ty, p, st);
-  return launch_conv_tma_impl<BN, false>(ta, tw, to, ty, p, st);
+  const bool bres = ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024;
+  if (p.bn_mode) {
+    if (p.epi_scale || p.res || p.epi_relu || p.stats) return SFB_ERR_UNSUPPORTED;
+    return bres ? launch_conv_tma_impl<BN, true, kEpiBnBwd>(ta, tw, to, ty, p, st)
+                : launch_conv_tma_impl<BN, false, kEpiBnBwd>(ta, tw, to, ty, p, st);
+  }
+  if (p.epi_scale || p.res || p.epi_relu) {
+    if (p.stats) return SFB_ERR_UNSUPPORTED;  // forward statistics go with the raw training output only
+    return bres ? launch_conv_tma_impl<BN, true, kEpiAffine>(ta, tw, to, ty, p, st)
+                : launch_conv_tma_impl<BN, false, kEpiAffine>(ta, tw, to, ty, p, st);
+  }
+  return bres ? launch_conv_tma_impl<BN, true, kEpiPlain>(ta, tw, to, ty, p, st)
+              : launch_conv_tma_impl<BN, false, kEpiPlain>(ta, tw, to, ty, p, st);
 }
 
 // ConvTmaParams fields of the fused BatchNorm-backward epilogue (sfb_conv_dgrad_bn)

@@ -161,6 +161,7 @@ class SlowFastEngine:
         self.graph_errors = []
         # static op lists replayed as CUDA graphs from the third run of a plan on (SFB_GRAPHS=0: always eager launches)
         self.use_graphs = _os.environ.get("SFB_GRAPHS", "1") != "0"
+        self.graphs_with_ddp = _os.environ.get("SFB_GRAPHS_DDP", "0") == "1"
         self.graph_after = 2
         self.prof = None     # list: bench.py sets it to time every plan entry with CUDA events
         self.capture = None  # dict: tools/layer_diag.py sets it to snapshot tagged intermediates (debug only)
@@ -482,15 +483,33 @@ class SlowFastEngine:
         k, s, p = L.k, L.s, L.p
         N, Ti, Hi, Wi = x.dims
         _, To, Ho, Wo = out.dims
-        f = self._fold_of(L, x, out, transposed) if (wp is None and pro is None and epi is None) else 1
+        f = self._fold_of(L, x, out, transposed) if (wp is None and pro is None) else 1
+        if f > 1 and epi is not None and residual is not None and not (
+                residual.coff == 0 and residual.ld == out.ld and residual.dims == out.dims):
+            f = 1  # the residual must fold the same way as the output
         if f > 1:
             # the same buffers seen as (N,T,H,W/f,f*ld): 128-byte rows for TMA, block-banded weights
             k, p = L.kf, L.pf
             cg, co = f * x.ld, f * out.ld
             g = ConvGeom(N, Ti, Hi, Wi // f, cg, To, Ho, Wo // f, co, k[0], k[1], k[2], 1, 1, 1, p[0], p[1], p[2],
                          cg, 0, co, 0, int(transposed))
-            assert residual is None or (residual.buf is out.buf and residual.coff == 0)
-            ep = Epilogue(0, 0, out.ptr() if residual else 0, co if residual else 0, 0, 0, L.sf.data_ptr() if stats else 0)
+            if epi is not None:
+                # inference: folded-BatchNorm coefficients per FOLDED column (j*ld + c -> channel c; pad lanes 0, so
+                # the pad lanes of the output stay 0 through the ReLU), re-derived right after the layer's sfb_bn_fold
+                scf = _f32(co, self.dev, zero=True)
+                shf = _f32(co, self.dev, zero=True)
+                plan.keep += [scf, shf]
+
+                def _replicate(scf=scf, shf=shf, sc=epi[0], sh=epi[1], n=L.Co, f=f, ld=out.ld):
+                    scf.view(f, ld)[:, :n].copy_(sc)
+                    shf.view(f, ld)[:, :n].copy_(sh)
+                    return 0
+                plan.folds.append((_replicate, (), None))
+                ep = Epilogue(scf.data_ptr(), shf.data_ptr(), residual.ptr() if residual else 0,
+                              f * residual.ld if residual else 0, 0, int(epi[2]), 0)
+            else:
+                assert residual is None or (residual.buf is out.buf and residual.coff == 0)
+                ep = Epilogue(0, 0, out.ptr() if residual else 0, co if residual else 0, 0, 0, L.sf.data_ptr() if stats else 0)
             wp = L.wptf if transposed else L.wpf
         else:
             cg = round_up(x.C, 16)
@@ -959,7 +978,9 @@ class SlowFastEngine:
             return False
         if self.graph_failed_all or plan.graph_failed.get(which):
             return False
-        if self.ddp is not None and not self.ddp.bucketer.use_avg:  # host-driven collectives (gloo) cannot be captured
+        if self.ddp is not None and (not self.ddp.bucketer.use_avg or not self.graphs_with_ddp):
+            # host-driven collectives (gloo) cannot be captured; NCCL ones can, opt-in (SFB_GRAPHS_DDP=1) until the
+            # capture of the side-stream all-reduces has been validated on the target box
             return False
         hit = plan.graphs.get(which)
         if hit is None:
