@@ -303,6 +303,42 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
                     int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
                     void* dz, int32_t dz_ld, int32_t dz_coff, void* stream);
 
+/* Backward of a ResBlock tail with a projection shortcut, O = ReLU(BN_c(y_c) + BN_s(y_s)) (first block of every stage;
+ * pytorchvideo ResBlock with branch1_conv / branch1_norm, reference model/my_slowfast.py:116-122): both BatchNorm
+ * backward passes share the masked gradient g = dO * mask(O), so ONE reduction and ONE apply pass serve both layers
+ * (replaces two sfb_bn_bwd_reduce + two sfb_bn_bwd_apply, which read dO and the mask four times).
+ *     dbeta_x += sum g ; dgamma_x += invstd_x * sum g*(y_x - mean_x) ;  dy_x = gamma_x*invstd_x*(g - dbeta_x/M - xhat_x*dgamma_x/M)
+ * mask_bits: packed ReLU mask of O as written by sfb_bn_add_relu(_raw).  dgamma / dbeta accumulate (zero them first). */
+typedef struct SfbBnTailSide {
+  const void* y;           /* raw conv output the BatchNorm normalised, bf16 (ptr, ld, coff) */
+  int32_t y_ld, y_coff;
+  const float* mean;       /* [C] batch mean, 1/sqrt(var + eps), BatchNorm weight */
+  const float* invstd;
+  const float* gamma;
+  float* dgamma;           /* [C] fp32 */
+  float* dbeta;
+  void* dy;                /* gradient of y, bf16 (ptr, ld, coff) */
+  int32_t dy_ld, dy_coff;
+} SfbBnTailSide;
+int sfb_bn_bwd_tail2(const void* dz, int32_t dz_ld, int32_t dz_coff, const uint8_t* mask_bits,
+                     const SfbBnTailSide* c, const SfbBnTailSide* s, int64_t M, int32_t C, void* stream);
+
+/* The whole backward of a stem's norm + activation + pool in two launches and without materialising the pool's input
+ * gradient (replaces autograd's max_pool3d_backward + threshold_backward + native_batch_norm_backward behind
+ * ResNetBasicStem, pytorchvideo create_res_basic_stem as configured at reference model/my_slowfast.py:107-113):
+ *     dz[n,t,h,w,c] = sfb_maxpool_bwd(dout, idx)                     -- rebuilt on the fly in both passes
+ *     g             = dz * [ y*scale + shift > 0 ]
+ *     dbeta += sum g ;  dgamma += invstd * sum g*(y - mean)            -- pass 1
+ *     dy    = gamma*invstd*(g - dbeta/M - xhat*dgamma/M)               -- pass 2 (the gradient of the stem conv's output)
+ * y is the raw stem conv output (N,T,H,W,C), dout / idx the pooled gradient and arg-max taps of sfb_maxpool_fwd.
+ * C/8 must divide 256. */
+int sfb_stem_pool_bn_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx,
+                         int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
+                         const void* y, int32_t y_ld, int32_t y_coff,
+                         const float* scale, const float* shift, const float* mean, const float* invstd,
+                         const float* gamma, float* dgamma, float* dbeta,
+                         void* dy, int32_t dy_ld, int32_t dy_coff, void* stream);
+
 /* replaces: PoolConcatPathway AvgPool3d(k, stride 1) + ResNetBasicHead Dropout + AdaptiveAvgPool3d(1)
  * (the Linear commutes with the mean).  feat[n, f_off + c] = mean_p drop(avgpool_k(x))[n, p, c].
  * dropout_p = 0 disables dropout; otherwise a counter-based mask from `seed` (recomputed in backward).

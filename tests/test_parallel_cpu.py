@@ -85,7 +85,7 @@ def test_engine_plan_inserts_one_launch_per_bucket():
     eng.ddp = EngineDDP(eng, bucket_mb=8.0)
     eng.refresh_weights(True)
     plan = eng.build_plan(2, 8, 8, 64, 64, True)
-    launches = [i for i, (fn, args, tag) in enumerate(plan.bwd) if getattr(fn, "__name__", "") == "<lambda>"]
+    launches = [i for i, (fn, args, tag) in enumerate(plan.bwd) if getattr(fn, "is_bucket_launch", False)]
     nb = len(eng.ddp.bucketer.buckets)
     assert nb >= 10 and len(launches) == nb
     assert launches[-1] == len(plan.bwd) - 1 or launches[-1] > len(plan.bwd) - 8  # stems finish last

@@ -40,6 +40,13 @@ class BnBwdFuse(C.Structure):
                 ("dbeta", C.c_void_p), ("C", C.c_int32), ("fold_ld", C.c_int32)]
 
 
+class BnTailSide(C.Structure):
+    """SfbBnTailSide (include/sfb200.h): one of the two BatchNorms of a projection-shortcut block tail"""
+    _fields_ = [("y", C.c_void_p), ("y_ld", C.c_int32), ("y_coff", C.c_int32), ("mean", C.c_void_p), ("invstd", C.c_void_p),
+                ("gamma", C.c_void_p), ("dgamma", C.c_void_p), ("dbeta", C.c_void_p), ("dy", C.c_void_p),
+                ("dy_ld", C.c_int32), ("dy_coff", C.c_int32)]
+
+
 _i32, _i64, _u64, _f32, _vp = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_void_p
 
 
@@ -87,6 +94,9 @@ SIGNATURES = {
                          _i32, _i64, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp],
     "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
     "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
+    "sfb_bn_bwd_tail2": [_vp, _i32, _i32, _vp, C.POINTER(BnTailSide), C.POINTER(BnTailSide), _i64, _i32, _vp],
+    "sfb_stem_pool_bn_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
+                             _vp, _vp, _i32, _i32, _vp],
     "sfb_head_pool_fwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
     "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
     "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],

@@ -598,6 +598,156 @@ bn_bwd_apply_kernel(View dz, View y, View msk, const uint8_t* __restrict__ mask_
   }
 }
 
+// ---- block tail with a projection shortcut: both BatchNorms in one reduce pass and one apply pass ----------------------------
+// O = ReLU(BN_c(y_c) + BN_s(y_s)) (first block of every stage): the two BatchNorm backward passes share the masked
+// gradient g = dO * mask(O).  Run one after the other they read dO and the mask four times; here one reduction
+// (dO, bits, y_c, y_s -> both layers' sums) and one apply (-> dy_c and dy_s) read them twice.
+struct BnTail2 {
+  View yc, ys;
+  const float* mean_c; const float* invstd_c; const float* gamma_c; float* dgamma_c; float* dbeta_c;
+  const float* mean_s; const float* invstd_s; const float* gamma_s; float* dgamma_s; float* dbeta_s;
+};
+constexpr int kTail2Unroll = 4;
+__global__ void __launch_bounds__(kRedThreads, 2)
+bn_bwd_tail2_reduce_kernel(View dz, const uint8_t* __restrict__ mask_bits, BnTail2 t, long long M, int C) {
+  __shared__ float red[kRedThreads * 24];
+  const int CV = C >> 3;
+  const int RL = kRedThreads / CV;
+  const int tx = threadIdx.x % CV;
+  const int ty = threadIdx.x / CV;
+  const int c = tx << 3;
+  float s1[8], sc_[8], ss_[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { s1[i] = 0.f; sc_[i] = 0.f; ss_[i] = 0.f; }
+  if (ty < RL) {
+    float mc[8], ms[8];
+    load8f(t.mean_c + c, mc);
+    load8f(t.mean_s + c, ms);
+    const long long stride = (long long)gridDim.x * RL;
+    for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * kTail2Unroll) {
+      uint4 qd[kTail2Unroll], qc[kTail2Unroll], qs[kTail2Unroll];
+      uint32_t qb[kTail2Unroll];
+#pragma unroll
+      for (int u = 0; u < kTail2Unroll; ++u) {
+        const long long m = m0 + u * stride;
+        if (m < M) {
+          qd[u] = vload(dz, m, c);
+          qc[u] = vload(t.yc, m, c);
+          qs[u] = vload(t.ys, m, c);
+          qb[u] = mask_bits[m * CV + tx];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kTail2Unroll; ++u) {
+        if (m0 + u * stride < M) {
+          float g[8], a[8], b[8];
+          unpack8(qd[u], g);
+          unpack8(qc[u], a);
+          unpack8(qs[u], b);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            g[i] = (qb[u] >> i) & 1u ? g[i] : 0.f;
+            s1[i] += g[i];
+            sc_[i] = fmaf(g[i], a[i] - mc[i], sc_[i]);
+            ss_[i] = fmaf(g[i], b[i] - ms[i], ss_[i]);
+          }
+        }
+      }
+    }
+    float ic[8], is[8];
+    load8f(t.invstd_c + c, ic);
+    load8f(t.invstd_s + c, is);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { sc_[i] *= ic[i]; ss_[i] *= is[i]; }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    red[threadIdx.x * 24 + i] = s1[i];
+    red[threadIdx.x * 24 + 8 + i] = sc_[i];
+    red[threadIdx.x * 24 + 16 + i] = ss_[i];
+  }
+  __syncthreads();
+  for (int q = threadIdx.x; q < CV * 24; q += kRedThreads) {
+    const int cv = q / 24, e = q % 24;
+    float acc = 0.f;
+    for (int r = 0; r < RL; ++r) acc += red[(r * CV + cv) * 24 + e];
+    if (e < 8) {
+      atomicAdd(t.dbeta_c + cv * 8 + e, acc);
+      atomicAdd(t.dbeta_s + cv * 8 + e, acc);
+    } else if (e < 16) {
+      atomicAdd(t.dgamma_c + cv * 8 + (e - 8), acc);
+    } else {
+      atomicAdd(t.dgamma_s + cv * 8 + (e - 16), acc);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kRedThreads, 2)
+bn_bwd_tail2_apply_kernel(View dz, const uint8_t* __restrict__ mask_bits, BnTail2 t, long long M, int C, float invM,
+                          ViewW dyc, ViewW dys) {
+  const int CV = C >> 3;
+  const int RL = kRedThreads / CV;
+  const int tx = threadIdx.x % CV;
+  const int ty = threadIdx.x / CV;
+  if (ty >= RL) return;
+  const int c = tx << 3;
+  // dy = gamma*invstd*(g - dbeta/M - xhat*dgamma/M) = k0*g - ka*y + kb per layer
+  float k0c[8], kac[8], kbc[8], k0s[8], kas[8], kbs[8];
+  {
+    float ga[8], dg[8], db[8], mu[8], is[8];
+    load8f(t.mean_c + c, mu); load8f(t.invstd_c + c, is); load8f(t.gamma_c + c, ga);
+    load8f(t.dgamma_c + c, dg); load8f(t.dbeta_c + c, db);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      k0c[i] = ga[i] * is[i];
+      kac[i] = k0c[i] * dg[i] * invM * is[i];
+      kbc[i] = kac[i] * mu[i] - k0c[i] * db[i] * invM;
+    }
+    load8f(t.mean_s + c, mu); load8f(t.invstd_s + c, is); load8f(t.gamma_s + c, ga);
+    load8f(t.dgamma_s + c, dg); load8f(t.dbeta_s + c, db);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      k0s[i] = ga[i] * is[i];
+      kas[i] = k0s[i] * dg[i] * invM * is[i];
+      kbs[i] = kas[i] * mu[i] - k0s[i] * db[i] * invM;
+    }
+  }
+  constexpr int U = 2;
+  const long long stride = (long long)gridDim.x * RL;
+  for (long long m0 = (long long)blockIdx.x * RL + ty; m0 < M; m0 += stride * U) {
+    uint4 qd[U], qc[U], qs[U];
+    uint32_t qb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long m = m0 + u * stride;
+      if (m < M) {
+        qd[u] = vload(dz, m, c);
+        qc[u] = vload(t.yc, m, c);
+        qs[u] = vload(t.ys, m, c);
+        qb[u] = mask_bits[m * CV + tx];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long m = m0 + u * stride;
+      if (m < M) {
+        float g[8], a[8], b[8], oc[8], os[8];
+        unpack8(qd[u], g);
+        unpack8(qc[u], a);
+        unpack8(qs[u], b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          g[i] = (qb[u] >> i) & 1u ? g[i] : 0.f;
+          oc[i] = fmaf(k0c[i], g[i], fmaf(-kac[i], a[i], kbc[i]));
+          os[i] = fmaf(k0s[i], g[i], fmaf(-kas[i], b[i], kbs[i]));
+        }
+        vstore(dyc, m, c, pack8(oc));
+        vstore(dys, m, c, pack8(os));
+      }
+    }
+  }
+}
+
 // ---- stem max-pool (1,3,3)/s(1,2,2)/p(0,1,1) with fused BN+ReLU on load ---------------------------------
 __global__ void maxpool_fwd_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, int N,
                                    int T, int H, int W, int C, ViewW out, uint8_t* __restrict__ idx_out) {
@@ -646,6 +796,118 @@ __global__ void maxpool_fwd_kernel(View y, const float* __restrict__ scale, cons
   }
 }
 
+// gradient of the stem max-pool w.r.t. its input pixel (h, w) of frame q, 8 channels from c: the sum over the (at most four)
+// windows that cover the pixel of dout[window] where the window's arg-max is this pixel
+__device__ __forceinline__ void maxpool_bwd_gather(const View& dout, const uint8_t* __restrict__ idxs, long long q, int h,
+                                                   int w, int c, int C, int Ho, int Wo, float* acc) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+  const int ha = (h + 1) >> 1, kha = h + 1 - 2 * ha;
+  const int wa = (w + 1) >> 1, kwa = w + 1 - 2 * wa;
+#pragma unroll
+  for (int a = 0; a < 2; ++a) {
+    const int ho = ha - a, kh = kha + 2 * a;
+    const bool vh = a == 0 ? ho < Ho : (kha == 0 && ho >= 0);
+#pragma unroll
+    for (int bq = 0; bq < 2; ++bq) {
+      const int wo = wa - bq, kw = kwa + 2 * bq;
+      const bool vw = bq == 0 ? wo < Wo : (kwa == 0 && wo >= 0);
+      if (vh && vw) {
+        const long long opix = (q * Ho + ho) * Wo + wo;
+        const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
+        uint4 d = vload(dout, opix, c);
+        const uint32_t tap4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
+        const uint32_t m0 = __vcmpeq4(pk.x, tap4), m1 = __vcmpeq4(pk.y, tap4);  // 0xFF per matching channel
+        d.x &= __byte_perm(m0, 0, 0x1100);
+        d.y &= __byte_perm(m0, 0, 0x3322);
+        d.z &= __byte_perm(m1, 0, 0x1100);
+        d.w &= __byte_perm(m1, 0, 0x3322);
+        float f[8];
+        unpack8(d, f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += f[i];
+      }
+    }
+  }
+}
+
+// ---- stem backward: max-pool backward fused with the stem BatchNorm(+ReLU) backward -------------------------------------
+// The stem outputs are the largest tensors of the network (batch 64: 0.8 + 0.4 GB).  Unfused, their backward is three
+// passes -- maxpool_bwd writes dz, bn_bwd_reduce reads dz and y, bn_bwd_apply reads both again and writes dy -- 7.9 GB.
+// Here dz is never materialised: both BatchNorm passes rebuild it from the pooled gradient (a quarter of the size, cache
+// resident across the four pixels of a window) -- reduce reads y, apply reads y and writes dy: 4.6 GB.
+// MODE 0: dbeta += sum g, dgamma += invstd * sum g*(y - mean), g = dz * [y*scale+shift > 0]   (block partial sums in shared memory)
+// MODE 1: dy = k0*g - ka*y + kb  with the finished sums (same algebra as bn_bwd_apply_kernel)
+constexpr int kStemBwdThreads = 256;
+template <int MODE>
+__global__ void __launch_bounds__(kStemBwdThreads)
+stem_pool_bn_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, View y, const float* __restrict__ scale,
+                        const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
+                        const float* __restrict__ gamma, float* dgamma, float* dbeta, int N, int T, int H, int W, int C,
+                        float invM, ViewW dy) {
+  __shared__ float red[kStemBwdThreads * 16];
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+  const int CV = C >> 3;           // divides the block size (C = 8 ... 64 here; checked on the host): a thread keeps its channels
+  const unsigned per_frame = (unsigned)(H * W * CV);
+  const long long q = blockIdx.y;  // frame n*T + t
+  const int c = (int)(threadIdx.x % (unsigned)CV) << 3;
+  float sc[8], sh[8], mu[8], k0[8], ka[8], kb[8], s1[8], s2[8];
+  load8f(scale + c, sc);
+  load8f(shift + c, sh);
+  load8f(mean + c, mu);
+  if (MODE == 1) {
+    float ga[8], is[8], dg[8], db[8];
+    load8f(gamma + c, ga); load8f(invstd + c, is); load8f(dgamma + c, dg); load8f(dbeta + c, db);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      k0[i] = ga[i] * is[i];
+      ka[i] = k0[i] * dg[i] * invM * is[i];
+      kb[i] = ka[i] * mu[i] - k0[i] * db[i] * invM;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < per_frame; idx += gridDim.x * blockDim.x) {
+    const unsigned pf = idx / (unsigned)CV;
+    const int w = (int)(pf % (unsigned)W);
+    const int h = (int)(pf / (unsigned)W);
+    const long long ipix = q * (H * W) + pf;
+    const uint4 yq = vload(y, ipix, c);
+    float g[8], yv[8];
+    maxpool_bwd_gather(dout, idxs, q, h, w, c, C, Ho, Wo, g);
+    unpack8(yq, yv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], sc[i], sh[i]) > 0.f ? g[i] : 0.f;
+    if (MODE == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], yv[i] - mu[i], s2[i]); }
+    } else {
+      float o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = fmaf(k0[i], g[i], fmaf(-ka[i], yv[i], kb[i]));
+      vstore(dy, ipix, c, pack8(o));
+    }
+  }
+  if (MODE == 0) {
+    float is[8];
+    load8f(invstd + c, is);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      red[threadIdx.x * 16 + i] = s1[i];
+      red[threadIdx.x * 16 + 8 + i] = s2[i] * is[i];
+    }
+    __syncthreads();
+    const int RL = kStemBwdThreads / CV;
+    for (int t = threadIdx.x; t < CV * 16; t += kStemBwdThreads) {
+      const int cv = t / 16, e = t % 16;
+      float acc = 0.f;
+      for (int r = 0; r < RL; ++r) acc += red[(r * CV + cv) * 16 + e];
+      if (e < 8) atomicAdd(dbeta + cv * 8 + e, acc);
+      else atomicAdd(dgamma + cv * 8 + (e - 8), acc);
+    }
+  }
+}
+
 __global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, int N, int T, int H, int W, int C,
                                    ViewW dz) {
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
@@ -658,41 +920,13 @@ __global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, 
     const int w = (int)(pf % (unsigned)W);
     const int h = (int)(pf / (unsigned)W);
     const long long ipix = q * (H * W) + pf;
-    float acc[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
     // The windows covering input (h, w): ho = (h+1)/2 with tap kh = h+1-2*ho (0 or 1) and, when that tap is 0, also
     // ho-1 with tap 2 -- same along w.  Written as two candidates per dimension with validity predicates instead of
     // parity tests inside a 3x3 tap loop: neighbouring lanes have opposite parities, so the tap loop made every warp
     // run all taps with half its lanes idle.  The arg-max bytes are compared four at a time and turned into
     // bf16-pair masks (no per-channel extract / compare / select).
-    const int ha = (h + 1) >> 1, kha = h + 1 - 2 * ha;
-    const int wa = (w + 1) >> 1, kwa = w + 1 - 2 * wa;
-#pragma unroll
-    for (int a = 0; a < 2; ++a) {
-      const int ho = ha - a, kh = kha + 2 * a;
-      const bool vh = a == 0 ? ho < Ho : (kha == 0 && ho >= 0);
-#pragma unroll
-      for (int bq = 0; bq < 2; ++bq) {
-        const int wo = wa - bq, kw = kwa + 2 * bq;
-        const bool vw = bq == 0 ? wo < Wo : (kwa == 0 && wo >= 0);
-        if (vh && vw) {
-          const long long opix = (q * Ho + ho) * Wo + wo;
-          const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
-          uint4 d = vload(dout, opix, c);
-          const uint32_t tap4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
-          const uint32_t m0 = __vcmpeq4(pk.x, tap4), m1 = __vcmpeq4(pk.y, tap4);  // 0xFF per matching channel
-          d.x &= __byte_perm(m0, 0, 0x1100);
-          d.y &= __byte_perm(m0, 0, 0x3322);
-          d.z &= __byte_perm(m1, 0, 0x1100);
-          d.w &= __byte_perm(m1, 0, 0x3322);
-          float f[8];
-          unpack8(d, f);
-#pragma unroll
-          for (int i = 0; i < 8; ++i) acc[i] += f[i];
-        }
-      }
-    }
+    float acc[8];
+    maxpool_bwd_gather(dout, idxs, q, h, w, c, C, Ho, Wo, acc);
     vstore(dz, ipix, c, pack8(acc));
   }
 }

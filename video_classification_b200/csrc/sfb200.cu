@@ -1341,6 +1341,33 @@ int sfb_bn_bwd_apply(const void* dz, int32_t dz_ld, int32_t dz_coff, const void*
   return SFB_OK;
 }
 
+int sfb_bn_bwd_tail2(const void* dz, int32_t dz_ld, int32_t dz_coff, const uint8_t* mask_bits, const SfbBnTailSide* c,
+                     const SfbBnTailSide* s, int64_t M, int32_t C, void* stream) {
+  if (M <= 0 || C <= 0 || (C & 7) || C > 2048 || !mask_bits || !c || !s) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dz, dz_ld, dz_coff, C)) return SFB_ERR_BAD_ARG;
+  const SfbBnTailSide* sides[2] = {c, s};
+  for (const SfbBnTailSide* q : sides) {
+    if (!q->mean || !q->invstd || !q->gamma || !q->dgamma || !q->dbeta) return SFB_ERR_BAD_ARG;
+    if (!view_ok(q->y, q->y_ld, q->y_coff, C) || !view_ok(q->dy, q->dy_ld, q->dy_coff, C)) return SFB_ERR_BAD_ARG;
+  }
+  View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
+  BnTail2 t;
+  t.yc = View{(const __nv_bfloat16*)c->y, c->y_ld, c->y_coff};
+  t.ys = View{(const __nv_bfloat16*)s->y, s->y_ld, s->y_coff};
+  t.mean_c = c->mean; t.invstd_c = c->invstd; t.gamma_c = c->gamma; t.dgamma_c = c->dgamma; t.dbeta_c = c->dbeta;
+  t.mean_s = s->mean; t.invstd_s = s->invstd; t.gamma_s = s->gamma; t.dgamma_s = s->dgamma; t.dbeta_s = s->dbeta;
+  ViewW vc{(__nv_bfloat16*)c->dy, c->dy_ld, c->dy_coff};
+  ViewW vs{(__nv_bfloat16*)s->dy, s->dy_ld, s->dy_coff};
+  const int RL = kRedThreads / (C >> 3);
+  const int grid_r = grid_for((M + (long long)RL * kTail2Unroll - 1) / ((long long)RL * kTail2Unroll), 1, 148 * 4);
+  bn_bwd_tail2_reduce_kernel<<<grid_r, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, mask_bits, t, M, C);
+  SFB_CHECK_LAUNCH("bn_bwd_tail2_reduce_kernel");
+  const int grid_a = grid_for((M + (long long)RL * 2 - 1) / ((long long)RL * 2), 1, 148 * 8);
+  bn_bwd_tail2_apply_kernel<<<grid_a, kRedThreads, 0, (cudaStream_t)stream>>>(vdz, mask_bits, t, M, C, 1.0f / (float)M, vc, vs);
+  SFB_CHECK_LAUNCH("bn_bwd_tail2_apply_kernel");
+  return SFB_OK;
+}
+
 int sfb_maxpool_fwd(const void* y, int32_t y_ld, int32_t y_coff, const float* scale, const float* shift, int32_t N,
                     int32_t T, int32_t H, int32_t W, int32_t C, void* out, int32_t o_ld, int32_t o_coff, uint8_t* idx,
                     void* stream) {
@@ -1369,6 +1396,32 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
   dim3 grid((unsigned)grid_for(per_frame, 256, 64), (unsigned)(N * T));
   maxpool_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vd, idx, N, T, H, W, C, vz);
   SFB_CHECK_LAUNCH("maxpool_bwd_kernel");
+  return SFB_OK;
+}
+
+int sfb_stem_pool_bn_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx, int32_t N, int32_t T,
+                         int32_t H, int32_t W, int32_t C, const void* y, int32_t y_ld, int32_t y_coff, const float* scale,
+                         const float* shift, const float* mean, const float* invstd, const float* gamma, float* dgamma,
+                         float* dbeta, void* dy, int32_t dy_ld, int32_t dy_coff, void* stream) {
+  if (N <= 0 || T <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7) || !idx) return SFB_ERR_BAD_ARG;
+  if (!scale || !shift || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dout, d_ld, d_coff, C) || !view_ok(y, y_ld, y_coff, C) || !view_ok(dy, dy_ld, dy_coff, C)) return SFB_ERR_BAD_ARG;
+  const int CV = C >> 3;
+  if (kStemBwdThreads % CV) return SFB_ERR_UNSUPPORTED;  // a thread keeps its 8 channels for the whole launch
+  if ((long long)N * T > 65535 || (long long)H * W * CV >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
+  View vd{(const __nv_bfloat16*)dout, d_ld, d_coff};
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  ViewW vz{(__nv_bfloat16*)dy, dy_ld, dy_coff};
+  const long long per_frame = (long long)H * W * CV;
+  // grid.x * block is a multiple of CV (256 % CV == 0): the grid-stride loop keeps a thread on its channel vector
+  dim3 grid((unsigned)grid_for(per_frame, kStemBwdThreads, 64), (unsigned)(N * T));
+  const float invM = 1.0f / ((float)N * (float)T * (float)H * (float)W);
+  stem_pool_bn_bwd_kernel<0><<<grid, kStemBwdThreads, 0, (cudaStream_t)stream>>>(vd, idx, vy, scale, shift, mean, invstd, gamma,
+                                                                                 dgamma, dbeta, N, T, H, W, C, invM, vz);
+  SFB_CHECK_LAUNCH("stem_pool_bn_bwd_kernel<reduce>");
+  stem_pool_bn_bwd_kernel<1><<<grid, kStemBwdThreads, 0, (cudaStream_t)stream>>>(vd, idx, vy, scale, shift, mean, invstd, gamma,
+                                                                                 dgamma, dbeta, N, T, H, W, C, invM, vz);
+  SFB_CHECK_LAUNCH("stem_pool_bn_bwd_kernel<apply>");
   return SFB_OK;
 }
 

@@ -129,7 +129,8 @@ class Plan:
         self.folds: List[Tuple] = []
         self.fold_key = None
         self.graphs = {}
-        self.graph_runs = {"fwd": 0, "bwd": 0}
+        self.graph_runs = {}
+        self.bwd_segments = None  # data parallel: the backward list cut at the bucket launches
         self.graph_failed = {}
 
 
@@ -906,9 +907,20 @@ class SlowFastEngine:
             self._emit(bwd, _probe, tag=(d["name"] + ".dO", dO))
             dyc = new_grad(yc)
             if s_ is not None:
-                self._bn_bwd(plan, bwd, c, dO, yc, O.bits, dyc)
+                # projection shortcut: both BatchNorms of the tail in one reduction + one apply pass (they share dO * mask)
                 dy1 = new_grad(y1)
-                self._bn_bwd(plan, bwd, s_, dO, y1, O.bits, dy1)
+                sides = []
+                for Lx, yx, dyx in ((c, yc, dyc), (s_, y1, dy1)):
+                    sides.append(_ffi.BnTailSide(yx.ptr(), yx.ld, yx.coff, Lx.mean.data_ptr(), Lx.invstd.data_ptr(),
+                                                 Lx.bn.weight.data_ptr(), Lx.dgamma.data_ptr(), Lx.dbeta.data_ptr(),
+                                                 dyx.ptr(), dyx.ld, dyx.coff))
+                plan.keep += sides
+                self._emit(bwd, self.lib.sfb_bn_bwd_tail2, dO.ptr(), dO.ld, dO.coff, O.bits.data_ptr(), C.byref(sides[0]),
+                           C.byref(sides[1]), yc.M, yc.C, self.stream, tag=(c.conv_name + ".dy", dyc))
+                if self.ddp is not None:
+                    for Lx in (c, s_):
+                        self.ddp.note_grad_ready(plan, bwd, Lx.bn.weight)
+                        self.ddp.note_grad_ready(plan, bwd, Lx.bn.bias)
             else:
                 # identity shortcut: the masked gradient g also flows straight to the block input
                 ensure_grad(X)
@@ -947,9 +959,21 @@ class SlowFastEngine:
             n_, t_, h_, w_ = y0.dims
             dz0 = new_grad(y0)
             g = out.grad
-            self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
-                       dz0.ptr(), dz0.ld, dz0.coff, self.stream)
-            self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
+            if 256 % max(L.Co // 8, 1) == 0 and L.Co % 8 == 0:
+                # max-pool backward + BatchNorm(+ReLU) backward in two passes that rebuild the pool's input gradient on
+                # the fly: the largest gradient tensor of the network is written once (as dy), never read back
+                bn = L.bn
+                self._emit(bwd, self.lib.sfb_stem_pool_bn_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_,
+                           L.Co, y0.ptr(), y0.ld, y0.coff, L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(),
+                           L.invstd.data_ptr(), bn.weight.data_ptr(), L.dgamma.data_ptr(), L.dbeta.data_ptr(),
+                           dz0.ptr(), dz0.ld, dz0.coff, self.stream, tag=(L.conv_name + ".dy", dz0))
+                if self.ddp is not None:
+                    self.ddp.note_grad_ready(plan, bwd, bn.weight)
+                    self.ddp.note_grad_ready(plan, bwd, bn.bias)
+            else:
+                self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
+                           dz0.ptr(), dz0.ld, dz0.coff, self.stream)
+                self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
             if isinstance(sr["x_in"], Act):
                 self._wgrad(plan, bwd, L, sr["x_in"], None, dz0)
             else:
@@ -978,13 +1002,9 @@ class SlowFastEngine:
             return False
         if self.graph_failed_all or plan.graph_failed.get(which):
             return False
-        if self.ddp is not None and (not self.ddp.bucketer.use_avg or not self.graphs_with_ddp):
-            # host-driven collectives (gloo) cannot be captured; NCCL ones can, opt-in (SFB_GRAPHS_DDP=1) until the
-            # capture of the side-stream all-reduces has been validated on the target box
-            return False
         hit = plan.graphs.get(which)
         if hit is None:
-            plan.graph_runs[which] += 1
+            plan.graph_runs[which] = plan.graph_runs.get(which, 0) + 1
             if plan.graph_runs[which] <= self.graph_after:
                 return False
             cur = torch.cuda.current_stream(self.dev)
@@ -1289,16 +1309,45 @@ class SlowFastEngine:
             if g is not None and g.data_ptr() == self.grad_views[id(prm)].data_ptr():
                 prm.grad = g.clone()
 
-        def body():
-            self.grad_flat.zero_()
-            if self.ddp is not None:
-                self.ddp.begin_backward(self)
-            self._run(plan.bwd)
-            if self.ddp is not None:
-                self.ddp.finish_backward(self)
+        if self.ddp is None or (self.graphs_with_ddp and self.ddp.bucketer.use_avg):
+            def body():
+                self.grad_flat.zero_()
+                if self.ddp is not None:
+                    self.ddp.begin_backward(self)
+                self._run(plan.bwd)
+                if self.ddp is not None:
+                    self.ddp.finish_backward(self)
 
-        if not self._graphed(plan, "bwd", body):
-            body()
+            if not self._graphed(plan, "bwd", body):
+                body()
+        else:
+            # data parallel: the bucket all-reduces are launched by the host between graph SEGMENTS (capturing NCCL's
+            # side-stream collectives inside one graph hung on this pool's driver / NCCL 2.28 -- profiles/ r3h; gloo
+            # collectives are host-driven anyway): the op list is cut at every bucket launch, each piece is its own graph
+            if plan.bwd_segments is None:
+                segs, cur_ops = [], []
+                for op in plan.bwd:
+                    if getattr(op[0], "is_bucket_launch", False):
+                        segs.append((cur_ops, op[0]))
+                        cur_ops = []
+                    else:
+                        cur_ops.append(op)
+                segs.append((cur_ops, None))
+                plan.bwd_segments = segs
+            self.ddp.begin_backward(self)
+            for i, (ops, launch) in enumerate(plan.bwd_segments):
+                def body(ops=ops, first=(i == 0)):
+                    if first:
+                        self.grad_flat.zero_()
+                    self._run(ops)
+
+                if not ops and i > 0:
+                    pass
+                elif not self._graphed(plan, ("bwd", i), body):
+                    body()
+                if launch is not None:
+                    launch()
+            self.ddp.finish_backward(self)
         # FRESH view objects, referenced by nobody else once returned: autograd then adopts them as .grad (no copy) instead
         # of cloning every gradient -- 332 device-to-device copies per step with views that the engine also holds
         flat = self.grad_flat

@@ -338,6 +338,24 @@ def maxpool_bwd(dout: Act, idx: torch.Tensor, dz: Act):
     return dz
 
 
+def bn_bwd_tail2(dz: Act, mask_bits: torch.Tensor, sides):
+    """sides = two tuples (y, mean, invstd, gamma, dgamma, dbeta, dy): both BatchNorms of a projection-shortcut tail in one
+    reduction + one apply pass (sfb_bn_bwd_tail2)"""
+    st = [_ffi.BnTailSide(y.ptr(), y.ld, y.coff, ptr(mean), ptr(invstd), ptr(gamma), ptr(dgamma), ptr(dbeta), dy.ptr(), dy.ld,
+                          dy.coff) for (y, mean, invstd, gamma, dgamma, dbeta, dy) in sides]
+    check(lib().sfb_bn_bwd_tail2(dz.ptr(), dz.ld, dz.coff, mask_bits.data_ptr(), C.byref(st[0]), C.byref(st[1]), dz.M, dz.C,
+                                 stream_ptr()), "sfb_bn_bwd_tail2")
+
+
+def stem_pool_bn_bwd(dout: Act, idx: torch.Tensor, y: Act, scale, shift, mean, invstd, gamma, dgamma, dbeta, dy: Act):
+    """max-pool backward + BatchNorm(+ReLU) backward of a stem, fused (sfb_stem_pool_bn_bwd)"""
+    N, T, H, W = y.dims
+    check(lib().sfb_stem_pool_bn_bwd(dout.ptr(), dout.ld, dout.coff, idx.data_ptr(), N, T, H, W, y.C, y.ptr(), y.ld, y.coff,
+                                     ptr(scale), ptr(shift), ptr(mean), ptr(invstd), ptr(gamma), ptr(dgamma), ptr(dbeta),
+                                     dy.ptr(), dy.ld, dy.coff, stream_ptr()), "sfb_stem_pool_bn_bwd")
+    return dy
+
+
 def head_pool_fwd(x: Act, k, dropout_p, seed, feat: torch.Tensor, f_off: int, seed_dev: torch.Tensor = None):
     N, T, H, W = x.dims
     check(lib().sfb_head_pool_fwd(x.ptr(), x.ld, x.coff, N, T, H, W, x.C, k[0], k[1], k[2], float(dropout_p), seed,

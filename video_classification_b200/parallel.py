@@ -154,7 +154,11 @@ class EngineDDP:
         b = self.bucketer.mark_ready(self.engine.grad_offsets[id(param)])
         if b is not None:
             bk = self.bucketer
-            lst.append((lambda bk=bk, b=b: bk.launch(b), (), None))
+
+            def launch(bk=bk, b=b):
+                return bk.launch(b)
+            launch.is_bucket_launch = True  # the engine cuts its backward CUDA graphs at these entries
+            lst.append((launch, (), None))
 
     # called around every execution of the backward op list ----------------------------------------
     def begin_backward(self, engine):
