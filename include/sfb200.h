@@ -323,22 +323,6 @@ typedef struct SfbBnTailSide {
 int sfb_bn_bwd_tail2(const void* dz, int32_t dz_ld, int32_t dz_coff, const uint8_t* mask_bits,
                      const SfbBnTailSide* c, const SfbBnTailSide* s, int64_t M, int32_t C, void* stream);
 
-/* The whole backward of a stem's norm + activation + pool in two launches and without materialising the pool's input
- * gradient (replaces autograd's max_pool3d_backward + threshold_backward + native_batch_norm_backward behind
- * ResNetBasicStem, pytorchvideo create_res_basic_stem as configured at reference model/my_slowfast.py:107-113):
- *     dz[n,t,h,w,c] = sfb_maxpool_bwd(dout, idx)                     -- rebuilt on the fly in both passes
- *     g             = dz * [ y*scale + shift > 0 ]
- *     dbeta += sum g ;  dgamma += invstd * sum g*(y - mean)            -- pass 1
- *     dy    = gamma*invstd*(g - dbeta/M - xhat*dgamma/M)               -- pass 2 (the gradient of the stem conv's output)
- * y is the raw stem conv output (N,T,H,W,C), dout / idx the pooled gradient and arg-max taps of sfb_maxpool_fwd.
- * C/8 must divide 256. */
-int sfb_stem_pool_bn_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx,
-                         int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
-                         const void* y, int32_t y_ld, int32_t y_coff,
-                         const float* scale, const float* shift, const float* mean, const float* invstd,
-                         const float* gamma, float* dgamma, float* dbeta,
-                         void* dy, int32_t dy_ld, int32_t dy_coff, void* stream);
-
 /* replaces: PoolConcatPathway AvgPool3d(k, stride 1) + ResNetBasicHead Dropout + AdaptiveAvgPool3d(1)
  * (the Linear commutes with the mean).  feat[n, f_off + c] = mean_p drop(avgpool_k(x))[n, p, c].
  * dropout_p = 0 disables dropout; otherwise a counter-based mask from `seed` (recomputed in backward).

@@ -149,7 +149,7 @@ def _worker(rank, world, port, backend, ret):
             loss.backward()
             opt.step()
             torch.cuda.synchronize(dev)
-            mark(f"step {it} done, graphs: {sorted(k for pl in eng.plans.values() for k in pl.graphs)} errors: {eng.graph_errors[:1]}")
+            mark(f"step {it} done, graphs: {sum(len(pl.graphs) for pl in eng.plans.values())} errors: {eng.graph_errors[:1]}")
         torch.cuda.synchronize(dev)
         # in the plain training loop .grad of every live parameter aliases the arena the all-reduce ran on (autograd
         # adopts the returned views; with retain_graph above it clones them, which is why (a) reads the arena itself)

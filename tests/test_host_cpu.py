@@ -116,12 +116,9 @@ def test_engine_plans_a_training_step_on_meta(variant, shape, lib):
     fused = [op for op in dgrads if op[0] is lib.sfb_conv_dgrad_bn]
     assert len(fused) == 2 * 16 * 2
     reduces = [op for op in plan.bwd if op[0] is lib.sfb_bn_bwd_reduce]
-    # ... the two stems run max-pool backward + BatchNorm backward as one fused pair of passes, and the eight blocks with
-    # a projection shortcut reduce both BatchNorms of their tail in one pass (sfb_bn_bwd_tail2)
-    assert len([op for op in plan.bwd if op[0] is lib.sfb_stem_pool_bn_bwd]) == 2
-    assert not [op for op in plan.bwd if op[0] is lib.sfb_maxpool_bwd]
+    # ... and the eight blocks with a projection shortcut reduce both BatchNorms of their tail in one pass
     assert len([op for op in plan.bwd if op[0] is lib.sfb_bn_bwd_tail2]) == 8
-    assert len(reduces) == n_conv - len(fused) - 2 - 16
+    assert len(reduces) == n_conv - len(fused) - 16
     assert tuple(plan.logits.shape) == (shape[0], 249)
     # the lateral output lands behind the Slow stage output in ONE buffer (torch.cat never happens)
     bufs = eng.tagged_buffers(plan)

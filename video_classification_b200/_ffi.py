@@ -95,8 +95,6 @@ SIGNATURES = {
     "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
     "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_bn_bwd_tail2": [_vp, _i32, _i32, _vp, C.POINTER(BnTailSide), C.POINTER(BnTailSide), _i64, _i32, _vp],
-    "sfb_stem_pool_bn_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp,
-                             _vp, _vp, _i32, _i32, _vp],
     "sfb_head_pool_fwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
     "sfb_head_pool_bwd": [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _f32, _u64, _vp, _vp, _i32, _i32, _vp],
     "sfb_fc_fwd": [_vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp],

@@ -831,83 +831,6 @@ __device__ __forceinline__ void maxpool_bwd_gather(const View& dout, const uint8
   }
 }
 
-// ---- stem backward: max-pool backward fused with the stem BatchNorm(+ReLU) backward -------------------------------------
-// The stem outputs are the largest tensors of the network (batch 64: 0.8 + 0.4 GB).  Unfused, their backward is three
-// passes -- maxpool_bwd writes dz, bn_bwd_reduce reads dz and y, bn_bwd_apply reads both again and writes dy -- 7.9 GB.
-// Here dz is never materialised: both BatchNorm passes rebuild it from the pooled gradient (a quarter of the size, cache
-// resident across the four pixels of a window) -- reduce reads y, apply reads y and writes dy: 4.6 GB.
-// MODE 0: dbeta += sum g, dgamma += invstd * sum g*(y - mean), g = dz * [y*scale+shift > 0]   (block partial sums in shared memory)
-// MODE 1: dy = k0*g - ka*y + kb  with the finished sums (same algebra as bn_bwd_apply_kernel)
-constexpr int kStemBwdThreads = 256;
-template <int MODE>
-__global__ void __launch_bounds__(kStemBwdThreads)
-stem_pool_bn_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, View y, const float* __restrict__ scale,
-                        const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
-                        const float* __restrict__ gamma, float* dgamma, float* dbeta, int N, int T, int H, int W, int C,
-                        float invM, ViewW dy) {
-  __shared__ float red[kStemBwdThreads * 16];
-  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
-  const int CV = C >> 3;           // divides the block size (C = 8 ... 64 here; checked on the host): a thread keeps its channels
-  const unsigned per_frame = (unsigned)(H * W * CV);
-  const long long q = blockIdx.y;  // frame n*T + t
-  const int c = (int)(threadIdx.x % (unsigned)CV) << 3;
-  float sc[8], sh[8], mu[8], k0[8], ka[8], kb[8], s1[8], s2[8];
-  load8f(scale + c, sc);
-  load8f(shift + c, sh);
-  load8f(mean + c, mu);
-  if (MODE == 1) {
-    float ga[8], is[8], dg[8], db[8];
-    load8f(gamma + c, ga); load8f(invstd + c, is); load8f(dgamma + c, dg); load8f(dbeta + c, db);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      k0[i] = ga[i] * is[i];
-      ka[i] = k0[i] * dg[i] * invM * is[i];
-      kb[i] = ka[i] * mu[i] - k0[i] * db[i] * invM;
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
-  for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < per_frame; idx += gridDim.x * blockDim.x) {
-    const unsigned pf = idx / (unsigned)CV;
-    const int w = (int)(pf % (unsigned)W);
-    const int h = (int)(pf / (unsigned)W);
-    const long long ipix = q * (H * W) + pf;
-    const uint4 yq = vload(y, ipix, c);
-    float g[8], yv[8];
-    maxpool_bwd_gather(dout, idxs, q, h, w, c, C, Ho, Wo, g);
-    unpack8(yq, yv);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) g[i] = fmaf(yv[i], sc[i], sh[i]) > 0.f ? g[i] : 0.f;
-    if (MODE == 0) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) { s1[i] += g[i]; s2[i] = fmaf(g[i], yv[i] - mu[i], s2[i]); }
-    } else {
-      float o[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) o[i] = fmaf(k0[i], g[i], fmaf(-ka[i], yv[i], kb[i]));
-      vstore(dy, ipix, c, pack8(o));
-    }
-  }
-  if (MODE == 0) {
-    float is[8];
-    load8f(invstd + c, is);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      red[threadIdx.x * 16 + i] = s1[i];
-      red[threadIdx.x * 16 + 8 + i] = s2[i] * is[i];
-    }
-    __syncthreads();
-    const int RL = kStemBwdThreads / CV;
-    for (int t = threadIdx.x; t < CV * 16; t += kStemBwdThreads) {
-      const int cv = t / 16, e = t % 16;
-      float acc = 0.f;
-      for (int r = 0; r < RL; ++r) acc += red[(r * CV + cv) * 16 + e];
-      if (e < 8) atomicAdd(dbeta + cv * 8 + e, acc);
-      else atomicAdd(dgamma + cv * 8 + (e - 8), acc);
-    }
-  }
-}
-
 __global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, int N, int T, int H, int W, int C,
                                    ViewW dz) {
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;

@@ -1399,32 +1399,6 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
   return SFB_OK;
 }
 
-int sfb_stem_pool_bn_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_t* idx, int32_t N, int32_t T,
-                         int32_t H, int32_t W, int32_t C, const void* y, int32_t y_ld, int32_t y_coff, const float* scale,
-                         const float* shift, const float* mean, const float* invstd, const float* gamma, float* dgamma,
-                         float* dbeta, void* dy, int32_t dy_ld, int32_t dy_coff, void* stream) {
-  if (N <= 0 || T <= 0 || H <= 0 || W <= 0 || C <= 0 || (C & 7) || !idx) return SFB_ERR_BAD_ARG;
-  if (!scale || !shift || !mean || !invstd || !gamma || !dgamma || !dbeta) return SFB_ERR_BAD_ARG;
-  if (!view_ok(dout, d_ld, d_coff, C) || !view_ok(y, y_ld, y_coff, C) || !view_ok(dy, dy_ld, dy_coff, C)) return SFB_ERR_BAD_ARG;
-  const int CV = C >> 3;
-  if (kStemBwdThreads % CV) return SFB_ERR_UNSUPPORTED;  // a thread keeps its 8 channels for the whole launch
-  if ((long long)N * T > 65535 || (long long)H * W * CV >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
-  View vd{(const __nv_bfloat16*)dout, d_ld, d_coff};
-  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
-  ViewW vz{(__nv_bfloat16*)dy, dy_ld, dy_coff};
-  const long long per_frame = (long long)H * W * CV;
-  // grid.x * block is a multiple of CV (256 % CV == 0): the grid-stride loop keeps a thread on its channel vector
-  dim3 grid((unsigned)grid_for(per_frame, kStemBwdThreads, 64), (unsigned)(N * T));
-  const float invM = 1.0f / ((float)N * (float)T * (float)H * (float)W);
-  stem_pool_bn_bwd_kernel<0><<<grid, kStemBwdThreads, 0, (cudaStream_t)stream>>>(vd, idx, vy, scale, shift, mean, invstd, gamma,
-                                                                                 dgamma, dbeta, N, T, H, W, C, invM, vz);
-  SFB_CHECK_LAUNCH("stem_pool_bn_bwd_kernel<reduce>");
-  stem_pool_bn_bwd_kernel<1><<<grid, kStemBwdThreads, 0, (cudaStream_t)stream>>>(vd, idx, vy, scale, shift, mean, invstd, gamma,
-                                                                                 dgamma, dbeta, N, T, H, W, C, invM, vz);
-  SFB_CHECK_LAUNCH("stem_pool_bn_bwd_kernel<apply>");
-  return SFB_OK;
-}
-
 int sfb_head_pool_fwd(const void* x, int32_t x_ld, int32_t x_coff, int32_t N, int32_t T, int32_t H, int32_t W, int32_t C,
                       int32_t kT, int32_t kH, int32_t kW, float dropout_p, uint64_t seed, const uint64_t* seed_dev,
                       float* feat, int32_t f_ld, int32_t f_off, void* stream) {

@@ -959,21 +959,12 @@ class SlowFastEngine:
             n_, t_, h_, w_ = y0.dims
             dz0 = new_grad(y0)
             g = out.grad
-            if 256 % max(L.Co // 8, 1) == 0 and L.Co % 8 == 0:
-                # max-pool backward + BatchNorm(+ReLU) backward in two passes that rebuild the pool's input gradient on
-                # the fly: the largest gradient tensor of the network is written once (as dy), never read back
-                bn = L.bn
-                self._emit(bwd, self.lib.sfb_stem_pool_bn_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_,
-                           L.Co, y0.ptr(), y0.ld, y0.coff, L.scale.data_ptr(), L.shift.data_ptr(), L.mean.data_ptr(),
-                           L.invstd.data_ptr(), bn.weight.data_ptr(), L.dgamma.data_ptr(), L.dbeta.data_ptr(),
-                           dz0.ptr(), dz0.ld, dz0.coff, self.stream, tag=(L.conv_name + ".dy", dz0))
-                if self.ddp is not None:
-                    self.ddp.note_grad_ready(plan, bwd, bn.weight)
-                    self.ddp.note_grad_ready(plan, bwd, bn.bias)
-            else:
-                self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
-                           dz0.ptr(), dz0.ld, dz0.coff, self.stream)
-                self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
+            # (a fused max-pool-backward + BatchNorm-backward pair that rebuilds the pool gradient in both passes was
+            # measured slower -- 3.1 ms against 0.8 + 1.0 ms: the gather through the arg-max bytes is the expensive part
+            # and ran twice; profiles/r3j_bench.json)
+            self._emit(bwd, self.lib.sfb_maxpool_bwd, g.ptr(), g.ld, g.coff, sr["idx"].data_ptr(), n_, t_, h_, w_, L.Co,
+                       dz0.ptr(), dz0.ld, dz0.coff, self.stream)
+            self._bn_bwd(plan, bwd, L, dz0, y0, None, dz0)
             if isinstance(sr["x_in"], Act):
                 self._wgrad(plan, bwd, L, sr["x_in"], None, dz0)
             else:

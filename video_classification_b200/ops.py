@@ -347,15 +347,6 @@ def bn_bwd_tail2(dz: Act, mask_bits: torch.Tensor, sides):
                                  stream_ptr()), "sfb_bn_bwd_tail2")
 
 
-def stem_pool_bn_bwd(dout: Act, idx: torch.Tensor, y: Act, scale, shift, mean, invstd, gamma, dgamma, dbeta, dy: Act):
-    """max-pool backward + BatchNorm(+ReLU) backward of a stem, fused (sfb_stem_pool_bn_bwd)"""
-    N, T, H, W = y.dims
-    check(lib().sfb_stem_pool_bn_bwd(dout.ptr(), dout.ld, dout.coff, idx.data_ptr(), N, T, H, W, y.C, y.ptr(), y.ld, y.coff,
-                                     ptr(scale), ptr(shift), ptr(mean), ptr(invstd), ptr(gamma), ptr(dgamma), ptr(dbeta),
-                                     dy.ptr(), dy.ld, dy.coff, stream_ptr()), "sfb_stem_pool_bn_bwd")
-    return dy
-
-
 def head_pool_fwd(x: Act, k, dropout_p, seed, feat: torch.Tensor, f_off: int, seed_dev: torch.Tensor = None):
     N, T, H, W = x.dims
     check(lib().sfb_head_pool_fwd(x.ptr(), x.ld, x.coff, N, T, H, W, x.C, k[0], k[1], k[2], float(dropout_p), seed,
