@@ -623,7 +623,7 @@ def main():
     if kernels:
         # dominant kernel = conv_tma_kernel<BN,BRES>: sfb_conv_gemm forward and input-gradient launches are the same
         # CUDA kernel (csrc/conv_tma.cuh); the weight gradient is a different kernel and listed in the breakdown
-        fam = [kernels[k] for k in ("sfb_conv_gemm[fprop]", "sfb_conv_gemm[dgrad]") if k in kernels]
+        fam = [kernels[k] for k in ("sfb_conv_gemm[fprop]", "sfb_conv_gemm[dgrad]", "sfb_conv_dgrad_bn") if k in kernels]
         if fam:
             ms = sum(v["ms"] for v in fam)
             tfl = sum(v["algorithmic_tflop"] for v in fam)
@@ -631,7 +631,8 @@ def main():
             # kernel launches, not API calls: a strided dgrad is one conv_tma_kernel launch per parity class
             nk = sum(v.get("kernel_launches", v["launches"]) for v in fam)
             ach = tfl * 1e3 / ms
-            line["roofline"] = {"kernel": "conv_tma_kernel (sfb_conv_gemm fprop + dgrad)", "bound": "tensor", "achieved": ach,
+            line["roofline"] = {"kernel": "conv_tma_kernel (sfb_conv_gemm fprop + dgrad, sfb_conv_dgrad_bn)", "bound": "tensor",
+                                "achieved": ach,
                                 "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach / peaks["sustained"],
                                 "traffic": None, "launches_per_step": nk, "api_calls_per_step": calls, "ms_per_step": ms,
                                 "algorithmic_tflop_per_step": tfl,

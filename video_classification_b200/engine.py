@@ -1056,9 +1056,10 @@ class SlowFastEngine:
         for name, e0, e1, args, _nk in self.prof:
             desc, gf = "", 0.0
             name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
-            if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
+            if name in ("sfb_conv_gemm", "sfb_conv_wgrad", "sfb_conv_dgrad_bn"):
                 g = args[0]._obj
-                kind = "wgrad" if name == "sfb_conv_wgrad" else ("dgrad" if g.transposed else "fprop")
+                kind = "wgrad" if name == "sfb_conv_wgrad" else ("dgrad+bn" if name == "sfb_conv_dgrad_bn" else
+                                                                  ("dgrad" if g.transposed else "fprop"))
                 M = getattr(g, "real_m", None) or (g.N * g.Ti * g.Hi * g.Wi if g.transposed else g.N * g.To * g.Ho * g.Wo)
                 gf = 2.0 * M * g.real_n * g.real_k / 1e9
                 desc = (f"{kind} in({g.Ti},{g.Hi},{g.Wi})x{g.Cg} out({g.To},{g.Ho},{g.Wo})x{g.Co} "
@@ -1092,9 +1093,11 @@ class SlowFastEngine:
             ms = e0.elapsed_time(e1)
             name = "sfb_conv_wgrad" if name == "sfb_conv_wgrad_folded" else name
             key = name
-            if name in ("sfb_conv_gemm", "sfb_conv_wgrad"):
+            if name in ("sfb_conv_gemm", "sfb_conv_wgrad", "sfb_conv_dgrad_bn"):
                 g = args[0]._obj
-                if name == "sfb_conv_gemm" and g.transposed:
+                if name == "sfb_conv_dgrad_bn":
+                    key = "sfb_conv_dgrad_bn"
+                elif name == "sfb_conv_gemm" and g.transposed:
                     key = "sfb_conv_gemm[dgrad]"
                 elif name == "sfb_conv_gemm":
                     key = "sfb_conv_gemm[fprop]"
@@ -1104,6 +1107,8 @@ class SlowFastEngine:
                 # algorithmic bytes: gathered tensor + written tensor (bf16), + the old value when accumulating in place
                 byt = 2.0 * g.N * (g.Ti * g.Hi * g.Wi * g.Cg + g.To * g.Ho * g.Wo * g.Co)
                 if name == "sfb_conv_gemm" and args[7]._obj.residual:
+                    byt += 2.0 * g.N * g.To * g.Ho * g.Wo * g.Co
+                if name == "sfb_conv_dgrad_bn":  # the y tile the fused BatchNorm-backward reduction reads
                     byt += 2.0 * g.N * g.To * g.Ho * g.Wo * g.Co
                 flops[key + "#bytes"] = flops.get(key + "#bytes", 0.0) + byt
                 flops[key + "#kernels"] = flops.get(key + "#kernels", 0.0) + nk
