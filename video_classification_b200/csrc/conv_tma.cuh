@@ -83,6 +83,9 @@ struct ConvTmaParams {
   //      tensor reads) disappears.
   int bn_mode;                 // 0: off, 1: mask recomputed from y*scale+shift > 0
   uint32_t ybuf_off;           // byte offset of the y tile (one staging tile)
+  int res_tile;                // kEpiAffine: the residual tile arrives by TMA through tmap_y into the same buffer, one
+                               // chunk ahead (per-thread global loads left the epilogue waiting on HBM once per chunk:
+                               // the block-tail convs of the eval forward ran at half their roofline)
   const float* bn_scale;
   const float* bn_shift;
   const float* bn_mean;
@@ -383,6 +386,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
     const bool want_stats = MODE == kEpiPlain && p.stats != nullptr;
     constexpr bool bnred = MODE == kEpiBnBwd;
+    // a side tile (y of the fused BatchNorm backward / the residual of the inference epilogue) travels by TMA
+    const bool tile = bnred || (MODE == kEpiAffine && p.res_tile);
+    // TMA stores alternate between two staging tiles when the second one exists and is not lent to the side tile
+    const bool dbl = p.stg2_off != 0 && (!tile || p.ybuf_off != p.stg2_off);
     const uint32_t ybuf = smem_u32(smem) + p.ybuf_off;
     uint32_t yphase = 0;
     bool y_issued = false;
@@ -405,13 +412,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         if (ch <= last_ch) {
           const int col0 = n0 + ch * CH;
           // (A) the TMA store that last used this staging tile must have finished reading it
-          const uint32_t stg = (!bnred && (nstaged & 1)) ? stg_b : stg_a;
+          const uint32_t stg = (dbl && (nstaged & 1)) ? stg_b : stg_a;
           ++nstaged;
           if (te == 0 && store_pending) {
-            if (p.stg2_off && !bnred) tma_store_wait_read1(); else tma_store_wait_read();
+            if (dbl) tma_store_wait_read1(); else tma_store_wait_read();
           }
           named_bar_sync(1, ET);
-          if (bnred && te == 0 && !y_issued) {
+          if (tile && te == 0 && !y_issued) {
             // first chunk of the CTA: its y tile travels while the accumulator is converted and staged (every later
             // tile is requested one chunk ahead, below)
             const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
@@ -444,7 +451,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               // the precomputed ones.
               uint4 rq[4];
               const bool has_res = rrow != nullptr && mv;
-              if (has_res) {
+              if (has_res && !tile) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                   rq[j] = nb + j * 8 < p.Co ? *reinterpret_cast<const uint4*>(rrow + nb + j * 8) : make_uint4(0, 0, 0, 0);
@@ -452,6 +459,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               float v[32];
               tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
               tmem_ld_wait();
+              if (tile) {
+                // residual tile (same swizzled layout as the staging tile: this thread's four 16-byte groups sit at soff[])
+                mbar_wait(y_bar, yphase, 17);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) rq[j] = lds_v4(ybuf + soff[j]);
+              }
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int nn = nb + j * 8;
@@ -481,6 +494,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               }
             }
           }
+          if (MODE == kEpiAffine && tile) yphase ^= 1;  // every epilogue thread, once per chunk (readers waited above)
           // (C) last chunk read: hand the accumulator buffer back to the MMA warp
           if (ch == last_ch) {
             tc_fence_before();
@@ -531,7 +545,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
             tma_store_commit();
             store_pending = true;
-            if (bnred) {
+            if (tile) {
               // every epilogue thread is past its reads of the y tile (barrier above): request the NEXT chunk's tile
               // now, so that it travels during that chunk's store wait, barrier and accumulator conversion
               y_issued = false;

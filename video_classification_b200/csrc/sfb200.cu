@@ -343,11 +343,17 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
   size_t smem_total = smem;
   const size_t stg2 = (smem - 1024 + 1023) / 1024 * 1024;  // swizzled tile: 1024-byte aligned
   pp.nstages = L::kStages;
-  if (1024 + stg2 + L::kStagingBytes <= 227 * 1024) {
+  const bool side_tile = p.bn_mode || p.res_tile;  // y of the fused BatchNorm backward / residual of the inference epilogue
+  if (side_tile && 1024 + stg2 + 2 * (size_t)L::kStagingBytes <= 227 * 1024) {
+    // room for both: stores stay double-buffered, the side tile gets a buffer of its own
+    pp.stg2_off = (uint32_t)stg2;
+    pp.ybuf_off = (uint32_t)(stg2 + L::kStagingBytes);
+    smem_total = 1024 + stg2 + 2 * (size_t)L::kStagingBytes;
+  } else if (1024 + stg2 + L::kStagingBytes <= 227 * 1024) {
     pp.stg2_off = (uint32_t)stg2;
     smem_total = 1024 + stg2 + L::kStagingBytes;
-    pp.ybuf_off = pp.stg2_off;   // fused BatchNorm backward: the second tile holds y (stores are single-buffered)
-  } else if (p.bn_mode) {
+    pp.ybuf_off = pp.stg2_off;   // the second tile holds the side tile (stores are single-buffered then)
+  } else if (side_tile) {
     // no room for another tile: the y tile takes the shared memory of the last pipeline stage(s)
     const int drop = (L::kStagingBytes + L::kStage - 1) / L::kStage;
     if (L::kStages - drop < 2) return SFB_ERR_UNSUPPORTED;
@@ -1009,6 +1015,12 @@ int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pr
                       q.Ht, q.Tt, 1, 1, 1, &to);
     if (rc) return rc;
     CUtensorMap ty = to;
+    if (!bn && q.res && !q.reduce_add) {
+      // inference epilogue with a residual: its tiles travel by TMA, one chunk ahead of the epilogue (same boxes as the store)
+      rc = get_act_tmap(q.res + q.res_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, q.res_ld, q.ocols, q.Wt, q.Ht, q.Tt, 1, 1, 1, &ty);
+      if (rc) return rc;
+      q.res_tile = 1;
+    }
     if (bn) {
       if (q.reduce_add || q.res || q.epi_scale || q.epi_relu || q.stats) return SFB_ERR_UNSUPPORTED;
       rc = get_act_tmap((const __nv_bfloat16*)bn->y + bn->y_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, bn->y_ld, q.ocols, q.Wt,

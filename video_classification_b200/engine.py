@@ -1,17 +1,21 @@
-"""Execution engine of the B200 SlowFast: compiles the parameter tree of my_slowfast.SlowFastB200 into a static
-list of libsfb200 kernel calls (forward, and backward for training) per input shape, with every activation /
-gradient buffer planned up front.
+"""Execution engine of the B200 SlowFast: compiles the parameter tree of my_slowfast.SlowFastB200 (or of
+res3d.SlowOnlyB200) into a static list of libsfb200 kernel calls (forward, and backward for training) per input shape,
+with every activation / gradient buffer planned up front, and replays the lists as CUDA graphs.
 
 Data flow (training), per conv layer L with BatchNorm:
-    conv_gemm  : raw y_L (bf16 NDHWC) + per-channel sum / sum-of-squares fused in the GEMM epilogue
-    bn_finalize: batch mean/var -> (scale, shift), running-stat update           (tiny)
-    consumer   : applies relu(y*scale+shift) while staging its operand (prologue) -- no standalone BN pass
-    block tail : out = relu(bn_c(y_c) + shortcut)                                  (one fused pass per ResBlock)
-The Fast->Slow lateral conv writes its raw output directly behind the Slow stage output in one
-channel-concatenated buffer (torch.cat of reference model/my_slowfast.py:343 never happens); its BN+ReLU is a
-per-channel prologue of the next stage (identity on the Slow channels).
-Backward mirrors this: bn_bwd_reduce/apply produce dy, conv_wgrad accumulates fp32 weight gradients into one flat
-arena (reverse-forward order, ready for bucketed all-reduce), conv_gemm(transposed) is dgrad.
+    conv_gemm        : raw y_L (bf16 NDHWC) + per-channel sum / sum-of-squares fused in the GEMM epilogue
+    bn_add_relu_raw  : finalises the batch statistics (mean/var -> scale, shift, running-stat update) and materialises
+                       z_L = relu(y_L*scale+shift), the next conv's operand -- one HBM-bound pass (training BatchNorm needs
+                       the statistics of the WHOLE tensor before anything can be normalised)
+    block tail       : out = relu(bn_c(y_c) + shortcut) + packed ReLU mask          (one fused pass per ResBlock)
+Inference: BatchNorm folded into per-channel (scale, shift); affine + residual + ReLU run in the GEMM epilogue, no
+elementwise pass at all.
+The Fast->Slow lateral conv's activated output lands directly behind the Slow stage output in one channel-concatenated
+buffer (torch.cat of reference model/my_slowfast.py:343 never happens, in either direction).
+Backward: the input-gradient GEMM that produces dz of a conv -> BN -> ReLU layer masks it and reduces that layer's
+dgamma / dbeta in its epilogue (sfb_conv_dgrad_bn); bn_bwd_apply turns the masked gradient into dy; conv_wgrad accumulates
+fp32 weight gradients into one flat arena (reverse-forward order, ready for bucketed all-reduce); block tails use the
+packed mask (bn_bwd_reduce / apply, or sfb_bn_bwd_tail2 for both BatchNorms of a projection-shortcut tail).
 """
 import ctypes as C
 from typing import Dict, List, Optional, Tuple

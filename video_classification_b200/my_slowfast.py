@@ -9,8 +9,10 @@ train.py:93-123 (delete_mismatch + load_state_dict), :182 (optim.Adam(model.para
 
 What differs is underneath: the torch.nn modules here only HOLD parameters and buffers; forward and
 backward of the whole network run in libsfb200.so (hand-written sm_100a kernels: tcgen05 implicit-GEMM
-Conv3d with fused BatchNorm statistics / prologue normalisation, zero-copy lateral concat, ...) driven by
-engine.SlowFastEngine through one torch.autograd.Function.  There is no PyTorch/cuDNN fallback.
+Conv3d whose epilogues produce the BatchNorm batch statistics in training, apply the folded BatchNorm +
+residual + ReLU in inference and reduce the BatchNorm backward sums in the input-gradient GEMMs; HBM-bound
+normalise / residual-tail passes; zero-copy lateral concat, ...) driven by engine.SlowFastEngine through one
+torch.autograd.Function.  There is no PyTorch/cuDNN fallback.
 
 Keyword-only extras (defaults == the reference as written) select the canonical 8/32 alpha=4 graph the
 benchmark names: fusion_conv_kernel, fusion_conv_stride, head_pool_kernel_sizes,
@@ -109,8 +111,9 @@ class _Head(_ParamTree):
 class FuseFastToSlow(_ParamTree):
     """Fast->Slow lateral connection (reference model/my_slowfast.py:260-344).  Live path: conv -> BN -> ReLU on
     the Fast tensor, channel-concatenated behind the Slow tensor.  In this implementation the lateral conv
-    writes straight into the channel-concatenated Slow buffer (no torch.cat copy) and its BatchNorm+ReLU is
-    applied by the consumers' operand prologue.  `residual` / `res_unit` are created exactly like the
+    writes its raw output and, in training, one normalise+ReLU pass (in inference the GEMM epilogue) puts the
+    activated values straight behind the Slow channels of the shared concat buffer (no torch.cat copy in either
+    direction).  `residual` / `res_unit` are created exactly like the
     reference does and, exactly like there, never used by forward (their .grad stays None)."""
 
     def __init__(self, conv_fast_to_slow: nn.ModuleList, residual: nn.Module, norm: Optional[nn.ModuleList] = None,
