@@ -570,3 +570,31 @@ def test_res3d_slow_only_parity():
     opt.step()
     with torch.no_grad():
         assert float(F.cross_entropy(product(x), y)) < float(loss_p)
+
+
+def test_rebound_parameter_storage_is_noticed():
+    """plans and CUDA graphs bake device addresses: `p.data = ...` (an EMA swap, a manual cast) or
+    load_state_dict(assign=True) must not leave the kernels reading the old storage"""
+    oracle, product = pu.build_pair("REF", True)
+    xs, xf = _clips("REF", 2, 64, 8, 8)
+    product.eval()
+    oracle.eval()
+    with torch.no_grad():
+        for _ in range(4):          # past the graph capture
+            a = product([xs, xf]).clone()
+        # (1) rebind the storage of one conv weight and one BatchNorm buffer to scaled copies
+        w = product.blocks[1].multipathway_blocks[0].res_blocks[0].branch2.conv_b.weight
+        w.data = (w.data * 0.5).clone()
+        rv = product.blocks[2].multipathway_blocks[1].res_blocks[0].branch2.norm_a.running_var
+        product.blocks[2].multipathway_blocks[1].res_blocks[0].branch2.norm_a.running_var = (rv * 4.0).clone()
+        oracle.load_state_dict(product.state_dict(), strict=True)
+        b = product([xs, xf]).clone()
+        ref_b = oracle([xs, xf])
+        assert pu.rel_max(b, ref_b) <= pu.LOGIT_TOL
+        assert pu.rel_max(b, a) > 1e-3  # the change is visible at all
+        # (2) replace the Parameter objects themselves
+        sd = {k: (v * 1.0).clone() for k, v in product.state_dict().items()}
+        sd["blocks.6.proj.bias"] = sd["blocks.6.proj.bias"] + 1.0
+        product.load_state_dict(sd, strict=True, assign=True)
+        c = product([xs, xf]).clone()
+        torch.testing.assert_close(c, b + 1.0, rtol=1e-4, atol=1e-4)

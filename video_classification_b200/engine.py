@@ -236,7 +236,9 @@ class SlowFastEngine:
         self.proj = self.head_mod.proj
         self.bn_modules = [l.bn for l in self.layers]
         self.bn_epoch = 0
-        self._bn_ptrs = [bn.running_mean.data_ptr() for bn in self.bn_modules]
+        self._bn_tensors = [t for bn in self.bn_modules for t in (bn.running_mean, bn.running_var)]
+        self._ptr_sig = None
+        self._objs_cache = None
 
     def _bind_bn_arena(self, plan: "Plan"):
         """BatchNorm scratch of ONE plan: [all raw sums | per layer scale, shift, mean, invstd].  Every plan owns its
@@ -306,13 +308,53 @@ class SlowFastEngine:
         self._pack_cache = {}
         self.bn_epoch += 1
 
+    def _current_objects(self):
+        """parameters and BatchNorm buffers as the module tree holds them NOW (dict lookups: nn.Module.__getattr__ costs
+        a microsecond per access, this runs on every forward)"""
+        par, buf = [], []
+        for l in self.layers:
+            bp = l.bn._parameters
+            par += [l.conv._parameters["weight"], bp["weight"], bp["bias"]]
+            bb = l.bn._buffers
+            buf += [bb["running_mean"], bb["running_var"]]
+        pp = self.proj._parameters
+        par += [pp["weight"], pp["bias"]]
+        return par, buf
+
+    def params_replaced(self) -> bool:
+        """True when a Parameter OBJECT of the module tree is no longer the one this engine was built around
+        (`load_state_dict(assign=True)`, `module.weight = nn.Parameter(...)`): gradients, the arena views and every plan
+        refer to the old objects, so the model builds a new engine."""
+        self._objs_cache = self._current_objects()  # reused by the address check of the same forward
+        return any(a is not b for a, b in zip(self._objs_cache[0], self.live_params))
+
+    def _check_baked_pointers(self):
+        """Plans (and the CUDA graphs captured from them) hold the device addresses of every parameter and BatchNorm
+        buffer.  Rebinding storage -- `p.data = ...`, a buffer attribute assigned anew, a swapped-in EMA copy -- would leave
+        the kernels reading the old memory without any error, so the addresses are compared on every forward (~550
+        `data_ptr()` calls, ~0.1 ms of host time hidden behind the GPU) and everything address-dependent is rebuilt when
+        one moved."""
+        par, buf = self._objs_cache or self._current_objects()
+        self._objs_cache = None
+        self._bn_tensors = buf
+        sig = tuple([t.data_ptr() for t in par] + [t.data_ptr() for t in buf])
+        if sig != self._ptr_sig:
+            if self._ptr_sig is not None:
+                self.plans.clear()
+                self.invalidate_weights()
+            self._ptr_sig = sig
+
     def _fold_key(self):
         """changes whenever a folded BatchNorm coefficient may be stale: any training forward of this engine (running
-        statistics), invalidate_weights(), or an in-place update of gamma / beta / the buffers that autograd can see"""
+        statistics), invalidate_weights() / moved storage, or an in-place update of gamma / beta / the buffers that
+        autograd can see"""
         v = 0
-        for bn in self.bn_modules:
-            v += bn.weight._version + bn.bias._version + bn.running_mean._version + bn.running_var._version
-        return (self.bn_epoch, v, tuple(self._bn_ptrs) == tuple(bn.running_mean.data_ptr() for bn in self.bn_modules))
+        for l in self.layers:
+            bp = l.bn._parameters
+            v += bp["weight"]._version + bp["bias"]._version
+        for t in self._bn_tensors:
+            v += t._version
+        return (self.bn_epoch, v)
 
     # ------------------------------------------------------------------ weights
     def _pack_tables(self, training: bool):
@@ -1234,6 +1276,7 @@ class SlowFastEngine:
     def forward(self, xs, xf, training: bool) -> Tuple[torch.Tensor, Plan]:
         """xs, xf: fp32 NCTHW clips (any strides), or xs = staging.RawClips and xf = None"""
         self.stream.value = torch.cuda.current_stream(self.dev).cuda_stream
+        self._check_baked_pointers()
         if xf is None and not torch.is_tensor(xs):
             self.refresh_weights(training)
             plan = self._stage_raw(xs, training)

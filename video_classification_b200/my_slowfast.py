@@ -233,6 +233,11 @@ class SlowFastB200(_ParamTree):
         raw = isinstance(x, RawClips)
         assert raw or (isinstance(x, (list, tuple)) and len(x) == 2), \
             "expects [slow, fast] NCTHW tensors (or staging.RawClips: uint8 frames, normalised on the device)"
+        if self._engine is not None and self._engine.params_replaced():
+            if self._engine.ddp is not None:
+                raise RuntimeError("parameters of the model were replaced (load_state_dict(assign=True)?) after "
+                                   "attach_ddp: call parallel.attach_ddp(model) again")
+            self._engine = None
         if self._engine is None:
             self._engine = SlowFastEngine(self)
         return run_model(self._engine, x, None) if raw else run_model(self._engine, x[0], x[1])

@@ -53,6 +53,11 @@ class SlowOnlyB200(_ParamTree):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         from .engine import SlowFastEngine, run_model
         assert torch.is_tensor(x) and x.dim() == 5, "expects one NCTHW tensor"
+        if self._engine is not None and self._engine.params_replaced():
+            if self._engine.ddp is not None:
+                raise RuntimeError("parameters of the model were replaced (load_state_dict(assign=True)?) after "
+                                   "attach_ddp: call parallel.attach_ddp(model) again")
+            self._engine = None
         if self._engine is None:
             self._engine = SlowFastEngine(self)
         return run_model(self._engine, x, None)
