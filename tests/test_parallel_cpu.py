@@ -130,3 +130,21 @@ def test_ensemble_gather_single_process_is_a_view_with_one_part():
     from video_classification_b200.parallel import gather_part_scores
     x = torch.rand(4, 9)
     assert torch.equal(gather_part_scores(x), x.unsqueeze(1))
+
+
+def test_tail_bucket_is_split_off_the_last_bucket():
+    """the gradients at the end of the arena (stems, first residual stage) are final last: they get a small bucket of
+    their own so that only a latency-sized all-reduce is exposed after backward"""
+    flat = torch.zeros(4000)
+    spans = [(0, 1000), (1000, 1000), (2000, 1000), (3000, 600), (3600, 200), (3800, 100), (3900, 100)]
+    b = GradBucketer(flat, spans, bucket_bytes=4 * 2500, tail_bytes=4 * 450)
+    # without the tail: [(0,2000), (2000,4000)]; the last 400 elements (3 spans <= 450) are cut off
+    assert b.buckets == [(0, 2000), (2000, 3600), (3600, 4000)]
+    assert [b.span_bucket[o] for o, _ in spans] == [0, 0, 1, 1, 2, 2, 2]
+    b.reset_counts()
+    assert b.mark_ready(3900) is None and b.mark_ready(3800) is None and b.mark_ready(3600) == 2
+    # the tail never swallows the whole last bucket: at least the bucket's first gradient stays in it
+    b2 = GradBucketer(flat, spans, bucket_bytes=4 * 2500, tail_bytes=4 * 5000)
+    assert b2.buckets == [(0, 2000), (2000, 3000), (3000, 4000)]
+    b3 = GradBucketer(flat, spans, bucket_bytes=4 * 2500)
+    assert b3.buckets == [(0, 2000), (2000, 4000)]

@@ -364,7 +364,15 @@ class SlowFastEngine:
         place -- and dropped by invalidate_weights()."""
         key = (bool(training), self.impl)
         tabs = self._pack_cache.get(key)
-        if tabs is not None and tabs["ptrs"] == [l.conv.weight.data_ptr() for l in self.layers]:
+
+        def ptr_sig():  # master weights AND every operand buffer the table writes (they are reallocated when impl changes)
+            out = []
+            for l in self.layers:
+                out.append(l.conv.weight.data_ptr())
+                for b in (l.wp, l.wpt, l.wps, l.wf, l.wpf, l.wptf):
+                    out.append(b.data_ptr() if b is not None else 0)
+            return out
+        if tabs is not None and tabs["ptrs"] == ptr_sig():
             return tabs
         P = _ffi.PackJob
         lv0, lv1 = [], []
@@ -411,7 +419,7 @@ class SlowFastEngine:
             nblk = C.c_int32(0)
             _ffi.check(self.lib.sfb_pack_plan(arr, len(jobs), tab.data_ptr(), nbytes, C.byref(nblk)), "sfb_pack_plan")
             levels.append((tab, len(jobs), nblk.value))
-        tabs = {"levels": levels, "ptrs": [l.conv.weight.data_ptr() for l in self.layers]}
+        tabs = {"levels": levels, "ptrs": ptr_sig()}
         self._pack_cache[key] = tabs
         return tabs
 
