@@ -381,6 +381,27 @@ int sfb_adam_plan(const SfbAdamJob* jobs, int32_t n_jobs, void* table_dev, int64
 int sfb_adam_step(const void* table_dev, int32_t n_jobs, int32_t total_blocks, int64_t step, double lr, double beta1,
                   double beta2, double eps, double weight_decay, double grad_scale, void* stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * BatchNorm3d(+ReLU) backward in ONE call that allocates nothing: the same two kernels as sfb_bn_bwd_reduce +
+ * sfb_bn_bwd_apply (ReLU mask recomputed from y*scale+shift, no mask tensor, no shortcut-gradient output), with the
+ * per-channel sums the two phases share (sum g, sum g*xhat: 2 * SFB_NOALLOC_MAX_C floats = 16 KB) in a file-scope
+ * `static __device__` array of the library instead of caller memory.  Every GPU that loads the library holds that array
+ * until the process exits; its address is looked up once per device (cudaGetSymbolAddress with that device current: the
+ * device that owns the buffers must be current when this is called).  The call issues one cudaMemsetAsync (the array keeps
+ * the previous call's sums), the two kernels and up to two device-to-device cudaMemcpyAsync on `stream`; it never calls
+ * cudaMalloc / cudaFree or an allocating library routine.
+ *   dy = gamma*invstd*(g - sum(g)/M - xhat*sum(g*xhat)/M),  g = dz * [relu ? (y*scale+shift > 0) : 1]   -> bf16
+ *   dgamma_out / dbeta_out (fp32 [C], each may be NULL): sum g*xhat / sum g, OVERWRITTEN (not accumulated).
+ * Limit: C <= SFB_NOALLOC_MAX_C (and C % 8 == 0 as everywhere); a larger C returns SFB_ERR_UNSUPPORTED and
+ * sfb_last_cuda_error() names the limit.  All calls on one GPU share the array: calls that overlap on the GPU (different
+ * streams, or graph branches that may run concurrently) race; order them on one stream or with events. */
+#define SFB_NOALLOC_MAX_C 2048
+int sfb_bn_bwd_noalloc(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
+                       const float* scale, const float* shift, const float* mean, const float* invstd,
+                       const float* gamma, int32_t relu, int64_t M, int32_t C, void* dy, int32_t dy_ld, int32_t dy_coff,
+                       float* dgamma_out, float* dbeta_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,6 +92,8 @@ SIGNATURES = {
     "sfb_bn_bwd_reduce": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _vp, _vp],
     "sfb_bn_bwd_apply": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                          _i32, _i64, _i32, _vp, _i32, _i32, _vp, _i32, _i32, _i32, _vp],
+    "sfb_bn_bwd_noalloc": [_vp, _i32, _i32, _vp, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _i32, _i32,
+                           _vp, _vp, _vp],
     "sfb_maxpool_fwd": [_vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp, _vp],
     "sfb_maxpool_bwd": [_vp, _i32, _i32, _vp, _i32, _i32, _i32, _i32, _i32, _vp, _i32, _i32, _vp],
     "sfb_bn_bwd_tail2": [_vp, _i32, _i32, _vp, C.POINTER(BnTailSide), C.POINTER(BnTailSide), _i64, _i32, _vp],

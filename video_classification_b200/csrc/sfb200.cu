@@ -1500,3 +1500,86 @@ int sfb_sparse_fuse_bwd(const float* dy, const float* x, const float* w, int32_t
 }
 
 }  // extern "C"
+
+// ---- BatchNorm(+ReLU) backward without any allocation (see sfb_bn_bwd_noalloc in include/sfb200.h) -----------------
+// The per-channel sums the reduce and apply phases share live in this file-scope device array: [0, kNoAllocMaxC) sum g,
+// [kNoAllocMaxC, 2*kNoAllocMaxC) sum g*xhat.  16 KB, held by every GPU that loads the library until the process exits.
+// In host code the name is only a handle for cudaGetSymbolAddress; the kernels get the address that call returns.
+namespace {
+constexpr int kNoAllocMaxC = SFB_NOALLOC_MAX_C;
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) float g_bn_bwd_sums[2 * kNoAllocMaxC];
+namespace {
+float* g_bn_bwd_sums_addr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+// device address of g_bn_bwd_sums on the CURRENT device, looked up once per device
+int noalloc_sums(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(e, "sfb_bn_bwd_noalloc: cudaGetDevice");
+  if (dev < 0 || dev >= kNoAllocMaxDevices) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "sfb_bn_bwd_noalloc: device ordinal %d outside [0, %d)", dev, kNoAllocMaxDevices);
+    return SFB_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_bn_bwd_sums_addr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_bn_bwd_sums);
+    if (e != cudaSuccess || !p) return cuda_fail(e, "sfb_bn_bwd_noalloc: cudaGetSymbolAddress(g_bn_bwd_sums)");
+    g_bn_bwd_sums_addr[dev] = static_cast<float*>(p);
+  }
+  *out = g_bn_bwd_sums_addr[dev];
+  return SFB_OK;
+}
+}  // namespace
+
+extern "C" int sfb_bn_bwd_noalloc(const void* dz, int32_t dz_ld, int32_t dz_coff, const void* y, int32_t y_ld, int32_t y_coff,
+                                  const float* scale, const float* shift, const float* mean, const float* invstd,
+                                  const float* gamma, int32_t relu, int64_t M, int32_t C, void* dy, int32_t dy_ld,
+                                  int32_t dy_coff, float* dgamma_out, float* dbeta_out, void* stream) {
+  if (C > kNoAllocMaxC) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "sfb_bn_bwd_noalloc: C = %d exceeds SFB_NOALLOC_MAX_C = %d (static scratch)",
+             (int)C, kNoAllocMaxC);
+    return SFB_ERR_UNSUPPORTED;
+  }
+  if (M <= 0 || C <= 0 || (C & 7) || !mean || !invstd || !gamma) return SFB_ERR_BAD_ARG;
+  if (!view_ok(dz, dz_ld, dz_coff, C) || !view_ok(y, y_ld, y_coff, C) || !view_ok(dy, dy_ld, dy_coff, C))
+    return SFB_ERR_BAD_ARG;
+  if (relu && (!scale || !shift)) return SFB_ERR_BAD_ARG;
+  float* sums = nullptr;
+  int rc = noalloc_sums(&sums);
+  if (rc != SFB_OK) return rc;
+  float* dbeta = sums;                   // sum g
+  float* dgamma = sums + kNoAllocMaxC;   // sum g * xhat
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the previous call's sums: the accumulators start from zero on the caller's stream
+  cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(float) * 2 * kNoAllocMaxC, st);
+  if (e != cudaSuccess) return cuda_fail(e, "sfb_bn_bwd_noalloc: cudaMemsetAsync");
+  View vdz{(const __nv_bfloat16*)dz, dz_ld, dz_coff};
+  View vy{(const __nv_bfloat16*)y, y_ld, y_coff};
+  View vm{nullptr, 0, 0};
+  ViewW vdy{(__nv_bfloat16*)dy, dy_ld, dy_coff};
+  ViewW vg{nullptr, 0, 0};
+  const int RL = kRedThreads / (C >> 3);
+  const int grid_r = grid_for((M + (long long)RL * kRedUnroll - 1) / ((long long)RL * kRedUnroll), 1, 148 * 8);
+  if (relu)
+    bn_bwd_reduce_kernel<0><<<grid_r, kRedThreads, 0, st>>>(vdz, vy, vm, nullptr, scale, shift, mean, invstd, M, C, dgamma, dbeta);
+  else
+    bn_bwd_reduce_kernel<3><<<grid_r, kRedThreads, 0, st>>>(vdz, vy, vm, nullptr, scale, shift, mean, invstd, M, C, dgamma, dbeta);
+  SFB_CHECK_LAUNCH("bn_bwd_reduce_kernel (noalloc)");
+  const int grid_a = grid_for((M + (long long)RL * kBnUnroll - 1) / ((long long)RL * kBnUnroll), 1, 148 * 8);
+  bn_bwd_apply_kernel<0, false><<<grid_a, kRedThreads, 0, st>>>(vdz, vy, vm, nullptr, scale, shift, mean, invstd, gamma, dgamma,
+                                                                dbeta, relu, M, C, 1.0f / (float)M, vdy, vg, 0);
+  SFB_CHECK_LAUNCH("bn_bwd_apply_kernel (noalloc)");
+  if (dgamma_out) {
+    e = cudaMemcpyAsync(dgamma_out, dgamma, sizeof(float) * C, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(e, "sfb_bn_bwd_noalloc: copy of dgamma");
+  }
+  if (dbeta_out) {
+    e = cudaMemcpyAsync(dbeta_out, dbeta, sizeof(float) * C, cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return cuda_fail(e, "sfb_bn_bwd_noalloc: copy of dbeta");
+  }
+  return SFB_OK;
+}

@@ -324,6 +324,19 @@ def bn_bwd_apply(dz: Act, y: Act, mask: Optional[Act], scale, shift, mean, invst
                                  int(g_accumulate), stream_ptr()), "sfb_bn_bwd_apply")
 
 
+NOALLOC_MAX_C = 2048  # SFB_NOALLOC_MAX_C in include/sfb200.h
+
+
+def bn_bwd_noalloc(dz: Act, y: Act, scale, shift, mean, invstd, gamma, relu, dy: Act, dgamma_out=None, dbeta_out=None):
+    """sfb_bn_bwd_noalloc: BatchNorm(+ReLU) backward whose per-channel sums live in the library's static device array
+    (no allocation anywhere in the call; C <= NOALLOC_MAX_C; calls that overlap on one GPU race -- include/sfb200.h)."""
+    check(lib().sfb_bn_bwd_noalloc(dz.ptr(), dz.ld, dz.coff, y.ptr(), y.ld, y.coff, ptr(scale), ptr(shift),
+                                   mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(), int(relu), y.M, y.C,
+                                   dy.ptr(), dy.ld, dy.coff, ptr(dgamma_out), ptr(dbeta_out), stream_ptr()),
+          "sfb_bn_bwd_noalloc")
+    return dy
+
+
 def maxpool_fwd(y: Act, scale, shift, out: Act, idx: Optional[torch.Tensor]):
     N, T, H, W = y.dims
     check(lib().sfb_maxpool_fwd(y.ptr(), y.ld, y.coff, ptr(scale), ptr(shift), N, T, H, W, y.C, out.ptr(), out.ld,
