@@ -83,6 +83,10 @@ struct ConvTmaParams {
   //      tensor reads) disappears.
   int bn_mode;                 // 0: off, 1: mask recomputed from y*scale+shift > 0
   uint32_t ybuf_off;           // byte offset of the y tile (one staging tile)
+  uint32_t ybuf2_off;          // second side tile (0: none): side tiles are then requested TWO chunks ahead.  With one
+                               // tile in flight a chunk could not take less than the HBM latency of its side tile
+                               // (request -> arrival -> math -> store -> next request): the residual convs of the eval
+                               // forward ran at 3 us per 128x128 chunk, 800 issue cycles of work in 5800
   int res_tile;                // kEpiAffine: the residual tile arrives by TMA through tmap_y into the same buffer, one
                                // chunk ahead (per-thread global loads left the epilogue waiting on HBM once per chunk:
                                // the block-tail convs of the eval forward ran at half their roofline)
@@ -124,6 +128,19 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
   return v;
 }
 
+// Values that do not change from tile to tile are computed once per CTA and made opaque here: left alone, the compiler
+// re-derives them inside the tile loop (ncu r3r, inference epilogue: 495 warp instructions per 32-column slice of which
+// ~140 were the arithmetic; the rest recomputed swizzled offsets, the aligned shared-memory base and parameter loads).
+__device__ __forceinline__ uint32_t keep_u32(uint32_t x) {
+  asm volatile("" : "+r"(x));
+  return x;
+}
+template <typename T>
+__device__ __forceinline__ T* keep_ptr(T* x) {
+  asm volatile("" : "+l"(x));
+  return x;
+}
+
 // Walk of a persistent CTA over its pixel patches (patch0, patch0 + step, ...) as (tw, th, tt, n) counters: the
 // mixed-radix decomposition is done once, every further tile is a few adds and compares instead of four divisions.
 struct PatchWalk {
@@ -163,7 +180,7 @@ struct ConvTmaCfg {
   static constexpr int kStagingOff = kStages * kStage;
   static constexpr int kStagingBytes = 128 * kChunk * 2;
   static constexpr int kBarOff = kStagingOff + kStagingBytes;          // full[S], empty[S], tfull[2], tempty[2]
-  static constexpr int kHolderOff = kBarOff + (2 * kStages + 6) * 8;   // + bres, ybar
+  static constexpr int kHolderOff = kBarOff + (2 * kStages + 7) * 8;   // + bres, ybar[2]
   static constexpr int kEnd = kHolderOff + 16;
   static constexpr int kBResOff = (kEnd + 1023) / 1024 * 1024;        // resident weights: nk blocks of [BN][128 B]
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
@@ -213,7 +230,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       mbar_init(&tempty_bar[b], L::kEpiWarps);
     }
     mbar_init(bres_bar, 1);
-    mbar_init(y_bar, 1);
+    mbar_init(&y_bar[0], 1);
+    mbar_init(&y_bar[1], 1);
     mbar_fence_init();
   }
   if (warp == 0 && lane == 0) {
@@ -224,8 +242,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   }
   if (p.bn_mode) {
     // rows of the y tile a box never writes (patches of fewer than 128 pixels) must read as finite numbers
-    for (int i = tid; i < L::kStagingBytes / 16; i += L::kThreads)
+    for (int i = tid; i < L::kStagingBytes / 16; i += L::kThreads) {
       reinterpret_cast<uint4*>(smem + p.ybuf_off)[i] = make_uint4(0, 0, 0, 0);
+      if (p.ybuf2_off) reinterpret_cast<uint4*>(smem + p.ybuf2_off)[i] = make_uint4(0, 0, 0, 0);
+    }
     fence_proxy_async_smem();
   }
   if (warp == 2) {
@@ -359,8 +379,9 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int olog = 31 - __clz(ocols);
     const uint32_t rb = (uint32_t)(ocols * 2);
     const uint32_t swz = rb == 128 ? 7u : (rb == 64 ? 3u : (rb == 32 ? 1u : 0u));
-    const uint32_t stg_a = smem_u32(smem + L::kStagingOff);
-    const uint32_t stg_b = p.stg2_off ? smem_u32(smem) + p.stg2_off : stg_a;
+    const uint32_t smem_e = keep_u32(smem_u32(smem));
+    const uint32_t stg_a = keep_u32(smem_e + L::kStagingOff);
+    const uint32_t stg_b = keep_u32(p.stg2_off ? smem_e + p.stg2_off : stg_a);
     uint32_t nstaged = 0;
     const uint32_t sub_bytes = 128u * rb;
     const int last_ch = min(NCH, (p.Co - n0 + CH - 1) / CH) - 1;
@@ -379,10 +400,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     for (int j = 0; j < 4; ++j) {
       const int cl = cslice * 32 + j * 8;
       uint32_t o = (uint32_t)(cl >> olog) * sub_bytes + (uint32_t)r * rb + (uint32_t)((cl & (ocols - 1)) * 2);
-      soff[j] = o ^ (((o >> 7) & swz) << 4);
+      soff[j] = keep_u32(o ^ (((o >> 7) & swz) << 4));
       const int cs = (warp - 2) * 8;
       o = (uint32_t)(cs >> olog) * sub_bytes + (uint32_t)(lane + 32 * j) * rb + (uint32_t)((cs & (ocols - 1)) * 2);
       toff[j] = o ^ (((o >> 7) & swz) << 4);
+      if (MODE != kEpiAffine) toff[j] = keep_u32(toff[j]);
     }
     const bool want_stats = MODE == kEpiPlain && p.stats != nullptr;
     constexpr bool bnred = MODE == kEpiBnBwd;
@@ -390,13 +412,47 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const bool tile = bnred || (MODE == kEpiAffine && p.res_tile);
     // TMA stores alternate between two staging tiles when the second one exists and is not lent to the side tile
     const bool dbl = p.stg2_off != 0 && (!tile || p.ybuf_off != p.stg2_off);
-    const uint32_t ybuf = smem_u32(smem) + p.ybuf_off;
-    uint32_t yphase = 0;
-    bool y_issued = false;
+    const uint32_t ybuf_a = keep_u32(smem_e + p.ybuf_off);
+    const uint32_t ybuf_b = keep_u32(p.ybuf2_off ? smem_e + p.ybuf2_off : ybuf_a);
+    // this thread's TMEM address (lane quadrant, 32-column slice) and its slice of the per-channel coefficients
+    const uint32_t tmem_t = keep_u32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(cslice * 32));
+    const float* const es_t = keep_ptr(p.epi_scale ? p.epi_scale + n0 + cslice * 32 : nullptr);
+    const float* const eb_t = keep_ptr(p.epi_shift ? p.epi_shift + n0 + cslice * 32 : nullptr);
+    // fused BatchNorm backward: channel of this warp's 8-column group in each chunk (pixel-folded launches: j % bn_ld)
+    uint32_t cbv[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) cbv[c] = bnred ? keep_u32((uint32_t)((n0 + c * CH + (warp - 2) * 8) % p.bn_ld)) : 0u;
+    const bool ydeep = p.ybuf2_off != 0;
+    uint32_t ycons = 0;  // side tiles consumed so far: tile i sits in buffer i & 1 (one buffer: always the first)
     bool store_pending = false;
     int it = 0;
     PatchWalk pw;
     pw.init(patch0, patch_step, p);
+    // side-tile requests (thread te == 0): a cursor over this CTA's chunks in the order the epilogue visits them; one or
+    // two requests are in flight ahead of the chunk being staged
+    PatchWalk pf = pw;
+    int pf_patch = patch0, pf_ch = 0;
+    uint32_t yreq = 0;
+    auto request_side_tile = [&]() {
+      if (pf_patch >= p.total_patches) return;
+      const int col = n0 + pf_ch * CH;
+      const int nsub = (min(CH, p.Co - col) + ocols - 1) >> olog;
+      uint64_t* bar = &y_bar[ydeep ? (yreq & 1) : 0];
+      const uint32_t dst = (yreq & 1) ? ybuf_b : ybuf_a;
+      mbar_arrive_expect_tx(bar, (uint32_t)nsub * (uint32_t)rows * rb);
+      for (int gsub = 0; gsub < nsub; ++gsub)
+        tma_load_5d(dst + gsub * sub_bytes, &tmap_y, bar, col + gsub * ocols, pf.tw * p.Wt, pf.th * p.Ht, pf.tt * p.Tt, pf.n);
+      ++yreq;
+      if (++pf_ch > last_ch) {
+        pf_ch = 0;
+        pf_patch += patch_step;
+        pf.next(p);
+      }
+    };
+    if (tile && te == 0) {
+      request_side_tile();
+      if (ydeep) request_side_tile();
+    }
     for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it, pw.next(p)) {
       const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
@@ -418,14 +474,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             if (dbl) tma_store_wait_read1(); else tma_store_wait_read();
           }
           named_bar_sync(1, ET);
-          if (tile && te == 0 && !y_issued) {
-            // first chunk of the CTA: its y tile travels while the accumulator is converted and staged (every later
-            // tile is requested one chunk ahead, below)
-            const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
-            mbar_arrive_expect_tx(y_bar, (uint32_t)nsub * (uint32_t)rows * rb);
-            for (int gsub = 0; gsub < nsub; ++gsub)
-              tma_load_5d(ybuf + gsub * sub_bytes, &tmap_y, y_bar, col0 + gsub * ocols, w0, h0, t0, n);
-          }
+          // this chunk's side tile: buffer, barrier and the parity of that barrier's current phase
+          const uint32_t ybuf = (ycons & 1) ? ybuf_b : ybuf_a;
+          uint64_t* const ybar = &y_bar[ydeep ? (ycons & 1) : 0];
+          const uint32_t yphase = ydeep ? ((ycons >> 1) & 1) : (ycons & 1);
           // (B) accumulator -> staging: this warp's 32-column slice
           {
             const int nb = col0 + cslice * 32;
@@ -433,7 +485,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               // training fprop / dgrad: convert and stage, nothing else (ragged last slice: only the live 8-column groups)
               if (nb < p.Co) {
                 float v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
+                tmem_ld32(tmem_t + (uint32_t)(buf * BN + ch * CH), v);
                 tmem_ld_wait();
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -457,11 +509,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                   rq[j] = nb + j * 8 < p.Co ? *reinterpret_cast<const uint4*>(rrow + nb + j * 8) : make_uint4(0, 0, 0, 0);
               }
               float v[32];
-              tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(buf * BN + ch * CH + cslice * 32), v);
+              tmem_ld32(tmem_t + (uint32_t)(buf * BN + ch * CH), v);
               tmem_ld_wait();
               if (tile) {
                 // residual tile (same swizzled layout as the staging tile: this thread's four 16-byte groups sit at soff[])
-                mbar_wait(y_bar, yphase, 17);
+                mbar_wait(ybar, yphase, 17);
 #pragma unroll
                 for (int j = 0; j < 4; ++j) rq[j] = lds_v4(ybuf + soff[j]);
               }
@@ -470,10 +522,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 const int nn = nb + j * 8;
                 if (nn < p.Co) {
                   float* f = v + j * 8;
-                  if (p.epi_scale) {
+                  if (es_t) {
                     float es[8], eb[8];
-                    load8f(p.epi_scale + nn, es);
-                    load8f(p.epi_shift + nn, eb);
+                    load8f(es_t + ch * CH + j * 8, es);
+                    load8f(eb_t + ch * CH + j * 8, eb);
 #pragma unroll
                     for (int i = 0; i < 8; ++i) f[i] = fmaf(f[i], es[i], eb[i]);
                   }
@@ -494,7 +546,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               }
             }
           }
-          if (MODE == kEpiAffine && tile) yphase ^= 1;  // every epilogue thread, once per chunk (readers waited above)
           // (C) last chunk read: hand the accumulator buffer back to the MMA warp
           if (ch == last_ch) {
             tc_fence_before();
@@ -505,11 +556,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           //      lanes split the 128 rows (as in (E)); the staged gradient is masked IN PLACE before it is stored
           if (bnred) {
             named_bar_sync(1, ET);                       // the whole gradient tile is staged
-            mbar_wait(y_bar, yphase, 16);
-            yphase ^= 1;
+            mbar_wait(ybar, yphase, 16);
             const int cg = col0 + (warp - 2) * 8;
             if (cg < p.Co) {
-              const int cb = cg % p.bn_ld;               // channel of this thread's first column
+              const int cb = (int)cbv[ch];               // channel of this thread's first column
               float sc[8], sh[8], mu[8];
               if (cb < p.bn_C) {                         // C is a multiple of 8: the group is real or pad as a whole
                 load8f(p.bn_scale + cb, sc);
@@ -545,27 +595,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
             tma_store_commit();
             store_pending = true;
-            if (tile) {
-              // every epilogue thread is past its reads of the y tile (barrier above): request the NEXT chunk's tile
-              // now, so that it travels during that chunk's store wait, barrier and accumulator conversion
-              y_issued = false;
-              int ncol = col0 + CH, nw = w0, nh = h0, nt = t0, nn_ = n;
-              bool have = ch < last_ch;
-              if (!have && patch + patch_step < p.total_patches) {
-                PatchWalk pn = pw;
-                pn.next(p);
-                ncol = n0; nw = pn.tw * p.Wt; nh = pn.th * p.Ht; nt = pn.tt * p.Tt; nn_ = pn.n;
-                have = true;
-              }
-              if (have) {
-                const int nsub2 = (min(CH, p.Co - ncol) + ocols - 1) >> olog;
-                mbar_arrive_expect_tx(y_bar, (uint32_t)nsub2 * (uint32_t)rows * rb);
-                for (int gsub = 0; gsub < nsub2; ++gsub)
-                  tma_load_5d(ybuf + gsub * sub_bytes, &tmap_y, y_bar, ncol + gsub * ocols, nw, nh, nt, nn_);
-                y_issued = true;
-              }
-            }
+            // every epilogue thread is past its reads of this chunk's side tile (barrier above): its buffer takes the
+            // next request, which travels during the following chunk(s)' store wait, barrier and conversion
+            if (tile) request_side_tile();
           }
+          if (tile) ++ycons;
           // (E) BatchNorm statistics from the staged tile (rows outside the tensor were staged as zeros): epilogue
           //     warp e owns the 8-column group e of the chunk, its lanes split the 128 rows (16-byte reads)
           if (want_stats) {
@@ -590,7 +624,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {
         const int col = n0 + ch * CH + (warp - 2) * 8;
-        const int cb = col % p.bn_ld;
+        const int cb = (int)cbv[ch];
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           float a = ssum[ch][c], b = ssq[ch][c];

@@ -333,33 +333,66 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
   *Wt = bw; *Ht = bh; *Tt = bt;
 }
 
+inline int side_depth() {
+  static const int d = [] {
+    const char* e = getenv("SFB_SIDE_DEPTH");
+    return e && *e ? atoi(e) : 2;
+  }();
+  return d;
+}
+
 template <int BN, bool BRES, int MODE>
 int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
                          const ConvTmaParams& p, cudaStream_t st) {
   using L = ConvTmaCfg<BN, BRES>;
   const size_t smem = L::smem_bytes(p.nk);
-  // second staging tile behind everything else when it still fits
+  // Shared memory behind the kernel's fixed layout holds up to three more swizzled tiles (1024-byte aligned): a second
+  // staging tile (TMA stores double-buffered) and one or two side tiles (y of the fused BatchNorm backward / residual
+  // of the inference epilogue).  What does not fit there takes the shared memory of the last pipeline stages.
   ConvTmaParams pp = p;
   size_t smem_total = smem;
-  const size_t stg2 = (smem - 1024 + 1023) / 1024 * 1024;  // swizzled tile: 1024-byte aligned
+  const size_t base = (smem - 1024 + 1023) / 1024 * 1024;
+  const size_t tile_bytes = L::kStagingBytes;
+  const int n_tail = 1024 + base >= 227 * 1024 ? 0 : (int)((227 * 1024 - 1024 - base) / tile_bytes);
   pp.nstages = L::kStages;
-  const bool side_tile = p.bn_mode || p.res_tile;  // y of the fused BatchNorm backward / residual of the inference epilogue
-  if (side_tile && 1024 + stg2 + 2 * (size_t)L::kStagingBytes <= 227 * 1024) {
-    // room for both: stores stay double-buffered, the side tile gets a buffer of its own
-    pp.stg2_off = (uint32_t)stg2;
-    pp.ybuf_off = (uint32_t)(stg2 + L::kStagingBytes);
-    smem_total = 1024 + stg2 + 2 * (size_t)L::kStagingBytes;
-  } else if (1024 + stg2 + L::kStagingBytes <= 227 * 1024) {
-    pp.stg2_off = (uint32_t)stg2;
-    smem_total = 1024 + stg2 + L::kStagingBytes;
-    pp.ybuf_off = pp.stg2_off;   // the second tile holds the side tile (stores are single-buffered then)
-  } else if (side_tile) {
-    // no room for another tile: the y tile takes the shared memory of the last pipeline stage(s)
-    const int drop = (L::kStagingBytes + L::kStage - 1) / L::kStage;
-    if (L::kStages - drop < 2) return SFB_ERR_UNSUPPORTED;
-    pp.nstages = L::kStages - drop;
-    pp.ybuf_off = (uint32_t)(pp.nstages * L::kStage);
+  pp.stg2_off = pp.ybuf_off = pp.ybuf2_off = 0;
+  const bool side_tile = p.bn_mode || p.res_tile;
+  int used = 0;
+  auto tail_slot = [&]() -> uint32_t { return used < n_tail ? (uint32_t)(base + (size_t)(used++) * tile_bytes) : 0u; };
+  auto steal = [&](int min_left) -> uint32_t {
+    const int drop = (int)((tile_bytes + L::kStage - 1) / L::kStage);
+    if (pp.nstages - drop < min_left) return 0u;
+    pp.nstages -= drop;
+    return (uint32_t)(pp.nstages * L::kStage);
+  };
+  pp.stg2_off = tail_slot();
+  if (side_tile) {
+    // with two side tiles the requests run two chunks ahead (ConvTmaParams::ybuf2_off); the fused dgrads keep at least
+    // two tiles of operands in flight (4 stages).  SFB_SIDE_DEPTH=1: one side tile, the arrangement of earlier builds.
+    const bool deep = side_depth() >= 2;
+    // the residual convs of the inference epilogue write 4x the columns they read: a tile's epilogue outlasts the
+    // operand loads of the next one several times over, so one tile of operands in flight is enough there
+    const int keep = MODE == kEpiAffine ? std::max(2, p.nk) : std::max(4, 2 * p.nk);
+    if (deep) {
+      pp.ybuf_off = tail_slot();
+      if (!pp.ybuf_off) pp.ybuf_off = steal(keep);
+      if (pp.ybuf_off) {
+        pp.ybuf2_off = tail_slot();
+        if (!pp.ybuf2_off) pp.ybuf2_off = steal(keep);
+      }
+    } else {
+      pp.ybuf_off = n_tail >= 2 ? tail_slot() : 0u;
+    }
+    if (!pp.ybuf_off) {
+      if (pp.stg2_off) {
+        pp.ybuf_off = pp.stg2_off;  // the second staging tile holds the side tile (stores are single-buffered then)
+      } else {
+        pp.ybuf_off = steal(2);
+        if (!pp.ybuf_off) return SFB_ERR_UNSUPPORTED;
+      }
+    }
   }
+  if (used) smem_total = 1024 + base + (size_t)used * tile_bytes;
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
   long long per_nt = num_sms() / p.n_tiles;
   if (per_nt < 1) per_nt = 1;
