@@ -470,10 +470,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           // (A) the TMA store that last used this staging tile must have finished reading it
           const uint32_t stg = (dbl && (nstaged & 1)) ? stg_b : stg_a;
           ++nstaged;
-          if (te == 0 && store_pending) {
-            if (dbl) tma_store_wait_read1(); else tma_store_wait_read();
+          //     -- one staging tile: wait and tell everybody here.  Two tiles: the wait sits in front of the barrier of
+          //     (D) of the PREVIOUS chunk (the store that used this tile was issued a whole chunk before that), so this
+          //     barrier and its skew disappear
+          if (!dbl) {
+            if (te == 0 && store_pending) tma_store_wait_read();
+            named_bar_sync(1, ET);
           }
-          named_bar_sync(1, ET);
           // this chunk's side tile: buffer, barrier and the parity of that barrier's current phase
           const uint32_t ybuf = (ycons & 1) ? ybuf_b : ybuf_a;
           uint64_t* const ybar = &y_bar[ydeep ? (ycons & 1) : 0];
@@ -586,6 +589,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           }
           // (D) staged tile -> global memory (TMA clips rows/columns outside the tensor)
           fence_proxy_async_smem();
+          if (dbl && te == 0 && store_pending) tma_store_wait_read();  // the other tile is free for the next chunk
           named_bar_sync(1, ET);
           if (te == 0) {
             const int nsub = (min(CH, p.Co - col0) + ocols - 1) >> olog;
