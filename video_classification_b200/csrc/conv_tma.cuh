@@ -128,19 +128,6 @@ __device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
   return v;
 }
 
-// Values that do not change from tile to tile are computed once per CTA and made opaque here: left alone, the compiler
-// re-derives them inside the tile loop (ncu r3r, inference epilogue: 495 warp instructions per 32-column slice of which
-// ~140 were the arithmetic; the rest recomputed swizzled offsets, the aligned shared-memory base and parameter loads).
-__device__ __forceinline__ uint32_t keep_u32(uint32_t x) {
-  asm volatile("" : "+r"(x));
-  return x;
-}
-template <typename T>
-__device__ __forceinline__ T* keep_ptr(T* x) {
-  asm volatile("" : "+l"(x));
-  return x;
-}
-
 // Walk of a persistent CTA over its pixel patches (patch0, patch0 + step, ...) as (tw, th, tt, n) counters: the
 // mixed-radix decomposition is done once, every further tile is a few adds and compares instead of four divisions.
 struct PatchWalk {

@@ -749,8 +749,48 @@ bn_bwd_tail2_apply_kernel(View dz, const uint8_t* __restrict__ mask_bits, BnTail
 }
 
 // ---- stem max-pool (1,3,3)/s(1,2,2)/p(0,1,1) with fused BN+ReLU on load ---------------------------------
-__global__ void maxpool_fwd_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, int N,
-                                   int T, int H, int W, int C, ViewW out, uint8_t* __restrict__ idx_out) {
+// general path of the pooling (some BatchNorm scale <= 0: the window maximum must be taken on the transformed values);
+// not inlined, so that its registers do not count against the kernel's common path
+__device__ __noinline__ void maxpool_fwd_general(const View& y, const float* scale, const float* shift, long long q,
+                                                 int ho, int wo, int c, int H, int W, int C, long long opix,
+                                                 const ViewW& out, uint8_t* idx_out) {
+  float s[8], b[8], best[8];
+  int bi[8];
+  load8f(scale + c, s);
+  load8f(shift + c, b);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; bi[i] = 0; }
+#pragma unroll
+  for (int kh = 0; kh < 3; ++kh) {
+    const int h = ho * 2 - 1 + kh;
+    if ((unsigned)h >= (unsigned)H) continue;
+#pragma unroll
+    for (int kw = 0; kw < 3; ++kw) {
+      const int w = wo * 2 - 1 + kw;
+      if ((unsigned)w >= (unsigned)W) continue;
+      float f[8];
+      unpack8(vload(y, (q * H + h) * W + w, c), f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float v = fmaxf(fmaf(f[i], s[i], b[i]), 0.f);
+        if (v > best[i]) { best[i] = v; bi[i] = kh * 3 + kw; }
+      }
+    }
+  }
+  vstore(out, opix, c, pack8(best));
+  if (idx_out) {
+    uint2 pk;
+    pk.x = (uint32_t)bi[0] | ((uint32_t)bi[1] << 8) | ((uint32_t)bi[2] << 16) | ((uint32_t)bi[3] << 24);
+    pk.y = (uint32_t)bi[4] | ((uint32_t)bi[5] << 8) | ((uint32_t)bi[6] << 16) | ((uint32_t)bi[7] << 24);
+    *reinterpret_cast<uint2*>(idx_out + (size_t)opix * C + c) = pk;
+  }
+}
+
+// 42 registers at most (6 blocks of 256 threads per SM): at 60 registers / 4 blocks the kernel waited on its nine tap
+// loads with half the warps an SM can hold (ncu r3u: 42 % warps active, 12 long-scoreboard stalls per issue, 2.7 TB/s)
+__global__ void __launch_bounds__(256, 6)
+maxpool_fwd_kernel(View y, const float* __restrict__ scale, const float* __restrict__ shift, int N,
+                   int T, int H, int W, int C, ViewW out, uint8_t* __restrict__ idx_out) {
   const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
   const int CV = C >> 3;
   // grid.y = frame (n*T + t), grid.x strides over the frame's (pixel, channel vector) pairs: 32-bit index math only
@@ -764,93 +804,152 @@ __global__ void maxpool_fwd_kernel(View y, const float* __restrict__ scale, cons
     const int ho = (int)(pf / (unsigned)Wo);
     const long long opix = q * (Ho * Wo) + pf;
     float s[8], b[8], best[8];
-    int bi[8];
-    if (scale) { load8f(scale + c, s); load8f(shift + c, b); }
+    bool monotone = true;
+    if (scale) {
+      load8f(scale + c, s);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { best[i] = -INFINITY; bi[i] = 0; }
+      for (int i = 0; i < 8; ++i) monotone = monotone && s[i] > 0.f;
+    }
+    // the coefficients are fetched again where they are used (through a pointer the compiler cannot match with the
+    // loads above), so that they do not occupy 16 registers across the tap loop
+    const float* const scale2 = keep_ptr(scale);
+    if (monotone) {
+      // BatchNorm scale > 0 (or no affine): ReLU(scale*y + shift) is non-decreasing in y, so the window maximum is taken
+      // on the RAW bf16 pairs (one compare-mask + two bitwise selects per pair and tap, against ~5 fp32 instructions
+      // per element and tap on the general path below -- the kernel was instruction-bound: ncu r3l, 2.9 TB/s) and the
+      // affine + ReLU is applied once to the winner.  Where the transformed values tie only because ReLU clamps them
+      // to 0 the recorded tap may differ from the general path's first-of-ties; the gradient routed there is masked by
+      // the BatchNorm backward's ReLU mask either way.
+      uint32_t bq[4], tq[4];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int h = ho * 2 - 1 + kh;
-      if ((unsigned)h >= (unsigned)H) continue;
+      for (int j = 0; j < 4; ++j) { bq[j] = 0xFF80FF80u; tq[j] = 0u; }  // -inf pairs
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int w = wo * 2 - 1 + kw;
-        if ((unsigned)w >= (unsigned)W) continue;
-        float f[8];
-        unpack8(vload(y, (q * H + h) * W + w, c), f);
+      for (int kh = 0; kh < 3; ++kh) {
+        const int h = ho * 2 - 1 + kh;
+        if ((unsigned)h >= (unsigned)H) continue;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          float v = f[i];
-          if (scale) v = fmaxf(fmaf(v, s[i], b[i]), 0.f);
-          if (v > best[i]) { best[i] = v; bi[i] = kh * 3 + kw; }
+        for (int kw = 0; kw < 3; ++kw) {
+          const int w = wo * 2 - 1 + kw;
+          if ((unsigned)w >= (unsigned)W) continue;
+          const uint4 qv = vload(y, (q * H + h) * W + w, c);
+          const uint32_t in[4] = {qv.x, qv.y, qv.z, qv.w};
+          const uint32_t tap2 = (uint32_t)(kh * 3 + kw) * 0x00010001u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (idx_out) {
+              const uint32_t m = __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&in[j]),
+                                             *reinterpret_cast<const __nv_bfloat162*>(&bq[j]));
+              bq[j] = (in[j] & m) | (bq[j] & ~m);
+              tq[j] = (tap2 & m) | (tq[j] & ~m);
+            } else {
+              const __nv_bfloat162 mx = __hmax2(*reinterpret_cast<const __nv_bfloat162*>(&in[j]),
+                                                *reinterpret_cast<const __nv_bfloat162*>(&bq[j]));
+              bq[j] = *reinterpret_cast<const uint32_t*>(&mx);
+            }
+          }
         }
       }
-    }
-    vstore(out, opix, c, pack8(best));
-    if (idx_out) {
-      uint2 pk;
-      pk.x = (uint32_t)bi[0] | ((uint32_t)bi[1] << 8) | ((uint32_t)bi[2] << 16) | ((uint32_t)bi[3] << 24);
-      pk.y = (uint32_t)bi[4] | ((uint32_t)bi[5] << 8) | ((uint32_t)bi[6] << 16) | ((uint32_t)bi[7] << 24);
-      *reinterpret_cast<uint2*>(idx_out + (size_t)opix * C + c) = pk;
-    }
-  }
-}
-
-// gradient of the stem max-pool w.r.t. its input pixel (h, w) of frame q, 8 channels from c: the sum over the (at most four)
-// windows that cover the pixel of dout[window] where the window's arg-max is this pixel
-__device__ __forceinline__ void maxpool_bwd_gather(const View& dout, const uint8_t* __restrict__ idxs, long long q, int h,
-                                                   int w, int c, int C, int Ho, int Wo, float* acc) {
+      uint4 o = make_uint4(bq[0], bq[1], bq[2], bq[3]);
+      if (scale2) {
+        load8f(scale2 + c, s);
+        load8f(shift + c, b);
+        unpack8(o, best);
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  const int ha = (h + 1) >> 1, kha = h + 1 - 2 * ha;
-  const int wa = (w + 1) >> 1, kwa = w + 1 - 2 * wa;
-#pragma unroll
-  for (int a = 0; a < 2; ++a) {
-    const int ho = ha - a, kh = kha + 2 * a;
-    const bool vh = a == 0 ? ho < Ho : (kha == 0 && ho >= 0);
-#pragma unroll
-    for (int bq = 0; bq < 2; ++bq) {
-      const int wo = wa - bq, kw = kwa + 2 * bq;
-      const bool vw = bq == 0 ? wo < Wo : (kwa == 0 && wo >= 0);
-      if (vh && vw) {
-        const long long opix = (q * Ho + ho) * Wo + wo;
-        const uint2 pk = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
-        uint4 d = vload(dout, opix, c);
-        const uint32_t tap4 = (uint32_t)(kh * 3 + kw) * 0x01010101u;
-        const uint32_t m0 = __vcmpeq4(pk.x, tap4), m1 = __vcmpeq4(pk.y, tap4);  // 0xFF per matching channel
-        d.x &= __byte_perm(m0, 0, 0x1100);
-        d.y &= __byte_perm(m0, 0, 0x3322);
-        d.z &= __byte_perm(m1, 0, 0x1100);
-        d.w &= __byte_perm(m1, 0, 0x3322);
-        float f[8];
-        unpack8(d, f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] += f[i];
+        for (int i = 0; i < 8; ++i) best[i] = fmaxf(fmaf(best[i], s[i], b[i]), 0.f);
+        o = pack8(best);
       }
+      vstore(out, opix, c, o);
+      if (idx_out) {
+        uint2 pk;
+        pk.x = __byte_perm(tq[0], tq[1], 0x6420);
+        pk.y = __byte_perm(tq[2], tq[3], 0x6420);
+        *reinterpret_cast<uint2*>(idx_out + (size_t)opix * C + c) = pk;
+      }
+      continue;
     }
+    maxpool_fwd_general(y, scale2, shift, q, ho, wo, c, H, W, C, opix, out, idx_out);
   }
 }
 
-__global__ void maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, int N, int T, int H, int W, int C,
-                                   ViewW dz) {
-  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;
+// Backward of the stem max-pool.  One thread owns a 2x2 block of input pixels (rows 2i, 2i+1; columns 2j, 2j+1) and 8
+// channels: the only windows that cover those pixels are (i+u, j+v), u, v in {0, 1} -- row 2i lies in window row i alone
+// (tap 1), row 2i+1 in window rows i (tap 2) and i+1 (tap 0), the same along w -- so four (arg-max bytes, gradient)
+// pairs are loaded once and serve four pixels; per input pixel the kernel loaded up to four of them (2.25 on average)
+// and was bound by its instruction count (ncu r3u: 96 % warps active, math-pipe throttle the top stall, 2.4 TB/s).
+// The arg-max bytes are compared four at a time and turned into bf16-pair masks; a pixel covered by ONE window takes
+// the masked gradient as it is, the others sum in fp32 (the same values as the per-pixel kernel produced).
+__device__ __forceinline__ uint4 maxpool_mask_tap(const uint4& d, const uint2& k, int tap) {
+  const uint32_t tap4 = (uint32_t)tap * 0x01010101u;
+  const uint32_t m0 = __vcmpeq4(k.x, tap4), m1 = __vcmpeq4(k.y, tap4);  // 0xFF per matching channel
+  uint4 r;
+  r.x = d.x & __byte_perm(m0, 0, 0x1100);
+  r.y = d.y & __byte_perm(m0, 0, 0x3322);
+  r.z = d.z & __byte_perm(m1, 0, 0x1100);
+  r.w = d.w & __byte_perm(m1, 0, 0x3322);
+  return r;
+}
+
+__global__ void __launch_bounds__(256, 4)
+maxpool_bwd_kernel(View dout, const uint8_t* __restrict__ idxs, int N, int T, int H, int W, int C, ViewW dz) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1;  // = ceil(H/2), ceil(W/2): one 2x2 block per window origin
   const int CV = C >> 3;
-  const unsigned per_frame = (unsigned)(H * W * CV);
+  const unsigned per_frame = (unsigned)(Ho * Wo * CV);
   const long long q = blockIdx.y;  // frame n*T + t
   for (unsigned idx = blockIdx.x * blockDim.x + threadIdx.x; idx < per_frame; idx += gridDim.x * blockDim.x) {
     const int c = (int)(idx % (unsigned)CV) << 3;
     const unsigned pf = idx / (unsigned)CV;
-    const int w = (int)(pf % (unsigned)W);
-    const int h = (int)(pf / (unsigned)W);
-    const long long ipix = q * (H * W) + pf;
-    // The windows covering input (h, w): ho = (h+1)/2 with tap kh = h+1-2*ho (0 or 1) and, when that tap is 0, also
-    // ho-1 with tap 2 -- same along w.  Written as two candidates per dimension with validity predicates instead of
-    // parity tests inside a 3x3 tap loop: neighbouring lanes have opposite parities, so the tap loop made every warp
-    // run all taps with half its lanes idle.  The arg-max bytes are compared four at a time and turned into
-    // bf16-pair masks (no per-channel extract / compare / select).
-    float acc[8];
-    maxpool_bwd_gather(dout, idxs, q, h, w, c, C, Ho, Wo, acc);
-    vstore(dz, ipix, c, pack8(acc));
+    const int j = (int)(pf % (unsigned)Wo);
+    const int i = (int)(pf / (unsigned)Wo);
+    uint4 d[2][2];
+    uint2 k[2][2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+#pragma unroll
+      for (int v = 0; v < 2; ++v) {
+        d[u][v] = make_uint4(0, 0, 0, 0);
+        k[u][v] = make_uint2(0xFFFFFFFFu, 0xFFFFFFFFu);  // matches no tap
+        if (i + u < Ho && j + v < Wo) {
+          const long long opix = (q * Ho + (i + u)) * Wo + (j + v);
+          k[u][v] = *reinterpret_cast<const uint2*>(idxs + (size_t)opix * C + c);
+          d[u][v] = vload(dout, opix, c);
+        }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const int h = 2 * i + a;
+      if (h >= H) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int w = 2 * j + b;
+        if (w >= W) continue;
+        const long long ipix = (q * H + h) * W + w;
+        // window rows / columns that cover this pixel and the tap it is in each of them
+        const int nu = a == 0 ? 1 : 2, nv = b == 0 ? 1 : 2;
+        if (nu == 1 && nv == 1) {
+          vstore(dz, ipix, c, maxpool_mask_tap(d[0][0], k[0][0], 1 * 3 + 1));
+          continue;
+        }
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (u >= nu) continue;
+          const int kh = a == 0 ? 1 : (u == 0 ? 2 : 0);
+#pragma unroll
+          for (int v = 0; v < 2; ++v) {
+            if (v >= nv) continue;
+            const int kw = b == 0 ? 1 : (v == 0 ? 2 : 0);
+            float f[8];
+            unpack8(maxpool_mask_tap(d[u][v], k[u][v], kh * 3 + kw), f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += f[e];
+          }
+        }
+        vstore(dz, ipix, c, pack8(acc));
+      }
+    }
   }
 }
 

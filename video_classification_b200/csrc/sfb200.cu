@@ -1437,7 +1437,8 @@ int sfb_maxpool_bwd(const void* dout, int32_t d_ld, int32_t d_coff, const uint8_
   View vd{(const __nv_bfloat16*)dout, d_ld, d_coff};
   ViewW vz{(__nv_bfloat16*)dz, dz_ld, dz_coff};
   if ((long long)N * T > 65535 || (long long)H * W * (C >> 3) >= (1ll << 31)) return SFB_ERR_UNSUPPORTED;
-  const long long per_frame = (long long)H * W * (C >> 3);
+  const int Hb = (H - 1) / 2 + 1, Wb = (W - 1) / 2 + 1;  // 2x2 blocks of input pixels = pooling windows
+  const long long per_frame = (long long)Hb * Wb * (C >> 3);
   dim3 grid((unsigned)grid_for(per_frame, 256, 64), (unsigned)(N * T));
   maxpool_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(vd, idx, N, T, H, W, C, vz);
   SFB_CHECK_LAUNCH("maxpool_bwd_kernel");
