@@ -60,6 +60,10 @@ CONV_CASES = [
     ("lateral0_3x1x1_8_16_s4", 2, 16, 6, 6, 8, 16, (3, 1, 1), (4, 1, 1)),
     ("odd_1x3x3_64_64_s2", 1, 3, 13, 11, 64, 64, (1, 3, 3), (1, 2, 2)),
     ("fast_1x1x1_32_64_s2", 2, 4, 14, 14, 32, 64, (1, 1, 1), (1, 2, 2)),
+    # halo-mode patches of the (1,3,3) 64-channel convs: 7-wide maps (pixel-folded Fast stages), a 15-wide map (second
+    # patch column of one pixel), partial patch rows
+    ("halo_1x3x3_64_64_w7", 2, 3, 28, 7, 64, 64, (1, 3, 3), (1, 1, 1)),
+    ("halo_1x3x3_64_64_w15", 1, 2, 17, 15, 64, 64, (1, 3, 3), (1, 1, 1)),
 ]
 
 

@@ -610,6 +610,8 @@ DGRAD_BN_CASES = [
     ("odd_b_1x3x3_32_32", 2, 5, 13, 11, 32, 32, (1, 3, 3), (1, 1, 1)),        # partial patches, 32-channel boxes
     ("fast_c_1x1x1_8_32", 2, 8, 12, 12, 8, 32, (1, 1, 1), (1, 1, 1)),         # 8 real channels in a 16-channel buffer
     ("fast_b_1x3x3_16_16_s2", 2, 8, 14, 14, 16, 16, (1, 3, 3), (1, 2, 2)),
+    ("halo_b_1x3x3_64_64_w7", 2, 3, 28, 7, 64, 64, (1, 3, 3), (1, 1, 1)),     # halo-mode patches (one box per tile)
+    ("halo_b_1x3x3_64_64_big", 2, 2, 56, 56, 64, 64, (1, 3, 3), (1, 1, 1)),
 ]
 
 
@@ -749,3 +751,31 @@ def test_bn_bwd_tail2_equals_two_separate_passes(C_):
         torch.testing.assert_close(dg2, dg, rtol=1e-4, atol=1e-4 * float(dg.abs().max()))
         torch.testing.assert_close(db2, db, rtol=1e-4, atol=1e-4 * float(db.abs().max()))
         assert kc.relerr(kc.from_act(dy2), kc.from_act(dy)) < 1e-2
+
+
+@pytest.mark.parametrize("name", ["1x3x3_64_64", "big_1x3x3_64_64", "halo_1x3x3_64_64_w7", "halo_1x3x3_64_64_w15"])
+def test_halo_mode_equals_tap_by_tap_boxes(name, monkeypatch):
+    """(1,3,3) 64-channel convs fetch ONE box per tile (patch + border) and read the nine taps through shifted
+    descriptors; SFB_HALO=0 fetches one box per tap.  Same MMAs in the same order: the results are identical."""
+    case = [c for c in kc.CONV_CASES if c[0] == name][0]
+    _, N, T, H, W, Ci, Co, k, s = case
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = kc.to_act(torch.randn((N, Ci, T, H, W), device=DEV, generator=g))
+    w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Ci * 9) ** 0.5
+    dy = kc.to_act(torch.randn((N, Co, T, H, W), device=DEV, generator=g))
+    wp = ops.pack_weight(w.contiguous(), x.C)
+    wpt = ops.pack_weight_dgrad(w.contiguous(), Co, s)
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("SFB_HALO", flag)
+        y = Act.empty(N, T, H, W, Co, zero=True)
+        stats = torch.zeros(2 * Co, device=DEV)
+        ops.conv_gemm(x, wp, y, k, s, (0, 1, 1), stats=stats)
+        dx = Act.empty(N, T, H, W, Ci, zero=True)
+        ops.conv_gemm(dy, wpt, dx, k, s, (0, 1, 1), transposed=True)
+        torch.cuda.synchronize()
+        outs[flag] = (y.buf.clone(), stats.clone(), dx.buf.clone())
+    assert torch.equal(outs["0"][0], outs["1"][0])
+    assert torch.equal(outs["0"][2], outs["1"][2])
+    torch.testing.assert_close(outs["1"][1], outs["0"][1], rtol=1e-5, atol=1e-3)   # fp32 atomics in another order
+    assert float(outs["1"][0].float().abs().max()) > 0

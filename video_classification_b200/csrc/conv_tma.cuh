@@ -90,6 +90,16 @@ struct ConvTmaParams {
   int res_tile;                // kEpiAffine: the residual tile arrives by TMA through tmap_y into the same buffer, one
                                // chunk ahead (per-thread global loads left the epilogue waiting on HBM once per chunk:
                                // the block-tail convs of the eval forward ran at half their roofline)
+  // ---- halo mode ((1,3,3) stride-1 convs on 64-channel pixels, weights resident): ONE box per tile brings the patch
+  //      with its one-pixel border, [Ht+2][Wt+2] pixels of 128 bytes; tap (kh, kw) is the same shared memory read
+  //      through a descriptor whose start is kh*(Wt+2) + kw pixel rows further on.  MMA row r stands for pixel
+  //      (r / pitch, r % pitch): the two rows per line that wrap into the next line are computed and thrown away.
+  //      Nine 16 KB boxes per tile became one of <= 21 KB: these layers were bound by the shared-memory bandwidth that
+  //      the TMA fills and the MMA operand reads share (ncu r3x: 36 % tensor, 36 % L2, 64 % SM throughput).
+  int halo;                    // 0 / 1
+  int pitch;                   // Wt + 2
+  uint32_t halo_stride;        // bytes between pipeline stages in halo mode (one stage = one tile's box)
+  uint32_t halo_bytes;         // bytes of one box: pitch * (Ht + 2) * 128
   const float* bn_scale;
   const float* bn_shift;
   const float* bn_mean;
@@ -193,6 +203,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   using L = ConvTmaCfg<BN, BRES>;
   constexpr int SMAX = L::kStages;
   const int S = p.nstages;
+  const bool halo = BRES && BN == 64 && p.halo != 0;  // only the 64-wide resident-weight instantiations carry the code
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
@@ -226,6 +237,14 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     tma_prefetch_desc(&tmap_w);
     tma_prefetch_desc(&tmap_o);
     if (p.bn_mode) tma_prefetch_desc(&tmap_y);
+  }
+  if (halo) {
+    // staging rows past the patch's Wt*Ht pixels are never written in halo mode and must read as zeros (statistics)
+    for (int i = tid; i < L::kStagingBytes / 16; i += L::kThreads) {
+      reinterpret_cast<uint4*>(smem + L::kStagingOff)[i] = make_uint4(0, 0, 0, 0);
+      if (p.stg2_off) reinterpret_cast<uint4*>(smem + p.stg2_off)[i] = make_uint4(0, 0, 0, 0);
+    }
+    fence_proxy_async_smem();
   }
   if (p.bn_mode) {
     // rows of the y tile a box never writes (patches of fewer than 128 pixels) must read as finite numbers
@@ -273,6 +292,16 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     pw.init(patch0, patch_step, p);
     for (int patch = patch0; patch < p.total_patches; patch += patch_step, pw.next(p)) {
       const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
+      if (halo) {
+        mbar_wait(&empty_bar[s], ph, 11);
+        if (leader) {
+          mbar_arrive_expect_tx(&full_bar[s], p.halo_bytes);
+          tma_load_5d(smem0 + (uint32_t)s * p.halo_stride, &tmap_a, &full_bar[s], 0, tw * p.Wt - 1, th * p.Ht - 1, tt, n);
+        }
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1; }
+        continue;
+      }
       const int bw = p.transposed ? tw * p.Wt + p.pW : tw * p.Wt * p.sW - p.pW;
       const int bh = p.transposed ? th * p.Ht + p.pH : th * p.Ht * p.sH - p.pH;
       const int bt = p.transposed ? tt * p.Tt + p.pT : tt * p.Tt * p.sT - p.pT;
@@ -329,6 +358,29 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+      if (halo) {
+        // one stage = the tile's box; tap (kh, kw) starts kh*pitch + kw pixel rows into it (mirrored for dgrad)
+        mbar_wait(&full_bar[s], ph, 13);
+        tc_fence_after();
+        const uint64_t ad_s = adesc0 + (uint64_t)(((uint32_t)s * p.halo_stride) >> 4);
+        if (leader) {
+          int kh = 0, kw = 0;
+          for (int tap = 0; tap < 9; ++tap) {
+            const int roff = p.transposed ? (2 - kh) * p.pitch + (2 - kw) : kh * p.pitch + kw;
+            const uint64_t ad0 = ad_s + (uint64_t)((uint32_t)(roff * 128) >> 4);
+            const uint64_t bd0 = bdesc0 + (uint64_t)(((uint32_t)tap * (BN * 128)) >> 4);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              umma_bf16(d_tmem, ad0 + (uint64_t)(kk * 2), bd0 + (uint64_t)(kk * 2), idesc, (tap | kk) != 0 ? 1u : 0u);
+            if (++kw == 3) { kw = 0; ++kh; }
+          }
+          umma_commit(&empty_bar[s]);
+          umma_commit(&tfull_bar[buf]);
+        }
+        __syncwarp();
+        if (++s == S) { s = 0; ph ^= 1; }
+        continue;
+      }
       for (int kc = 0; kc < p.nk; ++kc) {
         mbar_wait(&full_bar[s], ph, 13);
         tc_fence_after();
@@ -358,7 +410,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int q4 = warp & 3;             // TMEM lane quadrant this warp may read
     const int te = tid - 64;
     const int cslice = (warp - 2) >> 2;  // 32-column slice of the chunk
-    const int r = q4 * 32 + lane;
+    const int r_mma = q4 * 32 + lane;    // accumulator row (TMEM lane) of this thread
+    // halo mode: row r_mma is pixel (r_mma / pitch, r_mma % pitch) of the patch; its staging row is the compact index
+    const bool row_live = !halo || (r_mma % p.pitch < p.Wt && r_mma / p.pitch < p.Ht);
+    const int r = halo ? (row_live ? (r_mma / p.pitch) * p.Wt + r_mma % p.pitch : 0) : r_mma;
     const int ww = r % p.Wt;
     const int hh = (r / p.Wt) % p.Ht;
     const int tq = r / (p.Wt * p.Ht);
@@ -444,7 +499,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
       const int wo = w0 + ww, ho = h0 + hh, to = t0 + tq;
-      const bool mv = r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
+      const bool mv = row_live && r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
       const long long m = (p.res && mv) ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
       const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
       const int buf = it & 1;
@@ -482,7 +537,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                   if (nb + j * 8 < p.Co) {
                     uint4 pk = pack8(v + j * 8);
                     if (!mv) pk = make_uint4(0, 0, 0, 0);
-                    sts_v4(stg + soff[j], pk);
+                    if (row_live) sts_v4(stg + soff[j], pk);
                   }
                 }
               }
@@ -531,7 +586,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                   }
                   uint4 pk = pack8(f);
                   if (!mv) pk = make_uint4(0, 0, 0, 0);
-                  sts_v4(stg + soff[j], pk);
+                  if (row_live) sts_v4(stg + soff[j], pk);
                 }
               }
             }

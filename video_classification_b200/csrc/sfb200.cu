@@ -333,6 +333,14 @@ void pick_patch(int Wo, int Ho, int To, int sW, int sH, int sT, int* Wt, int* Ht
   *Wt = bw; *Ht = bh; *Tt = bt;
 }
 
+// bytes between the pipeline stages of a halo-mode launch: 168 pixel rows of 128 bytes (a box of <= 10 x 16 pixels plus
+// the two rows the last taps read past it)
+constexpr uint32_t kHaloStride = 168 * 128;
+inline bool halo_enabled() {  // SFB_HALO=0: tap-by-tap boxes for those layers too (read per call: tests compare both)
+  const char* e = getenv("SFB_HALO");
+  return !(e && *e == '0');
+}
+
 inline int side_depth() {
   static const int d = [] {
     const char* e = getenv("SFB_SIDE_DEPTH");
@@ -365,6 +373,16 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
     pp.nstages -= drop;
     return (uint32_t)(pp.nstages * L::kStage);
   };
+  if (p.halo) {
+    // three stages of kHaloStride bytes at the front of the pipeline area; the rest of it holds the extra tiles
+    if (!BRES || 3 * (size_t)kHaloStride + 3 * tile_bytes > (size_t)L::kStagingOff) return SFB_ERR_UNSUPPORTED;
+    pp.nstages = 3;
+    pp.stg2_off = 3 * kHaloStride;
+    if (side_tile) {
+      pp.ybuf_off = pp.stg2_off + (uint32_t)tile_bytes;
+      if (side_depth() >= 2) pp.ybuf2_off = pp.ybuf_off + (uint32_t)tile_bytes;
+    }
+  } else {
   pp.stg2_off = tail_slot();
   if (side_tile) {
     // with two side tiles the requests run two chunks ahead (ConvTmaParams::ybuf2_off); the fused dgrads keep at least
@@ -391,6 +409,7 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
         if (!pp.ybuf_off) return SFB_ERR_UNSUPPORTED;
       }
     }
+  }
   }
   if (used) smem_total = 1024 + base + (size_t)used * tile_bytes;
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
@@ -1025,6 +1044,22 @@ int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pr
     q.taps = taps; q.Ktot = p.Ktot; q.nk = p.nk;
     if (geom->Cg >= 64 && q.cchunks * taps != q.nk) return SFB_ERR_BAD_ARG;
     pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt);
+    // halo mode (ConvTmaParams::halo): (1,3,3) / stride 1 / pad (0,1,1) on 64-channel pixels with <= 64 outputs -- the
+    // conv_b of Slow res2 and of every pixel-folded Fast stage; the patch is <= 14 pixels wide so that a line of the box
+    // with its border is <= 16 pixel rows, and as tall as 128 MMA rows allow
+    int halo_gw = 0, halo_gh = 0;
+    if (halo_enabled() && taps == 9 && geom->kT == 1 && geom->kH == 3 && geom->kW == 3 && geom->sT == 1 && geom->sH == 1 &&
+        geom->sW == 1 && geom->pT == 0 && geom->pH == 1 && geom->pW == 1 && geom->Cg == 64 && bnt == 64 && p.nk == 9 &&
+        ConvTmaCfg<64, true>::smem_bytes(p.nk) <= 227 * 1024) {
+      const int wt = q.Wo + 2 <= 16 ? q.Wo : 14, pitch = wt + 2;
+      const int ht = std::min(q.Ho, 128 / pitch);
+      if ((ht + 2) * pitch <= (int)(kHaloStride / 128) && 2 * pitch + 2 + 128 <= (int)(kHaloStride / 128) && ht * wt >= 96) {
+        q.halo = 1; q.pitch = pitch; q.Wt = wt; q.Ht = ht; q.Tt = 1;
+        q.halo_stride = kHaloStride;
+        q.halo_bytes = (uint32_t)(pitch * (ht + 2) * 128);
+        halo_gw = pitch; halo_gh = ht + 2;
+      }
+    }
     q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
     q.n_tiles = (geom->Co + bnt - 1) / bnt;
     const long long tt = (long long)q.N * q.tilesT * q.tilesH * q.tilesW;
@@ -1040,8 +1075,12 @@ int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pr
     }
     CUtensorMap ta;
     const int sW = geom->transposed ? 1 : q.sW, sH = geom->transposed ? 1 : q.sH, sT = geom->transposed ? 1 : q.sT;
-    rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,
-                      q.Tt, sW, sH, sT, &ta);
+    if (q.halo)
+      rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, 64, halo_gw, halo_gh, 1,
+                        1, 1, 1, &ta);
+    else
+      rc = get_act_tmap((const __nv_bfloat16*)g + geom->g_coff, geom->Cg, gW, gH, gT, gN, geom->g_ld, q.box_k, q.Wt, q.Ht,
+                        q.Tt, sW, sH, sT, &ta);
     if (rc) return rc;
     CUtensorMap to;
     rc = get_act_tmap((const __nv_bfloat16*)out + geom->o_coff, geom->Co, q.Wo, q.Ho, q.To, q.N, geom->o_ld, q.ocols, q.Wt,
