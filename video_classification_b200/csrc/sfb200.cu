@@ -341,12 +341,9 @@ inline bool halo_enabled() {  // SFB_HALO=0: tap-by-tap boxes for those layers t
   return !(e && *e == '0');
 }
 
-inline int side_depth() {
-  static const int d = [] {
-    const char* e = getenv("SFB_SIDE_DEPTH");
-    return e && *e ? atoi(e) : 2;
-  }();
-  return d;
+inline int side_depth() {  // SFB_SIDE_DEPTH=1: one side tile (read per call, like SFB_HALO)
+  const char* e = getenv("SFB_SIDE_DEPTH");
+  return e && *e ? atoi(e) : 2;
 }
 
 template <int BN, bool BRES, int MODE>
