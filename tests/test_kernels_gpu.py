@@ -779,3 +779,36 @@ def test_halo_mode_equals_tap_by_tap_boxes(name, monkeypatch):
     assert torch.equal(outs["0"][2], outs["1"][2])
     torch.testing.assert_close(outs["1"][1], outs["0"][1], rtol=1e-5, atol=1e-3)   # fp32 atomics in another order
     assert float(outs["1"][0].float().abs().max()) > 0
+
+
+@pytest.mark.parametrize("name", ["3x1x1_1024_256", "big_3x1x1_640_256"])
+def test_cta_pair_mma_equals_single_cta(name, monkeypatch):
+    """The 256-wide streamed-weight convs run as CTA pairs (cta_group::2: one 256-row MMA over two neighbouring patches,
+    each CTA staging its own pixels and half of the weight tile); SFB_PAIR=0 runs them one CTA per tile.  Same MMAs on
+    the same operands in the same K order: identical results; an odd number of patches leaves the last pair half empty."""
+    case = [c for c in kc.CONV_CASES if c[0] == name][0]
+    _, N, T, H, W, Ci, Co, k, s = case
+    g = torch.Generator(device=DEV).manual_seed(5)
+    p = tuple(kk // 2 for kk in k)
+    for n_clips in (N, 1):                                      # 1 clip of 8x7x7: 4 patches (3 with T = 5 below)
+        Tn = T if n_clips == N else 5
+        x = kc.to_act(torch.randn((n_clips, Ci, Tn, H, W), device=DEV, generator=g))
+        w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Ci * k[0] * k[1] * k[2]) ** 0.5
+        dy = kc.to_act(torch.randn((n_clips, Co, Tn, H, W), device=DEV, generator=g))
+        wp = ops.pack_weight(w.contiguous(), x.C)
+        wpt = ops.pack_weight_dgrad(w.contiguous(), Co, s)
+        outs = {}
+        for flag in ("0", "1"):
+            monkeypatch.setenv("SFB_PAIR", flag)
+            y = Act.empty(n_clips, Tn, H, W, Co, zero=True)
+            stats = torch.zeros(2 * Co, device=DEV)
+            ops.conv_gemm(x, wp, y, k, s, p, stats=stats)
+            dx = Act.empty(n_clips, Tn, H, W, Ci, zero=True)
+            ops.conv_gemm(dy, wpt, dx, k, s, p, transposed=True)
+            torch.cuda.synchronize()
+            outs[flag] = (y.buf.clone(), stats.clone(), dx.buf.clone())
+        assert torch.equal(outs["0"][0], outs["1"][0])
+        assert torch.equal(outs["0"][2], outs["1"][2])
+        torch.testing.assert_close(outs["1"][1], outs["0"][1], rtol=1e-5, atol=1e-3)
+        ref = F.conv3d(kc.from_act(x), w.bfloat16().float(), stride=s, padding=p)
+        assert kc.relerr(kc.from_act(Act(outs["1"][0], 0, Co)), ref) < 2e-2

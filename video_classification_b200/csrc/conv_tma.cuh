@@ -36,6 +36,23 @@ __device__ __forceinline__ void tma_load_2d_u32(uint32_t smem_dst, const void* t
       : "memory");
 }
 
+// CTA-pair loads: the data lands in THIS CTA's shared memory, the transaction bytes are signalled on a barrier of the
+// pair's leader CTA (a shared::cluster address from mapa) -- what .cta_group::2 allows
+__device__ __forceinline__ void tma_load_5d_pair(uint32_t smem_dst, const void* tmap, uint32_t bar_cluster, int32_t c0,
+                                                 int32_t c1, int32_t c2, int32_t c3, int32_t c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const void* tmap, uint32_t bar_cluster, int32_t x,
+                                                 int32_t y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar_cluster), "r"(x), "r"(y)
+      : "memory");
+}
+
 // K-major shared-memory operand descriptor for a swizzle span of `span` bytes (128 / 64 / 32):
 // rows are `span` bytes apart, 8-row atoms are 8*span bytes apart (SBO); layout type 2 / 4 / 6.
 __device__ __forceinline__ uint64_t umma_smem_desc_kmajor(uint32_t smem_addr, uint32_t span) {
@@ -96,6 +113,7 @@ struct ConvTmaParams {
   //      (r / pitch, r % pitch): the two rows per line that wrap into the next line are computed and thrown away.
   //      Nine 16 KB boxes per tile became one of <= 21 KB: these layers were bound by the shared-memory bandwidth that
   //      the TMA fills and the MMA operand reads share (ncu r3x: 36 % tensor, 36 % L2, 64 % SM throughput).
+  int pair;                    // 1: launch the CTA-pair instantiation (cta_group::2) when the weights are streamed
   int halo;                    // 0 / 1
   int pitch;                   // Wt + 2
   uint32_t halo_stride;        // bytes between pipeline stages in halo mode (one stage = one tile's box)
@@ -166,11 +184,16 @@ struct PatchWalk {
 // BRES: the CTA's whole weight slice [BN][Ktot] stays resident in shared memory (loaded once; a persistent CTA works
 // on one N tile for its whole life), so a pipeline stage carries the activation boxes only.  Small-K layers were bound
 // by L2->SM traffic, of which the per-tile weight re-fetch was 1/3 (64->64 (1,3,3)) to 2/3 (64->256 pointwise).
-template <int BN, bool BRES = false>
+// PAIR: two CTAs of a cluster run one 256-row MMA (cta_group::2) on a 256-wide N tile; each CTA stages its own 128 pixel
+// rows and HALF of the weight tile (128 of the 256 rows): a stage is 32 KB instead of 48 and an MMA reads 8 KB of
+// operands per SM instead of 12 -- the streamed-weight layers were bound by that shared-memory traffic at ~68 % of the
+// MMA floor (fill 48 KB + operand reads 48 KB per 512 MMA cycles against a 128 B/clk port).
+template <int BN, bool BRES = false, bool PAIR = false>
 struct ConvTmaCfg {
-  static constexpr int kStages = BRES ? (BN >= 128 ? 6 : 8) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8));
+  static_assert(!PAIR || (BN == 256 && !BRES), "the CTA-pair kernel is the 256-wide streamed-weight one");
+  static constexpr int kStages = PAIR ? 6 : (BRES ? (BN >= 128 ? 6 : 8) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8)));
   static constexpr int kAStage = 128 * 128;  // 16 KB: 128 rows x (64 | 2x32 | 4x16) channels
-  static constexpr int kBStage = BRES ? 0 : BN * 128;
+  static constexpr int kBStage = BRES ? 0 : (PAIR ? 128 * 128 : BN * 128);
   static constexpr int kStage = kAStage + kBStage;
   static constexpr int kChunk = BN < 128 ? BN : 128;                  // output columns staged per pass
   static constexpr int kChunks = BN / kChunk;
@@ -195,12 +218,14 @@ struct ConvTmaCfg {
 //   kEpiAffine inference: folded-BatchNorm affine, residual, ReLU
 //   kEpiBnBwd  dgrad with the fused BatchNorm-backward reduction (ConvTmaParams::bn_*)
 enum { kEpiPlain = 0, kEpiAffine = 1, kEpiBnBwd = 2 };
-template <int BN, bool BRES = false, int MODE = kEpiPlain>
-__global__ void __launch_bounds__(ConvTmaCfg<BN, BRES>::kThreads, 1)
+template <int BN, bool BRES = false, int MODE = kEpiPlain, bool PAIR = false>
+__global__ void __launch_bounds__(ConvTmaCfg<BN, BRES, PAIR>::kThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                 const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_y,
                 const ConvTmaParams p) {
-  using L = ConvTmaCfg<BN, BRES>;
+  using L = ConvTmaCfg<BN, BRES, PAIR>;
+  // CTA pair: launched as clusters of two; rank 0 (the leader) issues the MMAs for both
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   constexpr int SMAX = L::kStages;
   const int S = p.nstages;
   const bool halo = BRES && BN == 64 && p.halo != 0;  // only the 64-wide resident-weight instantiations carry the code
@@ -220,12 +245,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   if (tid == 0) {
     for (int s = 0; s < SMAX; ++s) {
-      mbar_init(&full_bar[s], 1);
+      mbar_init(&full_bar[s], 1);  // pair: the leader arrives and expects the bytes of BOTH CTAs' loads
       mbar_init(&empty_bar[s], 1);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull_bar[b], 1);
-      mbar_init(&tempty_bar[b], L::kEpiWarps);
+      mbar_init(&tempty_bar[b], PAIR ? 2 * L::kEpiWarps : L::kEpiWarps);  // pair: the epilogues of both CTAs
     }
     mbar_init(bres_bar, 1);
     mbar_init(&y_bar[0], 1);
@@ -260,6 +285,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the peer's barriers are initialised before anything is signalled on them
   tc_fence_after();
   const uint32_t tmem_base = uniform_u32(*tmem_holder);
   const int rows = p.Wt * p.Ht * p.Tt;
@@ -268,9 +294,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const uint32_t sub_stride = (uint32_t)(128 * p.box_k * 2);
   const int khw = p.kH * p.kW;
   // this CTA's N tile and its walk over the pixel patches
-  const int nt = blockIdx.x % p.n_tiles;
-  const int patch0 = blockIdx.x / p.n_tiles;
-  const int patch_step = gridDim.x / p.n_tiles;
+  // (pair: the two CTAs take neighbouring patches 2q + rank of the same N tile; the last pair of an odd patch count
+  //  gives rank 1 a patch past the end -- its boxes are out of range: zero operands, clipped stores -- so that both
+  //  CTAs run the same number of tiles)
+  const int unit = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int n_units = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int nt = unit % p.n_tiles;
+  const int patch0 = PAIR ? 2 * (unit / p.n_tiles) + (int)rank : unit / p.n_tiles;
+  const int patch_step = PAIR ? 2 * (n_units / p.n_tiles) : n_units / p.n_tiles;
+  const int patch_lim = PAIR ? p.total_patches + (int)rank : p.total_patches;
   const int n0 = nt * BN;
 
   if (warp == 0) {
@@ -290,7 +322,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     uint32_t ph = 1;  // parity to wait on for "stage s is free"
     PatchWalk pw;
     pw.init(patch0, patch_step, p);
-    for (int patch = patch0; patch < p.total_patches; patch += patch_step, pw.next(p)) {
+    for (int patch = patch0; patch < patch_lim; patch += patch_step, pw.next(p)) {
       const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       if (halo) {
         mbar_wait(&empty_bar[s], ph, 11);
@@ -309,7 +341,21 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       for (int kc = 0; kc < p.nk; ++kc) {
         mbar_wait(&empty_bar[s], ph, 11);
         const uint32_t sa = smem0 + (uint32_t)s * L::kStage;
-        if (p.Cg >= 64) {
+        if (PAIR) {
+          // both CTAs' loads count their bytes on the leader's barrier (its own 16 KB of pixels and its half of the
+          // weight tile each); only the leader arrives.  The peer cannot get a phase ahead: it refills a stage only after
+          // the leader's MMAs on it were committed, i.e. after the leader saw this phase complete.
+          if (leader) {
+            const uint32_t fb = mapa_u32(smem_u32(&full_bar[s]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&full_bar[s], 2u * (box_bytes + (uint32_t)L::kBStage));
+            tma_load_5d_pair(sa, &tmap_a, fb, cc * 64, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
+            tma_load_2d_pair(sa + L::kAStage, &tmap_w, fb, p.wk0 + kc * 64, n0 + (int)rank * 128);
+          }
+          if (++cc == p.cchunks) {
+            cc = 0;
+            if (++kw == p.kW) { kw = 0; if (++kh == p.kH) { kh = 0; ++kt; } }
+          }
+        } else if (p.Cg >= 64) {
           if (leader) {
             mbar_arrive_expect_tx(&full_bar[s], box_bytes + (uint32_t)L::kBStage);
             tma_load_5d(sa, &tmap_a, &full_bar[s], cc * 64, bw + sgn * kw, bh + sgn * kh, bt + sgn * kt, n);
@@ -328,15 +374,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           }
           tap += nbox;
         }
-        if (!BRES && leader) tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
+        if (!BRES && !PAIR && leader) tma_load_2d_u32(sa + L::kAStage, &tmap_w, &full_bar[s], p.wk0 + kc * 64, n0);
         __syncwarp();
         if (++s == S) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 1) {
-    // ======================= MMA issuer (warp-uniform loop, one elected lane issues) =======================
+  } else if (warp == 1 && rank == 0) {
+    // ======================= MMA issuer (warp-uniform loop, one elected lane issues; pair: the leader CTA only) =======
     const bool leader = elect_one();
-    const uint32_t idesc = umma_idesc_bf16(128, BN, 0, 0);
+    const uint32_t idesc = umma_idesc_bf16(PAIR ? 256 : 128, BN, 0, 0);
     const uint32_t span = (uint32_t)(p.box_k * 2);
     // descriptors = constant + offset in the 14-bit start-address field: one add per operand per MMA
     const uint64_t adesc0 = umma_smem_desc_kmajor(smem_u32(smem), span);
@@ -353,7 +399,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     uint32_t ph = 0;
     int it = 0;
     if (BRES && patch0 < p.total_patches) mbar_wait(bres_bar, 0, 15);
-    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it) {
+    for (int patch = patch0; patch < patch_lim; patch += patch_step, ++it) {
       const int buf = it & 1;
       mbar_wait(&tempty_bar[buf], (uint32_t)(((it >> 1) & 1) ^ 1), 12);
       tc_fence_after();
@@ -390,17 +436,22 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         if (leader) {
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
-            if (kk < nkk) umma_bf16(d_tmem, ad0 + aoff[kk], bd0 + (uint64_t)(kk * 2), idesc, (kc | kk) != 0 ? 1u : 0u);
+            if (kk < nkk) {
+              if (PAIR) umma_bf16_pair(d_tmem, ad0 + aoff[kk], bd0 + (uint64_t)(kk * 2), idesc, (kc | kk) != 0 ? 1u : 0u);
+              else umma_bf16(d_tmem, ad0 + aoff[kk], bd0 + (uint64_t)(kk * 2), idesc, (kc | kk) != 0 ? 1u : 0u);
+            }
           }
-          umma_commit(&empty_bar[s]);
+          if (PAIR) umma_commit_pair(&empty_bar[s]); else umma_commit(&empty_bar[s]);
         }
         __syncwarp();
         if (++s == S) { s = 0; ph ^= 1; }
       }
-      if (leader) umma_commit(&tfull_bar[buf]);
+      if (leader) {
+        if (PAIR) umma_commit_pair(&tfull_bar[buf]); else umma_commit(&tfull_bar[buf]);
+      }
       __syncwarp();
     }
-  } else {
+  } else if (warp >= 2) {
     // ======================= epilogue (warps 2..5; TMEM lanes 32*(warp&3)..) =======================
     // TMEM -> registers -> (affine, residual, ReLU) -> bf16 -> swizzled staging tile in shared memory -> TMA store.
     // BatchNorm statistics are column sums of the staged (bf16-rounded) tile, kept in registers across all tiles.
@@ -476,7 +527,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     int pf_patch = patch0, pf_ch = 0;
     uint32_t yreq = 0;
     auto request_side_tile = [&]() {
-      if (pf_patch >= p.total_patches) return;
+      if (pf_patch >= patch_lim) return;
       const int col = n0 + pf_ch * CH;
       const int nsub = (min(CH, p.Co - col) + ocols - 1) >> olog;
       uint64_t* bar = &y_bar[ydeep ? (yreq & 1) : 0];
@@ -495,11 +546,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       request_side_tile();
       if (ydeep) request_side_tile();
     }
-    for (int patch = patch0; patch < p.total_patches; patch += patch_step, ++it, pw.next(p)) {
+    for (int patch = patch0; patch < patch_lim; patch += patch_step, ++it, pw.next(p)) {
       const int tw = pw.tw, th = pw.th, tt = pw.tt, n = pw.n;
       const int w0 = tw * p.Wt, h0 = th * p.Ht, t0 = tt * p.Tt;
       const int wo = w0 + ww, ho = h0 + hh, to = t0 + tq;
-      const bool mv = row_live && r < rows && wo < p.Wo && ho < p.Ho && to < p.To;
+      const bool mv = row_live && r < rows && wo < p.Wo && ho < p.Ho && to < p.To && n < p.N;
       const long long m = (p.res && mv) ? (((long long)n * p.To + to) * p.Ho + ho) * p.Wo + wo : 0;
       const __nv_bfloat16* rrow = p.res ? p.res + (size_t)m * p.res_ld + p.res_coff : nullptr;
       const int buf = it & 1;
@@ -595,7 +646,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           if (ch == last_ch) {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+            if (lane == 0) {
+              if (PAIR && rank != 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty_bar[buf]), 0));
+              else mbar_arrive(&tempty_bar[buf]);
+            }
           }
           // (C') fused BatchNorm(+ReLU) backward reduction: epilogue warp e owns the 8-column group e of the chunk, its
           //      lanes split the 128 rows (as in (E)); the staged gradient is masked IN PLACE before it is stored
@@ -709,6 +763,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // the leader's MMAs and commits touch the peer's shared memory and TMEM until here
   if (warp == 2) tmem_dealloc(tmem_base, L::kTmemCols);
 }
 

@@ -346,10 +346,15 @@ inline int side_depth() {  // SFB_SIDE_DEPTH=1: one side tile (read per call, li
   return e && *e ? atoi(e) : 2;
 }
 
-template <int BN, bool BRES, int MODE>
+inline bool pair_enabled() {  // SFB_PAIR=0: single-CTA MMAs for the streamed-weight 256-wide layers too
+  const char* e = getenv("SFB_PAIR");
+  return !(e && *e == '0');
+}
+
+template <int BN, bool BRES, int MODE, bool PAIR = false>
 int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const CUtensorMap& ty,
                          const ConvTmaParams& p, cudaStream_t st) {
-  using L = ConvTmaCfg<BN, BRES>;
+  using L = ConvTmaCfg<BN, BRES, PAIR>;
   const size_t smem = L::smem_bytes(p.nk);
   // Shared memory behind the kernel's fixed layout holds up to three more swizzled tiles (1024-byte aligned): a second
   // staging tile (TMA stores double-buffered) and one or two side tiles (y of the fused BatchNorm backward / residual
@@ -410,17 +415,39 @@ int launch_conv_tma_impl(const CUtensorMap& ta, const CUtensorMap& tw, const CUt
   }
   if (used) smem_total = 1024 + base + (size_t)used * tile_bytes;
   // one N tile per CTA: grid = (CTAs per N tile) * n_tiles, at most one CTA per SM
-  long long per_nt = num_sms() / p.n_tiles;
+  // (pair: one N tile per CTA PAIR, the pair walks neighbouring patches)
+  const int units = PAIR ? num_sms() / 2 : num_sms();
+  const int unit_patches = PAIR ? (p.total_patches + 1) / 2 : p.total_patches;
+  long long per_nt = units / p.n_tiles;
   if (per_nt < 1) per_nt = 1;
-  if (per_nt > p.total_patches) per_nt = p.total_patches;
-  const int grid = (int)per_nt * p.n_tiles;
+  if (per_nt > unit_patches) per_nt = unit_patches;
+  const int grid = (int)per_nt * p.n_tiles * (PAIR ? 2 : 1);
   static size_t attr_bytes = 0;
   if (smem_total > attr_bytes) {
-    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total);
+    cudaError_t e = cudaFuncSetAttribute(conv_tma_kernel<BN, BRES, MODE, PAIR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_total);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tma)");
     attr_bytes = smem_total;
   }
-  conv_tma_kernel<BN, BRES, MODE><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, ty, pp);
+  if (PAIR) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid, 1, 1);
+    cfg.blockDim = dim3((unsigned)L::kThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem_total;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, conv_tma_kernel<BN, BRES, MODE, PAIR>, ta, tw, to, ty, pp);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(conv_tma_kernel, CTA pair)");
+    return SFB_OK;
+  }
+  conv_tma_kernel<BN, BRES, MODE, PAIR><<<grid, L::kThreads, smem_total, st>>>(ta, tw, to, ty, pp);
   SFB_CHECK_LAUNCH("conv_tma_kernel");
   return SFB_OK;
 }
@@ -430,6 +457,19 @@ int launch_conv_tma(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensor
                     const ConvTmaParams& p, cudaStream_t st) {
   // weights resident in shared memory when the CTA's [BN][Ktot] slice fits next to the pipeline (see ConvTmaCfg)
   const bool bres = ConvTmaCfg<BN, true>::smem_bytes(p.nk) <= 227 * 1024;
+  if constexpr (BN == 256) {
+    if (p.pair && !bres) {
+      if (p.bn_mode) {
+        if (p.epi_scale || p.res || p.epi_relu || p.stats) return SFB_ERR_UNSUPPORTED;
+        return launch_conv_tma_impl<256, false, kEpiBnBwd, true>(ta, tw, to, ty, p, st);
+      }
+      if (p.epi_scale || p.res || p.epi_relu) {
+        if (p.stats) return SFB_ERR_UNSUPPORTED;
+        return launch_conv_tma_impl<256, false, kEpiAffine, true>(ta, tw, to, ty, p, st);
+      }
+      return launch_conv_tma_impl<256, false, kEpiPlain, true>(ta, tw, to, ty, p, st);
+    }
+  }
   if (p.bn_mode) {
     if (p.epi_scale || p.res || p.epi_relu || p.stats) return SFB_ERR_UNSUPPORTED;
     return bres ? launch_conv_tma_impl<BN, true, kEpiBnBwd>(ta, tw, to, ty, p, st)
@@ -1069,6 +1109,18 @@ int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pr
     if (q.res == p.out && q.res_ld == geom->o_ld && q.res_coff == geom->o_coff && !q.epi_scale && !q.epi_relu && !q.stats) {
       q.reduce_add = 1;
       q.res = nullptr;
+    }
+    // CTA pairs for the 256-wide layers whose weights are streamed (not resident) and whose tiles are long enough to be
+    // bound by the MMA operand traffic: the (3,1,1) / (1,3,3) convs of res3..res5 and the strided projections.  The
+    // stride-1 pointwise convs (conv_c and its dgrad) and short-K tiles are bound by their epilogue and HBM; coupling
+    // two CTAs per accumulator made them 10 % slower (profiles/r4b_ops_train_p0/p1.txt).
+    if (pair_enabled() && bnt == 256 && geom->Cg >= 64 && ConvTmaCfg<256, true>::smem_bytes(p.nk) > 227 * 1024 &&
+        q.n_tiles <= num_sms() / 2 &&
+        ((p.nk >= 10 && !pointwise) || (!bn && (q.epi_scale || q.epi_relu || (q.res && !q.reduce_add)) && p.nk >= 4))) {
+      // (the inference epilogue is lighter than the training one: there every streamed-weight layer gains, 15.25 -> 14.85 ms)
+      q.pair = 1;
+      rc = get_weight_tmap(wp, rows_pad, k_pad, 128, &tm);  // each CTA of a pair loads 128 of the tile's 256 rows
+      if (rc) return rc;
     }
     CUtensorMap ta;
     const int sW = geom->transposed ? 1 : q.sW, sH = geom->transposed ? 1 : q.sH, sT = geom->transposed ? 1 : q.sT;
