@@ -812,3 +812,34 @@ def test_cta_pair_mma_equals_single_cta(name, monkeypatch):
         torch.testing.assert_close(outs["1"][1], outs["0"][1], rtol=1e-5, atol=1e-3)
         ref = F.conv3d(kc.from_act(x), w.bfloat16().float(), stride=s, padding=p)
         assert kc.relerr(kc.from_act(Act(outs["1"][0], 0, Co)), ref) < 2e-2
+
+
+@pytest.mark.parametrize("name", ["3x1x1_256_128", "big_3x1x1_640_256", "lateral_3x1x1_32_64_s4"])
+def test_merged_hw_axis_equals_separate_axes(name, monkeypatch):
+    """Temporal convs ((3,1,1), laterals) tile a frame as ONE axis of H*W pixels (patches may cut it anywhere);
+    SFB_MERGE_HW=0 keeps H and W as separate patch axes.  Only the tiling differs: identical results."""
+    case = [c for c in kc.CONV_CASES if c[0] == name][0]
+    _, N, T, H, W, Ci, Co, k, s = case
+    g = torch.Generator(device=DEV).manual_seed(6)
+    p = tuple(kk // 2 for kk in k)
+    x = kc.to_act(torch.randn((N, Ci, T, H, W), device=DEV, generator=g))
+    w = torch.randn((Co, Ci) + k, device=DEV, generator=g) / (Ci * k[0]) ** 0.5
+    To, Ho, Wo = ops.conv_out_dims((T, H, W), k, s, p)
+    dy = kc.to_act(torch.randn((N, Co, To, Ho, Wo), device=DEV, generator=g))
+    wp = ops.pack_weight(w.contiguous(), x.C)
+    wpt = ops.pack_weight_dgrad(w.contiguous(), dy.C, s)
+    outs = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("SFB_MERGE_HW", flag)
+        y = Act.empty(N, To, Ho, Wo, Co, zero=True)
+        stats = torch.zeros(2 * Co, device=DEV)
+        ops.conv_gemm(x, wp, y, k, s, p, stats=stats)
+        dx = Act.empty(N, T, H, W, x.C, zero=True)
+        ops.conv_gemm(dy, wpt, dx, k, s, p, transposed=True)
+        torch.cuda.synchronize()
+        outs[flag] = (y.buf.clone(), stats.clone(), dx.buf.clone())
+    assert torch.equal(outs["0"][0], outs["1"][0])
+    assert torch.equal(outs["0"][2], outs["1"][2])
+    torch.testing.assert_close(outs["1"][1], outs["0"][1], rtol=1e-5, atol=1e-3)
+    ref = F.conv3d(kc.from_act(x)[:, :Ci], w.bfloat16().float(), stride=s, padding=p)
+    assert kc.relerr(kc.from_act(Act(outs["1"][0], 0, Co)), ref) < 2e-2

@@ -346,6 +346,10 @@ inline int side_depth() {  // SFB_SIDE_DEPTH=1: one side tile (read per call, li
   return e && *e ? atoi(e) : 2;
 }
 
+inline bool merge_hw_enabled() {
+  const char* e = getenv("SFB_MERGE_HW");
+  return !(e && *e == '0');
+}
 inline bool pair_enabled() {  // SFB_PAIR=0: single-CTA MMAs for the streamed-weight 256-wide layers too
   const char* e = getenv("SFB_PAIR");
   return !(e && *e == '0');
@@ -1069,6 +1073,13 @@ int conv_gemm_impl(const SfbConvGeom* geom, const void* g, const SfbPrologue* pr
     if (pointwise) {  // a 1x1x1 stride-1 conv is a plain GEMM over the flattened pixel list: full 128-row tiles
       gW = geom->N * geom->Ti * geom->Hi * geom->Wi; gH = gT = gN = 1;
       q.N = 1; q.To = 1; q.Ho = 1; q.Wo = p.M;
+    } else if (geom->kH == 1 && geom->kW == 1 && geom->sH == 1 && geom->sW == 1 && geom->pH == 0 && geom->pW == 0 &&
+               geom->Hi == geom->Ho && geom->Wi == geom->Wo && merge_hw_enabled()) {
+      // temporal convs ((3,1,1), the laterals): H and W carry no taps, so a frame is ONE axis of H*W pixels and a patch
+      // may cut it anywhere -- a 14 x 14 map tiles as 13 patches of (16 pixels x 8 frames) per clip instead of 14 of
+      // (14 x 2 x 4), which on 148 SMs is 6 rounds of tiles instead of 7 for the res4 layers (SFB_MERGE_HW=0: off)
+      gW = geom->Wi * geom->Hi; gH = 1;
+      q.Wo = geom->Wo * geom->Ho; q.Ho = 1;
     }
     q.Co = geom->Co; q.o_ld = geom->o_ld; q.o_coff = geom->o_coff;
     q.kT = geom->kT; q.kH = geom->kH; q.kW = geom->kW;
