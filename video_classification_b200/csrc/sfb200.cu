@@ -1259,6 +1259,12 @@ int conv_wgrad_impl(const SfbConvGeom* geom, const void* x, const SfbPrologue* p
     if (pointwise) {
       gW = p.M; gH = gT = gN = 1;
       q.N = 1; q.To = 1; q.Ho = 1; q.Wo = p.M;
+    } else if (geom->kH == 1 && geom->kW == 1 && geom->sH == 1 && geom->sW == 1 && geom->pH == 0 && geom->pW == 0 &&
+               geom->Hi == geom->Ho && geom->Wi == geom->Wo && merge_hw_enabled()) {
+      // temporal convs: one H*W axis, as in conv_gemm_impl (26 patches of 16 pixels x 4 frames per 14 x 14 x 8 clip
+      // instead of 32 of 14 x 4 x 1)
+      gW = geom->Wi * geom->Hi; gH = 1;
+      q.Wo = geom->Wo * geom->Ho; q.Ho = 1;
     }
     pick_patch(q.Wo, q.Ho, q.To, q.sW, q.sH, q.sT, &q.Wt, &q.Ht, &q.Tt, kWtRows);
     q.tilesW = (q.Wo + q.Wt - 1) / q.Wt; q.tilesH = (q.Ho + q.Ht - 1) / q.Ht; q.tilesT = (q.To + q.Tt - 1) / q.Tt;
